@@ -1,0 +1,102 @@
+/* libs2p_sm100.so -- C ABI of the B200-native S2P generator hot path.
+ *
+ * The reference ships no native code and no FFI for this path: its generator
+ * (`--netG=s2p`, /root/reference/README.md:33,59) is plain torch.nn modules whose
+ * source is absent from the snapshot.  Each entry point below
+ * therefore cites the torch.nn call it replaces inside the frozen restatement
+ * (oracle/s2p_oracle.py, ORACLE_SPEC v1) and the SURVEY.md section-8 row it covers.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (PyTorch allocates);
+ *     kernels never allocate, free or synchronise; all work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*), so every call is CUDA-graph capturable;
+ *   - activations: NHWC bf16, `pitch` = elements between consecutive pixels
+ *     (>= C, multiple of 8) so channel slices of a wider tensor can be passed;
+ *   - statistics / modulation vectors / state path: fp32;
+ *   - conv weights: pre-packed [Cout][R][S][Cin] bf16 (s2p_pack_conv_weight);
+ *   - return 0 on success, a negative S2P_ERR_* otherwise, text via
+ *     s2p_last_error_string(); there is no CPU fallback anywhere.
+ */
+#ifndef S2P_B200_H_
+#define S2P_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define S2P_OK 0
+#define S2P_ERR_BAD_ARG (-1)
+#define S2P_ERR_CUDA (-2)
+#define S2P_ERR_UNSUPPORTED (-3)
+
+#define S2P_ACT_NONE 0
+#define S2P_ACT_RELU 1
+#define S2P_ACT_LRELU 2 /* LeakyReLU(0.2) */
+
+#define S2P_IMG_F32_NCHW 0 /* [-1,1] float, oracle/driver-facing */
+#define S2P_IMG_U8_NHWC 1  /* uint8 HWC frames, rlkit/torch/slac/algo.py:174-175 */
+
+int s2p_version(void);
+const char* s2p_last_error_string(void);
+/* number of kernel launches this library has issued in this process (bench.py's gpu_launches). */
+long long s2p_launch_count(void);
+
+/* ---- (a4) implicit-GEMM convolution on tcgen05/TMEM fed by TMA -----------------
+ * replaces nn.Conv2d 3x3 s1/s2 and 1x1 (oracle: MATResBlk.conv_0/conv_1/conv_s,
+ * MAT.mlp_shared/mlp_gamma/mlp_beta, ImageEncoder.conv2/conv3, S2PGenerator.head).
+ * y = act(conv(x, w) + bias + residual); optionally emits per-image per-channel
+ * (sum, sumsq) partials of the STORED bf16 values for the following instance norm:
+ * stats_partial is [B][s2p_conv_stats_rows(Hout,Wout)][Cout][2] fp32.
+ * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in {1,3}, stride in {1,2}. */
+int s2p_conv_stats_rows(int Hout, int Wout);
+int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
+                       const void* residual, int res_pitch, void* y, int y_pitch,
+                       float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
+                       int stride, int act, void* stream);
+
+/* OIHW fp32 -> [Cout][R][S][Cin] bf16 rows, each weight multiplied by `scale`
+ * (used to fold the MAT blend factors at load time). */
+int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S,
+                         float scale, void* stream);
+
+/* ---- (a3) param-free instance norm + MAT modulation + LeakyReLU, one fused pass ---
+ * replaces F.instance_norm + the gamma/beta arithmetic of oracle MAT.forward + the
+ * F.leaky_relu that follows it (and F.interpolate(nearest x2) in front when up==2).
+ *   y[n,h,w,c] = act( (x[n,h/up,w/up,c]-mean)*rstd * (1 + gs[n,c] + gI[n,h,w,c]) + bs[n,c] + bI[n,h,w,c] )
+ * gb_spatial holds gI in channels [0,C) and bI in [C,2C) of each pixel; gs/bs/gb_spatial
+ * may be NULL (plain IN + act, oracle ImageEncoder).  C % 8 == 0. */
+int s2p_in_stats_finalize(const float* stats_partial, int rows, float* mean_rstd, int B, int C,
+                          int HW, float eps, void* stream);
+int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd, const float* gs,
+                     const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y,
+                     int y_pitch, int B, int H, int W, int C, int act, void* stream);
+
+/* ---- (a5 head/tail) Cin=3 stem conv and Cout=3 ToRGB + tanh --------------------
+ * stem: oracle ImageEncoder.conv1 (3->Cout 3x3 s1 p1) straight from the boundary
+ * image (fp32 NCHW in [-1,1] or uint8 NHWC mapped by u/127.5-1) to NHWC bf16, with
+ * statistics partials [B][s2p_stem_stats_rows(H,W)][Cout][2].
+ * tail: tanh(conv3x3(Cin->3)(lrelu(x)) + bias) -> fp32 NCHW and/or uint8 NHWC
+ * (floor((y+1)*127.5+0.5) clamped), oracle S2PGenerator.conv_img + to_uint8_hwc. */
+int s2p_stem_stats_rows(int H, int W);
+int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* w_oihw, const float* bias,
+                      void* y, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
+                      void* stream);
+int s2p_torgb_tanh_fwd(const void* x, int x_pitch, const float* w_oihw, const float* bias,
+                       float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,
+                       void* stream);
+
+/* ---- (a2) state encoder ---------------------------------------------------------
+ * pos_encode: oracle positional_encoding (nerf-pytorch embedding, include input).
+ * linear: y = act(x W^T + b), fp32 (oracle StateEncoder.layers, MAT.fc_gamma/fc_beta). */
+int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S, int n_freqs,
+                       void* stream);
+int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
+                   int y_pitch, int B, int K, int N, int act, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* S2P_B200_H_ */

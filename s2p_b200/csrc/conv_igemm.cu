@@ -1,0 +1,382 @@
+// Implicit-GEMM convolution for sm_100a: TMA (4-D tiled tensor map over the NHWC
+// activation, one box per filter tap) -> 128B-swizzled shared memory ->
+// tcgen05.mma (M=128, N=BLOCK_N, K=16, bf16 x bf16 -> f32 in TMEM) -> tcgen05.ld
+// epilogue (bias, residual add, activation, bf16 store, per-(n,c) statistics
+// partials for the following instance norm).
+//
+// GEMM view:  D[m, co] = sum_{r,s,ci} X[n, ho*st - pad + r, wo*st - pad + s, ci] * Wp[co, (r,s,ci)]
+//   m  = one output pixel of a (tile_h x tile_w) spatial tile of one image (<=128 rows)
+//   K  = R*S*Cin walked as (tap, 64-channel chunk) blocks; padding = TMA out-of-bounds zero fill
+//
+// Replaces the cuDNN convs behind nn.Conv2d in the (absent) reference generator
+// (oracle/s2p_oracle.py MATResBlk / MAT / ImageEncoder / head).
+//
+// Warp roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer
+// (warp 1 owns the TMEM allocation), warps 2..5 = epilogue (TMEM lane quarter = warp % 4).
+// Persistent: grid = min(#tiles, #SMs); static round-robin tile schedule, n-tile fastest so
+// CTAs running together share the activation tile in L2.  Accumulators are double
+// buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "ptx.cuh"
+#include "s2p_internal.h"
+
+namespace s2p {
+
+struct ConvParams {
+  int B, H, W;            // output spatial size
+  int Cin, Cout;
+  int R, S, pad, stride;
+  int tile_w, tile_h, tiles_x, tiles_y;
+  int num_m_tiles, num_n_tiles;
+  int out_pitch, res_pitch;
+  int act;                // 0 none, 1 relu, 2 lrelu(0.2)
+  const float* bias;
+  const __nv_bfloat16* residual;
+  __nv_bfloat16* out;
+  float* stats_partial;   // [B][tiles_per_img*4][Cout][2] (sum, sumsq) or null
+};
+
+template <int BLOCK_N>
+struct ConvCfg {
+  static constexpr int kBlockM = 128;
+  static constexpr int kBlockK = 64;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KB
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 192) ? 5 : (BLOCK_N >= 128) ? 6 : 8;
+  static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
+  static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 128 / 256 / 512
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+// transposed butterfly: on exit lane L holds sum over the warp's 32 rows of column L
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192, 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                  const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
+  using Cfg = ConvCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + Cfg::kStages;
+  uint64_t* tmem_full = bars + 2 * Cfg::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int i = 0; i < Cfg::kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const int cchunks = p.Cin / Cfg::kBlockK;
+  const int num_kb = p.R * p.S * cchunks;
+  const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
+  const uint32_t stage_tx = a_bytes + Cfg::kBBytes;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_tile = tile / p.num_n_tiles, n_tile = tile % p.num_n_tiles;
+      const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
+      const int h0 = (t / p.tiles_x) * p.tile_h, w0 = (t % p.tiles_x) * p.tile_w;
+      const int hin0 = h0 * p.stride - p.pad, win0 = w0 * p.stride - p.pad;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int tap = kb / cchunks, cc = kb % cchunks;
+        const int r = tap / p.S, s = tap % p.S;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+        tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
+        tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint64_t da = umma_desc_sw128(sa);
+        const uint64_t db = umma_desc_sw128(sa + Cfg::kABytes);
+#pragma unroll
+        for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
+          // +32 B per K=16 step inside the 128 B swizzle row (address field is >>4)
+          umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= 2) {
+    // ------------------------------------------------------------ epilogue
+    const int q = warp & 3;           // TMEM lane quarter this warp may read
+    const int m = q * 32 + lane;      // accumulator row = pixel inside the tile
+    const int my = m / p.tile_w, mx = m - my * p.tile_w;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int m_tile = tile / p.num_n_tiles, n_tile = tile % p.num_n_tiles;
+      const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
+      const int h = (t / p.tiles_x) * p.tile_h + my, w = (t % p.tiles_x) * p.tile_w + mx;
+      const bool valid = (my < p.tile_h) && (h < p.H) && (w < p.W);
+      const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
+      const int n0 = n_tile * BLOCK_N;
+
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t raw[32];
+        tmem_ld32(t_row + c * 32, raw);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        const int ch = n0 + c * 32;
+        if (p.bias != nullptr) {
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b = __ldg(b4 + j);
+            v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+          }
+        }
+        if (p.residual != nullptr && valid) {
+          const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + ch);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint4 rr = __ldg(r4 + j);
+            v[8 * j + 0] += bf16_lo(rr.x); v[8 * j + 1] += bf16_hi(rr.x);
+            v[8 * j + 2] += bf16_lo(rr.y); v[8 * j + 3] += bf16_hi(rr.y);
+            v[8 * j + 4] += bf16_lo(rr.z); v[8 * j + 5] += bf16_hi(rr.z);
+            v[8 * j + 6] += bf16_lo(rr.w); v[8 * j + 7] += bf16_hi(rr.w);
+          }
+        }
+        if (p.act == 1) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (p.act == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : 0.2f * v[j];
+        }
+        uint32_t packed[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+        if (valid) {
+          uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            o4[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        }
+        if (p.stats_partial != nullptr) {
+          // statistics of the values as stored (bf16-rounded), fixed reduction order
+          float s1[32], s2[32];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float a = valid ? bf16_lo(packed[j]) : 0.f;
+            const float b = valid ? bf16_hi(packed[j]) : 0.f;
+            s1[2 * j] = a; s1[2 * j + 1] = b;
+            s2[2 * j] = a * a; s2[2 * j + 1] = b * b;
+          }
+          const float cs = warp_colsum32(s1, lane);
+          const float cq = warp_colsum32(s2, lane);
+          const size_t prow = (static_cast<size_t>(img) * tiles_per_img + t) * 4 + q;
+          float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + ch + lane;
+          *dst = make_float2(cs, cq);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+}  // namespace s2p
+
+// =============================================================== host side
+namespace s2p {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// spatial tile (tile_w x tile_h <= 128 pixels) that wastes the fewest MMA rows
+void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
+  double best = -1.0;
+  int btw = 1, bth = 1;
+  for (int tw = 1; tw <= W && tw <= 128 && tw <= max_box_w; ++tw) {
+    int th = 128 / tw;
+    if (th > H) th = H;
+    if (th < 1) continue;
+    const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
+    const double eff = static_cast<double>(H) * W / (tiles * 128.0);
+    if (eff > best + 1e-9 || (eff > best - 1e-9 && tw > btw)) { best = eff; btw = tw; bth = th; }
+  }
+  *tw_out = btw;
+  *th_out = bth;
+}
+
+template <int BLOCK_N>
+static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
+  using Cfg = ConvCfg<BLOCK_N>;
+  static bool configured = false;
+  if (!configured) {
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  conv_igemm_kernel<BLOCK_N><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  count_launch();
+  return check_launch("conv_igemm_kernel");
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_conv_stats_rows(int Hout, int Wout) {
+  int tw, th;
+  s2p::conv_pick_tile(Hout, Wout, 128, &tw, &th);
+  return ((Wout + tw - 1) / tw) * ((Hout + th - 1) / th) * 4;
+}
+
+extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
+                                  const void* residual, int res_pitch, void* y, int y_pitch,
+                                  float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
+                                  int ksize, int stride, int act, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
+  S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
+  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
+  S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
+  S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
+  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
+  S2P_CHECK_ARG(y_pitch >= Cout && y_pitch % 8 == 0, "conv: y_pitch=%d", y_pitch);
+  S2P_CHECK_ARG(!residual || (res_pitch >= Cout && res_pitch % 8 == 0), "conv: res_pitch=%d", res_pitch);
+  S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(w_packed) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(residual) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
+                "conv: pointers must be 16-byte aligned");
+  EncodeTiledFn encode = get_encode_fn();
+  if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+
+  const int pad = ksize / 2;
+  ConvParams p{};
+  p.B = B;
+  p.H = (Hin + 2 * pad - ksize) / stride + 1;
+  p.W = (Win + 2 * pad - ksize) / stride + 1;
+  p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
+  conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
+  p.tiles_x = (p.W + p.tile_w - 1) / p.tile_w;
+  p.tiles_y = (p.H + p.tile_h - 1) / p.tile_h;
+  const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
+  p.num_m_tiles = B * p.tiles_x * p.tiles_y;
+  p.num_n_tiles = Cout / block_n;
+  p.out_pitch = y_pitch; p.res_pitch = res_pitch; p.act = act;
+  p.bias = bias;
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.out = static_cast<__nv_bfloat16*>(y);
+  p.stats_partial = stats_partial;
+
+  CUtensorMap ta, tb;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)x_pitch * 2, (cuuint64_t)x_pitch * 2 * Win,
+                             (cuuint64_t)x_pitch * 2 * Win * Hin};
+    cuuint32_t box[4] = {64, (cuuint32_t)(p.tile_w * stride), (cuuint32_t)(p.tile_h * stride), 1};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = encode(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box,
+                        estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: activation tensor map encode failed (CUresult %d)", (int)r);
+  }
+  {
+    const int K = ksize * ksize * Cin;
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Cout};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)block_n};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode(&tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_packed), dims, strides,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: weight tensor map encode failed (CUresult %d)", (int)r);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (block_n) {
+    case 256: return launch_conv<256>(ta, tb, p, st);
+    case 192: return launch_conv<192>(ta, tb, p, st);
+    case 128: return launch_conv<128>(ta, tb, p, st);
+    default: return launch_conv<64>(ta, tb, p, st);
+  }
+}

@@ -1,0 +1,131 @@
+// State encoder: nerf-style positional encoding and the
+// fp32 Linear(+LeakyReLU) layers of the StyleGAN-style mapping MLP and of the
+// per-MAT state heads (all heads of the generator are batched into ONE linear by the
+// host module).  Tiny next to the convs (0.006 GMAC of 56.4 per frame), so plain
+// fp32 CUDA-core SGEMM keeps the state path exact; latency at small batch is hidden
+// by capturing the whole forward in a CUDA graph.
+#include "ptx.cuh"
+#include "s2p_internal.h"
+
+namespace s2p {
+
+__global__ void pos_encode_kernel(const float* __restrict__ state, float* __restrict__ pe, int pe_pitch,
+                                  int B, int S, int L) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * S) return;
+  const int b = idx / S, i = idx % S;
+  const float s = state[idx];
+  float* row = pe + static_cast<size_t>(b) * pe_pitch;
+  row[i] = s;
+  float f = 1.f;
+  for (int k = 0; k < L; ++k) {
+    const float a = s * f;                 // exact: f is a power of two
+    row[S * (1 + 2 * k) + i] = sinf(a);    // accurate (non fast-math) range reduction
+    row[S * (2 + 2 * k) + i] = cosf(a);
+    f *= 2.f;
+  }
+}
+
+// y[B,N] = act(x[B,K] @ w[N,K]^T + bias).  64x64 tile, BK=16, 256 threads, 4x4 per thread.
+__global__ void __launch_bounds__(256)
+linear_kernel(const float* __restrict__ x, int x_pitch, const float* __restrict__ w,
+              const float* __restrict__ bias, float* __restrict__ y, int y_pitch, int B, int K, int N, int act) {
+  __shared__ float xs[16][64 + 4];
+  __shared__ float wsh[16][64 + 4];
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+      const int r = i / 16, kk = i % 16;
+      const int k = k0 + kk;
+      xs[kk][r] = (m0 + r < B && k < K) ? x[static_cast<size_t>(m0 + r) * x_pitch + k] : 0.f;
+      wsh[kk][r] = (n0 + r < N && k < K) ? w[static_cast<size_t>(n0 + r) * K + k] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = xs[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = wsh[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= B) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= N) continue;
+      float v = acc[i][j] + (bias ? bias[n] : 0.f);
+      if (act == 2) v = v > 0.f ? v : 0.2f * v;
+      else if (act == 1) v = fmaxf(v, 0.f);
+      y[static_cast<size_t>(m) * y_pitch + n] = v;
+    }
+  }
+}
+
+// OIHW fp32 -> [Cout][R][S][Cin] bf16
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Cout,
+                                        int Cin, int R, int S, float scale) {
+  const long long total = static_cast<long long>(Cout) * Cin * R * S;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int ci = static_cast<int>(i % Cin);
+    long long t = i / Cin;
+    const int s = static_cast<int>(t % S); t /= S;
+    const int r = static_cast<int>(t % R);
+    const int co = static_cast<int>(t / R);
+    dst[i] = __float2bfloat16_rn(w[((static_cast<long long>(co) * Cin + ci) * R + r) * S + s] * scale);
+  }
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S, int n_freqs,
+                                  void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(state && pe, "pos_encode: null pointer");
+  S2P_CHECK_ARG(B > 0 && S > 0 && n_freqs >= 0 && pe_pitch >= S * (1 + 2 * n_freqs), "pos_encode: bad dims");
+  const int total = B * S;
+  pos_encode_kernel<<<(total + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(state, pe, pe_pitch, B, S,
+                                                                                     n_freqs);
+  count_launch();
+  return check_launch("pos_encode_kernel");
+}
+
+extern "C" int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
+                              int y_pitch, int B, int K, int N, int act, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && w && y, "linear: null pointer");
+  S2P_CHECK_ARG(B > 0 && K > 0 && N > 0 && x_pitch >= K && y_pitch >= N, "linear: bad dims");
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "linear: act=%d", act);
+  dim3 grid((N + 63) / 64, (B + 63) / 64);
+  linear_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, x_pitch, w, bias, y, y_pitch, B, K, N, act);
+  count_launch();
+  return check_launch("linear_kernel");
+}
+
+extern "C" int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S, float scale,
+                                    void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(w_oihw && dst && Cout > 0 && Cin > 0 && R > 0 && S > 0, "pack_conv_weight: bad args");
+  const long long total = static_cast<long long>(Cout) * Cin * R * S;
+  const int blocks = static_cast<int>((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+  pack_conv_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w_oihw, static_cast<__nv_bfloat16*>(dst), Cout, Cin, R, S, scale);
+  count_launch();
+  return check_launch("pack_conv_weight_kernel");
+}

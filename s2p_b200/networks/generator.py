@@ -1,0 +1,333 @@
+"""B200-native ``netG`` for ``--netG=s2p``: same construction surface
+(``define_G(opt)``), same ``forward(image, state)``, same parameter names and
+shapes as ORACLE_SPEC v1 (so a state_dict moves between the two unchanged), but the
+forward is a fixed sequence of hand-written sm_100a kernels called through the C
+ABI (include/s2p_b200.h).  There is no CPU / eager fallback in this module.
+
+Boundary it replaces: the reference's absent generator behind
+``simple_test.py --netG=s2p`` / ``train.py --netG=s2p`` (/root/reference/README.md:33,59);
+semantics from /root/reference/rebuttal.md:6,71,146-154.
+
+Data layout in HBM: activations NHWC bf16; statistics, state path and modulation
+vectors fp32; conv weights packed [Cout][R][S][Cin] bf16 once per load.  The MAT
+blend factors sigmoid(blend_*) are folded into the packed gamma/beta conv weights
+and into the batched state-head linear at pack time, and the 3x3 ``mlp_shared``
+convs of all MATs that read the same encoder feature are merged into one wide conv.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..ops import ACT_LRELU, ACT_NONE, ACT_RELU
+
+
+class _MATParams(nn.Module):
+    def __init__(self, norm_nc, feat_nc, w_dim, nhidden):
+        super().__init__()
+        self.fc_gamma = nn.Linear(w_dim, norm_nc)
+        self.fc_beta = nn.Linear(w_dim, norm_nc)
+        self.mlp_shared = nn.Conv2d(feat_nc, nhidden, 3, 1, 1)
+        self.mlp_gamma = nn.Conv2d(nhidden, norm_nc, 3, 1, 1)
+        self.mlp_beta = nn.Conv2d(nhidden, norm_nc, 3, 1, 1)
+        self.blend_gamma = nn.Parameter(torch.zeros(()))
+        self.blend_beta = nn.Parameter(torch.zeros(()))
+        self.norm_nc = norm_nc
+
+
+class _BlockParams(nn.Module):
+    def __init__(self, fin, fout, feat_nc, w_dim, nhidden):
+        super().__init__()
+        fmid = min(fin, fout)
+        self.fin, self.fout, self.fmid = fin, fout, fmid
+        self.learned_shortcut = fin != fout
+        self.conv_0 = nn.Conv2d(fin, fmid, 3, 1, 1)
+        self.conv_1 = nn.Conv2d(fmid, fout, 3, 1, 1)
+        self.norm_0 = _MATParams(fin, feat_nc, w_dim, nhidden)
+        self.norm_1 = _MATParams(fmid, feat_nc, w_dim, nhidden)
+        if self.learned_shortcut:
+            self.conv_s = nn.Conv2d(fin, fout, 1, bias=False)
+            self.norm_s = _MATParams(fin, feat_nc, w_dim, nhidden)
+
+    def mats(self):
+        out = [("norm_0", self.norm_0), ("norm_1", self.norm_1)]
+        if self.learned_shortcut:
+            out.append(("norm_s", self.norm_s))
+        return out
+
+
+class _StateEncoderParams(nn.Module):
+    def __init__(self, state_dim, n_freqs, w_dim, n_layers):
+        super().__init__()
+        dims = [state_dim * (1 + 2 * n_freqs)] + [w_dim] * n_layers
+        self.layers = nn.ModuleList(nn.Linear(dims[i], dims[i + 1]) for i in range(n_layers))
+
+
+class _ImageEncoderParams(nn.Module):
+    def __init__(self, ngf):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, ngf, 3, 1, 1)
+        self.conv2 = nn.Conv2d(ngf, ngf * 2, 3, 2, 1)
+        self.conv3 = nn.Conv2d(ngf * 2, ngf * 4, 3, 2, 1)
+
+
+def _init_weights(net, init_type, gain):
+    # same distributions as SPADE's BaseNetwork.init_weights('xavier', 0.02); parity
+    # tests always load the oracle's state_dict, so only the distribution matters here
+    for m in net.modules():
+        if isinstance(m, (nn.Conv2d, nn.Linear)):
+            if init_type == "xavier":
+                nn.init.xavier_normal_(m.weight, gain=gain)
+                if m.bias is not None:
+                    nn.init.zeros_(m.bias)
+            elif init_type == "scaled":
+                nn.init.normal_(m.weight, 0.0, (1.0 / m.weight[0].numel()) ** 0.5)
+                if m.bias is not None:
+                    nn.init.normal_(m.bias, 0.0, 0.1)
+            else:
+                raise ValueError(f"unknown init_type {init_type}")
+
+
+class S2PGeneratorB200(nn.Module):
+    """forward(image, state) -> next frame.
+
+    image: fp32 NCHW [B,3,H,W] in [-1,1]  (or uint8 NHWC [B,H,W,3] dataset frames)
+    state: fp32 [B,S]
+    returns fp32 NCHW [B,3,H,W] in [-1,1]  (``forward_u8`` returns uint8 NHWC)
+    """
+
+    RES_OF_BLOCK = (4, 4, 2, 1, 1)  # downscale factor of each block's resolution
+
+    def __init__(self, opt):
+        super().__init__()
+        self.opt = opt
+        ngf, wd, nh = opt.ngf, opt.w_dim, opt.nhidden
+        if ngf % 64 != 0 or nh % 64 != 0:
+            raise ValueError("ngf and nhidden must be multiples of 64 for the tcgen05 conv kernel")
+        self.state_encoder = _StateEncoderParams(opt.state_dim, opt.pe_freqs, wd, opt.mapping_layers)
+        self.image_encoder = _ImageEncoderParams(ngf)
+        self.head = nn.Conv2d(ngf * 4, ngf * 8, 3, 1, 1)
+        self.block_0 = _BlockParams(ngf * 8, ngf * 8, ngf * 4, wd, nh)
+        self.block_1 = _BlockParams(ngf * 8, ngf * 8, ngf * 4, wd, nh)
+        self.block_2 = _BlockParams(ngf * 8, ngf * 4, ngf * 2, wd, nh)
+        self.block_3 = _BlockParams(ngf * 4, ngf * 2, ngf, wd, nh)
+        self.block_4 = _BlockParams(ngf * 2, ngf, ngf, wd, nh)
+        self.conv_img = nn.Conv2d(ngf, 3, 3, 1, 1)
+        _init_weights(self, getattr(opt, "init_type", "xavier"), getattr(opt, "init_variance", 0.02))
+        self.max_microbatch = int(getattr(opt, "max_microbatch", 128))
+        self._packed = None
+        self._ws = {}
+
+    # ------------------------------------------------------------------ packing
+    def blocks(self):
+        return [self.block_0, self.block_1, self.block_2, self.block_3, self.block_4]
+
+    def load_state_dict(self, *a, **k):
+        r = super().load_state_dict(*a, **k)
+        self._packed = None
+        return r
+
+    def _apply(self, fn, *a, **k):
+        self._packed = None
+        self._ws = {}
+        return super()._apply(fn, *a, **k)
+
+    @torch.no_grad()
+    def pack(self):
+        """Pre-pack weights for the kernels (call again after changing parameters)."""
+        dev = self.head.weight.device
+        if dev.type != "cuda":
+            raise RuntimeError("S2PGeneratorB200 runs on CUDA only (--gpu_ids=-1 is the oracle's CPU path)")
+        P = {}
+        f32 = lambda t: t.detach().float().contiguous()  # noqa: E731
+        P["se"] = [(f32(l.weight), f32(l.bias)) for l in self.state_encoder.layers]
+        enc = self.image_encoder
+        P["stem_w"], P["stem_b"] = f32(enc.conv1.weight), f32(enc.conv1.bias)
+        P["e2_w"], P["e2_b"] = ops.pack_conv_weight(enc.conv2.weight), f32(enc.conv2.bias)
+        P["e3_w"], P["e3_b"] = ops.pack_conv_weight(enc.conv3.weight), f32(enc.conv3.bias)
+        P["head_w"], P["head_b"] = ops.pack_conv_weight(self.head.weight), f32(self.head.bias)
+        P["img_w"], P["img_b"] = f32(self.conv_img.weight), f32(self.conv_img.bias)
+        # group the MATs by the encoder feature they are conditioned on
+        groups = {4: [], 2: [], 1: []}
+        for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
+            for name, mat in blk.mats():
+                groups[ds].append((bi, name, mat))
+        nh = self.opt.nhidden
+        head_w, head_b = [], []
+        off = 0
+        P["mat"] = {}
+        P["shared"] = {}
+        for ds, mats in groups.items():
+            sw = torch.cat([m.mlp_shared.weight.detach().float() for _, _, m in mats], dim=0)
+            sb = torch.cat([m.mlp_shared.bias.detach().float() for _, _, m in mats], dim=0).contiguous()
+            P["shared"][ds] = (ops.pack_conv_weight(sw), sb, sw.shape[0])
+            for j, (bi, name, m) in enumerate(mats):
+                a = torch.sigmoid(m.blend_gamma.detach().float())
+                c = torch.sigmoid(m.blend_beta.detach().float())
+                C = m.norm_nc
+                gbw = torch.cat([m.mlp_gamma.weight.detach().float() * (1 - a),
+                                 m.mlp_beta.weight.detach().float() * (1 - c)], dim=0)
+                gbb = torch.cat([m.mlp_gamma.bias.detach().float() * (1 - a),
+                                 m.mlp_beta.bias.detach().float() * (1 - c)], dim=0).contiguous()
+                head_w += [m.fc_gamma.weight.detach().float() * a, m.fc_beta.weight.detach().float() * c]
+                head_b += [m.fc_gamma.bias.detach().float() * a, m.fc_beta.bias.detach().float() * c]
+                P["mat"][(bi, name)] = dict(C=C, gb_w=ops.pack_conv_weight(gbw), gb_b=gbb, h_off=j * nh,
+                                            s_off=off, ds=ds)
+                off += 2 * C
+        P["heads_w"] = torch.cat(head_w, dim=0).contiguous()
+        P["heads_b"] = torch.cat(head_b, dim=0).contiguous()
+        P["heads_n"] = off
+        P["blk"] = []
+        for blk in self.blocks():
+            d = dict(c0_w=ops.pack_conv_weight(blk.conv_0.weight), c0_b=f32(blk.conv_0.bias),
+                     c1_w=ops.pack_conv_weight(blk.conv_1.weight), c1_b=f32(blk.conv_1.bias))
+            if blk.learned_shortcut:
+                d["cs_w"] = ops.pack_conv_weight(blk.conv_s.weight)
+            P["blk"].append(d)
+        self._packed = P
+        return self
+
+    # ------------------------------------------------------------------ workspace
+    def _buf(self, name, shape, dtype):
+        key = (name, tuple(shape), dtype)
+        t = self._ws.get(key)
+        if t is None:
+            t = torch.empty(shape, dtype=dtype, device=self.head.weight.device)
+            self._ws[key] = t
+        return t
+
+    def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False):
+        B, hin, win, _ = x.shape
+        ho = (hin + 2 * (k // 2) - k) // stride + 1
+        wo = (win + 2 * (k // 2) - k) // stride + 1
+        y = self._buf(name, (B, ho, wo, cout), torch.bfloat16)
+        mr = None
+        st = None
+        if want_stats:
+            st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
+        ops.conv_igemm(x, w, b, cout, k, stride, act, residual, y, st)
+        if want_stats:
+            mr = self._buf(name + ".mr", (B, cout, 2), torch.float32)
+            ops.in_stats_finalize(st, ho * wo, 1e-5, mr)
+        return y, mr
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def _forward_mb(self, image, state, out_f32, out_u8):
+        P = self._packed
+        opt = self.opt
+        ngf, nh = opt.ngf, opt.nhidden
+        if image.dtype == torch.uint8:
+            B, H, W, _ = image.shape
+        else:
+            B, _, H, W = image.shape
+        if H % 4 or W % 4:
+            raise RuntimeError("image height/width must be multiples of 4")
+        bf = torch.bfloat16
+        # ---- state encoder (fp32)
+        h = ops.pos_encode(state, opt.pe_freqs, self._buf("pe", (B, state.shape[1] * (1 + 2 * opt.pe_freqs)), torch.float32))
+        for i, (w, b) in enumerate(P["se"]):
+            h = ops.linear(h, w, b, ACT_LRELU, self._buf(f"se{i % 2}", (B, w.shape[0]), torch.float32))
+        gsbs = ops.linear(h, P["heads_w"], P["heads_b"], ACT_NONE, self._buf("gsbs", (B, P["heads_n"]), torch.float32))
+        # ---- image encoder
+        e1 = self._buf("e1", (B, H, W, ngf), bf)
+        st = self._buf("e1.st", (B, ops.stem_stats_rows(H, W), ngf, 2), torch.float32)
+        ops.stem_conv(image, P["stem_w"], P["stem_b"], ngf, e1, st)
+        mr = ops.in_stats_finalize(st, H * W, 1e-5, self._buf("e1.mr", (B, ngf, 2), torch.float32))
+        f = {1: ops.mat_norm(e1, mr, act=ACT_LRELU, out=self._buf("f1", (B, H, W, ngf), bf))}
+        e2, mr = self._conv("e2", f[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True)
+        f[2] = ops.mat_norm(e2, mr, act=ACT_LRELU, out=self._buf("f2", tuple(e2.shape), bf))
+        e3, mr = self._conv("e3", f[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True)
+        f[4] = ops.mat_norm(e3, mr, act=ACT_LRELU, out=self._buf("f4", tuple(e3.shape), bf))
+        # ---- merged mlp_shared convs: one wide conv per conditioning feature
+        hs = {}
+        for ds in (4, 2, 1):
+            sw, sb, n = P["shared"][ds]
+            hs[ds], _ = self._conv(f"hs{ds}", f[ds], sw, sb, n, 3, 1, ACT_RELU)
+        # ---- trunk
+        x, mr_x = self._conv("head", f[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True)
+        cur = 4
+        for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
+            up = cur // ds
+            cur = ds
+            hh, ww = H // ds, W // ds
+            pb = P["blk"][bi]
+            last = bi == len(self.RES_OF_BLOCK) - 1
+
+            def mat(name, xin, mr_in, up_, act, tag):
+                m = P["mat"][(bi, name)]
+                C = m["C"]
+                hsl = hs[ds][..., m["h_off"]:m["h_off"] + nh]
+                gb, _ = self._conv(f"gb{ds}", hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1) if False else (None, None)
+                gbuf = self._buf(f"gb{ds}.{2 * C}", (B, hh, ww, 2 * C), bf)
+                ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
+                gs = gsbs[:, m["s_off"]:m["s_off"] + C]
+                bs = gsbs[:, m["s_off"] + C:m["s_off"] + 2 * C]
+                return ops.mat_norm(xin, mr_in, gs, bs, gbuf, up_, act, self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
+
+            if blk.learned_shortcut:
+                t = mat("norm_s", x, mr_x, up, ACT_NONE, "s")
+                xs, _ = self._conv(f"xs{bi}", t, pb["cs_w"], None, blk.fout, 1, 1)
+            else:
+                if up != 1:
+                    raise RuntimeError("identity shortcut across an upsample is not part of ORACLE_SPEC v1")
+                xs = x
+            t = mat("norm_0", x, mr_x, up, ACT_LRELU, "a")
+            dx, mr_dx = self._conv(f"dx{bi}", t, pb["c0_w"], pb["c0_b"], blk.fmid, 3, 1, want_stats=True)
+            t = mat("norm_1", dx, mr_dx, 1, ACT_LRELU, "b")
+            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1, residual=xs, want_stats=not last)
+        ops.torgb_tanh(x, P["img_w"], P["img_b"], out_f32, out_u8)
+
+    def _run(self, image, state, want_f32=True, want_u8=False):
+        if not image.is_cuda or not state.is_cuda:
+            raise RuntimeError("S2PGeneratorB200.forward needs CUDA tensors; there is no CPU fallback "
+                               "(the CPU restatement lives in oracle/ and is test infrastructure)")
+        if self._packed is None:
+            self.pack()
+        if image.dtype == torch.uint8:
+            B, H, W = image.shape[0], image.shape[1], image.shape[2]
+        elif image.dtype == torch.float32:
+            B, H, W = image.shape[0], image.shape[2], image.shape[3]
+        else:
+            raise RuntimeError(f"image dtype {image.dtype} unsupported (fp32 NCHW or uint8 NHWC)")
+        image = image.contiguous()
+        state = state.contiguous().float()
+        out_f32 = torch.empty(B, 3, H, W, dtype=torch.float32, device=image.device) if want_f32 else None
+        out_u8 = torch.empty(B, H, W, 3, dtype=torch.uint8, device=image.device) if want_u8 else None
+        mb = self.max_microbatch
+        for s in range(0, B, mb):
+            e = min(B, s + mb)
+            self._forward_mb(image[s:e], state[s:e], None if out_f32 is None else out_f32[s:e],
+                             None if out_u8 is None else out_u8[s:e])
+        return out_f32, out_u8
+
+    def forward(self, image, state):
+        return self._run(image, state, True, False)[0]
+
+    def forward_u8(self, frames_u8_nhwc, state):
+        """dataset-facing variant: uint8 HWC frames in, uint8 HWC frames out
+        (image_observations -> image_observations_tp1, rlkit/torch/slac/algo.py:174-175)."""
+        return self._run(frames_u8_nhwc, state, False, True)[1]
+
+    @torch.no_grad()
+    def rollout(self, image, states):
+        """N-step autoregressive synthesis (README.md:30-33, --seq_len): the fp32 output
+        is fed back unquantised.  states: [B, N, S] -> frames [B, N, 3, H, W]."""
+        outs = []
+        img = image
+        for k in range(states.shape[1]):
+            img = self.forward(img, states[:, k])
+            outs.append(img)
+        return torch.stack(outs, dim=1)
+
+
+def define_G(opt):
+    """SPADE-style factory (README.md:33,59: --netG=s2p, --gpu_ids)."""
+    if opt.netG != "s2p":
+        raise ValueError(f"s2p_b200 implements --netG=s2p only, got {opt.netG}")
+    if not opt.gpu_ids:
+        raise RuntimeError("--gpu_ids=-1 (CPU) is not served by s2p_b200: it has no CPU fallback. "
+                           "The CPU restatement is oracle/s2p_oracle.py (test infrastructure).")
+    net = S2PGeneratorB200(opt)
+    return net.to(torch.device("cuda", opt.gpu_ids[0]))

@@ -1,0 +1,193 @@
+"""Tensor-level wrappers over the C ABI (one function per exported kernel).
+
+PyTorch is plumbing here: it owns device memory and the stream; every function
+passes raw pointers + sizes to libs2p_sm100.so.  Activations are NHWC bf16
+tensors ``[B, H, W, C]``; a channel slice ``t[..., a:b]`` of such a tensor is a
+valid argument (the pixel pitch is read from ``t.stride(2)``).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, IMG_F32_NCHW, IMG_U8_NHWC  # noqa: F401
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _require_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("s2p_b200 ops need CUDA tensors: there is no CPU path (use oracle/ for a CPU run)")
+
+
+def _nhwc_pitch(t: torch.Tensor, what: str) -> int:
+    """pixel pitch of an NHWC (possibly channel-sliced) bf16 tensor"""
+    if t.dtype != torch.bfloat16 or t.dim() != 4:
+        raise RuntimeError(f"{what}: expected a 4-D bf16 NHWC tensor, got {tuple(t.shape)} {t.dtype}")
+    b, h, w, c = t.shape
+    pitch = t.stride(2)
+    if t.stride(3) != 1 or t.stride(1) != pitch * w or (b > 1 and t.stride(0) != pitch * w * h):
+        raise RuntimeError(f"{what}: tensor is not pixel-contiguous NHWC (strides {t.stride()})")
+    return pitch
+
+
+def conv_stats_rows(hout: int, wout: int) -> int:
+    return int(_lib.load().s2p_conv_stats_rows(hout, wout))
+
+
+def stem_stats_rows(h: int, w: int) -> int:
+    return int(_lib.load().s2p_stem_stats_rows(h, w))
+
+
+def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scale: float = 1.0) -> torch.Tensor:
+    """OIHW fp32 -> [Cout, R*S*Cin] bf16 (tap-major, channel-minor)."""
+    _require_cuda(w_oihw)
+    w = w_oihw.detach().contiguous().float()
+    co, ci, r, s = w.shape
+    if out is None:
+        out = torch.empty(co, r * s * ci, dtype=torch.bfloat16, device=w.device)
+    assert out.is_contiguous() and out.numel() == w.numel() and out.dtype == torch.bfloat16
+    _lib.check(_lib.load().s2p_pack_conv_weight(w.data_ptr(), out.data_ptr(), co, ci, r, s, float(scale), _stream()),
+               "s2p_pack_conv_weight")
+    return out
+
+
+def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None):
+    """y = act(conv(x) + bias + residual); returns y.  ``stats`` (fp32
+    [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given."""
+    _require_cuda(x, w_packed, bias, residual, out, stats)
+    b, hin, win, cin = x.shape
+    pad = ksize // 2
+    hout = (hin + 2 * pad - ksize) // stride + 1
+    wout = (win + 2 * pad - ksize) // stride + 1
+    if out is None:
+        out = torch.empty(b, hout, wout, cout, dtype=torch.bfloat16, device=x.device)
+    if tuple(out.shape) != (b, hout, wout, cout):
+        raise RuntimeError(f"conv_igemm: out shape {tuple(out.shape)} != {(b, hout, wout, cout)}")
+    if w_packed.dtype != torch.bfloat16 or w_packed.numel() != cout * ksize * ksize * cin or not w_packed.is_contiguous():
+        raise RuntimeError("conv_igemm: packed weight has the wrong size/dtype")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout or not bias.is_contiguous()):
+        raise RuntimeError("conv_igemm: bias must be contiguous fp32 [Cout]")
+    if stats is not None:
+        rows = conv_stats_rows(hout, wout)
+        if stats.dtype != torch.float32 or stats.numel() != b * rows * cout * 2 or not stats.is_contiguous():
+            raise RuntimeError("conv_igemm: stats buffer has the wrong size")
+    res_pitch = 0
+    if residual is not None:
+        if tuple(residual.shape) != tuple(out.shape):
+            raise RuntimeError("conv_igemm: residual shape mismatch")
+        res_pitch = _nhwc_pitch(residual, "residual")
+    _lib.check(
+        _lib.load().s2p_conv_igemm_fwd(
+            x.data_ptr(), _nhwc_pitch(x, "x"), w_packed.data_ptr(), _ptr(bias), _ptr(residual), res_pitch,
+            out.data_ptr(), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout, ksize, stride, act,
+            _stream()),
+        "s2p_conv_igemm_fwd")
+    return out
+
+
+def in_stats_finalize(stats: torch.Tensor, hw: int, eps: float = 1e-5, out=None) -> torch.Tensor:
+    """partials [B, rows, C, 2] -> (mean, rstd) [B, C, 2] fp32"""
+    _require_cuda(stats)
+    b, rows, c, _ = stats.shape
+    if out is None:
+        out = torch.empty(b, c, 2, dtype=torch.float32, device=stats.device)
+    _lib.check(_lib.load().s2p_in_stats_finalize(stats.data_ptr(), rows, out.data_ptr(), b, c, hw, float(eps), _stream()),
+               "s2p_in_stats_finalize")
+    return out
+
+
+def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, out=None):
+    """y = act(((x_up - mean) * rstd) * (1 + gs + gI) + bs + bI); gs/bs are [B, C]
+    fp32 views (row pitch taken from stride(0)); gb_spatial is NHWC bf16 with 2C
+    channels (gI | bI) at the OUTPUT resolution."""
+    _require_cuda(x, mean_rstd, gs, bs, gb_spatial, out)
+    b, hx, wx, c = x.shape
+    h, w = hx * up, wx * up
+    if out is None:
+        out = torch.empty(b, h, w, c, dtype=torch.bfloat16, device=x.device)
+    if tuple(out.shape) != (b, h, w, c):
+        raise RuntimeError("mat_norm: out shape mismatch")
+    if tuple(mean_rstd.shape) != (b, c, 2) or mean_rstd.dtype != torch.float32 or not mean_rstd.is_contiguous():
+        raise RuntimeError("mat_norm: mean_rstd must be contiguous fp32 [B, C, 2]")
+    gpitch = 0
+    if gs is not None:
+        if gs.dtype != torch.float32 or tuple(gs.shape) != (b, c) or gs.stride(1) != 1 or bs.stride() != gs.stride():
+            raise RuntimeError("mat_norm: gs/bs must be fp32 [B, C] views with equal strides")
+        gpitch = gs.stride(0)
+    gbp = 0
+    if gb_spatial is not None:
+        if tuple(gb_spatial.shape) != (b, h, w, 2 * c):
+            raise RuntimeError("mat_norm: gb_spatial must be [B, H, W, 2C]")
+        gbp = _nhwc_pitch(gb_spatial, "gb_spatial")
+    _lib.check(
+        _lib.load().s2p_mat_norm_fwd(
+            x.data_ptr(), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs), _ptr(bs), gpitch,
+            _ptr(gb_spatial), gbp, out.data_ptr(), _nhwc_pitch(out, "out"), b, h, w, c, act, _stream()),
+        "s2p_mat_norm_fwd")
+    return out
+
+
+def stem_conv(image, w_oihw, bias, cout, out=None, stats=None):
+    """Cin=3 3x3 conv from the boundary image: fp32 NCHW [B,3,H,W] or uint8 NHWC [B,H,W,3]."""
+    _require_cuda(image, w_oihw, bias, out, stats)
+    if image.dtype == torch.uint8:
+        b, h, w, _ = image.shape
+        fmt = IMG_U8_NHWC
+    elif image.dtype == torch.float32:
+        b, _, h, w = image.shape
+        fmt = IMG_F32_NCHW
+    else:
+        raise RuntimeError(f"stem_conv: unsupported image dtype {image.dtype}")
+    if not image.is_contiguous():
+        raise RuntimeError("stem_conv: image must be contiguous")
+    if out is None:
+        out = torch.empty(b, h, w, cout, dtype=torch.bfloat16, device=image.device)
+    _lib.check(
+        _lib.load().s2p_stem_conv_fwd(image.data_ptr(), fmt, w_oihw.data_ptr(), _ptr(bias), out.data_ptr(),
+                                      _nhwc_pitch(out, "out"), _ptr(stats), b, h, w, cout, _stream()),
+        "s2p_stem_conv_fwd")
+    return out
+
+
+def torgb_tanh(x, w_oihw, bias, out_f32=None, out_u8=None):
+    _require_cuda(x, w_oihw, bias, out_f32, out_u8)
+    b, h, w, cin = x.shape
+    if out_f32 is None and out_u8 is None:
+        out_f32 = torch.empty(b, 3, h, w, dtype=torch.float32, device=x.device)
+    _lib.check(
+        _lib.load().s2p_torgb_tanh_fwd(x.data_ptr(), _nhwc_pitch(x, "x"), w_oihw.data_ptr(), _ptr(bias),
+                                       _ptr(out_f32), _ptr(out_u8), b, h, w, cin, _stream()),
+        "s2p_torgb_tanh_fwd")
+    return out_f32 if out_f32 is not None else out_u8
+
+
+def pos_encode(state, n_freqs, out=None):
+    _require_cuda(state, out)
+    b, s = state.shape
+    d = s * (1 + 2 * n_freqs)
+    if out is None:
+        out = torch.empty(b, d, dtype=torch.float32, device=state.device)
+    _lib.check(_lib.load().s2p_pos_encode_fwd(state.data_ptr(), out.data_ptr(), out.stride(0), b, s, n_freqs, _stream()),
+               "s2p_pos_encode_fwd")
+    return out
+
+
+def linear(x, w, bias, act=ACT_NONE, out=None):
+    _require_cuda(x, w, bias, out)
+    b, k = x.shape
+    n = w.shape[0]
+    if out is None:
+        out = torch.empty(b, n, dtype=torch.float32, device=x.device)
+    if x.dtype != torch.float32 or w.dtype != torch.float32 or not w.is_contiguous() or x.stride(1) != 1:
+        raise RuntimeError("linear: fp32 row-major operands required")
+    _lib.check(_lib.load().s2p_linear_fwd(x.data_ptr(), x.stride(0), w.data_ptr(), _ptr(bias), out.data_ptr(),
+                                          out.stride(0), b, k, n, act, _stream()), "s2p_linear_fwd")
+    return out
