@@ -1,0 +1,321 @@
+"""Benchmark of the S2P generator hot path (BASELINE.json metric: generated frames/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl reference]
+
+One "step" = one pass of the generator over one batch of B synthetic dataset rows
+per rank (uint8 HWC frame + fp32 state -> uint8 HWC next frame): the unit of work of
+BASELINE.json configs[3] (bulk synthesis, batch-sharded over 1/2/4/8 GPUs, weak
+scaling: B rows per rank per step) and, per frame, the same forward as configs[2]
+(the 5-step rollout at batch 1024).  configs[1]/[4] (GAN training) are not built yet
+(DESIGN.md "out of scope this round").
+  value : frames/s, inputs resident in HBM, CUDA-event timed, max over ranks.
+  e2e   : frames/s through s2p_b200.synthesis.BulkSynthesizer with pinned HOST
+          buffers: H2D of every row and D2H of every result inside the timed region.
+  roofline : the tcgen05 implicit-GEMM conv (dominant kernel class), measured live with
+          CUDA events around every conv launch of one instrumented step.
+  cpu_baseline : the fp32 oracle on the host cores (bounded sample), rank 0, N=1 only.
+`--impl reference` times the oracle (the reference's generator source is absent, see
+DESIGN.md) on the host cores with all threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "generated_frames_per_sec"
+UNIT = "frames/s"
+ENV = "cheetah"
+GMAC_PER_FRAME_IGEMM = None  # filled from the layer list at run time
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--batch", type=int, default=1024)
+    p.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
+    p.add_argument("--cpu-sample", type=int, default=16, help="frames per CPU-baseline forward")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def workload_config(args, world):
+    return {"workload": "bulk synthesis (BASELINE configs[3]): uint8 HWC frame + fp32 state -> uint8 HWC next frame, "
+                        f"{ENV}, {args.batch} rows per rank per step; per-frame forward identical to configs[2]",
+            "env_type": ENV, "rows_per_rank_per_step": args.batch, "global_rows_per_step": args.batch * world,
+            "image": "100x100x3 uint8", "state_dim": 17, "parallelism": f"shard{world}",
+            "weights": "random init (ORACLE_SPEC v1 'scaled' init, seed 1234)",
+            "l2_policy": "inputs+activations per step (>=3 GB) exceed the 126 MB L2; no explicit flush"}
+
+
+# ---------------------------------------------------------------------------- CPU legs
+def cpu_oracle_fps(sample, repeats, threads=None):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import s2p_oracle as O
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    torch.manual_seed(1234)
+    net = O.define_G(O.make_options(env_type=ENV, init_type="scaled")).eval()
+    g = torch.Generator().manual_seed(0)
+    frames = torch.randint(0, 256, (sample, 100, 100, 3), dtype=torch.uint8, generator=g)
+    states = torch.randn(sample, 17, generator=g)
+    times = []
+    with torch.no_grad():
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            out = O.to_uint8_hwc(net(O.from_uint8_hwc(frames), states))
+            times.append(time.perf_counter() - t0)
+    assert out.shape == frames.shape
+    return sample / min(times), sample / (sum(times) / len(times)), threads, times
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = args.cpu_sample
+    # warmup + steps forwards of `sample` frames each; bounded: ~0.6 s/frame/8 cores
+    fps_best, fps_mean, threads, times = cpu_oracle_fps(sample, args.warmup + args.steps)
+    timed = times[args.warmup:] or times
+    ms = 1e3 * sum(timed) / len(timed)
+    value = sample / (ms / 1e3)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, max(1, args.gpus)),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"{sample} frames per step (the oracle: reference generator source is absent)"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [t.strip() for t in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._loop, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------- GPU arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import s2p_b200
+    from s2p_b200 import _lib, ops
+    from s2p_b200.synthesis import BulkSynthesizer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with torch.distributed.run (see module docstring)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    opt = s2p_b200.make_options(env_type=ENV, gpu_ids=str(local), init_type="scaled")
+    torch.manual_seed(1234)
+    net = s2p_b200.define_G(opt)
+    net.pack()
+    B = args.batch
+    g = torch.Generator().manual_seed(100 + rank)
+    frames_h = torch.randint(0, 256, (B, 100, 100, 3), dtype=torch.uint8, generator=g).pin_memory()
+    states_h = torch.randn(B, 17, generator=g).pin_memory()
+    out_h = torch.empty_like(frames_h).pin_memory()
+    frames_d, states_d = frames_h.to(dev), states_h.to(dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing
+    for _ in range(args.warmup):
+        net.forward_u8(frames_d, states_d)
+    barrier()
+    with ClockSampler(local) as clk:
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            res = net.forward_u8(frames_d, states_d)
+        e1.record()
+        barrier()
+        launches = _lib.launch_count() - l0
+        ms_dev = max_over_ranks(e0.elapsed_time(e1))
+        # ---- end to end through the public bulk API with host buffers
+        synth = BulkSynthesizer(net, batch=min(B, 256))
+        for _ in range(max(1, args.warmup // 2)):
+            synth.synthesize(frames_h, states_h, out_h)
+        barrier()
+        synth.h2d_bytes = synth.d2h_bytes = 0
+        e0.record()
+        for _ in range(args.steps):
+            synth.synthesize(frames_h, states_h, out_h)
+        e1.record()
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    assert torch.equal(out_h.to(dev), res), "e2e result differs from the device-resident result"
+    clocks = clk.summary()
+
+    # ---- instrumented step: CUDA events around every conv / norm launch (rank 0)
+    roof, roof_norm, shares = None, None, None
+    if rank == 0:
+        roof, roof_norm, shares = instrumented_step(net, frames_d, states_d, ops, torch)
+
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    frames_total = B * world * args.steps
+    value = frames_total / (ms_dev / 1e3)
+    e2e = frames_total / (ms_e2e / 1e3)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(args, world),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": synth.h2d_bytes // args.steps,
+                    "d2h_bytes_per_step": synth.d2h_bytes // args.steps, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_norm": roof_norm,
+            "kernel_time_share": shares}
+    if world == 1 and not args.no_cpu_baseline:
+        best, mean, threads, times = cpu_oracle_fps(args.cpu_sample, 2)
+        line["cpu_baseline"] = {"value": best, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"{args.cpu_sample} frames x 2 forwards of the fp32 oracle (best of 2), "
+                                          "same uint8->uint8 row workload"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def instrumented_step(net, frames_d, states_d, ops, torch):
+    """One extra step with a CUDA-event pair around every conv / norm launch."""
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+    rec = {"conv": [], "norm": [], "other": []}
+    orig = {n: getattr(ops, n) for n in ("conv_igemm", "mat_norm", "stem_conv", "torgb_tanh", "linear",
+                                         "pos_encode", "in_stats_finalize")}
+
+    def wrap(name, kind, work_fn):
+        fn = orig[name]
+
+        def inner(*a, **k):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            r = fn(*a, **k)
+            e.record()
+            rec[kind].append((s, e, work_fn(*a, **k) if work_fn else 0.0))
+            return r
+        return inner
+
+    def conv_flops(x, w_packed, bias, cout, ksize, stride=1, *a, **k):
+        b, h, w, cin = x.shape
+        ho = (h + 2 * (ksize // 2) - ksize) // stride + 1
+        wo = (w + 2 * (ksize // 2) - ksize) // stride + 1
+        return 2.0 * b * ho * wo * cout * cin * ksize * ksize
+
+    def norm_bytes(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=2, out=None):
+        b, hx, wx, c = x.shape
+        px = b * hx * up * wx * up
+        return 2.0 * c * (b * hx * wx) + 2.0 * c * px + (4.0 * c * px if gb_spatial is not None else 0.0)
+
+    ops.conv_igemm = wrap("conv_igemm", "conv", conv_flops)
+    ops.mat_norm = wrap("mat_norm", "norm", norm_bytes)
+    for n in ("stem_conv", "torgb_tanh", "linear", "pos_encode", "in_stats_finalize"):
+        setattr(ops, n, wrap(n, "other", None))
+    try:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        net.forward_u8(frames_d, states_d)
+        t1.record()
+        torch.cuda.synchronize()
+    finally:
+        for n, fn in orig.items():
+            setattr(ops, n, fn)
+    total = t0.elapsed_time(t1)
+    tms = {k: sum(s.elapsed_time(e) for s, e, _ in v) for k, v in rec.items()}
+    work = {k: sum(w for _, _, w in v) for k, v in rec.items()}
+    nconv, nnorm = len(rec["conv"]), len(rec["norm"])
+    ach_tf = work["conv"] / (tms["conv"] / 1e3) / 1e12
+    ach_gb = work["norm"] / (tms["norm"] / 1e3) / 1e9
+    roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM; all launches of one step)", "bound": "tensor",
+            "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
+            "peak_source": src, "launches": nconv, "avg_launch_ms": tms["conv"] / nconv,
+            "flops_per_launch_avg": work["conv"] / nconv}
+    roof_norm = {"kernel": "mat_norm_kernel (fused IN + MAT modulation + LeakyReLU; all launches of one step)",
+                 "bound": "hbm", "achieved": ach_gb, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gb / hbm_peak,
+                 "traffic": None, "peak_source": src, "launches": nnorm, "avg_launch_ms": tms["norm"] / nnorm,
+                 "bytes_per_launch_avg": work["norm"] / nnorm}
+    shares = {k: tms[k] / total for k in tms}
+    shares["step_ms_instrumented"] = total
+    return roof, roof_norm, shares
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

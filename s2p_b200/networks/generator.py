@@ -259,7 +259,6 @@ class S2PGeneratorB200(nn.Module):
                 m = P["mat"][(bi, name)]
                 C = m["C"]
                 hsl = hs[ds][..., m["h_off"]:m["h_off"] + nh]
-                gb, _ = self._conv(f"gb{ds}", hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1) if False else (None, None)
                 gbuf = self._buf(f"gb{ds}.{2 * C}", (B, hh, ww, 2 * C), bf)
                 ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
                 gs = gsbs[:, m["s_off"]:m["s_off"] + C]

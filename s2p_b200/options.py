@@ -1,0 +1,35 @@
+"""SPADE-style options for the S2P drivers.  Flag names follow the reference's
+documented command lines (/root/reference/README.md:33 simple_test.py, :59 train.py);
+the option parser itself is absent from the reference snapshot."""
+from __future__ import annotations
+
+import argparse
+
+STATE_DIM = {"cheetah": 17, "walker": 24}  # cheetah: normalize_configs_dict.pkl; walker: DMC observation size
+IMAGE_SIZE = 100  # examples/iql/mujoco_finetune.py:242,327
+
+
+def make_options(argv=None, **overrides):
+    p = argparse.ArgumentParser("s2p_b200", add_help=False)
+    p.add_argument("--netG", type=str, default="s2p")
+    p.add_argument("--env_type", type=str, default="cheetah", choices=sorted(STATE_DIM))
+    p.add_argument("--gpu_ids", type=str, default="0")
+    p.add_argument("--batchSize", type=int, default=16)
+    p.add_argument("--dataroot", type=str, default="./datasets")
+    p.add_argument("--start_idx", type=int, default=0)
+    p.add_argument("--seq_len", type=int, default=5)
+    p.add_argument("--ngf", type=int, default=64)
+    p.add_argument("--nhidden", type=int, default=128)
+    p.add_argument("--w_dim", type=int, default=512)
+    p.add_argument("--pe_freqs", type=int, default=10)
+    p.add_argument("--mapping_layers", type=int, default=8)
+    p.add_argument("--init_type", type=str, default="xavier")
+    p.add_argument("--init_variance", type=float, default=0.02)
+    p.add_argument("--max_microbatch", type=int, default=128)
+    opt, _ = p.parse_known_args(argv if argv is not None else [])
+    for k, v in overrides.items():
+        setattr(opt, k, v)
+    if isinstance(opt.gpu_ids, str):
+        opt.gpu_ids = [int(t) for t in opt.gpu_ids.split(",") if t.strip() and int(t) >= 0]
+    opt.state_dim = STATE_DIM[opt.env_type]
+    return opt

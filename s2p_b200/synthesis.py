@@ -1,0 +1,110 @@
+"""Bulk augmented-dataset synthesis: the reference's unpublished "generation code"
+(/root/reference/README.md:54, TODO in the reference) between the state-transition
+rollout and the SLAC loader:
+
+    image_observations_tp1[i] = netG(image_observations[i], next_observations[i])
+
+Row schema (pinned by the reference on both sides): frames are uint8 HWC
+[N,100,100,3] (rlkit/torch/slac/algo.py:174-175,189-190), states are float32 [N,S]
+(state_transition_rollout.py:62-64,222-224).  Rows are independent, so N GPUs take
+contiguous index ranges with no data-path collective (SURVEY.md section 8 e).
+
+Host side of each rank: pinned staging buffers, a copy-in stream, the compute stream
+and a copy-out stream, double buffered so H2D of batch i+1 and D2H of batch i-1
+overlap the kernels of batch i.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+def shard_range(n_rows: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous, balanced partition [lo, hi) of n_rows over `world` ranks (the first
+    n_rows % world ranks take one extra row)."""
+    if world <= 0 or not (0 <= rank < world) or n_rows < 0:
+        raise ValueError(f"bad shard request n_rows={n_rows} rank={rank} world={world}")
+    base, rem = divmod(n_rows, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class BulkSynthesizer:
+    def __init__(self, net, batch: int = 1024):
+        self.net = net
+        self.batch = int(batch)
+        self.device = next(net.parameters()).device
+        if self.device.type != "cuda":
+            raise RuntimeError("BulkSynthesizer needs the generator on a CUDA device (no CPU fallback)")
+        self._copy_in = torch.cuda.Stream(self.device)
+        self._copy_out = torch.cuda.Stream(self.device)
+        self._slots = None
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def _make_slots(self, h, w, s):
+        b = self.batch
+        slots = []
+        for _ in range(2):
+            slots.append(dict(
+                frames=torch.empty(b, h, w, 3, dtype=torch.uint8, device=self.device),
+                states=torch.empty(b, s, dtype=torch.float32, device=self.device),
+                out=torch.empty(b, h, w, 3, dtype=torch.uint8, device=self.device),
+                loaded=torch.cuda.Event(), computed=torch.cuda.Event(), drained=torch.cuda.Event()))
+        self._slots = (slots, (h, w, s))
+
+    @staticmethod
+    def _as_host_tensor(a, dtype):
+        t = torch.from_numpy(a) if isinstance(a, np.ndarray) else a
+        if t.dtype != dtype or t.is_cuda or not t.is_contiguous():
+            raise RuntimeError(f"expected a contiguous host {dtype} array")
+        return t
+
+    @torch.no_grad()
+    def synthesize(self, frames, states, out=None):
+        """frames: host uint8 [N,H,W,3]; states: host float32 [N,S]; returns host uint8
+        [N,H,W,3] (written into `out` when given; pinned memory makes the copies async)."""
+        frames = self._as_host_tensor(frames, torch.uint8)
+        states = self._as_host_tensor(states, torch.float32)
+        n, h, w, _ = frames.shape
+        if states.shape[0] != n:
+            raise RuntimeError("frames and states disagree on the number of rows")
+        if out is None:
+            out = torch.empty_like(frames, pin_memory=True)
+        out = self._as_host_tensor(out, torch.uint8)
+        if self._slots is None or self._slots[1] != (h, w, states.shape[1]):
+            self._make_slots(h, w, states.shape[1])
+        slots = self._slots[0]
+        compute = torch.cuda.current_stream(self.device)
+        nb = (n + self.batch - 1) // self.batch
+        for i in range(nb):
+            lo, hi = i * self.batch, min(n, (i + 1) * self.batch)
+            m = hi - lo
+            sl = slots[i % 2]
+            with torch.cuda.stream(self._copy_in):
+                if i >= 2:
+                    self._copy_in.wait_event(sl["computed"])      # slot's inputs consumed
+                sl["frames"][:m].copy_(frames[lo:hi], non_blocking=True)
+                sl["states"][:m].copy_(states[lo:hi], non_blocking=True)
+                sl["loaded"].record(self._copy_in)
+            compute.wait_event(sl["loaded"])
+            if i >= 2:
+                compute.wait_event(sl["drained"])                  # slot's output copied out
+            res = self.net.forward_u8(sl["frames"][:m], sl["states"][:m])
+            sl["out"][:m].copy_(res)
+            sl["computed"].record(compute)
+            with torch.cuda.stream(self._copy_out):
+                self._copy_out.wait_event(sl["computed"])
+                out[lo:hi].copy_(sl["out"][:m], non_blocking=True)
+                sl["drained"].record(self._copy_out)
+            self.h2d_bytes += m * (h * w * 3 + states.shape[1] * 4)
+            self.d2h_bytes += m * h * w * 3
+        compute.wait_stream(self._copy_out)
+        return out
+
+    def synthesize_shard(self, frames, states, rank: int, world: int, out=None):
+        """This rank's contiguous slice of a dataset every rank can see (e.g. a memory
+        map): returns (lo, hi, frames_tp1[lo:hi])."""
+        lo, hi = shard_range(frames.shape[0], rank, world)
+        res = self.synthesize(frames[lo:hi], states[lo:hi], out)
+        return lo, hi, res

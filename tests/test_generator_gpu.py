@@ -1,0 +1,120 @@
+"""GPU: end-to-end parity of the B200 generator (through s2p_b200's public surface,
+which calls the C ABI) against the frozen fp32 oracle and its golden fixtures.
+Tolerances (bf16 activations, fp32 accumulate/statistics): PSNR >= 50 dB on
+[0,1]-mapped images (BASELINE.json north_star) and a stated max-abs."""
+import pytest
+import torch
+
+import common
+import s2p_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+MAX_ABS = 0.08     # on the [-1,1] output, 'scaled' (O(1) activations) init
+PSNR_MIN = 50.0    # BASELINE.json north_star, on the spec's own random init (SPADE xavier, gain 0.02)
+# 'scaled' is this repo's stress init: O(1) activations everywhere and a saturating tanh, so
+# every bf16 rounding of the ~30 stored activations shows up in the output.  Measured 48.4 dB
+# (round 1, bf16 gamma/beta maps); the floor below guards against regressions.
+PSNR_MIN_STRESS = 47.0
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    import s2p_b200
+    return s2p_b200
+
+
+def _pair(pkg, env, init):
+    ora = common.build_oracle(env, init)
+    net = pkg.define_G(pkg.make_options(env_type=env, gpu_ids="0"))
+    net.load_state_dict(ora.state_dict())
+    return ora, net
+
+
+@pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2"])
+def test_one_step_vs_golden_and_oracle(pkg, name):
+    case = common.manifest()["cases"][name]
+    ora, net = _pair(pkg, case["env"], case["init_type"])
+    image, states = common.make_inputs(case["env"], case["batch"], 1)
+    out = net(image.cuda(), states[:, 0].cuda()).cpu()
+    gold = torch.from_numpy(common.load_golden(name)["first"])
+    with torch.no_grad():
+        ref = ora.cuda()(image.cuda(), states[:, 0].cuda()).cpu()
+    assert (ref - gold).abs().max().item() <= 1e-3, "oracle on GPU disagrees with its CPU golden"
+    assert out.shape == gold.shape and torch.isfinite(out).all()
+    p = common.psnr01(out, gold)
+    e = (out - gold).abs().max().item()
+    print(f"{name}: psnr={p:.1f} dB max_abs={e:.3e}")
+    assert p >= (PSNR_MIN_STRESS if case["init_type"] == "scaled" else PSNR_MIN)
+    assert e <= (MAX_ABS if case["init_type"] == "scaled" else 1e-4)
+
+
+def test_rollout_5_steps(pkg):
+    """N-step autoregressive synthesis (README.md:30-33).  Per-step parity is checked
+    teacher-forced (oracle and B200 step from the SAME previous frame), because a
+    random-weight generator amplifies any input perturbation from step to step; the
+    free-running distance to the golden rollout is reported and loosely bounded."""
+    name = "cheetah_scaled_roll5_b1"
+    case = common.manifest()["cases"][name]
+    ora, net = _pair(pkg, case["env"], case["init_type"])
+    ora = ora.cuda()
+    image, states = common.make_inputs(case["env"], 1, 5)
+    out = net.rollout(image.cuda(), states.cuda())
+    assert out.shape == (1, 5, 3, 100, 100)
+    prev = image.cuda()
+    for k in range(5):
+        with torch.no_grad():
+            ref = ora(prev, states[:, k].cuda())
+        p = common.psnr01(out[:, k].cpu(), ref.cpu())
+        print(f"rollout step {k + 1}: teacher-forced psnr={p:.1f} dB")
+        assert p >= PSNR_MIN_STRESS
+        prev = out[:, k]
+    gold = common.load_golden(name)
+    p1 = common.psnr01(out[:, 0].cpu(), torch.from_numpy(gold["first"]))
+    p5 = common.psnr01(out[:, -1].cpu(), torch.from_numpy(gold["last"]))
+    print(f"rollout free-running vs golden: step1 psnr={p1:.1f} step5 psnr={p5:.1f}")
+    assert p1 >= PSNR_MIN_STRESS and p5 >= 25.0
+
+
+def test_bit_stable_and_batch_invariant(pkg):
+    """same bytes run to run, and independent of batch composition / micro-batching /
+    sharding (the multi-GPU bulk path relies on this: SURVEY.md section 8 e)."""
+    _, net = _pair(pkg, "cheetah", "scaled")
+    image, states = common.make_inputs("cheetah", 6, 1, seed_img=5, seed_state=6)
+    image, st = image.cuda(), states[:, 0].cuda()
+    a = net(image, st)
+    b = net(image, st)
+    assert torch.equal(a, b)
+    parts = torch.cat([net(image[:2], st[:2]), net(image[2:5], st[2:5]), net(image[5:], st[5:])])
+    assert torch.equal(a, parts)
+    net.max_microbatch = 4
+    assert torch.equal(a, net(image, st))
+
+
+def test_uint8_dataset_path(pkg):
+    ora, net = _pair(pkg, "cheetah", "scaled")
+    g = torch.Generator().manual_seed(4)
+    frames = torch.randint(0, 256, (3, 100, 100, 3), dtype=torch.uint8, generator=g)
+    _, states = common.make_inputs("cheetah", 3, 1)
+    out = net.forward_u8(frames.cuda(), states[:, 0].cuda()).cpu()
+    with torch.no_grad():
+        ref = O.to_uint8_hwc(ora(O.from_uint8_hwc(frames), states[:, 0]))
+    assert out.dtype == torch.uint8 and out.shape == (3, 100, 100, 3)
+    d = (out.int() - ref.int()).abs()
+    print(f"u8: max diff {d.max().item()} LSB, mean {d.float().mean().item():.4f}")
+    assert d.max().item() <= 12 and d.float().mean().item() <= 1.0   # 48 dB ~ 1 LSB rms
+    # f32 path on the same frames agrees with the u8-in path
+    f = net(O.from_uint8_hwc(frames).cuda(), states[:, 0].cuda())
+    assert (O.to_uint8_hwc(f.cpu()).int() - out.int()).abs().max().item() <= 1
+
+
+def test_state_changes_output(pkg):
+    _, net = _pair(pkg, "cheetah", "scaled")
+    image, states = common.make_inputs("cheetah", 2, 2)
+    a = net(image.cuda(), states[:, 0].cuda())
+    b = net(image.cuda(), states[:, 1].cuda())
+    assert (a - b).abs().max().item() > 1e-3

@@ -1,0 +1,74 @@
+"""CPU: host logic of the multi-GPU bulk path (world_size 2, gloo).  Generation shards
+by contiguous index range with no data-path collective (SURVEY.md section 8 e); what
+has to be right on the host is the partition and the max-over-ranks timing plumbing."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from s2p_b200.synthesis import BulkSynthesizer, shard_range
+
+
+@pytest.mark.parametrize("n,world", [(1_000_000, 8), (10, 3), (7, 8), (0, 2), (1024, 1), (1001, 4)])
+def test_shard_range_partitions_exactly(n, world):
+    ranges = [shard_range(n, r, world) for r in range(world)]
+    assert ranges[0][0] == 0 and ranges[-1][1] == n
+    for (a0, a1), (b0, b1) in zip(ranges, ranges[1:]):
+        assert a1 == b0 and a0 <= a1
+    sizes = [hi - lo for lo, hi in ranges]
+    assert max(sizes) - min(sizes) <= 1
+
+
+def test_shard_range_rejects_bad_rank():
+    with pytest.raises(ValueError):
+        shard_range(10, 2, 2)
+    with pytest.raises(ValueError):
+        shard_range(10, 0, 0)
+
+
+def test_bulk_synthesizer_needs_cuda():
+    import s2p_b200
+    net = s2p_b200.S2PGeneratorB200(s2p_b200.make_options())
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        BulkSynthesizer(net)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n_rows, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = shard_range(n_rows, rank, world)
+    # each rank "synthesises" its slice: mark rows with rank+1 (stand-in for the GPU step)
+    mine = torch.zeros(n_rows, dtype=torch.int64)
+    mine[lo:hi] = rank + 1
+    dist.all_reduce(mine, op=dist.ReduceOp.SUM)          # test-only gather of the coverage map
+    t = torch.tensor([10.0 * (rank + 1)], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)             # bench.py's max-over-ranks timing
+    if rank == 0:
+        q.put((mine.tolist(), float(t.item())))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharding_gloo():
+    world, n_rows = 2, 11
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_rows, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    cover, tmax = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert cover == [1] * 6 + [2] * 5       # every row owned by exactly one rank, contiguous
+    assert tmax == 20.0
