@@ -255,8 +255,8 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
     rec = {"conv": [], "norm": [], "other": []}
-    orig = {n: getattr(ops, n) for n in ("conv_igemm", "mat_norm", "stem_conv", "torgb_tanh", "linear",
-                                         "pos_encode", "in_stats_finalize")}
+    orig = {n: getattr(ops, n) for n in ("conv_igemm", "conv_mat_fused", "mat_norm", "stem_conv", "torgb_tanh",
+                                         "linear", "pos_encode", "in_stats_finalize", "mat_prepare")}
 
     def wrap(name, kind, work_fn):
         fn = orig[name]
@@ -281,9 +281,14 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
         px = b * hx * up * wx * up
         return 2.0 * c * (b * hx * wx) + 2.0 * c * px + (4.0 * c * px if gb_spatial is not None else 0.0)
 
+    def fused_flops(h, w_packed_gb, x, mod_table, up=1, act=2, ksize=3, out=None):
+        b, hh, ww, cin = h.shape
+        return 2.0 * b * hh * ww * (2 * x.shape[3]) * cin * ksize * ksize
+
     ops.conv_igemm = wrap("conv_igemm", "conv", conv_flops)
+    ops.conv_mat_fused = wrap("conv_mat_fused", "conv", fused_flops)
     ops.mat_norm = wrap("mat_norm", "norm", norm_bytes)
-    for n in ("stem_conv", "torgb_tanh", "linear", "pos_encode", "in_stats_finalize"):
+    for n in ("stem_conv", "torgb_tanh", "linear", "pos_encode", "in_stats_finalize", "mat_prepare"):
         setattr(ops, n, wrap(n, "other", None))
     try:
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -300,7 +305,8 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     nconv, nnorm = len(rec["conv"]), len(rec["norm"])
     ach_tf = work["conv"] / (tms["conv"] / 1e3) / 1e12
     ach_gb = work["norm"] / (tms["norm"] / 1e3) / 1e9
-    roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM; all launches of one step)", "bound": "tensor",
+    roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM, plain and MAT-fused epilogues; all launches of one step)",
+            "bound": "tensor",
             "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
             "peak_source": src, "launches": nconv, "avg_launch_ms": tms["conv"] / nconv,
             "flops_per_launch_avg": work["conv"] / nconv}

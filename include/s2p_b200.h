@@ -74,6 +74,26 @@ int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd,
                      const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y,
                      int y_pitch, int B, int H, int W, int C, int act, void* stream);
 
+/* ---- (a3 fused into a4) gamma/beta conv with the MAT norm applied in its epilogue ----
+ * replaces, in ONE kernel, oracle MAT.mlp_gamma + MAT.mlp_beta (nn.Conv2d 3x3) and the
+ * whole of F.instance_norm + modulation + F.leaky_relu (+ F.interpolate(x2) when up==2):
+ * the spatial gamma/beta maps never leave TMEM.
+ *   acc[pix, :] = conv(h, w_packed_gb)                         (2C columns per pixel)
+ *   y[n,h,w,c]  = act( (x[n,h/up,w/up,c]*A + Bc) * (G1 + gamma_acc) + (B0 + beta_acc) )
+ * with (A, Bc, G1, B0) = mod_table[n][c] from s2p_mat_prepare (A = rstd, Bc = -mean*rstd,
+ * G1 = 1 + gs + bias_gamma, B0 = bs + bias_beta).
+ * Weight rows are tile-interleaved: with ct = s2p_mat_fused_ct(C), rows
+ * [2*ct*j, 2*ct*j+ct) are gamma channels [ct*j, ct*(j+1)) and the next ct rows the beta
+ * channels of the same range (so one accumulator tile holds both for its channels).
+ * bias_gb in s2p_mat_prepare is in plain [gamma(C) | beta(C)] order.
+ * Requires Cin % 64 == 0, C in {32, 64} or C % 128 == 0. */
+int s2p_mat_fused_ct(int C);
+int s2p_mat_prepare(const float* stats_partial, int rows, const float* gs, const float* bs, int gsbs_pitch,
+                    const float* bias_gb, float* mod_table, int B, int C, int HW, float eps, void* stream);
+int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, const void* x, int x_pitch,
+                           int up, const float* mod_table, void* y, int y_pitch, int B, int H, int W,
+                           int Cin, int C, int ksize, int act, void* stream);
+
 /* ---- (a5 head/tail) Cin=3 stem conv and Cout=3 ToRGB + tanh --------------------
  * stem: oracle ImageEncoder.conv1 (3->Cout 3x3 s1 p1) straight from the boundary
  * image (fp32 NCHW in [-1,1] or uint8 NHWC mapped by u/127.5-1) to NHWC bf16, with

@@ -33,6 +33,11 @@ struct ConvParams {
   const __nv_bfloat16* residual;
   __nv_bfloat16* out;
   float* stats_partial;   // [B][tiles_per_img*4][Cout][2] (sum, sumsq) or null
+  // fused MAT epilogue (conv_mat_fused): the accumulators are the spatial gamma|beta maps,
+  // the stored value is act((x*A + Bc) * (G1 + gamma) + (B0 + beta)) with (A,Bc,G1,B0) = mat_tab[n][c]
+  const __nv_bfloat16* mat_x;   // pre-norm activation [B][H/up][W/up][mat_x_pitch]
+  const float4* mat_tab;        // [B][mat_C]
+  int mat_x_pitch, mat_up, mat_C;
 };
 
 template <int BLOCK_N>
@@ -63,7 +68,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool FUSED_MAT>
 __global__ void __launch_bounds__(192, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
@@ -174,6 +179,51 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
+      if constexpr (FUSED_MAT) {
+        constexpr int CT = BLOCK_N / 2;   // channels per n-tile: columns [0,CT) = gamma, [CT,2CT) = beta
+        size_t xpix;
+        if (p.mat_up == 2) {
+          xpix = (static_cast<size_t>(img) * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
+        } else {
+          xpix = pix;
+        }
+#pragma unroll 1
+        for (int c = 0; c < CT / 32; ++c) {
+          uint32_t rg[32], rb[32];
+          tmem_ld32(t_row + c * 32, rg);
+          tmem_ld32(t_row + CT + c * 32, rb);
+          tmem_ld_wait();
+          const int ch = n_tile * CT + c * 32;
+          if (valid) {
+            const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch);
+            const float4* tab = p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch;
+            uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 xr = __ldg(x4 + j);
+              const uint32_t xw[4] = {xr.x, xr.y, xr.z, xr.w};
+              uint32_t ow[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float o2[2];
+#pragma unroll
+                for (int hlf = 0; hlf < 2; ++hlf) {
+                  const int k = 8 * j + 2 * e + hlf;
+                  const float4 t = __ldg(tab + k);
+                  const float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
+                  const float xh = fmaf(xv, t.x, t.y);
+                  float v = fmaf(xh, t.z + __uint_as_float(rg[k]), t.w + __uint_as_float(rb[k]));
+                  if (p.act == 2) v = v > 0.f ? v : 0.2f * v;
+                  else if (p.act == 1) v = fmaxf(v, 0.f);
+                  o2[hlf] = v;
+                }
+                ow[e] = pack_bf16x2(o2[0], o2[1]);
+              }
+              o4[j] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+            }
+          }
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t raw[32];
@@ -235,6 +285,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           *dst = make_float2(cs, cq);
         }
       }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -284,18 +335,18 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
   *th_out = bth;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool FUSED_MAT>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
-    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N>,
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, FUSED_MAT>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_igemm_kernel<BLOCK_N><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  conv_igemm_kernel<BLOCK_N, FUSED_MAT><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
   count_launch();
   return check_launch("conv_igemm_kernel");
 }
@@ -308,31 +359,15 @@ extern "C" int s2p_conv_stats_rows(int Hout, int Wout) {
   return ((Wout + tw - 1) / tw) * ((Hout + th - 1) / th) * 4;
 }
 
-extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
-                                  const void* residual, int res_pitch, void* y, int y_pitch,
-                                  float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
-                                  int ksize, int stride, int act, void* stream) {
-  using namespace s2p;
-  S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
-  S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
-  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
-  S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
-  S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv: ksize=%d unsupported", ksize);
-  S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
-  S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
-  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
-  S2P_CHECK_ARG(y_pitch >= Cout && y_pitch % 8 == 0, "conv: y_pitch=%d", y_pitch);
-  S2P_CHECK_ARG(!residual || (res_pitch >= Cout && res_pitch % 8 == 0), "conv: res_pitch=%d", res_pitch);
-  S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 &&
-                    (reinterpret_cast<uintptr_t>(w_packed) & 15) == 0 &&
-                    (reinterpret_cast<uintptr_t>(residual) & 15) == 0 &&
-                    (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
-                "conv: pointers must be 16-byte aligned");
+namespace s2p {
+
+// Shared host path of the two conv entry points: validates the GEMM geometry, builds the
+// two tensor maps and launches.  `p` arrives with the epilogue fields already filled.
+static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B, int Hin, int Win, int Cin,
+                         int Cout, int ksize, int stride, int block_n, bool fused, ConvParams p, void* stream) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-
   const int pad = ksize / 2;
-  ConvParams p{};
   p.B = B;
   p.H = (Hin + 2 * pad - ksize) / stride + 1;
   p.W = (Win + 2 * pad - ksize) / stride + 1;
@@ -340,14 +375,8 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
   conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
   p.tiles_x = (p.W + p.tile_w - 1) / p.tile_w;
   p.tiles_y = (p.H + p.tile_h - 1) / p.tile_h;
-  const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
   p.num_m_tiles = B * p.tiles_x * p.tiles_y;
   p.num_n_tiles = Cout / block_n;
-  p.out_pitch = y_pitch; p.res_pitch = res_pitch; p.act = act;
-  p.bias = bias;
-  p.residual = static_cast<const __nv_bfloat16*>(residual);
-  p.out = static_cast<__nv_bfloat16*>(y);
-  p.stats_partial = stats_partial;
 
   CUtensorMap ta, tb;
   {
@@ -373,10 +402,76 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: weight tensor map encode failed (CUresult %d)", (int)r);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  switch (block_n) {
-    case 256: return launch_conv<256>(ta, tb, p, st);
-    case 192: return launch_conv<192>(ta, tb, p, st);
-    case 128: return launch_conv<128>(ta, tb, p, st);
-    default: return launch_conv<64>(ta, tb, p, st);
+  if (fused) {
+    switch (block_n) {
+      case 256: return launch_conv<256, true>(ta, tb, p, st);
+      case 128: return launch_conv<128, true>(ta, tb, p, st);
+      default: return launch_conv<64, true>(ta, tb, p, st);
+    }
   }
+  switch (block_n) {
+    case 256: return launch_conv<256, false>(ta, tb, p, st);
+    case 192: return launch_conv<192, false>(ta, tb, p, st);
+    case 128: return launch_conv<128, false>(ta, tb, p, st);
+    default: return launch_conv<64, false>(ta, tb, p, st);
+  }
+}
+
+static inline bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
+
+}  // namespace s2p
+
+extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
+                                  const void* residual, int res_pitch, void* y, int y_pitch,
+                                  float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
+                                  int ksize, int stride, int act, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
+  S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
+  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
+  S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
+  S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
+  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
+  S2P_CHECK_ARG(y_pitch >= Cout && y_pitch % 8 == 0, "conv: y_pitch=%d", y_pitch);
+  S2P_CHECK_ARG(!residual || (res_pitch >= Cout && res_pitch % 8 == 0), "conv: res_pitch=%d", res_pitch);
+  S2P_CHECK_ARG(aligned16(x) && aligned16(y) && aligned16(w_packed) && aligned16(residual) && aligned16(bias),
+                "conv: pointers must be 16-byte aligned");
+  ConvParams p{};
+  p.out_pitch = y_pitch; p.res_pitch = res_pitch; p.act = act;
+  p.bias = bias;
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.out = static_cast<__nv_bfloat16*>(y);
+  p.stats_partial = stats_partial;
+  const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
+  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, block_n, false, p, stream);
+}
+
+extern "C" int s2p_mat_fused_ct(int C) { return C >= 128 ? 128 : C; }
+
+extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, const void* x,
+                                      int x_pitch, int up, const float* mod_table, void* y, int y_pitch, int B,
+                                      int H, int W, int Cin, int C, int ksize, int act, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(h && w_packed_gb && x && mod_table && y, "conv_mat_fused: null pointer");
+  S2P_CHECK_ARG(B > 0 && H > 0 && W > 0, "conv_mat_fused: bad dims B=%d H=%d W=%d", B, H, W);
+  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv_mat_fused: Cin=%d must be a multiple of 64", Cin);
+  S2P_CHECK_ARG(C >= 32 && C % 32 == 0 && (C < 128 || C % 128 == 0),
+                "conv_mat_fused: C=%d must be 32, 64 or a multiple of 128", C);
+  S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv_mat_fused: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "conv_mat_fused: act=%d unsupported", act);
+  S2P_CHECK_ARG(up == 1 || (up == 2 && H % 2 == 0 && W % 2 == 0), "conv_mat_fused: up=%d H=%d W=%d", up, H, W);
+  S2P_CHECK_ARG(h_pitch >= Cin && h_pitch % 8 == 0, "conv_mat_fused: h_pitch=%d", h_pitch);
+  S2P_CHECK_ARG(x_pitch >= C && x_pitch % 8 == 0 && y_pitch >= C && y_pitch % 8 == 0, "conv_mat_fused: pitch");
+  S2P_CHECK_ARG(aligned16(h) && aligned16(x) && aligned16(y) && aligned16(w_packed_gb) && aligned16(mod_table),
+                "conv_mat_fused: pointers must be 16-byte aligned");
+  ConvParams p{};
+  p.out_pitch = y_pitch; p.act = act;
+  p.out = static_cast<__nv_bfloat16*>(y);
+  p.mat_x = static_cast<const __nv_bfloat16*>(x);
+  p.mat_tab = reinterpret_cast<const float4*>(mod_table);
+  p.mat_x_pitch = x_pitch; p.mat_up = up; p.mat_C = C;
+  const int block_n = 2 * s2p_mat_fused_ct(C);
+  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, block_n, true, p, stream);
 }

@@ -33,6 +33,38 @@ __global__ void in_stats_finalize_kernel(const float2* __restrict__ partial, int
       make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps))));
 }
 
+// Statistics finalize + per-(n,c) modulation table for the fused conv epilogue
+// (s2p_conv_mat_fused_fwd):  tab[n][c] = (rstd, -mean*rstd, 1 + gs + bias_gamma, bs + bias_beta).
+__global__ void mat_prepare_kernel(const float2* __restrict__ partial, int rows, const float* __restrict__ gs,
+                                   const float* __restrict__ bs, int gsbs_pitch, const float* __restrict__ bias_gb,
+                                   float4* __restrict__ tab, int B, int C, double inv_hw, float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = blockIdx.y;
+  if (c >= C) return;
+  const float2* src = partial + static_cast<size_t>(n) * rows * C + c;
+  double s = 0.0, q = 0.0;
+  for (int r = 0; r < rows; ++r) {
+    const float2 v = __ldg(src + static_cast<size_t>(r) * C);
+    s += static_cast<double>(v.x);
+    q += static_cast<double>(v.y);
+  }
+  const double mean = s * inv_hw;
+  double var = q * inv_hw - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+  const float fmean = static_cast<float>(mean);
+  float g1 = 1.f, b0 = 0.f;
+  if (gs != nullptr) {
+    g1 += __ldg(gs + static_cast<size_t>(n) * gsbs_pitch + c);
+    b0 += __ldg(bs + static_cast<size_t>(n) * gsbs_pitch + c);
+  }
+  if (bias_gb != nullptr) {
+    g1 += __ldg(bias_gb + c);
+    b0 += __ldg(bias_gb + C + c);
+  }
+  tab[static_cast<size_t>(n) * C + c] = make_float4(rstd, -fmean * rstd, g1, b0);
+}
+
 struct NormParams {
   const __nv_bfloat16* x;
   const float2* mean_rstd;   // [B][C]
@@ -148,6 +180,22 @@ extern "C" int s2p_in_stats_finalize(const float* stats_partial, int rows, float
       1.0 / static_cast<double>(HW), eps);
   count_launch();
   return check_launch("in_stats_finalize_kernel");
+}
+
+extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float* gs, const float* bs,
+                               int gsbs_pitch, const float* bias_gb, float* mod_table, int B, int C, int HW,
+                               float eps, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(stats_partial && mod_table, "mat_prepare: null pointer");
+  S2P_CHECK_ARG(rows > 0 && B > 0 && C > 0 && HW > 0, "mat_prepare: bad dims");
+  S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_prepare: gs and bs must both be given or both null");
+  S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(mod_table) & 15) == 0, "mat_prepare: table must be 16-byte aligned");
+  dim3 grid((C + 127) / 128, B);
+  mat_prepare_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float2*>(stats_partial), rows, gs, bs, gsbs_pitch, bias_gb,
+      reinterpret_cast<float4*>(mod_table), B, C, 1.0 / static_cast<double>(HW), eps);
+  count_launch();
+  return check_launch("mat_prepare_kernel");
 }
 
 extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd, const float* gs,

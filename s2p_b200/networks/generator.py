@@ -116,6 +116,9 @@ class S2PGeneratorB200(nn.Module):
         self.conv_img = nn.Conv2d(ngf, 3, 3, 1, 1)
         _init_weights(self, getattr(opt, "init_type", "xavier"), getattr(opt, "init_variance", 0.02))
         self.max_microbatch = int(getattr(opt, "max_microbatch", 128))
+        # fuse_mat: the gamma/beta conv applies the MAT norm in its own epilogue (default).
+        # False keeps the two-kernel form (conv -> bf16 maps -> mat_norm kernel).
+        self.fuse_mat = bool(getattr(opt, "fuse_mat", True))
         self._packed = None
         self._ws = {}
 
@@ -166,8 +169,10 @@ class S2PGeneratorB200(nn.Module):
                 a = torch.sigmoid(m.blend_gamma.detach().float())
                 c = torch.sigmoid(m.blend_beta.detach().float())
                 C = m.norm_nc
-                gbw = torch.cat([m.mlp_gamma.weight.detach().float() * (1 - a),
-                                 m.mlp_beta.weight.detach().float() * (1 - c)], dim=0)
+                wg = m.mlp_gamma.weight.detach().float() * (1 - a)
+                wb = m.mlp_beta.weight.detach().float() * (1 - c)
+                # fused path: rows tile-interleaved (gamma|beta per accumulator tile); bias stays plain
+                gbw = ops.interleave_gamma_beta(wg, wb) if self.fuse_mat else torch.cat([wg, wb], dim=0)
                 gbb = torch.cat([m.mlp_gamma.bias.detach().float() * (1 - a),
                                  m.mlp_beta.bias.detach().float() * (1 - c)], dim=0).contiguous()
                 head_w += [m.fc_gamma.weight.detach().float() * a, m.fc_beta.weight.detach().float() * c]
@@ -197,7 +202,10 @@ class S2PGeneratorB200(nn.Module):
             self._ws[key] = t
         return t
 
-    def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False):
+    def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False,
+              finalize=True):
+        """returns (y, stats) where stats is the finalized (mean, rstd) table when `finalize`,
+        else the raw (partials, HW) pair consumed by ops.mat_prepare."""
         B, hin, win, _ = x.shape
         ho = (hin + 2 * (k // 2) - k) // stride + 1
         wo = (win + 2 * (k // 2) - k) // stride + 1
@@ -208,6 +216,8 @@ class S2PGeneratorB200(nn.Module):
             st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
         ops.conv_igemm(x, w, b, cout, k, stride, act, residual, y, st)
         if want_stats:
+            if not finalize:
+                return y, (st, ho * wo)
             mr = self._buf(name + ".mr", (B, cout, 2), torch.float32)
             ops.in_stats_finalize(st, ho * wo, 1e-5, mr)
         return y, mr
@@ -246,7 +256,9 @@ class S2PGeneratorB200(nn.Module):
             sw, sb, n = P["shared"][ds]
             hs[ds], _ = self._conv(f"hs{ds}", f[ds], sw, sb, n, 3, 1, ACT_RELU)
         # ---- trunk
-        x, mr_x = self._conv("head", f[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True)
+        fuse = self.fuse_mat
+        x, mr_x = self._conv("head", f[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True,
+                             finalize=not fuse)
         cur = 4
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
             up = cur // ds
@@ -259,10 +271,16 @@ class S2PGeneratorB200(nn.Module):
                 m = P["mat"][(bi, name)]
                 C = m["C"]
                 hsl = hs[ds][..., m["h_off"]:m["h_off"] + nh]
-                gbuf = self._buf(f"gb{ds}.{2 * C}", (B, hh, ww, 2 * C), bf)
-                ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
                 gs = gsbs[:, m["s_off"]:m["s_off"] + C]
                 bs = gsbs[:, m["s_off"] + C:m["s_off"] + 2 * C]
+                if fuse:
+                    st_in, hw_in = mr_in
+                    tab = ops.mat_prepare(st_in, hw_in, gs, bs, m["gb_b"], 1e-5,
+                                          self._buf(f"tab.{C}.{tag}", (B, C, 4), torch.float32))
+                    return ops.conv_mat_fused(hsl, m["gb_w"], xin, tab, up_, act, 3,
+                                              self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
+                gbuf = self._buf(f"gb{ds}.{2 * C}", (B, hh, ww, 2 * C), bf)
+                ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
                 return ops.mat_norm(xin, mr_in, gs, bs, gbuf, up_, act, self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
 
             if blk.learned_shortcut:
@@ -273,9 +291,11 @@ class S2PGeneratorB200(nn.Module):
                     raise RuntimeError("identity shortcut across an upsample is not part of ORACLE_SPEC v1")
                 xs = x
             t = mat("norm_0", x, mr_x, up, ACT_LRELU, "a")
-            dx, mr_dx = self._conv(f"dx{bi}", t, pb["c0_w"], pb["c0_b"], blk.fmid, 3, 1, want_stats=True)
+            dx, mr_dx = self._conv(f"dx{bi}", t, pb["c0_w"], pb["c0_b"], blk.fmid, 3, 1, want_stats=True,
+                                   finalize=not fuse)
             t = mat("norm_1", dx, mr_dx, 1, ACT_LRELU, "b")
-            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1, residual=xs, want_stats=not last)
+            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1, residual=xs,
+                                 want_stats=not last, finalize=not fuse)
         ops.torgb_tanh(x, P["img_w"], P["img_b"], out_f32, out_u8)
 
     def _run(self, image, state, want_f32=True, want_u8=False):

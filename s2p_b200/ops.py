@@ -135,6 +135,65 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
     return out
 
 
+def mat_fused_ct(c: int) -> int:
+    return int(_lib.load().s2p_mat_fused_ct(c))
+
+
+def interleave_gamma_beta(w_gamma: torch.Tensor, w_beta: torch.Tensor) -> torch.Tensor:
+    """[C, ...] gamma rows and [C, ...] beta rows -> [2C, ...] in the tile-interleaved row
+    order s2p_conv_mat_fused_fwd expects (ct gamma rows, ct beta rows, ...)."""
+    c = w_gamma.shape[0]
+    ct = mat_fused_ct(c)
+    parts = []
+    for j in range(0, c, ct):
+        parts += [w_gamma[j:j + ct], w_beta[j:j + ct]]
+    return torch.cat(parts, dim=0).contiguous()
+
+
+def mat_prepare(stats, hw, gs, bs, bias_gb, eps: float = 1e-5, out=None):
+    """partials [B, rows, C, 2] + state gamma/beta [B, C] + conv bias [2C] -> table [B, C, 4] fp32"""
+    _require_cuda(stats, gs, bs, bias_gb, out)
+    b, rows, c, _ = stats.shape
+    if out is None:
+        out = torch.empty(b, c, 4, dtype=torch.float32, device=stats.device)
+    if tuple(out.shape) != (b, c, 4) or out.dtype != torch.float32 or not out.is_contiguous():
+        raise RuntimeError("mat_prepare: table must be contiguous fp32 [B, C, 4]")
+    gpitch = 0
+    if gs is not None:
+        if gs.dtype != torch.float32 or tuple(gs.shape) != (b, c) or gs.stride(1) != 1 or bs.stride() != gs.stride():
+            raise RuntimeError("mat_prepare: gs/bs must be fp32 [B, C] views with equal strides")
+        gpitch = gs.stride(0)
+    if bias_gb is not None and (bias_gb.dtype != torch.float32 or bias_gb.numel() != 2 * c or not bias_gb.is_contiguous()):
+        raise RuntimeError("mat_prepare: bias_gb must be contiguous fp32 [2C]")
+    _lib.check(_lib.load().s2p_mat_prepare(stats.data_ptr(), rows, _ptr(gs), _ptr(bs), gpitch, _ptr(bias_gb),
+                                           out.data_ptr(), b, c, hw, float(eps), _stream()), "s2p_mat_prepare")
+    return out
+
+
+def conv_mat_fused(h, w_packed_gb, x, mod_table, up=1, act=ACT_LRELU, ksize=3, out=None):
+    """y = act(IN(x_up) * (1 + gs + conv_gamma(h)) + bs + conv_beta(h)) in one kernel: the
+    gamma/beta conv's accumulators are consumed by its own epilogue."""
+    _require_cuda(h, w_packed_gb, x, mod_table, out)
+    b, hh, ww, cin = h.shape
+    bx, hx, wx, c = x.shape
+    if bx != b or hx * up != hh or wx * up != ww:
+        raise RuntimeError(f"conv_mat_fused: x {tuple(x.shape)} (up={up}) does not match h {tuple(h.shape)}")
+    if out is None:
+        out = torch.empty(b, hh, ww, c, dtype=torch.bfloat16, device=h.device)
+    if tuple(out.shape) != (b, hh, ww, c):
+        raise RuntimeError("conv_mat_fused: out shape mismatch")
+    if w_packed_gb.dtype != torch.bfloat16 or w_packed_gb.numel() != 2 * c * ksize * ksize * cin or not w_packed_gb.is_contiguous():
+        raise RuntimeError("conv_mat_fused: packed weight has the wrong size/dtype")
+    if tuple(mod_table.shape) != (b, c, 4) or mod_table.dtype != torch.float32 or not mod_table.is_contiguous():
+        raise RuntimeError("conv_mat_fused: mod_table must be contiguous fp32 [B, C, 4]")
+    _lib.check(
+        _lib.load().s2p_conv_mat_fused_fwd(
+            h.data_ptr(), _nhwc_pitch(h, "h"), w_packed_gb.data_ptr(), x.data_ptr(), _nhwc_pitch(x, "x"), up,
+            mod_table.data_ptr(), out.data_ptr(), _nhwc_pitch(out, "out"), b, hh, ww, cin, c, ksize, act, _stream()),
+        "s2p_conv_mat_fused_fwd")
+    return out
+
+
 def stem_conv(image, w_oihw, bias, cout, out=None, stats=None):
     """Cin=3 3x3 conv from the boundary image: fp32 NCHW [B,3,H,W] or uint8 NHWC [B,H,W,3]."""
     _require_cuda(image, w_oihw, bias, out, stats)

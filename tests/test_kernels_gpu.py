@@ -132,6 +132,49 @@ def test_mat_norm(ops, c, up, hx):
     assert (y.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 1e-3
 
 
+@pytest.mark.parametrize("c,up,hx,b", [(64, 1, 100, 2), (128, 2, 50, 2), (256, 2, 25, 3), (512, 1, 25, 3),
+                                       (128, 1, 20, 2), (32, 1, 9, 1)])
+def test_conv_mat_fused(ops, c, up, hx, b):
+    """gamma/beta conv with the MAT norm in its epilogue == conv_igemm -> mat_norm restated in
+    torch fp32 (oracle MAT.forward arithmetic on bf16-rounded operands)."""
+    g = torch.Generator().manual_seed(c * 3 + up)
+    nh = 128
+    h = hx * up
+    x = (torch.randn(b, hx, hx, c, generator=g) * 2 + 0.5).cuda().to(torch.bfloat16)
+    hid = torch.relu(torch.randn(b, h, h, 2 * nh, generator=g)).cuda().to(torch.bfloat16)[..., nh:]   # channel slice
+    wg = (torch.randn(c, nh, 3, 3, generator=g) / (9 * nh) ** 0.5).cuda()
+    wb = (torch.randn(c, nh, 3, 3, generator=g) / (9 * nh) ** 0.5).cuda()
+    bias = (torch.randn(2 * c, generator=g) * 0.2).cuda()
+    gsbs = (torch.randn(b, 2 * c + 8, generator=g) * 0.3).cuda()
+    gs, bs = gsbs[:, :c], gsbs[:, c:2 * c]
+    # statistics partials as a producing conv would emit them: one row holding the full sums
+    xf = x.float()
+    st = torch.zeros(b, 3, c, 2, device="cuda")
+    st[:, 1, :, 0] = xf.sum(dim=(1, 2))
+    st[:, 1, :, 1] = (xf * xf).sum(dim=(1, 2))
+    tab = ops.mat_prepare(st, hx * hx, gs, bs, bias)
+    mean = xf.mean(dim=(1, 2))
+    rstd = 1 / torch.sqrt(xf.var(dim=(1, 2), unbiased=False) + 1e-5)
+    assert torch.allclose(tab[..., 0], rstd, rtol=1e-4, atol=1e-6)
+    assert torch.allclose(tab[..., 1], -mean * rstd, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(tab[..., 2], 1 + gs + bias[:c], atol=1e-6)
+    assert torch.allclose(tab[..., 3], bs + bias[c:], atol=1e-6)
+    wp = ops.pack_conv_weight(ops.interleave_gamma_beta(wg, wb))
+    hf = hid.float().permute(0, 3, 1, 2)
+    gi = nhwc(F.conv2d(hf, wg.to(torch.bfloat16).float(), None, 1, 1))
+    bi = nhwc(F.conv2d(hf, wb.to(torch.bfloat16).float(), None, 1, 1))
+    xu = xf.repeat_interleave(up, dim=1).repeat_interleave(up, dim=2)
+    xh = (xu - mean[:, None, None]) * rstd[:, None, None]
+    full = xh * (1 + gs[:, None, None] + bias[:c] + gi) + bs[:, None, None] + bias[c:] + bi
+    for act, fn in ((2, lambda t: F.leaky_relu(t, 0.2)), (0, lambda t: t)):
+        y = ops.conv_mat_fused(hid, wp, x, tab, up, act)
+        ref = fn(full)
+        assert torch.isfinite(y.float()).all()
+        assert (y.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 2e-3
+    y2 = ops.conv_mat_fused(hid, wp, x, tab, up, 0)
+    assert torch.equal(y, y2)          # bit-stable
+
+
 def test_stem_and_tail(ops):
     g = torch.Generator().manual_seed(11)
     img = (torch.rand(3, 3, 100, 100, generator=g) * 2 - 1).cuda()
