@@ -255,7 +255,7 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
     rec = {"conv": [], "norm": [], "other": []}
-    orig = {n: getattr(ops, n) for n in ("conv_igemm", "conv_mat_fused", "mat_norm", "stem_conv", "torgb_tanh",
+    orig = {n: getattr(ops, n) for n in ("conv_igemm", "conv_mat_fused", "mat_norm", "stem_conv", "torgb_tanh", "torgb_igemm",
                                          "linear", "pos_encode", "in_stats_finalize", "mat_prepare")}
 
     def wrap(name, kind, work_fn):
@@ -288,7 +288,7 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     ops.conv_igemm = wrap("conv_igemm", "conv", conv_flops)
     ops.conv_mat_fused = wrap("conv_mat_fused", "conv", fused_flops)
     ops.mat_norm = wrap("mat_norm", "norm", norm_bytes)
-    for n in ("stem_conv", "torgb_tanh", "linear", "pos_encode", "in_stats_finalize", "mat_prepare"):
+    for n in ("stem_conv", "torgb_tanh", "torgb_igemm", "linear", "pos_encode", "in_stats_finalize", "mat_prepare"):
         setattr(ops, n, wrap(n, "other", None))
     try:
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

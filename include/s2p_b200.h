@@ -108,6 +108,15 @@ int s2p_torgb_tanh_fwd(const void* x, int x_pitch, const float* w_oihw, const fl
                        float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,
                        void* stream);
 
+/* ToRGB on the tensor cores: the same implicit-GEMM pipeline with a 16-column accumulator
+ * tile (3 live columns).  x must already be activated (the producing conv applies the
+ * LeakyReLU of oracle S2PGenerator.forward in its epilogue); w_packed16 is
+ * [16][R*S*Cin] bf16, rows 0..2 = s2p_pack_conv_weight(conv_img.weight), rows 3..15 zero.
+ * out = tanh(conv3x3(x) + bias) -> fp32 NCHW and/or uint8 NHWC.  Cin % 64 == 0. */
+int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, const float* bias,
+                        float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,
+                        void* stream);
+
 /* ---- (a2) state encoder ---------------------------------------------------------
  * pos_encode: oracle positional_encoding (nerf-pytorch embedding, include input).
  * linear: y = act(x W^T + b), fp32 (oracle StateEncoder.layers, MAT.fc_gamma/fc_beta). */

@@ -32,6 +32,7 @@ SIGNATURES = {
     "s2p_stem_stats_rows": (_i, [_i, _i]),
     "s2p_stem_conv_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
     "s2p_torgb_tanh_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_torgb_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_pos_encode_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }

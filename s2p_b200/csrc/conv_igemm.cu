@@ -38,7 +38,12 @@ struct ConvParams {
   const __nv_bfloat16* mat_x;   // pre-norm activation [B][H/up][W/up][mat_x_pitch]
   const float4* mat_tab;        // [B][mat_C]
   int mat_x_pitch, mat_up, mat_C;
+  // ToRGB epilogue (BLOCK_N = 16, 3 live columns): tanh(acc + bias) -> fp32 NCHW and/or uint8 NHWC
+  float* rgb_f32;
+  uint8_t* rgb_u8;
 };
+
+enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
 
 template <int BLOCK_N>
 struct ConvCfg {
@@ -49,8 +54,9 @@ struct ConvCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 192) ? 5 : (BLOCK_N >= 128) ? 6 : 8;
   static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
-  static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 128 / 256 / 512
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 32 / 128 / 256 / 512
+  static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kTabBytes;
 };
 
 // transposed butterfly: on exit lane L holds sum over the warp's 32 rows of column L
@@ -68,7 +74,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-template <int BLOCK_N, bool FUSED_MAT>
+template <int BLOCK_N, int EPI>
 __global__ void __launch_bounds__(192, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
@@ -81,6 +87,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float4* tab_smem = reinterpret_cast<float4*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -176,10 +183,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
       const int n0 = n_tile * BLOCK_N;
 
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
-      if constexpr (FUSED_MAT) {
+      if constexpr (EPI == kEpiMat) {
         constexpr int CT = BLOCK_N / 2;   // channels per n-tile: columns [0,CT) = gamma, [CT,2CT) = beta
         size_t xpix;
         if (p.mat_up == 2) {
@@ -187,21 +192,39 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         } else {
           xpix = pix;
         }
+        // everything that does not depend on the accumulators is fetched BEFORE the wait:
+        // this tile's table rows go to shared memory, the first x chunk to registers.
+        const int ch0 = n_tile * CT;
+        float4* tab_s = tab_smem + acc * 128;
+        const int et = threadIdx.x - 64;   // 0..127 inside the epilogue group
+        if (et < CT) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
+        const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0);
+        uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch0);
+        uint4 xn[4];
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) xn[j] = __ldg(x4 + j);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // table rows visible to the 4 epilogue warps
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < CT / 32; ++c) {
           uint32_t rg[32], rb[32];
           tmem_ld32(t_row + c * 32, rg);
           tmem_ld32(t_row + CT + c * 32, rb);
+          uint4 xr[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) xr[j] = xn[j];
+          if (valid && c + 1 < CT / 32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) xn[j] = __ldg(x4 + (c + 1) * 4 + j);
+          }
           tmem_ld_wait();
-          const int ch = n_tile * CT + c * 32;
           if (valid) {
-            const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch);
-            const float4* tab = p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch;
-            uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint4 xr = __ldg(x4 + j);
-              const uint32_t xw[4] = {xr.x, xr.y, xr.z, xr.w};
+              const uint32_t xw[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w};
               uint32_t ow[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
@@ -209,7 +232,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
                 for (int hlf = 0; hlf < 2; ++hlf) {
                   const int k = 8 * j + 2 * e + hlf;
-                  const float4 t = __ldg(tab + k);
+                  const float4 t = tab_s[c * 32 + k];
                   const float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
                   const float xh = fmaf(xv, t.x, t.y);
                   float v = fmaf(xh, t.z + __uint_as_float(rg[k]), t.w + __uint_as_float(rb[k]));
@@ -219,15 +242,56 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 }
                 ow[e] = pack_bf16x2(o2[0], o2[1]);
               }
-              o4[j] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+              o4[c * 4 + j] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
             }
           }
         }
+      } else if constexpr (EPI == kEpiToRGB) {
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+        uint32_t r16[16];
+        tmem_ld16(t_row, r16);
+        tmem_ld_wait();
+        if (valid) {
+          float o[3];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) o[k] = tanhf(__uint_as_float(r16[k]) + (p.bias ? __ldg(p.bias + k) : 0.f));
+          const int HW = p.H * p.W;
+          const int rem = h * p.W + w;
+          if (p.rgb_f32 != nullptr) {
+            float* of = p.rgb_f32 + static_cast<size_t>(img) * 3 * HW + rem;
+            of[0] = o[0]; of[HW] = o[1]; of[2 * HW] = o[2];
+          }
+          if (p.rgb_u8 != nullptr) {
+            uint8_t* ou = p.rgb_u8 + pix * 3;
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+              ou[k] = static_cast<uint8_t>(fminf(fmaxf(floorf((o[k] + 1.f) * 127.5f + 0.5f), 0.f), 255.f));
+          }
+        }
       } else {
+      const bool has_res = (p.residual != nullptr) && valid;
+      const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + n0);
+      uint4 rn[4];
+      if (has_res) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + j);
+      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t raw[32];
         tmem_ld32(t_row + c * 32, raw);
+        uint4 rc[4];
+        if (has_res) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) rc[j] = rn[j];
+          if (c + 1 < BLOCK_N / 32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + (c + 1) * 4 + j);
+          }
+        }
         tmem_ld_wait();
         float v[32];
 #pragma unroll
@@ -241,11 +305,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
             v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
           }
         }
-        if (p.residual != nullptr && valid) {
-          const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + ch);
+        if (has_res) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const uint4 rr = __ldg(r4 + j);
+            const uint4 rr = rc[j];
             v[8 * j + 0] += bf16_lo(rr.x); v[8 * j + 1] += bf16_hi(rr.x);
             v[8 * j + 2] += bf16_lo(rr.y); v[8 * j + 3] += bf16_hi(rr.y);
             v[8 * j + 4] += bf16_lo(rr.z); v[8 * j + 5] += bf16_hi(rr.z);
@@ -335,18 +398,18 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
   *th_out = bth;
 }
 
-template <int BLOCK_N, bool FUSED_MAT>
+template <int BLOCK_N, int EPI>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N>;
   static bool configured = false;
   if (!configured) {
-    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, FUSED_MAT>,
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_igemm_kernel<BLOCK_N, FUSED_MAT><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  conv_igemm_kernel<BLOCK_N, EPI><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
   count_launch();
   return check_launch("conv_igemm_kernel");
 }
@@ -364,7 +427,7 @@ namespace s2p {
 // Shared host path of the two conv entry points: validates the GEMM geometry, builds the
 // two tensor maps and launches.  `p` arrives with the epilogue fields already filled.
 static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B, int Hin, int Win, int Cin,
-                         int Cout, int ksize, int stride, int block_n, bool fused, ConvParams p, void* stream) {
+                         int Cout, int ksize, int stride, int block_n, int epi, ConvParams p, void* stream) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   const int pad = ksize / 2;
@@ -402,18 +465,19 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: weight tensor map encode failed (CUresult %d)", (int)r);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (fused) {
+  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, p, st);
+  if (epi == kEpiMat) {
     switch (block_n) {
-      case 256: return launch_conv<256, true>(ta, tb, p, st);
-      case 128: return launch_conv<128, true>(ta, tb, p, st);
-      default: return launch_conv<64, true>(ta, tb, p, st);
+      case 256: return launch_conv<256, kEpiMat>(ta, tb, p, st);
+      case 128: return launch_conv<128, kEpiMat>(ta, tb, p, st);
+      default: return launch_conv<64, kEpiMat>(ta, tb, p, st);
     }
   }
   switch (block_n) {
-    case 256: return launch_conv<256, false>(ta, tb, p, st);
-    case 192: return launch_conv<192, false>(ta, tb, p, st);
-    case 128: return launch_conv<128, false>(ta, tb, p, st);
-    default: return launch_conv<64, false>(ta, tb, p, st);
+    case 256: return launch_conv<256, kEpiPlain>(ta, tb, p, st);
+    case 192: return launch_conv<192, kEpiPlain>(ta, tb, p, st);
+    case 128: return launch_conv<128, kEpiPlain>(ta, tb, p, st);
+    default: return launch_conv<64, kEpiPlain>(ta, tb, p, st);
   }
 }
 
@@ -445,7 +509,7 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
   p.out = static_cast<__nv_bfloat16*>(y);
   p.stats_partial = stats_partial;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
-  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, block_n, false, p, stream);
+  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, block_n, kEpiPlain, p, stream);
 }
 
 extern "C" int s2p_mat_fused_ct(int C) { return C >= 128 ? 128 : C; }
@@ -473,5 +537,22 @@ extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_
   p.mat_tab = reinterpret_cast<const float4*>(mod_table);
   p.mat_x_pitch = x_pitch; p.mat_up = up; p.mat_C = C;
   const int block_n = 2 * s2p_mat_fused_ct(C);
-  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, block_n, true, p, stream);
+  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, block_n, kEpiMat, p, stream);
+}
+
+extern "C" int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, const float* bias,
+                                   float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,
+                                   void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && w_packed16, "torgb_igemm: null pointer");
+  S2P_CHECK_ARG(out_f32_nchw || out_u8_nhwc, "torgb_igemm: no output buffer given");
+  S2P_CHECK_ARG(B > 0 && H > 0 && W > 0, "torgb_igemm: bad dims");
+  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "torgb_igemm: Cin=%d must be a multiple of 64", Cin);
+  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "torgb_igemm: x_pitch=%d", x_pitch);
+  S2P_CHECK_ARG(aligned16(x) && aligned16(w_packed16), "torgb_igemm: pointers must be 16-byte aligned");
+  ConvParams p{};
+  p.bias = bias;
+  p.rgb_f32 = out_f32_nchw;
+  p.rgb_u8 = out_u8_nhwc;
+  return conv_dispatch(x, x_pitch, w_packed16, B, H, W, Cin, 16, 3, 1, 16, kEpiToRGB, p, stream);
 }

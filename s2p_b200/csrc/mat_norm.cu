@@ -12,20 +12,40 @@
 
 namespace s2p {
 
-// One warp per (n, 32-channel group): lanes own channels, loop over partial rows in a
-// fixed order -> run-to-run bit-stable.  mean_rstd[n][c] = (mean, 1/sqrt(var+eps)).
-__global__ void in_stats_finalize_kernel(const float2* __restrict__ partial, int rows, float2* __restrict__ out,
-                                         int B, int C, double inv_hw, float eps) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  const int n = blockIdx.y;
-  if (c >= C) return;
-  const float2* src = partial + static_cast<size_t>(n) * rows * C + c;
+// Statistics reduction shared by the two finalize kernels.  blockDim = (32 channels, 8 row
+// slices): slice k sums partial rows k, k+8, ... in fp64, then the 8 slices are combined
+// in a fixed order -> run-to-run bit-stable, and 8x the memory parallelism of a serial walk.
+__device__ __forceinline__ bool reduce_partials(const float2* __restrict__ partial, int rows, int C, int n, int c,
+                                                double& s_out, double& q_out) {
+  __shared__ double sh[2][8][32];
   double s = 0.0, q = 0.0;
-  for (int r = 0; r < rows; ++r) {
-    const float2 v = __ldg(src + static_cast<size_t>(r) * C);
-    s += static_cast<double>(v.x);
-    q += static_cast<double>(v.y);
+  if (c < C) {
+    const float2* src = partial + static_cast<size_t>(n) * rows * C + c;
+    for (int r = threadIdx.y; r < rows; r += 8) {
+      const float2 v = __ldg(src + static_cast<size_t>(r) * C);
+      s += static_cast<double>(v.x);
+      q += static_cast<double>(v.y);
+    }
   }
+  sh[0][threadIdx.y][threadIdx.x] = s;
+  sh[1][threadIdx.y][threadIdx.x] = q;
+  __syncthreads();
+  if (threadIdx.y != 0 || c >= C) return false;
+  s = 0.0; q = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { s += sh[0][k][threadIdx.x]; q += sh[1][k][threadIdx.x]; }
+  s_out = s; q_out = q;
+  return true;
+}
+
+// mean_rstd[n][c] = (mean, 1/sqrt(var+eps)).  grid = (ceil(C/32), B).
+__global__ void __launch_bounds__(256)
+in_stats_finalize_kernel(const float2* __restrict__ partial, int rows, float2* __restrict__ out,
+                         int B, int C, double inv_hw, float eps) {
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  const int n = blockIdx.y;
+  double s, q;
+  if (!reduce_partials(partial, rows, C, n, c, s, q)) return;
   const double mean = s * inv_hw;
   double var = q * inv_hw - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -35,19 +55,14 @@ __global__ void in_stats_finalize_kernel(const float2* __restrict__ partial, int
 
 // Statistics finalize + per-(n,c) modulation table for the fused conv epilogue
 // (s2p_conv_mat_fused_fwd):  tab[n][c] = (rstd, -mean*rstd, 1 + gs + bias_gamma, bs + bias_beta).
-__global__ void mat_prepare_kernel(const float2* __restrict__ partial, int rows, const float* __restrict__ gs,
-                                   const float* __restrict__ bs, int gsbs_pitch, const float* __restrict__ bias_gb,
-                                   float4* __restrict__ tab, int B, int C, double inv_hw, float eps) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256)
+mat_prepare_kernel(const float2* __restrict__ partial, int rows, const float* __restrict__ gs,
+                   const float* __restrict__ bs, int gsbs_pitch, const float* __restrict__ bias_gb,
+                   float4* __restrict__ tab, int B, int C, double inv_hw, float eps) {
+  const int c = blockIdx.x * 32 + threadIdx.x;
   const int n = blockIdx.y;
-  if (c >= C) return;
-  const float2* src = partial + static_cast<size_t>(n) * rows * C + c;
-  double s = 0.0, q = 0.0;
-  for (int r = 0; r < rows; ++r) {
-    const float2 v = __ldg(src + static_cast<size_t>(r) * C);
-    s += static_cast<double>(v.x);
-    q += static_cast<double>(v.y);
-  }
+  double s, q;
+  if (!reduce_partials(partial, rows, C, n, c, s, q)) return;
   const double mean = s * inv_hw;
   double var = q * inv_hw - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -174,8 +189,8 @@ extern "C" int s2p_in_stats_finalize(const float* stats_partial, int rows, float
   using namespace s2p;
   S2P_CHECK_ARG(stats_partial && mean_rstd, "stats_finalize: null pointer");
   S2P_CHECK_ARG(rows > 0 && B > 0 && C > 0 && HW > 0, "stats_finalize: bad dims");
-  dim3 grid((C + 127) / 128, B);
-  in_stats_finalize_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  dim3 grid((C + 31) / 32, B), block(32, 8);
+  in_stats_finalize_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float2*>(stats_partial), rows, reinterpret_cast<float2*>(mean_rstd), B, C,
       1.0 / static_cast<double>(HW), eps);
   count_launch();
@@ -190,8 +205,8 @@ extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float
   S2P_CHECK_ARG(rows > 0 && B > 0 && C > 0 && HW > 0, "mat_prepare: bad dims");
   S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_prepare: gs and bs must both be given or both null");
   S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(mod_table) & 15) == 0, "mat_prepare: table must be 16-byte aligned");
-  dim3 grid((C + 127) / 128, B);
-  mat_prepare_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  dim3 grid((C + 31) / 32, B), block(32, 8);
+  mat_prepare_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float2*>(stats_partial), rows, gs, bs, gsbs_pitch, bias_gb,
       reinterpret_cast<float4*>(mod_table), B, C, 1.0 / static_cast<double>(HW), eps);
   count_launch();

@@ -10,25 +10,53 @@
 
 namespace s2p {
 
-constexpr int kStemStrip = 256;   // pixels per CTA = one statistics partial row
+constexpr int kStemRows = 8;      // output rows per CTA = one statistics partial row
+constexpr int kStemMaxW = 256;
 
+// CTA = kStemRows full-width output rows of one image.  The (rows+2) x (W+2) x 3 input patch is
+// converted to fp32 once into shared memory; a thread owns 8 output channels x 4 consecutive
+// pixels of a row, so every weight float4 read from shared memory feeds 16 FMAs.
 template <bool U8>
 __global__ void __launch_bounds__(256)
 stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oihw,
                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int y_pitch,
                  float2* __restrict__ stats, int H, int W, int Cout, int rows) {
   extern __shared__ float sm[];
-  float* ws = sm;                         // [27][Cout]
-  float* red = sm + 27 * Cout;            // [slots][Cout][2]
+  const int PW = W + 2;
+  float* ws = sm;                                   // [27][Cout], tap = ci*9 + r*3 + s
+  float* patch = ws + 27 * Cout;                    // [3][kStemRows+2][PW]
+  float* red = patch + 3 * (kStemRows + 2) * PW;    // [slots][Cout][2]
   const int groups = Cout / 8;
   const int slots = blockDim.x / groups;
   const int g = threadIdx.x % groups, slot = threadIdx.x / groups;
   const int c0 = g * 8;
   const int n = blockIdx.y;
+  const int h0 = blockIdx.x * kStemRows;
+  const int nrows = min(kStemRows, H - h0);
   const int HW = H * W;
   for (int i = threadIdx.x; i < 27 * Cout; i += blockDim.x) {
-    const int tap = i / Cout, co = i % Cout;     // tap = ci*9 + r*3 + s (OIHW order)
+    const int tap = i / Cout, co = i % Cout;
     ws[i] = w_oihw[co * 27 + tap];
+  }
+  for (int i = threadIdx.x; i < 3 * (kStemRows + 2) * PW; i += blockDim.x) {
+    const int pw = i % PW;
+    const int pr = (i / PW) % (kStemRows + 2);
+    const int ci = i / (PW * (kStemRows + 2));
+    const int hh = h0 + pr - 1, ww = pw - 1;
+    float v = 0.f;
+    if (hh >= 0 && hh < H && ww >= 0 && ww < W) {
+      if (U8) {
+        const uint8_t* im = static_cast<const uint8_t*>(image);
+        // two separately rounded steps (no FMA contraction): bit-identical to the driver-side
+        // `u.float() * (1/127.5) - 1` conversion, so the uint8 and fp32 entries agree exactly
+        v = __fadd_rn(__fmul_rn(static_cast<float>(__ldg(im + (static_cast<size_t>(n) * HW + hh * W + ww) * 3 + ci)),
+                                1.0f / 127.5f), -1.0f);
+      } else {
+        const float* im = static_cast<const float*>(image);
+        v = __ldg(im + (static_cast<size_t>(n) * 3 + ci) * HW + hh * W + ww);
+      }
+    }
+    patch[i] = v;
   }
   __syncthreads();
   float bv[8];
@@ -38,50 +66,51 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
 
-  const int pix0 = blockIdx.x * kStemStrip;
-  const int pix1 = min(pix0 + kStemStrip, HW);
-  for (int pix = pix0 + slot; pix < pix1; pix += slots) {
-    const int h = pix / W, w = pix - h * W;
-    float acc[8];
+  const int gpr = (W + 3) / 4;                      // 4-pixel groups per row
+  for (int pg = slot; pg < nrows * gpr; pg += slots) {
+    const int lr = pg / gpr, w0 = (pg - lr * gpr) * 4;
+    float acc[4][8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = bv[j];
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = bv[j];
 #pragma unroll
     for (int ci = 0; ci < 3; ++ci) {
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
-        const int hh = h + r - 1;
+        const float* prow = patch + (ci * (kStemRows + 2) + lr + r) * PW + w0;
+        float in[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) in[i] = (w0 + i < PW) ? prow[i] : 0.f;
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
-          const int ww = w + s - 1;
-          float v = 0.f;
-          if (hh >= 0 && hh < H && ww >= 0 && ww < W) {
-            if (U8) {
-              const uint8_t* im = static_cast<const uint8_t*>(image);
-              v = static_cast<float>(__ldg(im + (static_cast<size_t>(n) * HW + hh * W + ww) * 3 + ci)) *
-                      (1.0f / 127.5f) - 1.0f;
-            } else {
-              const float* im = static_cast<const float*>(image);
-              v = __ldg(im + (static_cast<size_t>(n) * 3 + ci) * HW + hh * W + ww);
-            }
+          const float4 wa = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0);
+          const float4 wb = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0 + 4);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float v = in[i + s];
+            acc[i][0] = fmaf(v, wa.x, acc[i][0]); acc[i][1] = fmaf(v, wa.y, acc[i][1]);
+            acc[i][2] = fmaf(v, wa.z, acc[i][2]); acc[i][3] = fmaf(v, wa.w, acc[i][3]);
+            acc[i][4] = fmaf(v, wb.x, acc[i][4]); acc[i][5] = fmaf(v, wb.y, acc[i][5]);
+            acc[i][6] = fmaf(v, wb.z, acc[i][6]); acc[i][7] = fmaf(v, wb.w, acc[i][7]);
           }
-          const float4 w0 = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0);
-          const float4 w1 = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0 + 4);
-          acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
-          acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
-          acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
-          acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
         }
       }
     }
-    uint4 ov = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
-                          pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
-    *reinterpret_cast<uint4*>(y + (static_cast<size_t>(n) * HW + pix) * y_pitch + c0) = ov;
-    const uint32_t pk[4] = {ov.x, ov.y, ov.z, ov.w};
+    const size_t pix0 = static_cast<size_t>(n) * HW + static_cast<size_t>(h0 + lr) * W + w0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float a = bf16_lo(pk[j]), b = bf16_hi(pk[j]);
-      s1[2 * j] += a; s1[2 * j + 1] += b;
-      s2[2 * j] += a * a; s2[2 * j + 1] += b * b;
+    for (int i = 0; i < 4; ++i) {
+      if (w0 + i >= W) break;
+      uint4 ov = make_uint4(pack_bf16x2(acc[i][0], acc[i][1]), pack_bf16x2(acc[i][2], acc[i][3]),
+                            pack_bf16x2(acc[i][4], acc[i][5]), pack_bf16x2(acc[i][6], acc[i][7]));
+      *reinterpret_cast<uint4*>(y + (pix0 + i) * y_pitch + c0) = ov;
+      const uint32_t pk[4] = {ov.x, ov.y, ov.z, ov.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a = bf16_lo(pk[j]), b = bf16_hi(pk[j]);
+        s1[2 * j] += a; s1[2 * j + 1] += b;
+        s2[2 * j] += a * a; s2[2 * j + 1] += b * b;
+      }
     }
   }
   if (stats == nullptr) return;
@@ -93,7 +122,7 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
   __syncthreads();
   for (int c = threadIdx.x; c < Cout; c += blockDim.x) {
     float a = 0.f, b = 0.f;
-    for (int s = 0; s < slots; ++s) { a += red[(s * Cout + c) * 2]; b += red[(s * Cout + c) * 2 + 1]; }
+    for (int sl = 0; sl < slots; ++sl) { a += red[(sl * Cout + c) * 2]; b += red[(sl * Cout + c) * 2 + 1]; }
     stats[(static_cast<size_t>(n) * rows + blockIdx.x) * Cout + c] = make_float2(a, b);
   }
 }
@@ -173,22 +202,29 @@ torgb_tanh_kernel(const __nv_bfloat16* __restrict__ x, int x_pitch, const float*
 
 }  // namespace s2p
 
-extern "C" int s2p_stem_stats_rows(int H, int W) { return (H * W + s2p::kStemStrip - 1) / s2p::kStemStrip; }
+extern "C" int s2p_stem_stats_rows(int H, int W) { (void)W; return (H + s2p::kStemRows - 1) / s2p::kStemRows; }
 
 extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* w_oihw, const float* bias,
                                  void* y, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
                                  void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(image && w_oihw && y, "stem: null pointer");
-  S2P_CHECK_ARG(B > 0 && H > 0 && W > 0, "stem: bad dims");
+  S2P_CHECK_ARG(B > 0 && H > 0 && W > 0 && W <= kStemMaxW, "stem: bad dims (W <= %d)", kStemMaxW);
   S2P_CHECK_ARG(Cout % 8 == 0 && Cout >= 8 && Cout <= 256 && 256 % (Cout / 8) == 0, "stem: Cout=%d", Cout);
   S2P_CHECK_ARG(y_pitch >= Cout && y_pitch % 8 == 0, "stem: y_pitch=%d", y_pitch);
   S2P_CHECK_ARG(image_fmt == S2P_IMG_F32_NCHW || image_fmt == S2P_IMG_U8_NHWC, "stem: image_fmt=%d", image_fmt);
   const int rows = s2p_stem_stats_rows(H, W);
   const int slots = 256 / (Cout / 8);
-  const size_t smem = (27 * Cout + slots * Cout * 2) * sizeof(float);
+  const size_t smem = (27 * Cout + 3 * (kStemRows + 2) * (W + 2) + slots * Cout * 2) * sizeof(float);
   dim3 grid(rows, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static size_t smem_configured = 48 * 1024;
+  if (smem > smem_configured) {
+    S2P_CHECK_ARG(smem <= 200 * 1024, "stem: W=%d Cout=%d needs %zu bytes of shared memory", W, Cout, smem);
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(stem_conv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(stem_conv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_configured = smem;
+  }
   if (image_fmt == S2P_IMG_U8_NHWC)
     stem_conv_kernel<true><<<grid, 256, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
                                                     reinterpret_cast<float2*>(stats_partial), H, W, Cout, rows);

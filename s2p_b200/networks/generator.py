@@ -150,7 +150,7 @@ class S2PGeneratorB200(nn.Module):
         P["e2_w"], P["e2_b"] = ops.pack_conv_weight(enc.conv2.weight), f32(enc.conv2.bias)
         P["e3_w"], P["e3_b"] = ops.pack_conv_weight(enc.conv3.weight), f32(enc.conv3.bias)
         P["head_w"], P["head_b"] = ops.pack_conv_weight(self.head.weight), f32(self.head.bias)
-        P["img_w"], P["img_b"] = f32(self.conv_img.weight), f32(self.conv_img.bias)
+        P["img_w"], P["img_b"] = ops.pack_torgb_weight(f32(self.conv_img.weight)), f32(self.conv_img.bias)
         # group the MATs by the encoder feature they are conditioned on
         groups = {4: [], 2: [], 1: []}
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
@@ -224,7 +224,18 @@ class S2PGeneratorB200(nn.Module):
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
-    def _forward_mb(self, image, state, out_f32, out_u8):
+    def _state_path(self, state):
+        """state encoder + every MAT's state heads for the WHOLE batch in one pass
+        (fp32): [B, S] -> [B, 2*sum(C)] rows of (gs | bs) per MAT."""
+        P, opt = self._packed, self.opt
+        B = state.shape[0]
+        h = ops.pos_encode(state, opt.pe_freqs, self._buf("pe", (B, state.shape[1] * (1 + 2 * opt.pe_freqs)), torch.float32))
+        for i, (w, b) in enumerate(P["se"]):
+            h = ops.linear(h, w, b, ACT_LRELU, self._buf(f"se{i % 2}", (B, w.shape[0]), torch.float32))
+        return ops.linear(h, P["heads_w"], P["heads_b"], ACT_NONE, self._buf("gsbs", (B, P["heads_n"]), torch.float32))
+
+    @torch.no_grad()
+    def _forward_mb(self, image, gsbs, out_f32, out_u8):
         P = self._packed
         opt = self.opt
         ngf, nh = opt.ngf, opt.nhidden
@@ -235,11 +246,6 @@ class S2PGeneratorB200(nn.Module):
         if H % 4 or W % 4:
             raise RuntimeError("image height/width must be multiples of 4")
         bf = torch.bfloat16
-        # ---- state encoder (fp32)
-        h = ops.pos_encode(state, opt.pe_freqs, self._buf("pe", (B, state.shape[1] * (1 + 2 * opt.pe_freqs)), torch.float32))
-        for i, (w, b) in enumerate(P["se"]):
-            h = ops.linear(h, w, b, ACT_LRELU, self._buf(f"se{i % 2}", (B, w.shape[0]), torch.float32))
-        gsbs = ops.linear(h, P["heads_w"], P["heads_b"], ACT_NONE, self._buf("gsbs", (B, P["heads_n"]), torch.float32))
         # ---- image encoder
         e1 = self._buf("e1", (B, H, W, ngf), bf)
         st = self._buf("e1.st", (B, ops.stem_stats_rows(H, W), ngf, 2), torch.float32)
@@ -294,9 +300,11 @@ class S2PGeneratorB200(nn.Module):
             dx, mr_dx = self._conv(f"dx{bi}", t, pb["c0_w"], pb["c0_b"], blk.fmid, 3, 1, want_stats=True,
                                    finalize=not fuse)
             t = mat("norm_1", dx, mr_dx, 1, ACT_LRELU, "b")
-            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1, residual=xs,
+            # the last block's output is only ever read through LeakyReLU (ToRGB): apply it here
+            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1,
+                                 act=ACT_LRELU if last else ACT_NONE, residual=xs,
                                  want_stats=not last, finalize=not fuse)
-        ops.torgb_tanh(x, P["img_w"], P["img_b"], out_f32, out_u8)
+        ops.torgb_igemm(x, P["img_w"], P["img_b"], out_f32, out_u8)
 
     def _run(self, image, state, want_f32=True, want_u8=False):
         if not image.is_cuda or not state.is_cuda:
@@ -315,9 +323,10 @@ class S2PGeneratorB200(nn.Module):
         out_f32 = torch.empty(B, 3, H, W, dtype=torch.float32, device=image.device) if want_f32 else None
         out_u8 = torch.empty(B, H, W, 3, dtype=torch.uint8, device=image.device) if want_u8 else None
         mb = self.max_microbatch
+        gsbs = self._state_path(state)
         for s in range(0, B, mb):
             e = min(B, s + mb)
-            self._forward_mb(image[s:e], state[s:e], None if out_f32 is None else out_f32[s:e],
+            self._forward_mb(image[s:e], gsbs[s:e], None if out_f32 is None else out_f32[s:e],
                              None if out_u8 is None else out_u8[s:e])
         return out_f32, out_u8
 

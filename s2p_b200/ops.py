@@ -228,6 +228,31 @@ def torgb_tanh(x, w_oihw, bias, out_f32=None, out_u8=None):
     return out_f32 if out_f32 is not None else out_u8
 
 
+def pack_torgb_weight(w_oihw: torch.Tensor) -> torch.Tensor:
+    """[3, Cin, 3, 3] fp32 -> [16, 9*Cin] bf16 (rows 3..15 zero) for torgb_igemm."""
+    co, ci, r, s_ = w_oihw.shape
+    if co > 16:
+        raise RuntimeError("pack_torgb_weight: at most 16 output channels")
+    out = torch.zeros(16, r * s_ * ci, dtype=torch.bfloat16, device=w_oihw.device)
+    pack_conv_weight(w_oihw, out[:co])
+    return out
+
+
+def torgb_igemm(x_activated, w_packed16, bias, out_f32=None, out_u8=None):
+    """tanh(conv3x3(x) + bias) on the tensor cores; x is already LeakyReLU'd."""
+    _require_cuda(x_activated, w_packed16, bias, out_f32, out_u8)
+    b, h, w, cin = x_activated.shape
+    if out_f32 is None and out_u8 is None:
+        out_f32 = torch.empty(b, 3, h, w, dtype=torch.float32, device=x_activated.device)
+    if w_packed16.dtype != torch.bfloat16 or tuple(w_packed16.shape) != (16, 9 * cin) or not w_packed16.is_contiguous():
+        raise RuntimeError("torgb_igemm: packed weight must be contiguous bf16 [16, 9*Cin]")
+    _lib.check(
+        _lib.load().s2p_torgb_igemm_fwd(x_activated.data_ptr(), _nhwc_pitch(x_activated, "x"), w_packed16.data_ptr(),
+                                        _ptr(bias), _ptr(out_f32), _ptr(out_u8), b, h, w, cin, _stream()),
+        "s2p_torgb_igemm_fwd")
+    return out_f32 if out_f32 is not None else out_u8
+
+
 def pos_encode(state, n_freqs, out=None):
     _require_cuda(state, out)
     b, s = state.shape

@@ -38,7 +38,8 @@ def test_host_only_entry_points(repo_root):
     assert lib.s2p_conv_stats_rows(100, 100) == 320
     assert lib.s2p_conv_stats_rows(50, 50) == 80
     assert lib.s2p_conv_stats_rows(25, 25) == 20
-    assert lib.s2p_stem_stats_rows(100, 100) == 40
+    assert lib.s2p_stem_stats_rows(100, 100) == 13   # 8 full-width rows per CTA
+    assert lib.s2p_mat_fused_ct(512) == 128 and lib.s2p_mat_fused_ct(64) == 64
     assert lib.s2p_launch_count() == 0
 
 

@@ -203,6 +203,28 @@ def test_stem_and_tail(ops):
     assert (o8.float() - r8).abs().mean().item() <= 1e-3
 
 
+def test_torgb_igemm(ops):
+    g = torch.Generator().manual_seed(17)
+    xt = F.leaky_relu(torch.randn(3, 100, 100, 64, generator=g), 0.2).cuda().to(torch.bfloat16)
+    w3 = (torch.randn(3, 64, 3, 3, generator=g) / 24).cuda()
+    b3 = (torch.randn(3, generator=g) * 0.1).cuda()
+    wp = ops.pack_torgb_weight(w3)
+    of = torch.empty(3, 3, 100, 100, device="cuda")
+    o8 = torch.empty(3, 100, 100, 3, dtype=torch.uint8, device="cuda")
+    ops.torgb_igemm(xt, wp, b3, of, o8)
+    ref = torch.tanh(F.conv2d(xt.float().permute(0, 3, 1, 2), w3.to(torch.bfloat16).float(), b3, 1, 1))
+    assert (of - ref).abs().max().item() <= 2e-5
+    r8 = torch.floor((ref + 1) * 127.5 + 0.5).clamp(0, 255).permute(0, 2, 3, 1)
+    assert (o8.float() - r8).abs().max().item() <= 1.0
+    assert (o8.float() - r8).abs().mean().item() <= 1e-3
+    # ragged size + only one of the outputs
+    xs = torch.randn(2, 20, 36, 128, generator=g).cuda().to(torch.bfloat16)
+    w5 = (torch.randn(3, 128, 3, 3, generator=g) / 34).cuda()
+    o = ops.torgb_igemm(xs, ops.pack_torgb_weight(w5), None)
+    ref = torch.tanh(F.conv2d(xs.float().permute(0, 3, 1, 2), w5.to(torch.bfloat16).float(), None, 1, 1))
+    assert (o - ref).abs().max().item() <= 2e-5
+
+
 def test_state_encoder_kernels(ops):
     g = torch.Generator().manual_seed(13)
     s = (torch.randn(33, 17, generator=g) * 10).cuda()
