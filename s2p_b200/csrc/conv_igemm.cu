@@ -16,6 +16,8 @@
 // Persistent: grid = min(#tiles, #SMs); static round-robin tile schedule, n-tile fastest so
 // CTAs running together share the activation tile in L2.  Accumulators are double
 // buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include <stdlib.h>
+
 #include "ptx.cuh"
 #include "s2p_internal.h"
 
@@ -45,14 +47,15 @@ struct ConvParams {
 
 enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, int CL>
 struct ConvCfg {
   static constexpr int kBlockM = 128;
   static constexpr int kBlockK = 64;
-  static constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KB
-  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;        // 16 KB
+  static constexpr int kBBytes = BLOCK_N / CL * kBlockK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 192) ? 5 : (BLOCK_N >= 128) ? 6 : 8;
+  static constexpr int kMaxStages = (220 * 1024) / kStageBytes;
+  static constexpr int kStages = kMaxStages > 8 ? 8 : kMaxStages;
   static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
   static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 32 / 128 / 256 / 512
   static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
@@ -74,11 +77,11 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-template <int BLOCK_N, int EPI>
+template <int BLOCK_N, int EPI, int CL>
 __global__ void __launch_bounds__(192, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N>;
+  using Cfg = ConvCfg<BLOCK_N, CL>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -101,30 +104,43 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4);
+      mbar_init(&tmem_empty[i], 4 * CL);   // the leader's MMA thread waits for both CTAs' epilogue warps
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 1) {
+    if constexpr (CL > 1) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CL > 1) cluster_sync_all();   // peers' barriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  // CL == 2: a CTA pair (cta_group::2) walks two adjacent m-tiles of the same n-tile as ONE
+  // 256-row UMMA.  Each CTA loads its own 128 activation rows and HALF of the weight tile, so the
+  // bytes entering each SM's shared memory per MMA drop from 48 KB to 32 KB per k-block (the
+  // L2->SM ingest port, ~70 B/clk, is what bounds the single-CTA kernel).  The leader (rank 0)
+  // issues the MMAs; its commits release the stages and publish the accumulators in both CTAs.
+  // super tile = (pair of m-tiles, n-tile); an odd last m-tile gets a dummy partner (TMA zero
+  // fill, nothing stored).
+  const uint32_t cta_rank = (CL > 1) ? cluster_ctarank() : 0;
+  const int num_tiles = ((p.num_m_tiles + CL - 1) / CL) * p.num_n_tiles;
+  const int tile_first = blockIdx.x / CL, tile_step = gridDim.x / CL;
   const int tiles_per_img = p.tiles_x * p.tiles_y;
   const int cchunks = p.Cin / Cfg::kBlockK;
   const int num_kb = p.R * p.S * cchunks;
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
-  const uint32_t stage_tx = a_bytes + Cfg::kBBytes;
+  const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
 
   if (warp == 0 && lane == 0) {
     // ------------------------------------------------------------ TMA producer
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_tile = tile / p.num_n_tiles, n_tile = tile % p.num_n_tiles;
-      const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+      const int m_tile = (tile / p.num_n_tiles) * CL + cta_rank, n_tile = tile % p.num_n_tiles;
+      const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;   // img == B for a dummy tile
       const int h0 = (t / p.tiles_x) * p.tile_h, w0 = (t % p.tiles_x) * p.tile_w;
       const int hin0 = h0 * p.stride - p.pad, win0 = w0 * p.stride - p.pad;
       for (int kb = 0; kb < num_kb; ++kb) {
@@ -133,19 +149,27 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
-        mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-        tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
-        tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+        if constexpr (CL > 1) {
+          constexpr int kPart = BLOCK_N / CL;
+          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+          const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+          tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
+          tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
+        } else {
+          mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+          tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+        }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N);
+  } else if (warp == 1 && lane == 0 && cta_rank == 0) {
+    // ------------------------------------------------------------ MMA issuer (pair leader)
+    constexpr uint32_t idesc = umma_idesc_bf16(128 * CL, BLOCK_N);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -160,10 +184,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
         for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
           // +32 B per K=16 step inside the 128 B swizzle row (address field is >>4)
-          umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          if constexpr (CL > 1) umma_bf16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
         }
-        umma_commit(&empty_bar[stage]);
-        if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
+        if constexpr (CL > 1) {
+          umma_commit_pair(&empty_bar[stage], 3);
+          if (kb == num_kb - 1) umma_commit_pair(&tmem_full[acc], 3);
+        } else {
+          umma_commit(&empty_bar[stage]);
+          if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
+        }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
@@ -173,13 +203,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int m = q * 32 + lane;      // accumulator row = pixel inside the tile
     const int my = m / p.tile_w, mx = m - my * p.tile_w;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      const int m_tile = tile / p.num_n_tiles, n_tile = tile % p.num_n_tiles;
+      const int m_tile = (tile / p.num_n_tiles) * CL + cta_rank, n_tile = tile % p.num_n_tiles;
+      const bool live = m_tile < p.num_m_tiles;     // false only for a cluster's dummy tile
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
       const int h = (t / p.tiles_x) * p.tile_h + my, w = (t % p.tiles_x) * p.tile_w + mx;
-      const bool valid = (my < p.tile_h) && (h < p.H) && (w < p.W);
+      const bool valid = live && (my < p.tile_h) && (h < p.H) && (w < p.W);
       const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
       const int n0 = n_tile * BLOCK_N;
 
@@ -197,7 +228,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int ch0 = n_tile * CT;
         float4* tab_s = tab_smem + acc * 128;
         const int et = threadIdx.x - 64;   // 0..127 inside the epilogue group
-        if (et < CT) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
+        if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
         const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0);
         uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch0);
         uint4 xn[4];
@@ -331,7 +362,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int j = 0; j < 4; ++j)
             o4[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
         }
-        if (p.stats_partial != nullptr) {
+        if (p.stats_partial != nullptr && live) {
           // statistics of the values as stored (bf16-rounded), fixed reduction order
           float s1[32], s2[32];
 #pragma unroll
@@ -351,13 +382,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) {
+        if constexpr (CL > 1) mbar_arrive_cluster(map_to_cta(&tmem_empty[acc], 0));
+        else mbar_arrive(&tmem_empty[acc]);
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  if constexpr (CL > 1) cluster_sync_all();   // neither CTA leaves (or frees TMEM) while the pair is still working
+  if (warp == 1) {
+    if constexpr (CL > 1) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+    else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
 }
 
 }  // namespace s2p
@@ -398,20 +436,49 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
   *th_out = bth;
 }
 
-template <int BLOCK_N, int EPI>
-static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
-  using Cfg = ConvCfg<BLOCK_N>;
+template <int BLOCK_N, int EPI, int CL>
+static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
+  using Cfg = ConvCfg<BLOCK_N, CL>;
   static bool configured = false;
   if (!configured) {
-    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI>,
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI, CL>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured = true;
   }
-  const int tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_igemm_kernel<BLOCK_N, EPI><<<grid, 192, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  const int super_tiles = ((p.num_m_tiles + CL - 1) / CL) * p.num_n_tiles;
+  const int max_clusters = num_sms() / CL;
+  const int grid = (super_tiles < max_clusters ? super_tiles : max_clusters) * CL;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(192, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, p));
   count_launch();
   return check_launch("conv_igemm_kernel");
+}
+
+// cluster size along M (CTAs sharing one multicast weight tile): 2 unless S2P_CONV_CLUSTER=1
+int conv_cluster_size() {
+  static int cl = 0;
+  if (cl == 0) {
+    const char* e = getenv("S2P_CONV_CLUSTER");
+    cl = (e != nullptr && e[0] == '1') ? 1 : 2;
+  }
+  return cl;
+}
+
+template <int BLOCK_N, int EPI>
+static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
+  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, p, st);
+  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, p, st);
 }
 
 }  // namespace s2p
@@ -457,7 +524,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     const int K = ksize * ksize * Cin;
     cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Cout};
     cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)block_n};
+    cuuint32_t box[2] = {64, (cuuint32_t)(block_n / conv_cluster_size())};   // each CTA loads its share
     cuuint32_t estr[2] = {1, 1};
     CUresult r = encode(&tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_packed), dims, strides,
                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
