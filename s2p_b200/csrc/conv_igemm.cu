@@ -78,7 +78,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 }
 
 template <int BLOCK_N, int EPI, int CL>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
@@ -104,7 +104,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4 * CL);   // the leader's MMA thread waits for both CTAs' epilogue warps
+      mbar_init(&tmem_empty[i], 8 * CL);   // the leader's MMA thread waits for both CTAs' 8 epilogue warps
     }
     fence_barrier_init();
   }
@@ -198,193 +198,223 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else if (warp >= 2) {
-    // ------------------------------------------------------------ epilogue
-    const int q = warp & 3;           // TMEM lane quarter this warp may read
+    // ------------------------------------------------------------ epilogue (8 warps)
+    // warp -> TMEM lane quarter q (hardware rule: warp%4) and one half of the tile's columns.
+    // TMEM loads are software pipelined (the load of step i+1 is in flight while step i is
+    // converted and stored), operands that do not depend on the accumulators are fetched before
+    // the accumulator wait, and the accumulator buffer is released right after its last load.
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64;  // 0..255 inside the epilogue group
     const int m = q * 32 + lane;      // accumulator row = pixel inside the tile
     const int my = m / p.tile_w, mx = m - my * p.tile_w;
+    const float* bias_s = p.bias;
+    if constexpr (EPI == kEpiPlain) {
+      // bias vector staged in shared memory once per CTA (broadcast LDS instead of global loads)
+      if (p.bias != nullptr && p.Cout <= 1024) {
+        float* bs = reinterpret_cast<float*>(tab_smem);
+        for (int i = et; i < p.Cout; i += 256) bs[i] = __ldg(p.bias + i);
+        bias_s = bs;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+      }
+    }
     int it = 0;
     for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       const int m_tile = (tile / p.num_n_tiles) * CL + cta_rank, n_tile = tile % p.num_n_tiles;
-      const bool live = m_tile < p.num_m_tiles;     // false only for a cluster's dummy tile
+      const bool live = m_tile < p.num_m_tiles;     // false only for a pair's dummy tile
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
       const int h = (t / p.tiles_x) * p.tile_h + my, w = (t % p.tiles_x) * p.tile_w + mx;
       const bool valid = live && (my < p.tile_h) && (h < p.H) && (w < p.W);
       const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
       const int n0 = n_tile * BLOCK_N;
-
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
+
+      auto release_acc = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CL > 1) mbar_arrive_cluster(map_to_cta(&tmem_empty[acc], 0));
+          else mbar_arrive(&tmem_empty[acc]);
+        }
+      };
+
       if constexpr (EPI == kEpiMat) {
-        constexpr int CT = BLOCK_N / 2;   // channels per n-tile: columns [0,CT) = gamma, [CT,2CT) = beta
+        constexpr int CT = BLOCK_N / 2;        // channels per n-tile: columns [0,CT) = gamma, [CT,2CT) = beta
+        constexpr int kSteps = CT / 32;        // 16-channel steps per warp (each warp owns CT/2 channels)
+        const int cw = half * (CT / 2);        // first channel (inside the tile) of this warp
         size_t xpix;
         if (p.mat_up == 2) {
           xpix = (static_cast<size_t>(img) * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
         } else {
           xpix = pix;
         }
-        // everything that does not depend on the accumulators is fetched BEFORE the wait:
-        // this tile's table rows go to shared memory, the first x chunk to registers.
         const int ch0 = n_tile * CT;
         float4* tab_s = tab_smem + acc * 128;
-        const int et = threadIdx.x - 64;   // 0..127 inside the epilogue group
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
-        const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0);
-        uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch0);
-        uint4 xn[4];
-        if (valid) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) xn[j] = __ldg(x4 + j);
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // table rows visible to the 4 epilogue warps
+        const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0 + cw);
+        uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch0 + cw);
+        uint4 xn[2];
+        if (valid) { xn[0] = __ldg(x4); xn[1] = __ldg(x4 + 1); }
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < CT / 32; ++c) {
-          uint32_t rg[32], rb[32];
-          tmem_ld32(t_row + c * 32, rg);
-          tmem_ld32(t_row + CT + c * 32, rb);
-          uint4 xr[4];
+        uint32_t rg[16], rb[16];
+        tmem_ld16(t_row + cw, rg);
+        tmem_ld16(t_row + CT + cw, rb);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) xr[j] = xn[j];
-          if (valid && c + 1 < CT / 32) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) xn[j] = __ldg(x4 + (c + 1) * 4 + j);
-          }
+        for (int sidx = 0; sidx < kSteps; ++sidx) {
           tmem_ld_wait();
+          float g[16], bt[16];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) { g[k] = __uint_as_float(rg[k]); bt[k] = __uint_as_float(rb[k]); }
+          const uint4 xr0 = xn[0], xr1 = xn[1];
+          if (sidx + 1 < kSteps) {
+            tmem_ld16(t_row + cw + (sidx + 1) * 16, rg);
+            tmem_ld16(t_row + CT + cw + (sidx + 1) * 16, rb);
+            if (valid) { xn[0] = __ldg(x4 + (sidx + 1) * 2); xn[1] = __ldg(x4 + (sidx + 1) * 2 + 1); }
+          } else {
+            release_acc();
+          }
           if (valid) {
+            const uint32_t xw[8] = {xr0.x, xr0.y, xr0.z, xr0.w, xr1.x, xr1.y, xr1.z, xr1.w};
+            uint32_t ow[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t xw[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w};
-              uint32_t ow[4];
+            for (int e = 0; e < 8; ++e) {
+              float o2[2];
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float o2[2];
-#pragma unroll
-                for (int hlf = 0; hlf < 2; ++hlf) {
-                  const int k = 8 * j + 2 * e + hlf;
-                  const float4 t = tab_s[c * 32 + k];
-                  const float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
-                  const float xh = fmaf(xv, t.x, t.y);
-                  float v = fmaf(xh, t.z + __uint_as_float(rg[k]), t.w + __uint_as_float(rb[k]));
-                  if (p.act == 2) v = v > 0.f ? v : 0.2f * v;
-                  else if (p.act == 1) v = fmaxf(v, 0.f);
-                  o2[hlf] = v;
-                }
-                ow[e] = pack_bf16x2(o2[0], o2[1]);
+              for (int hlf = 0; hlf < 2; ++hlf) {
+                const int k = 2 * e + hlf;
+                const float4 tb = tab_s[cw + sidx * 16 + k];
+                const float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
+                const float xh = fmaf(xv, tb.x, tb.y);
+                float v = fmaf(xh, tb.z + g[k], tb.w + bt[k]);
+                if (p.act == 2) v = v > 0.f ? v : 0.2f * v;
+                else if (p.act == 1) v = fmaxf(v, 0.f);
+                o2[hlf] = v;
               }
-              o4[c * 4 + j] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+              ow[e] = pack_bf16x2(o2[0], o2[1]);
             }
+            o4[sidx * 2] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+            o4[sidx * 2 + 1] = make_uint4(ow[4], ow[5], ow[6], ow[7]);
           }
         }
       } else if constexpr (EPI == kEpiToRGB) {
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
-        uint32_t r16[16];
-        tmem_ld16(t_row, r16);
-        tmem_ld_wait();
-        if (valid) {
-          float o[3];
+        if (half == 0) {
+          uint32_t r16[16];
+          tmem_ld16(t_row, r16);
+          tmem_ld_wait();
+          release_acc();
+          if (valid) {
+            float o[3];
 #pragma unroll
-          for (int k = 0; k < 3; ++k) o[k] = tanhf(__uint_as_float(r16[k]) + (p.bias ? __ldg(p.bias + k) : 0.f));
-          const int HW = p.H * p.W;
-          const int rem = h * p.W + w;
-          if (p.rgb_f32 != nullptr) {
-            float* of = p.rgb_f32 + static_cast<size_t>(img) * 3 * HW + rem;
-            of[0] = o[0]; of[HW] = o[1]; of[2 * HW] = o[2];
-          }
-          if (p.rgb_u8 != nullptr) {
-            uint8_t* ou = p.rgb_u8 + pix * 3;
+            for (int k = 0; k < 3; ++k) o[k] = tanhf(__uint_as_float(r16[k]) + (p.bias ? __ldg(p.bias + k) : 0.f));
+            const int HW = p.H * p.W;
+            const int rem = h * p.W + w;
+            if (p.rgb_f32 != nullptr) {
+              float* of = p.rgb_f32 + static_cast<size_t>(img) * 3 * HW + rem;
+              of[0] = o[0]; of[HW] = o[1]; of[2 * HW] = o[2];
+            }
+            if (p.rgb_u8 != nullptr) {
+              uint8_t* ou = p.rgb_u8 + pix * 3;
 #pragma unroll
-            for (int k = 0; k < 3; ++k)
-              ou[k] = static_cast<uint8_t>(fminf(fmaxf(floorf((o[k] + 1.f) * 127.5f + 0.5f), 0.f), 255.f));
+              for (int k = 0; k < 3; ++k)
+                ou[k] = static_cast<uint8_t>(fminf(fmaxf(floorf((o[k] + 1.f) * 127.5f + 0.5f), 0.f), 255.f));
+            }
           }
+        } else {
+          release_acc();
         }
       } else {
-      const bool has_res = (p.residual != nullptr) && valid;
-      const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + n0);
-      uint4 rn[4];
-      if (has_res) {
+        constexpr int kChunks = BLOCK_N / 64;          // 32-column chunks per warp
+        const int cbeg = half * kChunks;
+        const bool has_res = (p.residual != nullptr) && valid;
+        const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + n0 + cbeg * 32);
+        uint4 rn[4];
+        if (has_res) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + j);
-      }
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
+          for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + j);
+        }
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
         uint32_t raw[32];
-        tmem_ld32(t_row + c * 32, raw);
-        uint4 rc[4];
-        if (has_res) {
+        tmem_ld32(t_row + cbeg * 32, raw);
+#pragma unroll 1
+        for (int i = 0; i < kChunks; ++i) {
+          const int c = cbeg + i;
+          tmem_ld_wait();
+          float v[32];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) rc[j] = rn[j];
-          if (c + 1 < BLOCK_N / 32) {
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+          uint4 rc[4];
+          if (has_res) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + (c + 1) * 4 + j);
+            for (int j = 0; j < 4; ++j) rc[j] = rn[j];
+          }
+          if (i + 1 < kChunks) {
+            tmem_ld32(t_row + (c + 1) * 32, raw);
+            if (has_res) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + (i + 1) * 4 + j);
+            }
+          } else {
+            release_acc();
+          }
+          const int ch = n0 + c * 32;
+          if (bias_s != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(bias_s + ch);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 bb = b4[j];
+              v[4 * j + 0] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+            }
+          }
+          if (has_res) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 rr = rc[j];
+              v[8 * j + 0] += bf16_lo(rr.x); v[8 * j + 1] += bf16_hi(rr.x);
+              v[8 * j + 2] += bf16_lo(rr.y); v[8 * j + 3] += bf16_hi(rr.y);
+              v[8 * j + 4] += bf16_lo(rr.z); v[8 * j + 5] += bf16_hi(rr.z);
+              v[8 * j + 6] += bf16_lo(rr.w); v[8 * j + 7] += bf16_hi(rr.w);
+            }
+          }
+          if (p.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (p.act == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : 0.2f * v[j];
+          }
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+          if (valid) {
+            uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              o4[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+          }
+          if (p.stats_partial != nullptr && live) {
+            // statistics of the values as stored (bf16-rounded), fixed reduction order
+            float s1[32], s2[32];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float a = valid ? bf16_lo(packed[j]) : 0.f;
+              const float b = valid ? bf16_hi(packed[j]) : 0.f;
+              s1[2 * j] = a; s1[2 * j + 1] = b;
+              s2[2 * j] = a * a; s2[2 * j + 1] = b * b;
+            }
+            const float cs = warp_colsum32(s1, lane);
+            const float cq = warp_colsum32(s2, lane);
+            const size_t prow = (static_cast<size_t>(img) * tiles_per_img + t) * 4 + q;
+            float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + ch + lane;
+            *dst = make_float2(cs, cq);
           }
         }
-        tmem_ld_wait();
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-        const int ch = n0 + c * 32;
-        if (p.bias != nullptr) {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(b4 + j);
-            v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-          }
-        }
-        if (has_res) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint4 rr = rc[j];
-            v[8 * j + 0] += bf16_lo(rr.x); v[8 * j + 1] += bf16_hi(rr.x);
-            v[8 * j + 2] += bf16_lo(rr.y); v[8 * j + 3] += bf16_hi(rr.y);
-            v[8 * j + 4] += bf16_lo(rr.z); v[8 * j + 5] += bf16_hi(rr.z);
-            v[8 * j + 6] += bf16_lo(rr.w); v[8 * j + 7] += bf16_hi(rr.w);
-          }
-        }
-        if (p.act == 1) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        } else if (p.act == 2) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : 0.2f * v[j];
-        }
-        uint32_t packed[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-        if (valid) {
-          uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            o4[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-        }
-        if (p.stats_partial != nullptr && live) {
-          // statistics of the values as stored (bf16-rounded), fixed reduction order
-          float s1[32], s2[32];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float a = valid ? bf16_lo(packed[j]) : 0.f;
-            const float b = valid ? bf16_hi(packed[j]) : 0.f;
-            s1[2 * j] = a; s1[2 * j + 1] = b;
-            s2[2 * j] = a * a; s2[2 * j + 1] = b * b;
-          }
-          const float cs = warp_colsum32(s1, lane);
-          const float cq = warp_colsum32(s2, lane);
-          const size_t prow = (static_cast<size_t>(img) * tiles_per_img + t) * 4 + q;
-          float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + ch + lane;
-          *dst = make_float2(cs, cq);
-        }
-      }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (CL > 1) mbar_arrive_cluster(map_to_cta(&tmem_empty[acc], 0));
-        else mbar_arrive(&tmem_empty[acc]);
       }
     }
   }
@@ -450,7 +480,7 @@ static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const Co
   const int grid = (super_tiles < max_clusters ? super_tiles : max_clusters) * CL;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);
-  cfg.blockDim = dim3(192, 1, 1);
+  cfg.blockDim = dim3(320, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
