@@ -92,7 +92,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float4* tab_smem = reinterpret_cast<float4*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -134,7 +134,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
 
-  if (warp == 0 && lane == 0) {
+  // The producer and MMA loops run with the whole warp converged (uniform control flow, uniform
+  // operands) and elect one lane only around the asynchronous issue itself: a loop written under
+  // `lane == 0` forces the compiler to serialise every uniform-datapath operand through
+  // elect/R2UR waterfall loops (~700 clk per k-block, which used to bound every layer).
+  if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     int stage = 0;
     uint32_t phase = 0;
@@ -143,58 +147,67 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;   // img == B for a dummy tile
       const int h0 = (t / p.tiles_x) * p.tile_h, w0 = (t % p.tiles_x) * p.tile_w;
       const int hin0 = h0 * p.stride - p.pad, win0 = w0 * p.stride - p.pad;
+      int r = 0, sx = 0, cc = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
-        const int tap = kb / cchunks, cc = kb % cchunks;
-        const int r = tap / p.S, s = tap % p.S;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * Cfg::kStageBytes;
-        uint8_t* sb = sa + Cfg::kABytes;
-        if constexpr (CL > 1) {
-          constexpr int kPart = BLOCK_N / CL;
-          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-          const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
-          tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
-          tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
-        } else {
-          mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-          tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + s, hin0 + r, img);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+        if (elect_one()) {
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          if constexpr (CL > 1) {
+            constexpr int kPart = BLOCK_N / CL;
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+            const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+            tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+            tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+          }
         }
+        __syncwarp();
+        if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && lane == 0 && cta_rank == 0) {
-    // ------------------------------------------------------------ MMA issuer (pair leader)
-    constexpr uint32_t idesc = umma_idesc_bf16(128 * CL, BLOCK_N);
-    int stage = 0;
-    uint32_t phase = 0;
-    int it = 0;
-    for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (pair leader only)
+    if (cta_rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CL, BLOCK_N);
+      const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-        const uint64_t da = umma_desc_sw128(sa);
-        const uint64_t db = umma_desc_sw128(sa + Cfg::kABytes);
+        const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            // descriptor start-address field is in 16-byte units: stage and operand offsets add directly
+            const uint64_t da = desc0 + static_cast<uint64_t>(stage * (Cfg::kStageBytes >> 4));
+            const uint64_t db = da + (Cfg::kABytes >> 4);
 #pragma unroll
-        for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
-          // +32 B per K=16 step inside the 128 B swizzle row (address field is >>4)
-          if constexpr (CL > 1) umma_bf16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
+              // +32 B per K=16 step inside the 128 B swizzle row
+              if constexpr (CL > 1) umma_bf16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+              else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            if constexpr (CL > 1) {
+              umma_commit_pair(&empty_bar[stage], 3);
+              if (kb == num_kb - 1) umma_commit_pair(&tmem_full[acc], 3);
+            } else {
+              umma_commit(&empty_bar[stage]);
+              if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
+            }
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        if constexpr (CL > 1) {
-          umma_commit_pair(&empty_bar[stage], 3);
-          if (kb == num_kb - 1) umma_commit_pair(&tmem_full[acc], 3);
-        } else {
-          umma_commit(&empty_bar[stage]);
-          if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
-        }
-        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp >= 2) {
