@@ -43,6 +43,7 @@ struct ConvParams {
   // ToRGB epilogue (BLOCK_N = 16, 3 live columns): tanh(acc + bias) -> fp32 NCHW and/or uint8 NHWC
   float* rgb_f32;
   uint8_t* rgb_u8;
+  int debug;   // S2P_CONV_DEBUG (timing experiments only): 1 = skip the plain epilogue's global stores
 };
 
 enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
@@ -54,12 +55,13 @@ struct ConvCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;        // 16 KB
   static constexpr int kBBytes = BLOCK_N / CL * kBlockK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kMaxStages = (220 * 1024) / kStageBytes;
+  static constexpr int kStoreBytes = 8 * 2048;   // per-epilogue-warp 32 x 64 B transpose rows
+  static constexpr int kMaxStages = (204 * 1024) / kStageBytes;
   static constexpr int kStages = kMaxStages > 8 ? 8 : kMaxStages;
   static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
   static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 32 / 128 / 256 / 512
   static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kTabBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes;
 };
 
 // transposed butterfly: on exit lane L holds sum over the warp's 32 rows of column L
@@ -77,6 +79,35 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
+// Coalesced store of a warp's 32 accumulator rows x (NCH x 8) bf16 channels.  In the TMEM
+// layout a thread owns one pixel row, so a direct store makes every warp-level st.global touch
+// 32 different lines with 16 B each (LSU-bound on wide outputs).  The rows are transposed
+// through a warp-private, XOR-swizzled (bank-conflict-free) shared-memory tile instead, and
+// written back with NCH lanes per pixel: whole 32 B sectors, 32/NCH pixels per instruction.
+template <int NCH>
+__device__ __forceinline__ void warp_store_rows(uint8_t* stg, const uint32_t* packed, __nv_bfloat16* out_col,
+                                                int out_pitch, uint32_t pix, bool valid, int lane) {
+  constexpr int kRow = NCH * 16;
+  const int wkey = (NCH == 4) ? (lane >> 1) : (lane >> 2);
+#pragma unroll
+  for (int j = 0; j < NCH; ++j)
+    *reinterpret_cast<uint4*>(stg + lane * kRow + ((j ^ wkey) & (NCH - 1)) * 16) =
+        make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+  __syncwarp();
+  constexpr int kRowsPerInst = 32 / NCH;
+  const int j = lane % NCH;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int rr = i * kRowsPerInst + lane / NCH;
+    const int rkey = (NCH == 4) ? (rr >> 1) : (rr >> 2);
+    const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * kRow + ((j ^ rkey) & (NCH - 1)) * 16);
+    const uint32_t rpix = __shfl_sync(0xffffffffu, pix, rr);
+    const int rvalid = __shfl_sync(0xffffffffu, static_cast<int>(valid), rr);
+    if (rvalid) *reinterpret_cast<uint4*>(out_col + static_cast<size_t>(rpix) * out_pitch + j * 8) = v;
+  }
+  __syncwarp();
+}
+
 template <int BLOCK_N, int EPI, int CL>
 __global__ void __launch_bounds__(320, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
@@ -91,6 +122,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float4* tab_smem = reinterpret_cast<float4*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
+  uint8_t* store_smem = smem + Cfg::kStages * Cfg::kStageBytes + 256 + Cfg::kTabBytes;
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -267,7 +299,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         float4* tab_s = tab_smem + acc * 128;
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
         const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0 + cw);
-        uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch0 + cw);
         uint4 xn[2];
         if (valid) { xn[0] = __ldg(x4); xn[1] = __ldg(x4 + 1); }
         asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps
@@ -290,6 +321,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           } else {
             release_acc();
           }
+          uint32_t ow_out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
           if (valid) {
             const uint32_t xw[8] = {xr0.x, xr0.y, xr0.z, xr0.w, xr1.x, xr1.y, xr1.z, xr1.w};
             uint32_t ow[8];
@@ -309,9 +341,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
               }
               ow[e] = pack_bf16x2(o2[0], o2[1]);
             }
-            o4[sidx * 2] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-            o4[sidx * 2 + 1] = make_uint4(ow[4], ow[5], ow[6], ow[7]);
+            ow_out[0] = ow[0]; ow_out[1] = ow[1]; ow_out[2] = ow[2]; ow_out[3] = ow[3];
+            ow_out[4] = ow[4]; ow_out[5] = ow[5]; ow_out[6] = ow[6]; ow_out[7] = ow[7];
           }
+          warp_store_rows<2>(store_smem + (warp - 2) * 2048, ow_out, p.out + ch0 + cw + sidx * 16, p.out_pitch,
+                             static_cast<uint32_t>(pix), valid, lane);
         }
       } else if constexpr (EPI == kEpiToRGB) {
         mbar_wait(&tmem_full[acc], acc_phase);
@@ -405,12 +439,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           uint32_t packed[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-          if (valid) {
-            uint4* o4 = reinterpret_cast<uint4*>(p.out + pix * p.out_pitch + ch);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              o4[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-          }
+          if (!(p.debug & 1))
+            warp_store_rows<4>(store_smem + (warp - 2) * 2048, packed, p.out + ch, p.out_pitch,
+                               static_cast<uint32_t>(pix), valid, lane);
           if (p.stats_partial != nullptr && live) {
             // statistics of the values as stored (bf16-rounded), fixed reduction order
             float s1[32], s2[32];
@@ -541,10 +572,17 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   const int pad = ksize / 2;
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("S2P_CONV_DEBUG"); dbg = e ? atoi(e) : 0; }
+    p.debug = dbg;
+  }
   p.B = B;
   p.H = (Hin + 2 * pad - ksize) / stride + 1;
   p.W = (Win + 2 * pad - ksize) / stride + 1;
   p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
+  if (static_cast<long long>(B) * p.H * p.W >= (1LL << 32))
+    return set_error(S2P_ERR_BAD_ARG, "conv: B*H*W must be below 2^32 pixels per call");
   conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
   p.tiles_x = (p.W + p.tile_w - 1) / p.tile_w;
   p.tiles_y = (p.H + p.tile_h - 1) / p.tile_h;
