@@ -303,16 +303,34 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     tms = {k: sum(s.elapsed_time(e) for s, e, _ in v) for k, v in rec.items()}
     work = {k: sum(w for _, _, w in v) for k, v in rec.items()}
     nconv, nnorm = len(rec["conv"]), len(rec["norm"])
+    traffic_conv = traffic_norm = None
+    try:   # DRAM bytes per launch from the committed ncu pass of the same forward (128-frame micro-batch)
+        import csv
+        with open(os.path.join(ROOT, "profiles", "r01_kernel_metrics.csv")) as f:
+            rows = list(csv.DictReader(l for l in f if not l.startswith("==")))
+        by = {}
+        for r in rows:
+            if r["Metric Name"] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                by.setdefault((r["ID"], r["Kernel Name"]), 0.0)
+                by[(r["ID"], r["Kernel Name"])] += float(r["Metric Value"].replace(",", "")) * \
+                    {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[r["Metric Unit"]]
+        c = [v for (i, k), v in by.items() if "conv_igemm" in k]
+        n = [v for (i, k), v in by.items() if "mat_norm" in k]
+        traffic_conv = sum(c) / len(c) if c else None
+        traffic_norm = sum(n) / len(n) if n else None
+    except Exception:
+        pass
     ach_tf = work["conv"] / (tms["conv"] / 1e3) / 1e12
     ach_gb = work["norm"] / (tms["norm"] / 1e3) / 1e9
     roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM, plain and MAT-fused epilogues; all launches of one step)",
             "bound": "tensor",
-            "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": None,
+            "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": traffic_conv,
+            "traffic_note": "avg dram__bytes_read+write per conv launch, profiles/r01_kernel_metrics.csv (ncu, 128-frame micro-batch)",
             "peak_source": src, "launches": nconv, "avg_launch_ms": tms["conv"] / nconv,
             "flops_per_launch_avg": work["conv"] / nconv}
     roof_norm = {"kernel": "mat_norm_kernel (fused IN + MAT modulation + LeakyReLU; all launches of one step)",
                  "bound": "hbm", "achieved": ach_gb, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gb / hbm_peak,
-                 "traffic": None, "peak_source": src, "launches": nnorm, "avg_launch_ms": tms["norm"] / nnorm,
+                 "traffic": traffic_norm, "peak_source": src, "launches": nnorm, "avg_launch_ms": tms["norm"] / nnorm,
                  "bytes_per_launch_avg": work["norm"] / nnorm}
     shares = {k: tms[k] / total for k in tms}
     shares["step_ms_instrumented"] = total
