@@ -57,6 +57,19 @@ int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const f
                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
                        int stride, int act, void* stream);
 
+/* ---- (a8) weight gradient of the convolution (training) -----------------------------
+ * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]
+ * replaces the autograd backward of nn.Conv2d w.r.t. its weight (oracle: every conv of
+ * S2PGenerator / MultiscaleDiscriminator).  x, dy: NHWC bf16; dW: fp32 OIHW (nn.Conv2d layout).
+ * tcgen05 with MN-major operands straight from the NHWC tensors (no transpose pass); split-K
+ * partials in `workspace` (s2p_conv_wgrad_workspace_bytes) combined in a fixed order.
+ * Cin % 64 == 0, Cout % 8 == 0, ksize in 1..4, stride in {1,2}. */
+long long s2p_conv_wgrad_workspace_bytes(int B, int Hin, int Win, int Cin, int Cout, int ksize, int stride,
+                                         int pad);
+int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, float* dw_oihw, void* workspace,
+                   long long workspace_bytes, int B, int Hin, int Win, int Cin, int Cout, int ksize,
+                   int stride, int pad, int accumulate, void* stream);
+
 /* OIHW fp32 -> [Cout][R][S][Cin] bf16 rows, each weight multiplied by `scale`
  * (used to fold the MAT blend factors at load time). */
 int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S,

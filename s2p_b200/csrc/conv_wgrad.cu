@@ -1,0 +1,356 @@
+// Weight gradient of the implicit-GEMM convolution on tcgen05 (training path, SURVEY.md
+// section 8 a8: backward of the nn.Conv2d layers of generator and discriminator).
+//
+//   dW[co, r, s, ci] = sum_{n,ho,wo} dY[n, ho, wo, co] * X[n, ho*st - pad + r, wo*st - pad + s, ci]
+//
+// GEMM view per filter tap: D_tap[co, ci] = sum_pix A[co, pix] * B_tap[ci, pix] with K = pixels.
+// Both operands are NHWC in HBM, i.e. the GEMM's M (co) / N (ci) index is the contiguous one:
+// "MN-major" UMMA operands.  A TMA box {64 channels, tile_w, tile_h, 1} lands in shared memory as
+// [pixel rows][128 B] with the 128B swizzle, which IS the canonical MN-major SWIZZLE_128B layout
+// (64 MN elements per row, 8 K rows per 1024 B atom, atoms along K at SBO = 1024 B, the next 64
+// MN elements at LBO = rows * 128 B), so no transpose pass over the activations is needed.
+//
+// CTA = (128-wide co tile, BN-wide ci tile, one filter row r): S accumulators of BN columns in
+// TMEM (S*BN <= 512), looping over its share of the pixel tiles (split-K over gridDim.z);
+// partial results go to fp32 [split][Cout][R][S][Cin] and are combined in a fixed order by
+// wgrad_reduce_kernel (bit-stable: no atomics), which also writes the OIHW layout of nn.Conv2d.
+// Warp roles: warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..5 epilogue.
+#include <stdlib.h>
+
+#include "ptx.cuh"
+#include "s2p_internal.h"
+
+namespace s2p {
+
+struct WgradParams {
+  int B, Ho, Wo;            // dY spatial size
+  int Cin, Cout, R, S, pad, stride;
+  int tile_w, tile_h, tiles_x, tiles_y;
+  int kb_rows;              // tile_w * tile_h (multiple of 16)
+  int num_pix_tiles;        // B * tiles_x * tiles_y
+  float* partial;           // [splits][Cout][R][S][Cin]
+};
+
+// MN-major, SWIZZLE_128B shared-memory descriptor: LBO = byte distance between 64-element MN
+// blocks, SBO = byte distance between 8-row K groups (1024 B).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// kind::f16, D=f32, A=B=bf16, both MN-major (bits 15 / 16)
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(uint32_t M, uint32_t N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+constexpr int kWgStages = 2;
+
+template <int BN, int TAPS>
+__global__ void __launch_bounds__(192, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
+                  const WgradParams p) {
+  constexpr int kAtomsA = 2;              // 128 co = two 64-wide MN blocks
+  constexpr int kAtomsB = BN / 64;
+  constexpr uint32_t kTmemCols = (TAPS * BN <= 128) ? 128 : (TAPS * BN <= 256) ? 256 : 512;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int atom_bytes = p.kb_rows * 128;                       // one 64-channel block of one tile
+  const int atom_stride = (atom_bytes + 1023) & ~1023;          // keep every block 1024-B aligned
+  const int stage_bytes = (kAtomsA + TAPS * kAtomsB) * atom_stride;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kWgStages;
+  uint64_t* done_bar = bars + 2 * kWgStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int co0 = blockIdx.x * 128;
+  const int ci_tiles = p.Cin / BN;
+  const int ci0 = (blockIdx.y % ci_tiles) * BN;
+  const int r = blockIdx.y / ci_tiles;            // filter row of this CTA
+  const int split = blockIdx.z, splits = gridDim.z;
+  const int t_begin = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * split / splits);
+  const int t_end = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * (split + 1) / splits);
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const uint32_t stage_tx = static_cast<uint32_t>((kAtomsA + TAPS * kAtomsB) * atom_bytes);
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t_begin; t < t_end; ++t) {
+      const int img = t / tiles_per_img, tt = t % tiles_per_img;
+      const int h0 = (tt / p.tiles_x) * p.tile_h, w0 = (tt % p.tiles_x) * p.tile_w;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        uint8_t* s0 = smem + stage * stage_bytes;
+        mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+#pragma unroll
+        for (int a = 0; a < kAtomsA; ++a)
+          tma_load_4d(s0 + a * atom_stride, &tmap_dy, &full_bar[stage], co0 + 64 * a, w0, h0, img);
+#pragma unroll
+        for (int s = 0; s < TAPS; ++s)
+#pragma unroll
+          for (int b = 0; b < kAtomsB; ++b)
+            tma_load_4d(s0 + (kAtomsA + s * kAtomsB + b) * atom_stride, &tmap_x, &full_bar[stage], ci0 + 64 * b,
+                        w0 * p.stride - p.pad + s, h0 * p.stride - p.pad + r, img);
+      }
+      __syncwarp();
+      if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_bf16_mn(128, BN);
+    const uint32_t lbo = static_cast<uint32_t>(atom_stride), sbo = 1024u;
+    int stage = 0;
+    uint32_t phase = 0;
+    const int ksteps = p.kb_rows / 16;
+    for (int t = t_begin; t < t_end; ++t) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t s0 = smem_u32(smem + stage * stage_bytes);
+        const uint64_t da = umma_desc_mn_sw128(s0, lbo, sbo);
+        for (int s = 0; s < TAPS; ++s) {
+          const uint64_t db = umma_desc_mn_sw128(s0 + (kAtomsA + s * kAtomsB) * atom_stride, lbo, sbo);
+          for (int k = 0; k < ksteps; ++k) {
+            // K = 16 pixel rows = two 8-row groups = 2048 B further into every 64-channel block
+            umma_bf16(tmem_base + s * BN, da + static_cast<uint64_t>(k * (2048 >> 4)),
+                      db + static_cast<uint64_t>(k * (2048 >> 4)), idesc, (t != t_begin || k != 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty_bar[stage]);
+        if (t == t_end - 1) umma_commit(done_bar);
+      }
+      __syncwarp();
+      if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue: TMEM -> fp32 partials
+    const int q = warp & 3;
+    const int co = co0 + q * 32 + lane;
+    if (t_end > t_begin) {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+    }
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    for (int s = 0; s < TAPS; ++s) {
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t raw[32];
+        if (t_end > t_begin) {
+          tmem_ld32(t_row + s * BN + c * 32, raw);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) raw[j] = 0u;
+        }
+        if (co < p.Cout) {
+          float4* dst = reinterpret_cast<float4*>(
+              p.partial + (((static_cast<size_t>(split) * p.Cout + co) * p.R + r) * p.S + s) * p.Cin + ci0 + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            dst[j] = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]),
+                                 __uint_as_float(raw[4 * j + 2]), __uint_as_float(raw[4 * j + 3]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
+}
+
+// dW_oihw[co][ci][r][s] (+)= sum_split partial[split][co][r][s][ci]   (fixed order)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw_oihw, int splits,
+                                    int Cout, int Cin, int R, int S, int accumulate) {
+  const long long total = static_cast<long long>(Cout) * R * S * Cin;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < splits; ++k) acc += partial[k * total + i];
+    const int ci = static_cast<int>(i % Cin);
+    long long t = i / Cin;
+    const int s = static_cast<int>(t % S); t /= S;
+    const int r = static_cast<int>(t % R);
+    const int co = static_cast<int>(t / R);
+    float* d = dw_oihw + ((static_cast<long long>(co) * Cin + ci) * R + r) * S + s;
+    *d = accumulate ? *d + acc : acc;
+  }
+}
+
+// pixel tile for the K dimension: tile_w * tile_h a multiple of 16, <= 128 rows, fewest wasted rows
+static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out) {
+  double best = -1.0;
+  int btw = 16, bth = 1;
+  for (int tw = 1; tw <= W && tw <= 128; ++tw) {
+    for (int th = 1; th <= H && tw * th <= 128; ++th) {
+      if ((tw * th) % 16) continue;
+      const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
+      const double eff = static_cast<double>(H) * W / (tiles * static_cast<double>(tw * th));
+      // prefer efficiency, then bigger tiles (fewer pipeline turns)
+      const double score = eff + 1e-4 * tw * th;
+      if (score > best) { best = score; btw = tw; bth = th; }
+    }
+  }
+  *tw_out = btw;
+  *th_out = bth;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn wg_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+struct WgradPlan {
+  WgradParams p;
+  int bn, taps, splits, smem_bytes;
+  dim3 grid;
+};
+
+static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int stride, int pad, WgradPlan* pl) {
+  WgradParams& p = pl->p;
+  p = WgradParams{};
+  p.B = B;
+  p.Ho = (Hin + 2 * pad - ksize) / stride + 1;
+  p.Wo = (Win + 2 * pad - ksize) / stride + 1;
+  p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
+  wgrad_pick_tile(p.Ho, p.Wo, &p.tile_w, &p.tile_h);
+  p.tiles_x = (p.Wo + p.tile_w - 1) / p.tile_w;
+  p.tiles_y = (p.Ho + p.tile_h - 1) / p.tile_h;
+  p.kb_rows = p.tile_w * p.tile_h;
+  p.num_pix_tiles = B * p.tiles_x * p.tiles_y;
+  pl->taps = ksize;
+  const int atom = p.kb_rows * 128;
+  pl->bn = (Cin % 128 == 0 && ksize * 128 <= 512 && kWgStages * (2 + ksize * 2) * atom <= 200 * 1024) ? 128 : 64;
+  const int ctas = ((Cout + 127) / 128) * (Cin / pl->bn) * ksize;
+  int splits = (2 * num_sms() + ctas - 1) / ctas;
+  if (splits > p.num_pix_tiles) splits = p.num_pix_tiles;
+  if (splits < 1) splits = 1;
+  pl->splits = splits;
+  pl->grid = dim3((Cout + 127) / 128, (Cin / pl->bn) * ksize, splits);
+  const int atom_stride = (p.kb_rows * 128 + 1023) & ~1023;
+  pl->smem_bytes = kWgStages * (2 + pl->taps * (pl->bn / 64)) * atom_stride + 1024 + 128;
+  return S2P_OK;
+}
+
+template <int BN, int TAPS>
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradPlan& pl, cudaStream_t st) {
+  static int configured = 0;
+  if (pl.smem_bytes > configured) {
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BN, TAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        pl.smem_bytes));
+    configured = pl.smem_bytes;
+  }
+  conv_wgrad_kernel<BN, TAPS><<<pl.grid, 192, pl.smem_bytes, st>>>(tdy, tx, pl.p);
+  count_launch();
+  return check_launch("conv_wgrad_kernel");
+}
+
+}  // namespace s2p
+
+extern "C" long long s2p_conv_wgrad_workspace_bytes(int B, int Hin, int Win, int Cin, int Cout, int ksize,
+                                                    int stride, int pad) {
+  using namespace s2p;
+  if (B <= 0 || Hin <= 0 || Win <= 0 || Cin <= 0 || Cin % 64 || Cout <= 0 || ksize < 1 || ksize > 4 || stride < 1)
+    return -1;
+  WgradPlan pl;
+  wgrad_plan(B, Hin, Win, Cin, Cout, ksize, stride, pad, &pl);
+  return static_cast<long long>(pl.splits) * Cout * ksize * ksize * Cin * 4;
+}
+
+extern "C" int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, float* dw_oihw,
+                              void* workspace, long long workspace_bytes, int B, int Hin, int Win, int Cin,
+                              int Cout, int ksize, int stride, int pad, int accumulate, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && dy && dw_oihw && workspace, "wgrad: null pointer");
+  S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "wgrad: bad dims");
+  S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "wgrad: Cin=%d must be a multiple of 64", Cin);
+  S2P_CHECK_ARG(Cout > 0 && Cout % 8 == 0, "wgrad: Cout=%d must be a multiple of 8", Cout);
+  S2P_CHECK_ARG(ksize >= 1 && ksize <= 4 && (stride == 1 || stride == 2) && pad >= 0 && pad <= 3, "wgrad: k/stride/pad");
+  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0 && dy_pitch >= Cout && dy_pitch % 8 == 0, "wgrad: pitch");
+  S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) |
+                  reinterpret_cast<uintptr_t>(workspace)) & 15) == 0, "wgrad: 16-byte alignment");
+  WgradPlan pl;
+  wgrad_plan(B, Hin, Win, Cin, Cout, ksize, stride, pad, &pl);
+  const long long need = static_cast<long long>(pl.splits) * Cout * ksize * ksize * Cin * 4;
+  S2P_CHECK_ARG(workspace_bytes >= need, "wgrad: workspace %lld < %lld bytes", workspace_bytes, need);
+  S2P_CHECK_ARG(pl.smem_bytes <= 227 * 1024, "wgrad: tile needs %d bytes of shared memory", pl.smem_bytes);
+  EncodeTiledFn encode = wg_encode_fn();
+  if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable");
+  pl.p.partial = static_cast<float*>(workspace);
+  const WgradParams& p = pl.p;
+  CUtensorMap tdy, tx;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)Cout, (cuuint64_t)p.Wo, (cuuint64_t)p.Ho, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)dy_pitch * 2, (cuuint64_t)dy_pitch * 2 * p.Wo,
+                             (cuuint64_t)dy_pitch * 2 * p.Wo * p.Ho};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(&tdy, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(dy), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "wgrad: dY tensor map encode failed (%d)", (int)r);
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)x_pitch * 2, (cuuint64_t)x_pitch * 2 * Win,
+                             (cuuint64_t)x_pitch * 2 * Win * Hin};
+    cuuint32_t box[4] = {64, (cuuint32_t)(p.tile_w * stride), (cuuint32_t)(p.tile_h * stride), 1};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = encode(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "wgrad: x tensor map encode failed (%d)", (int)r);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc;
+  if (pl.bn == 128) {
+    switch (ksize) {
+      case 1: rc = launch_wgrad<128, 1>(tdy, tx, pl, st); break;
+      case 3: rc = launch_wgrad<128, 3>(tdy, tx, pl, st); break;
+      case 4: rc = launch_wgrad<128, 4>(tdy, tx, pl, st); break;
+      default: return set_error(S2P_ERR_UNSUPPORTED, "wgrad: ksize=%d", ksize);
+    }
+  } else {
+    switch (ksize) {
+      case 1: rc = launch_wgrad<64, 1>(tdy, tx, pl, st); break;
+      case 3: rc = launch_wgrad<64, 3>(tdy, tx, pl, st); break;
+      case 4: rc = launch_wgrad<64, 4>(tdy, tx, pl, st); break;
+      default: return set_error(S2P_ERR_UNSUPPORTED, "wgrad: ksize=%d", ksize);
+    }
+  }
+  if (rc != S2P_OK) return rc;
+  const long long total = static_cast<long long>(Cout) * ksize * ksize * Cin;
+  const int blocks = static_cast<int>((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(workspace), dw_oihw, pl.splits, Cout, Cin,
+                                              ksize, ksize, accumulate);
+  count_launch();
+  return check_launch("wgrad_reduce_kernel");
+}

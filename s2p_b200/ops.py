@@ -93,6 +93,35 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
     return out
 
 
+_wgrad_ws = {}
+
+
+def conv_wgrad(x, dy, ksize, stride=1, pad=None, out=None, accumulate=False):
+    """dW (fp32 OIHW) of conv(x, W) given dy; x, dy NHWC bf16."""
+    _require_cuda(x, dy, out)
+    b, hin, win, cin = x.shape
+    cout = dy.shape[3]
+    pad = ksize // 2 if pad is None else pad
+    if out is None:
+        out = torch.empty(cout, cin, ksize, ksize, dtype=torch.float32, device=x.device)
+        accumulate = False
+    if tuple(out.shape) != (cout, cin, ksize, ksize) or out.dtype != torch.float32 or not out.is_contiguous():
+        raise RuntimeError("conv_wgrad: out must be contiguous fp32 [Cout, Cin, k, k]")
+    lib = _lib.load()
+    need = int(lib.s2p_conv_wgrad_workspace_bytes(b, hin, win, cin, cout, ksize, stride, pad))
+    if need < 0:
+        raise RuntimeError("conv_wgrad: unsupported shape")
+    key = x.device.index
+    ws = _wgrad_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
+        _wgrad_ws[key] = ws
+    _lib.check(lib.s2p_conv_wgrad(x.data_ptr(), _nhwc_pitch(x, "x"), dy.data_ptr(), _nhwc_pitch(dy, "dy"), out.data_ptr(),
+                                  ws.data_ptr(), ws.numel(), b, hin, win, cin, cout, ksize, stride, pad,
+                                  1 if accumulate else 0, _stream()), "s2p_conv_wgrad")
+    return out
+
+
 def in_stats_finalize(stats: torch.Tensor, hw: int, eps: float = 1e-5, out=None) -> torch.Tensor:
     """partials [B, rows, C, 2] -> (mean, rstd) [B, C, 2] fp32"""
     _require_cuda(stats)

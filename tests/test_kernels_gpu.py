@@ -175,6 +175,34 @@ def test_conv_mat_fused(ops, c, up, hx, b):
     assert torch.equal(y, y2)          # bit-stable
 
 
+WGRAD_CASES = [  # b, h, w, cin, cout, k, stride
+    (1, 16, 16, 64, 128, 1, 1), (1, 16, 16, 64, 128, 3, 1), (2, 25, 25, 128, 128, 3, 1), (2, 100, 100, 64, 64, 3, 1),
+    (2, 50, 50, 128, 256, 3, 1), (3, 100, 100, 64, 128, 3, 2), (2, 25, 25, 512, 512, 3, 1), (2, 50, 50, 256, 128, 1, 1),
+    (1, 7, 9, 64, 64, 3, 1), (2, 20, 36, 64, 72, 3, 1),
+]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES, ids=lambda c: "-".join(map(str, c)))
+def test_conv_wgrad(ops, case):
+    """dW of the conv against torch autograd on the same bf16-rounded x and dy (fp32 accumulate:
+    only the summation order differs)."""
+    b, h, w, cin, cout, k, st = case
+    g = torch.Generator().manual_seed(cin + cout + k)
+    pad = k // 2
+    x = torch.randn(b, h, w, cin, generator=g).cuda().to(torch.bfloat16)
+    ho, wo = (h + 2 * pad - k) // st + 1, (w + 2 * pad - k) // st + 1
+    dy = torch.randn(b, ho, wo, cout, generator=g).cuda().to(torch.bfloat16)
+    dw = ops.conv_wgrad(x, dy, k, st)
+    wt = torch.zeros(cout, cin, k, k, device="cuda", requires_grad=True)
+    F.conv2d(x.float().permute(0, 3, 1, 2), wt, None, st, pad).backward(dy.float().permute(0, 3, 1, 2))
+    ref = wt.grad
+    assert torch.isfinite(dw).all()
+    assert (dw - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() + 1e-3
+    dw2 = ops.conv_wgrad(x, dy, k, st, out=dw.clone(), accumulate=True)
+    assert torch.allclose(dw2, 2 * dw, rtol=1e-6, atol=1e-6)
+    assert torch.equal(ops.conv_wgrad(x, dy, k, st), dw)      # bit-stable split-K
+
+
 def test_stem_and_tail(ops):
     g = torch.Generator().manual_seed(11)
     img = (torch.rand(3, 3, 100, 100, generator=g) * 2 - 1).cuda()
