@@ -160,7 +160,7 @@ def run_b200(args):
 
     opt = s2p_b200.make_options(env_type=ENV, gpu_ids=str(local), init_type="scaled")
     torch.manual_seed(1234)
-    net = s2p_b200.define_G(opt)
+    net = s2p_b200.define_G(opt).eval()
     net.pack()
     B = args.batch
     g = torch.Generator().manual_seed(100 + rank)

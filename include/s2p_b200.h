@@ -107,6 +107,19 @@ int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, 
                            int up, const float* mod_table, void* y, int y_pitch, int B, int H, int W,
                            int Cin, int C, int ksize, int act, void* stream);
 
+/* backward of s2p_mat_norm_fwd (training; replaces autograd through F.instance_norm, the MAT
+ * modulation, F.leaky_relu and F.interpolate(nearest x2) of oracle MAT / MATResBlk):
+ *   d_gb  [B][H][W][2C] bf16 : gradient of the spatial (gI | bI) map          (NULL iff gb_spatial NULL)
+ *   sums  [B][C][4] fp32     : (d gs, d bs, S1, S2) per (n, c)
+ *   dx    [B][H/up][W/up][C] : gradient w.r.t. the pre-norm activation, plus `add` when given
+ *   dxhat [B][H][W][C] bf16 and partial [B][s2p_mat_norm_bwd_chunks][C][4] fp32 are scratch. */
+int s2p_mat_norm_bwd_chunks(int B, int H, int W, int C);
+int s2p_mat_norm_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, int up, const float* mean_rstd,
+                     const float* gs, const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch,
+                     int act, void* d_gb, int dgb_pitch, void* dxhat, int dxh_pitch, float* partial,
+                     float* sums, const void* add, int add_pitch, void* dx, int dx_pitch, int B, int H, int W,
+                     int C, void* stream);
+
 /* ---- (a5 head/tail) Cin=3 stem conv and Cout=3 ToRGB + tanh --------------------
  * stem: oracle ImageEncoder.conv1 (3->Cout 3x3 s1 p1) straight from the boundary
  * image (fp32 NCHW in [-1,1] or uint8 NHWC mapped by u/127.5-1) to NHWC bf16, with

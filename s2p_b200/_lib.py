@@ -31,6 +31,9 @@ SIGNATURES = {
     "s2p_mat_fused_ct": (_i, [_i]),
     "s2p_mat_prepare": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _f, _vp]),
     "s2p_conv_mat_fused_fwd": (_i, [_vp, _i, _vp, _vp, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2p_mat_norm_bwd_chunks": (_i, [_i, _i, _i, _i]),
+    "s2p_mat_norm_bwd": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _vp, _vp,
+                              _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2p_stem_stats_rows": (_i, [_i, _i]),
     "s2p_stem_conv_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
     "s2p_torgb_tanh_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),

@@ -1,0 +1,126 @@
+"""Differentiable wrappers of the C-ABI kernels for the GAN training step
+(the reference's train.py --netG=s2p, README.md:59).
+
+torch.autograd is the tape only: every forward and backward below is one of this
+repo's sm_100a kernels (conv forward / dgrad = the tcgen05 implicit GEMM, wgrad = the
+MN-major tcgen05 kernel, norm backward = the fused reduce + dx kernels).  Activations
+and their gradients are NHWC bf16; parameters and their gradients are fp32 in the
+nn.Conv2d / nn.Linear layouts, so a stock optimiser state_dict stays compatible.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .ops import ACT_LRELU, ACT_NONE, ACT_RELU
+
+
+def _act_grad(dy: torch.Tensor, y: torch.Tensor, act: int) -> torch.Tensor:
+    """gradient through ReLU / LeakyReLU(0.2) given the activated output y (sign(y) = sign(pre))."""
+    if act == ACT_NONE:
+        return dy
+    if act == ACT_RELU:
+        return dy * (y > 0)
+    return torch.where(y > 0, dy, dy * 0.2)
+
+
+class ConvFn(torch.autograd.Function):
+    """y = act(conv(x, W) + b + residual); x, residual, y NHWC bf16; W fp32 OIHW, b fp32."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, stride, act, stats):
+        cout, cin, k, _ = weight.shape
+        wp = ops.pack_conv_weight(weight)
+        y = ops.conv_igemm(x, wp, None if bias is None else bias.detach().float().contiguous(), cout, k, stride, act,
+                           residual, None, stats)
+        ctx.save_for_backward(x, weight, y if act != ACT_NONE else None)
+        ctx.cfg = (k, stride, act, bias is not None, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        k, stride, act, has_bias, has_res = ctx.cfg
+        dy = dy.contiguous()
+        if act != ACT_NONE:
+            dy = _act_grad(dy, y, act)
+        dx = dw = db = dres = None
+        if ctx.needs_input_grad[0]:
+            cout, cin = weight.shape[0], weight.shape[1]
+            # dgrad = the same implicit GEMM with the filter flipped and in/out channels swapped
+            wt = weight.detach().flip(2, 3).transpose(0, 1).contiguous()
+            g = dy
+            if stride == 2:   # transposed conv: zero-insert the gradient, then a stride-1 conv
+                b, ho, wo, _ = dy.shape
+                g = torch.zeros(b, x.shape[1], x.shape[2], cout, dtype=dy.dtype, device=dy.device)
+                g[:, 0:2 * ho:2, 0:2 * wo:2] = dy
+            dx = ops.conv_igemm(g, ops.pack_conv_weight(wt), None, cin, k, 1, ACT_NONE)
+        if ctx.needs_input_grad[1]:
+            dw = ops.conv_wgrad(x, dy, k, stride)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = dy.float().sum(dim=(0, 1, 2))
+        if has_res and ctx.needs_input_grad[3]:
+            dres = dy
+        return dx, dw, db, dres, None, None, None
+
+
+def conv(x, weight, bias=None, residual=None, stride=1, act=ACT_NONE, stats=None):
+    return ConvFn.apply(x, weight, bias, residual, stride, act, stats)
+
+
+class MatNormFn(torch.autograd.Function):
+    """y = act(IN(up(x)) * (1 + gs + gI) + bs + bI); statistics come precomputed (mean_rstd)."""
+
+    @staticmethod
+    def forward(ctx, x, mean_rstd, gs, bs, gb, up, act):
+        y = ops.mat_norm(x, mean_rstd, gs, bs, gb, up, act)
+        ctx.save_for_backward(x, mean_rstd, gs, bs, gb)
+        ctx.cfg = (up, act)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, mean_rstd, gs, bs, gb = ctx.saved_tensors
+        up, act = ctx.cfg
+        dx, d_gb, sums = ops.mat_norm_bwd(dy.contiguous(), x, mean_rstd, gs, bs, gb, up, act)
+        dgs = sums[..., 0] if gs is not None else None
+        dbs = sums[..., 1] if bs is not None else None
+        return dx, None, dgs, dbs, d_gb, None, None
+
+
+def mat_norm(x, mean_rstd, gs=None, bs=None, gb=None, up=1, act=ACT_LRELU):
+    return MatNormFn.apply(x, mean_rstd, gs, bs, gb, up, act)
+
+
+class LinearFn(torch.autograd.Function):
+    """y = act(x W^T + b), fp32, on the repo's own SGEMM kernel (state encoder / MAT state heads)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act):
+        y = ops.linear(x.contiguous(), weight.contiguous(), bias, act)
+        ctx.save_for_backward(x, weight, y if act != ACT_NONE else None)
+        ctx.act = act
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = _act_grad(dy.contiguous(), y, ctx.act) if ctx.act != ACT_NONE else dy.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.linear(dy, weight.t().contiguous(), None, ACT_NONE)             # [B,N] x [N,K]
+        if ctx.needs_input_grad[1]:
+            dw = ops.linear(dy.t().contiguous(), x.t().contiguous(), None, ACT_NONE)  # [N,B] x [B,K]
+        if ctx.needs_input_grad[2]:
+            db = dy.sum(dim=0)
+        return dx, dw, db, None
+
+
+def linear(x, weight, bias=None, act=ACT_NONE):
+    return LinearFn.apply(x, weight, bias, act)
+
+
+def conv_stats(y_shape, device):
+    """scratch for the conv epilogue's statistics partials of an output of shape [B,H,W,C]"""
+    b, h, w, c = y_shape
+    return torch.empty(b, ops.conv_stats_rows(h, w), c, 2, dtype=torch.float32, device=device)

@@ -257,3 +257,266 @@ extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float*
   count_launch();
   return check_launch("mat_norm_kernel");
 }
+
+// =====================================================================================
+// Backward of the fused IN + MAT modulation + activation (training path).
+//   forward:  xh = (x_up - mean) * rstd ;  g = 1 + gs + gI ;  pre = xh * g + bs + bI ;  y = act(pre)
+//   pass A (mat_norm_bwd_reduce_kernel), one read of dy / x / (gI,bI), per output pixel:
+//       dpre = dy * act'(pre) ;  dgI = dpre * xh ;  dbI = dpre ;  dxh = dpre * g
+//       writes the spatial (dgI | dbI) map and dxh (bf16), and per-(n,c) partial sums
+//       (sum dpre*xh, sum dpre, sum dxh, sum dxh*xh) in a fixed order (no atomics)
+//   sum4_finalize_kernel: partial rows -> sums[n][c][4]   (dgs, dbs, S1, S2)
+//   pass B (mat_norm_bwd_dx_kernel), per INPUT pixel (the x2 nearest upsample's backward is the
+//       sum over the 2x2 children):  dx = rstd * (sum_children dxh - S1/N - xh * S2/N) (+ add)
+// =====================================================================================
+namespace s2p {
+
+struct NormBwdParams {
+  const __nv_bfloat16* dy;
+  const __nv_bfloat16* x;
+  const float2* mean_rstd;
+  const float* gs;
+  const float* bs;
+  const __nv_bfloat16* gb;
+  __nv_bfloat16* dgb;
+  __nv_bfloat16* dxh;
+  float4* partial;
+  int dy_pitch, x_pitch, gb_pitch, dgb_pitch, dxh_pitch, gsbs_pitch;
+  int B, H, W, C, up, act;
+  int pix_per_cta, chunks;
+};
+
+__device__ __forceinline__ uint4 pack8(const float (&o)[8]) {
+  return make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                    pack_bf16x2(o[6], o[7]));
+}
+
+template <bool HAS_GB, bool UP2>
+__global__ void __launch_bounds__(256) mat_norm_bwd_reduce_kernel(const NormBwdParams p) {
+  extern __shared__ float4 red[];            // [blockDim.y][C]
+  const int cg = threadIdx.x, c0 = cg * 8, n = blockIdx.y;
+  float sc[8], sh[8], g1[8], b0[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float2 mr = __ldg(p.mean_rstd + static_cast<size_t>(n) * p.C + c0 + j);
+    sc[j] = mr.y;
+    sh[j] = -mr.x * mr.y;
+    g1[j] = 1.f + (p.gs ? __ldg(p.gs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 0.f);
+    b0[j] = p.bs ? __ldg(p.bs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 0.f;
+  }
+  float a0[8], a1[8], a2[8], a3[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; a2[j] = 0.f; a3[j] = 0.f; }
+  const int HW = p.H * p.W;
+  const int Wx = UP2 ? (p.W >> 1) : p.W, Hx = UP2 ? (p.H >> 1) : p.H;
+  const int pix_begin = blockIdx.x * p.pix_per_cta;
+  const int pix_end = min(pix_begin + p.pix_per_cta, HW);
+  const size_t img_pix = static_cast<size_t>(n) * HW;
+  const size_t img_pix_x = static_cast<size_t>(n) * Hx * Wx;
+  for (int pix = pix_begin + threadIdx.y; pix < pix_end; pix += blockDim.y) {
+    size_t xpix;
+    if (UP2) {
+      const int h = pix / p.W, w = pix - h * p.W;
+      xpix = img_pix_x + static_cast<size_t>(h >> 1) * Wx + (w >> 1);
+    } else {
+      xpix = img_pix + pix;
+    }
+    const uint4 xv = __ldg(reinterpret_cast<const uint4*>(p.x + xpix * p.x_pitch + c0));
+    const uint4 dv = ld_stream(p.dy + (img_pix + pix) * p.dy_pitch + c0);
+    float xf[8], df[8], gf[8], bf[8];
+    unpack8(xv, xf);
+    unpack8(dv, df);
+    if (HAS_GB) {
+      const __nv_bfloat16* g = p.gb + (img_pix + pix) * p.gb_pitch + c0;
+      unpack8(ld_stream(g), gf);
+      unpack8(ld_stream(g + p.C), bf);
+    }
+    float dg[8], db[8], dx[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xh = fmaf(xf[j], sc[j], sh[j]);
+      const float g = HAS_GB ? g1[j] + gf[j] : g1[j];
+      const float b = HAS_GB ? b0[j] + bf[j] : b0[j];
+      const float pre = fmaf(xh, g, b);
+      float d = df[j];
+      if (p.act == 2) d = pre > 0.f ? d : 0.2f * d;
+      else if (p.act == 1) d = pre > 0.f ? d : 0.f;
+      dg[j] = d * xh;
+      db[j] = d;
+      dx[j] = d * g;
+      a0[j] += dg[j];
+      a1[j] += d;
+      a2[j] += dx[j];
+      a3[j] += dx[j] * xh;
+    }
+    if (HAS_GB) {
+      __nv_bfloat16* o = p.dgb + (img_pix + pix) * p.dgb_pitch + c0;
+      st_stream(o, pack8(dg));
+      st_stream(o + p.C, pack8(db));
+    }
+    st_stream(p.dxh + (img_pix + pix) * p.dxh_pitch + c0, pack8(dx));
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y * p.C + c0 + j] = make_float4(a0[j], a1[j], a2[j], a3[j]);
+  __syncthreads();
+  for (int c = threadIdx.y * blockDim.x + threadIdx.x; c < p.C; c += blockDim.x * blockDim.y) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < static_cast<int>(blockDim.y); ++k) {
+      const float4 v = red[k * p.C + c];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    p.partial[(static_cast<size_t>(n) * p.chunks + blockIdx.x) * p.C + c] = s;
+  }
+}
+
+__global__ void sum4_finalize_kernel(const float4* __restrict__ partial, int rows, float4* __restrict__ out, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = blockIdx.y;
+  if (c >= C) return;
+  double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+  for (int r = 0; r < rows; ++r) {
+    const float4 v = __ldg(partial + (static_cast<size_t>(n) * rows + r) * C + c);
+    s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+  }
+  out[static_cast<size_t>(n) * C + c] = make_float4((float)s0, (float)s1, (float)s2, (float)s3);
+}
+
+// one thread = one INPUT pixel x 8 channels
+template <bool UP2>
+__global__ void __launch_bounds__(256)
+mat_norm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dxh, int dxh_pitch, const __nv_bfloat16* __restrict__ x,
+                       int x_pitch, const float2* __restrict__ mean_rstd, const float4* __restrict__ sums,
+                       const __nv_bfloat16* __restrict__ add, int add_pitch, __nv_bfloat16* __restrict__ dx,
+                       int dx_pitch, int B, int Hx, int Wx, int C) {
+  const int groups = C / 8;
+  const long long total = static_cast<long long>(B) * Hx * Wx * groups;
+  const long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (idx >= total) return;
+  const int cg = static_cast<int>(idx % groups);
+  const long long xpix = idx / groups;
+  const int n = static_cast<int>(xpix / (Hx * Wx));
+  const int rem = static_cast<int>(xpix - static_cast<long long>(n) * Hx * Wx);
+  const int c0 = cg * 8;
+  float D[8];
+  if (UP2) {
+    const int h = rem / Wx, w = rem - h * Wx;
+    const int W = 2 * Wx;
+    const size_t base = (static_cast<size_t>(n) * (2 * Hx) + 2 * h) * W + 2 * w;
+    float t[8];
+    unpack8(ld_stream(dxh + base * dxh_pitch + c0), D);
+    unpack8(ld_stream(dxh + (base + 1) * dxh_pitch + c0), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) D[j] += t[j];
+    unpack8(ld_stream(dxh + (base + W) * dxh_pitch + c0), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) D[j] += t[j];
+    unpack8(ld_stream(dxh + (base + W + 1) * dxh_pitch + c0), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) D[j] += t[j];
+  } else {
+    unpack8(ld_stream(dxh + static_cast<size_t>(xpix) * dxh_pitch + c0), D);
+  }
+  float xf[8], af[8];
+  unpack8(__ldg(reinterpret_cast<const uint4*>(x + static_cast<size_t>(xpix) * x_pitch + c0)), xf);
+  if (add != nullptr) unpack8(__ldg(reinterpret_cast<const uint4*>(add + static_cast<size_t>(xpix) * add_pitch + c0)), af);
+  const float inv_n = 1.f / static_cast<float>(Hx * Wx);
+  float o[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float2 mr = __ldg(mean_rstd + static_cast<size_t>(n) * C + c0 + j);
+    const float4 s = __ldg(sums + static_cast<size_t>(n) * C + c0 + j);
+    const float xh = (xf[j] - mr.x) * mr.y;
+    float v = mr.y * (D[j] - s.z * inv_n - xh * s.w * inv_n);
+    if (add != nullptr) v += af[j];
+    o[j] = v;
+  }
+  *reinterpret_cast<uint4*>(dx + static_cast<size_t>(xpix) * dx_pitch + c0) = pack8(o);
+}
+
+static void norm_bwd_geometry(int B, int H, int W, int C, int* py_out, int* chunks_out, int* ppc_out) {
+  const int groups = C / 8;
+  int py = 256 / groups;
+  if (py < 1) py = 1;
+  const int HW = H * W;
+  int chunks = (HW + py * 16 - 1) / (py * 16);
+  const int max_chunks = (num_sms() * 8 + B - 1) / B;
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  const int ppc = (HW + chunks - 1) / chunks;
+  *py_out = py;
+  *ppc_out = ppc;
+  *chunks_out = (HW + ppc - 1) / ppc;
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_mat_norm_bwd_chunks(int B, int H, int W, int C) {
+  if (B <= 0 || H <= 0 || W <= 0 || C <= 0 || C % 8) return -1;
+  int py, chunks, ppc;
+  s2p::norm_bwd_geometry(B, H, W, C, &py, &chunks, &ppc);
+  return chunks;
+}
+
+extern "C" int s2p_mat_norm_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, int up,
+                                const float* mean_rstd, const float* gs, const float* bs, int gsbs_pitch,
+                                const void* gb_spatial, int gb_pitch, int act, void* d_gb, int dgb_pitch,
+                                void* dxhat, int dxh_pitch, float* partial, float* sums, const void* add,
+                                int add_pitch, void* dx, int dx_pitch, int B, int H, int W, int C, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy && x && mean_rstd && dxhat && partial && sums && dx, "mat_norm_bwd: null pointer");
+  S2P_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && C <= 2048, "mat_norm_bwd: bad dims");
+  S2P_CHECK_ARG(up == 1 || (up == 2 && H % 2 == 0 && W % 2 == 0), "mat_norm_bwd: up=%d", up);
+  S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_norm_bwd: gs/bs");
+  S2P_CHECK_ARG((gb_spatial == nullptr) == (d_gb == nullptr), "mat_norm_bwd: gb / d_gb must come together");
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "mat_norm_bwd: act=%d", act);
+  S2P_CHECK_ARG(dy_pitch % 8 == 0 && x_pitch % 8 == 0 && dxh_pitch % 8 == 0 && dx_pitch % 8 == 0 &&
+                    gb_pitch % 8 == 0 && dgb_pitch % 8 == 0 && add_pitch % 8 == 0, "mat_norm_bwd: pitch");
+  NormBwdParams p{};
+  p.dy = static_cast<const __nv_bfloat16*>(dy);
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.mean_rstd = reinterpret_cast<const float2*>(mean_rstd);
+  p.gs = gs; p.bs = bs;
+  p.gb = static_cast<const __nv_bfloat16*>(gb_spatial);
+  p.dgb = static_cast<__nv_bfloat16*>(d_gb);
+  p.dxh = static_cast<__nv_bfloat16*>(dxhat);
+  p.partial = reinterpret_cast<float4*>(partial);
+  p.dy_pitch = dy_pitch; p.x_pitch = x_pitch; p.gb_pitch = gb_pitch; p.dgb_pitch = dgb_pitch;
+  p.dxh_pitch = dxh_pitch; p.gsbs_pitch = gsbs_pitch;
+  p.B = B; p.H = H; p.W = W; p.C = C; p.up = up; p.act = act;
+  int py;
+  norm_bwd_geometry(B, H, W, C, &py, &p.chunks, &p.pix_per_cta);
+  dim3 block(C / 8, py), grid(p.chunks, B);
+  const size_t smem = static_cast<size_t>(py) * C * sizeof(float4);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  S2P_CHECK_ARG(smem <= 48 * 1024, "mat_norm_bwd: C=%d needs %zu bytes of shared memory", C, smem);
+  if (gb_spatial) {
+    if (up == 2) mat_norm_bwd_reduce_kernel<true, true><<<grid, block, smem, st>>>(p);
+    else mat_norm_bwd_reduce_kernel<true, false><<<grid, block, smem, st>>>(p);
+  } else {
+    if (up == 2) mat_norm_bwd_reduce_kernel<false, true><<<grid, block, smem, st>>>(p);
+    else mat_norm_bwd_reduce_kernel<false, false><<<grid, block, smem, st>>>(p);
+  }
+  count_launch();
+  int rc = check_launch("mat_norm_bwd_reduce_kernel");
+  if (rc != S2P_OK) return rc;
+  sum4_finalize_kernel<<<dim3((C + 127) / 128, B), 128, 0, st>>>(reinterpret_cast<const float4*>(partial), p.chunks,
+                                                               reinterpret_cast<float4*>(sums), C);
+  count_launch();
+  rc = check_launch("sum4_finalize_kernel");
+  if (rc != S2P_OK) return rc;
+  const int Hx = H / up, Wx = W / up;
+  const long long total = static_cast<long long>(B) * Hx * Wx * (C / 8);
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  if (up == 2)
+    mat_norm_bwd_dx_kernel<true><<<blocks, 256, 0, st>>>(p.dxh, dxh_pitch, p.x, x_pitch, p.mean_rstd,
+                                                         reinterpret_cast<const float4*>(sums),
+                                                         static_cast<const __nv_bfloat16*>(add), add_pitch,
+                                                         static_cast<__nv_bfloat16*>(dx), dx_pitch, B, Hx, Wx, C);
+  else
+    mat_norm_bwd_dx_kernel<false><<<blocks, 256, 0, st>>>(p.dxh, dxh_pitch, p.x, x_pitch, p.mean_rstd,
+                                                          reinterpret_cast<const float4*>(sums),
+                                                          static_cast<const __nv_bfloat16*>(add), add_pitch,
+                                                          static_cast<__nv_bfloat16*>(dx), dx_pitch, B, Hx, Wx, C);
+  count_launch();
+  return check_launch("mat_norm_bwd_dx_kernel");
+}

@@ -331,7 +331,99 @@ class S2PGeneratorB200(nn.Module):
         return out_f32, out_u8
 
     def forward(self, image, state):
+        # train.py semantics: a module in train() mode under grad mode returns a differentiable
+        # output; eval() / no_grad() take the fused inference schedule
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            return self.forward_train(image, state)
         return self._run(image, state, True, False)[0]
+
+    # ------------------------------------------------------------------ training forward
+    def forward_train(self, image, state):
+        """Differentiable forward for train.py's G / D steps (README.md:59): same arithmetic as
+        the inference schedule, recorded on the autograd tape through s2p_b200.autograd (every
+        forward and backward op is one of this repo's kernels).  The MAT norm runs in its
+        two-kernel form here because its backward needs the spatial gamma/beta maps."""
+        from .. import autograd as A
+        import torch.nn.functional as F
+        opt = self.opt
+        nh = opt.nhidden
+        if not image.is_cuda:
+            raise RuntimeError("S2PGeneratorB200 needs CUDA tensors; there is no CPU fallback")
+        B, _, H, W = image.shape
+        dev = image.device
+        bf = torch.bfloat16
+
+        def conv_in(x, conv, stride=1, act=ACT_NONE, residual=None, want_stats=True, weight=None, bias=None):
+            w = conv.weight if weight is None else weight
+            b = conv.bias if bias is None else bias
+            k = w.shape[2]
+            ho = (x.shape[1] + 2 * (k // 2) - k) // stride + 1
+            wo = (x.shape[2] + 2 * (k // 2) - k) // stride + 1
+            st = A.conv_stats((B, ho, wo, w.shape[0]), dev) if want_stats else None
+            y = A.conv(x, w, b, residual, stride, act, st)
+            mr = ops.in_stats_finalize(st, ho * wo) if want_stats else None
+            return y, mr
+
+        # ---- state path (fp32)
+        h = ops.pos_encode(state.contiguous().float(), opt.pe_freqs)
+        for lin in self.state_encoder.layers:
+            h = A.linear(h, lin.weight, lin.bias, ACT_LRELU)
+        wlat = h
+        # ---- image encoder; the 3-channel image is zero-padded to 64 channels so the stem is a
+        # regular tensor-core conv with a regular weight gradient
+        x0 = torch.zeros(B, H, W, 64, dtype=bf, device=dev)
+        x0[..., :3] = image.permute(0, 2, 3, 1)
+        enc = self.image_encoder
+        e1, mr = conv_in(x0, enc.conv1, weight=F.pad(enc.conv1.weight, (0, 0, 0, 0, 0, 61)))
+        f = {1: A.mat_norm(e1, mr)}
+        e2, mr = conv_in(f[1], enc.conv2, stride=2)
+        f[2] = A.mat_norm(e2, mr)
+        e3, mr = conv_in(f[2], enc.conv3, stride=2)
+        f[4] = A.mat_norm(e3, mr)
+        # ---- merged mlp_shared convs
+        groups = {4: [], 2: [], 1: []}
+        for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
+            for name, m in blk.mats():
+                groups[ds].append((bi, name, m))
+        hs = {}
+        for ds, mats in groups.items():
+            sw = torch.cat([m.mlp_shared.weight for _, _, m in mats], dim=0)
+            sb = torch.cat([m.mlp_shared.bias for _, _, m in mats], dim=0)
+            hcat, _ = conv_in(f[ds], None, act=ACT_RELU, want_stats=False, weight=sw, bias=sb)
+            for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
+                hs[(bi, name)] = hsl
+
+        def mat(bi, name, m, xin, mr_in, up, act):
+            a = torch.sigmoid(m.blend_gamma)
+            c = torch.sigmoid(m.blend_beta)
+            gs = A.linear(wlat, m.fc_gamma.weight * a, m.fc_gamma.bias * a)
+            bs = A.linear(wlat, m.fc_beta.weight * c, m.fc_beta.bias * c)
+            gbw = torch.cat([m.mlp_gamma.weight * (1 - a), m.mlp_beta.weight * (1 - c)], dim=0)
+            gbb = torch.cat([m.mlp_gamma.bias * (1 - a), m.mlp_beta.bias * (1 - c)], dim=0)
+            gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb)
+            return A.mat_norm(xin, mr_in, gs, bs, gb, up, act)
+
+        x, mr_x = conv_in(f[4], self.head)
+        cur = 4
+        nblk = len(self.RES_OF_BLOCK)
+        for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
+            up = cur // ds
+            cur = ds
+            last = bi == nblk - 1
+            if blk.learned_shortcut:
+                t = mat(bi, "norm_s", blk.norm_s, x, mr_x, up, ACT_NONE)
+                xs, _ = conv_in(t, blk.conv_s, want_stats=False)
+            else:
+                xs = x
+            t = mat(bi, "norm_0", blk.norm_0, x, mr_x, up, ACT_LRELU)
+            dx, mr_dx = conv_in(t, blk.conv_0)
+            t = mat(bi, "norm_1", blk.norm_1, dx, mr_dx, 1, ACT_LRELU)
+            x, mr_x = conv_in(t, blk.conv_1, act=ACT_LRELU if last else ACT_NONE, residual=xs, want_stats=not last)
+        # ToRGB: 3 output channels zero-padded to 64 so it runs (and differentiates) on the igemm kernels
+        wi = F.pad(self.conv_img.weight, (0, 0, 0, 0, 0, 0, 0, 61))
+        bi_ = F.pad(self.conv_img.bias, (0, 61))
+        rgb, _ = conv_in(x, None, want_stats=False, weight=wi, bias=bi_)
+        return torch.tanh(rgb[..., :3].float()).permute(0, 3, 1, 2).contiguous()
 
     def forward_u8(self, frames_u8_nhwc, state):
         """dataset-facing variant: uint8 HWC frames in, uint8 HWC frames out

@@ -164,6 +164,33 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
     return out
 
 
+def mat_norm_bwd(dy, x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, add=None):
+    """backward of mat_norm: returns (dx [B,H/up,W/up,C] bf16 (+add), d_gb [B,H,W,2C] bf16 or None,
+    sums [B,C,4] fp32 = (d gs, d bs, S1, S2))."""
+    _require_cuda(dy, x, mean_rstd, gs, bs, gb_spatial, add)
+    b, h, w, c = dy.shape
+    hx, wx = h // up, w // up
+    if tuple(x.shape) != (b, hx, wx, c):
+        raise RuntimeError("mat_norm_bwd: x shape mismatch")
+    dev = dy.device
+    lib = _lib.load()
+    chunks = int(lib.s2p_mat_norm_bwd_chunks(b, h, w, c))
+    d_gb = torch.empty(b, h, w, 2 * c, dtype=torch.bfloat16, device=dev) if gb_spatial is not None else None
+    dxh = torch.empty(b, h, w, c, dtype=torch.bfloat16, device=dev)
+    partial = torch.empty(b, chunks, c, 4, dtype=torch.float32, device=dev)
+    sums = torch.empty(b, c, 4, dtype=torch.float32, device=dev)
+    dx = torch.empty(b, hx, wx, c, dtype=torch.bfloat16, device=dev)
+    gpitch = gs.stride(0) if gs is not None else 0
+    _lib.check(
+        lib.s2p_mat_norm_bwd(
+            dy.data_ptr(), _nhwc_pitch(dy, "dy"), x.data_ptr(), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs),
+            _ptr(bs), gpitch, _ptr(gb_spatial), 0 if gb_spatial is None else _nhwc_pitch(gb_spatial, "gb"), act,
+            _ptr(d_gb), 2 * c, dxh.data_ptr(), c, partial.data_ptr(), sums.data_ptr(), _ptr(add),
+            0 if add is None else _nhwc_pitch(add, "add"), dx.data_ptr(), c, b, h, w, c, _stream()),
+        "s2p_mat_norm_bwd")
+    return dx, d_gb, sums
+
+
 def mat_fused_ct(c: int) -> int:
     return int(_lib.load().s2p_mat_fused_ct(c))
 

@@ -32,7 +32,7 @@ def _pair(pkg, env, init):
     ora = common.build_oracle(env, init)
     net = pkg.define_G(pkg.make_options(env_type=env, gpu_ids="0"))
     net.load_state_dict(ora.state_dict())
-    return ora, net
+    return ora, net.eval()
 
 
 @pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2"])
@@ -132,6 +132,7 @@ def test_fused_and_unfused_mat_agree(pkg):
     ora, net = _pair(pkg, "cheetah", "scaled")
     net2 = pkg.define_G(pkg.make_options(env_type="cheetah", gpu_ids="0", fuse_mat=False))
     net2.load_state_dict(ora.state_dict())
+    net2.eval()
     image, states = common.make_inputs("cheetah", 2, 1)
     a = net(image.cuda(), states[:, 0].cuda()).cpu()
     b = net2(image.cuda(), states[:, 0].cuda()).cpu()
