@@ -50,12 +50,13 @@ long long s2p_launch_count(void);
  * y = act(conv(x, w) + bias + residual); optionally emits per-image per-channel
  * (sum, sumsq) partials of the STORED bf16 values for the following instance norm:
  * stats_partial is [B][s2p_conv_stats_rows(Hout,Wout)][Cout][2] fp32.
- * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in {1,3}, stride in {1,2}. */
+ * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in 1..4 (3x3/1x1: generator; 4x4: discriminator),
+ * stride in {1,2}, explicit symmetric zero padding `pad` (nn.Conv2d padding). */
 int s2p_conv_stats_rows(int Hout, int Wout);
 int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
                        const void* residual, int res_pitch, void* y, int y_pitch,
                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
-                       int stride, int act, void* stream);
+                       int stride, int pad, int act, void* stream);
 
 /* ---- (a8) weight gradient of the convolution (training) -----------------------------
  * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]
@@ -150,6 +151,10 @@ int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S
                        void* stream);
 int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
                    int y_pitch, int B, int K, int N, int act, void* stream);
+
+/* ---- (a8) optimiser: torch.optim.Adam's update on fp32 tensors, one fused pass ------------ */
+int s2p_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                  float beta1, float beta2, float eps, int step, void* stream);
 
 #ifdef __cplusplus
 }

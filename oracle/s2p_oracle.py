@@ -307,3 +307,111 @@ if __name__ == "__main__":
     m = flops_per_frame()
     for k, v in m.items():
         print(f"{k:12s} {v / 1e9:8.3f} GMAC")
+
+
+# ======================================================================================
+# ORACLE_SPEC v1.1 -- training side, BUILDER-DEFINED like the
+# generator above (the reference's train.py, discriminator and losses are absent from the
+# snapshot; semantics from rebuttal.md:71,131-135,188 "L1 + GAN + perceptual" and the SPADE
+# lineage README.md:72-75).  v1.1 only ADDS classes; the generator spec is unchanged.
+#
+#   NLayerDiscriminator(input_nc=6): conv4x4 s2 p2 (6->64) + LReLU(0.2)
+#       conv4x4 s2 p2 (64->128) + IN + LReLU ; conv4x4 s2 p2 (128->256) + IN + LReLU
+#       conv4x4 s1 p2 (256->512) + IN + LReLU ; conv4x4 s1 p2 (512->1)
+#       forward returns the 5 intermediate outputs (the last one = patch logits)
+#   MultiscaleDiscriminator(num_D=2): D_0 on the input, D_1 on AvgPool2d(3, 2, 1,
+#       count_include_pad=False)(input); input = cat(prev_image, image) on channels
+#   losses: hinge GAN (D: mean relu(1 - D(real)) + mean relu(1 + D(fake)); G: -mean D(fake)),
+#       averaged over scales; feature matching L1 over the intermediate outputs (lambda 10,
+#       / num_D); L1(fake, real) * lambda_l1 (10).  The VGG19 perceptual term of the paper
+#       needs ImageNet weights (not available offline): lambda_vgg = 0 in this spec.
+#   optimiser: Adam(lr 2e-4, betas (0.0, 0.9)) for G and for D (SPADE TTUR off).
+# ======================================================================================
+class NLayerDiscriminator(nn.Module):
+    def __init__(self, input_nc=6, ndf=64, n_layers=4):
+        super().__init__()
+        kw, padw = 4, 2
+        nf = ndf
+        seq = [[nn.Conv2d(input_nc, nf, kw, 2, padw), nn.LeakyReLU(0.2)]]
+        for n in range(1, n_layers):
+            nf_prev, nf = nf, min(nf * 2, 512)
+            stride = 1 if n == n_layers - 1 else 2
+            seq.append([nn.Conv2d(nf_prev, nf, kw, stride, padw), nn.InstanceNorm2d(nf, eps=1e-5, affine=False),
+                        nn.LeakyReLU(0.2)])
+        seq.append([nn.Conv2d(nf, 1, kw, 1, padw)])
+        for i, layers in enumerate(seq):
+            self.add_module(f"model{i}", nn.Sequential(*layers))
+        self.n_models = len(seq)
+
+    def forward(self, x):
+        feats = []
+        for i in range(self.n_models):
+            x = getattr(self, f"model{i}")(x)
+            feats.append(x)
+        return feats
+
+
+class MultiscaleDiscriminator(nn.Module):
+    def __init__(self, opt=None, input_nc=6, ndf=64, n_layers=4, num_D=2):
+        super().__init__()
+        self.num_D = num_D
+        for i in range(num_D):
+            self.add_module(f"discriminator_{i}", NLayerDiscriminator(input_nc, ndf, n_layers))
+        init_weights(self, getattr(opt, "init_type", "xavier") if opt is not None else "xavier",
+                     getattr(opt, "init_variance", 0.02) if opt is not None else 0.02)
+
+    def forward(self, x):
+        out = []
+        for i in range(self.num_D):
+            out.append(getattr(self, f"discriminator_{i}")(x))
+            x = F.avg_pool2d(x, 3, 2, 1, count_include_pad=False)
+        return out
+
+
+def define_D(opt=None):
+    return MultiscaleDiscriminator(opt)
+
+
+LAMBDA_FEAT = 10.0
+LAMBDA_L1 = 10.0
+ADAM = dict(lr=2e-4, betas=(0.0, 0.9))
+
+
+def hinge_d_loss(pred_real, pred_fake):
+    loss = 0.0
+    for r, f in zip(pred_real, pred_fake):
+        loss = loss + F.relu(1.0 - r[-1]).mean() + F.relu(1.0 + f[-1]).mean()
+    return loss / len(pred_real)
+
+
+def generator_losses(pred_fake, pred_real, fake, real):
+    """dict of the G-step loss terms (SPADE Pix2PixModel.compute_generator_loss shape)."""
+    num_d = len(pred_fake)
+    gan = sum(-f[-1].mean() for f in pred_fake) / num_d
+    feat = 0.0
+    for f, r in zip(pred_fake, pred_real):
+        for a, b in zip(f[:-1], r[:-1]):
+            feat = feat + F.l1_loss(a, b.detach()) * LAMBDA_FEAT / num_d
+    return {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+
+
+def training_step(netG, netD, optG, optD, prev_image, state, real_image):
+    """one G step then one D step (SPADE Pix2PixTrainer order); returns (g_losses, d_loss, fake)."""
+    fake = netG(prev_image, state)
+    pred = netD(torch.cat([torch.cat([prev_image, fake], 1), torch.cat([prev_image, real_image], 1)], 0))
+    pred_fake = [[t[: t.shape[0] // 2] for t in p] for p in pred]
+    pred_real = [[t[t.shape[0] // 2:] for t in p] for p in pred]
+    g_losses = generator_losses(pred_fake, pred_real, fake, real_image)
+    optG.zero_grad(set_to_none=True)
+    sum(g_losses.values()).backward()
+    optG.step()
+    with torch.no_grad():
+        fake_d = fake.detach()
+    pred = netD(torch.cat([torch.cat([prev_image, fake_d], 1), torch.cat([prev_image, real_image], 1)], 0))
+    pred_fake = [[t[: t.shape[0] // 2] for t in p] for p in pred]
+    pred_real = [[t[t.shape[0] // 2:] for t in p] for p in pred]
+    d_loss = hinge_d_loss(pred_real, pred_fake)
+    optD.zero_grad(set_to_none=True)
+    d_loss.backward()
+    optD.step()
+    return g_losses, d_loss, fake_d

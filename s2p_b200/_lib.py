@@ -22,7 +22,7 @@ SIGNATURES = {
     "s2p_last_error_string": (C.c_char_p, []),
     "s2p_launch_count": (C.c_longlong, []),
     "s2p_conv_stats_rows": (_i, [_i, _i]),
-    "s2p_conv_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2p_conv_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_conv_wgrad_workspace_bytes": (C.c_longlong, [_i, _i, _i, _i, _i, _i, _i, _i]),
     "s2p_conv_wgrad": (_i, [_vp, _i, _vp, _i, _vp, _vp, C.c_longlong, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_pack_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp]),
@@ -38,6 +38,7 @@ SIGNATURES = {
     "s2p_stem_conv_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
     "s2p_torgb_tanh_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_torgb_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_adam_step": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _i, _vp]),
     "s2p_pos_encode_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }

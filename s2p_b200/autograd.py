@@ -28,19 +28,20 @@ class ConvFn(torch.autograd.Function):
     """y = act(conv(x, W) + b + residual); x, residual, y NHWC bf16; W fp32 OIHW, b fp32."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, stride, act, stats):
+    def forward(ctx, x, weight, bias, residual, stride, act, stats, pad):
         cout, cin, k, _ = weight.shape
+        pad = k // 2 if pad is None else pad
         wp = ops.pack_conv_weight(weight)
         y = ops.conv_igemm(x, wp, None if bias is None else bias.detach().float().contiguous(), cout, k, stride, act,
-                           residual, None, stats)
+                           residual, None, stats, pad)
         ctx.save_for_backward(x, weight, y if act != ACT_NONE else None)
-        ctx.cfg = (k, stride, act, bias is not None, residual is not None)
+        ctx.cfg = (k, stride, act, bias is not None, residual is not None, pad)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, weight, y = ctx.saved_tensors
-        k, stride, act, has_bias, has_res = ctx.cfg
+        k, stride, act, has_bias, has_res, pad = ctx.cfg
         dy = dy.contiguous()
         if act != ACT_NONE:
             dy = _act_grad(dy, y, act)
@@ -52,20 +53,21 @@ class ConvFn(torch.autograd.Function):
             g = dy
             if stride == 2:   # transposed conv: zero-insert the gradient, then a stride-1 conv
                 b, ho, wo, _ = dy.shape
-                g = torch.zeros(b, x.shape[1], x.shape[2], cout, dtype=dy.dtype, device=dy.device)
+                g = torch.zeros(b, x.shape[1] + 2 * pad - k + 1, x.shape[2] + 2 * pad - k + 1, cout, dtype=dy.dtype,
+                                device=dy.device)
                 g[:, 0:2 * ho:2, 0:2 * wo:2] = dy
-            dx = ops.conv_igemm(g, ops.pack_conv_weight(wt), None, cin, k, 1, ACT_NONE)
+            dx = ops.conv_igemm(g, ops.pack_conv_weight(wt), None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
         if ctx.needs_input_grad[1]:
-            dw = ops.conv_wgrad(x, dy, k, stride)
+            dw = ops.conv_wgrad(x, dy, k, stride, pad)
         if has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum(dim=(0, 1, 2))
         if has_res and ctx.needs_input_grad[3]:
             dres = dy
-        return dx, dw, db, dres, None, None, None
+        return dx, dw, db, dres, None, None, None, None
 
 
-def conv(x, weight, bias=None, residual=None, stride=1, act=ACT_NONE, stats=None):
-    return ConvFn.apply(x, weight, bias, residual, stride, act, stats)
+def conv(x, weight, bias=None, residual=None, stride=1, act=ACT_NONE, stats=None, pad=None):
+    return ConvFn.apply(x, weight, bias, residual, stride, act, stats, pad)
 
 
 class MatNormFn(torch.autograd.Function):

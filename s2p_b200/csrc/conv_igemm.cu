@@ -568,10 +568,9 @@ namespace s2p {
 // Shared host path of the two conv entry points: validates the GEMM geometry, builds the
 // two tensor maps and launches.  `p` arrives with the epilogue fields already filled.
 static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B, int Hin, int Win, int Cin,
-                         int Cout, int ksize, int stride, int block_n, int epi, ConvParams p, void* stream) {
+                         int Cout, int ksize, int stride, int pad, int block_n, int epi, ConvParams p, void* stream) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-  const int pad = ksize / 2;
   {
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("S2P_CONV_DEBUG"); dbg = e ? atoi(e) : 0; }
@@ -636,13 +635,14 @@ static inline bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t
 extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
                                   const void* residual, int res_pitch, void* y, int y_pitch,
                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
-                                  int ksize, int stride, int act, void* stream) {
+                                  int ksize, int stride, int pad, int act, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
   S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
   S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
   S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
-  S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(ksize >= 1 && ksize <= 4, "conv: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(pad >= 0 && pad < ksize && Hin + 2 * pad >= ksize && Win + 2 * pad >= ksize, "conv: pad=%d", pad);
   S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
   S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
   S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
@@ -657,7 +657,7 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
   p.out = static_cast<__nv_bfloat16*>(y);
   p.stats_partial = stats_partial;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
-  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, block_n, kEpiPlain, p, stream);
+  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream);
 }
 
 extern "C" int s2p_mat_fused_ct(int C) { return C >= 128 ? 128 : C; }
@@ -685,7 +685,7 @@ extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_
   p.mat_tab = reinterpret_cast<const float4*>(mod_table);
   p.mat_x_pitch = x_pitch; p.mat_up = up; p.mat_C = C;
   const int block_n = 2 * s2p_mat_fused_ct(C);
-  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, block_n, kEpiMat, p, stream);
+  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, ksize / 2, block_n, kEpiMat, p, stream);
 }
 
 extern "C" int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, const float* bias,
@@ -702,5 +702,5 @@ extern "C" int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_pac
   p.bias = bias;
   p.rgb_f32 = out_f32_nchw;
   p.rgb_u8 = out_u8_nhwc;
-  return conv_dispatch(x, x_pitch, w_packed16, B, H, W, Cin, 16, 3, 1, 16, kEpiToRGB, p, stream);
+  return conv_dispatch(x, x_pitch, w_packed16, B, H, W, Cin, 16, 3, 1, 1, 16, kEpiToRGB, p, stream);
 }

@@ -92,7 +92,36 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat
   }
 }
 
+// torch.optim.Adam update (no weight decay, no amsgrad), fp32 master parameters
+__global__ void adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
+                                 float bc1, float bc2_sqrt) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] -= (lr / bc1) * (mi / denom);
+  }
+}
+
 }  // namespace s2p
+
+extern "C" int s2p_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                             float lr, float beta1, float beta2, float eps, int step, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && n > 0 && step >= 1, "adam_step: bad args");
+  const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
+  const float bc2 = 1.f - powf(beta2, static_cast<float>(step));
+  const int blocks = static_cast<int>((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+  adam_step_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
+                                                                         beta2, eps, bc1, sqrtf(bc2));
+  count_launch();
+  return check_launch("adam_step_kernel");
+}
 
 extern "C" int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S, int n_freqs,
                                   void* stream) {

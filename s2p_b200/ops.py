@@ -59,12 +59,12 @@ def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scal
     return out
 
 
-def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None):
+def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None, pad=None):
     """y = act(conv(x) + bias + residual); returns y.  ``stats`` (fp32
     [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given."""
     _require_cuda(x, w_packed, bias, residual, out, stats)
     b, hin, win, cin = x.shape
-    pad = ksize // 2
+    pad = ksize // 2 if pad is None else pad
     hout = (hin + 2 * pad - ksize) // stride + 1
     wout = (win + 2 * pad - ksize) // stride + 1
     if out is None:
@@ -87,7 +87,7 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
     _lib.check(
         _lib.load().s2p_conv_igemm_fwd(
             x.data_ptr(), _nhwc_pitch(x, "x"), w_packed.data_ptr(), _ptr(bias), _ptr(residual), res_pitch,
-            out.data_ptr(), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout, ksize, stride, act,
+            out.data_ptr(), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout, ksize, stride, pad, act,
             _stream()),
         "s2p_conv_igemm_fwd")
     return out
@@ -331,3 +331,14 @@ def linear(x, w, bias, act=ACT_NONE, out=None):
     _lib.check(_lib.load().s2p_linear_fwd(x.data_ptr(), x.stride(0), w.data_ptr(), _ptr(bias), out.data_ptr(),
                                           out.stride(0), b, k, n, act, _stream()), "s2p_linear_fwd")
     return out
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):
+    """in-place torch.optim.Adam update of one fp32 tensor"""
+    _require_cuda(param, grad, exp_avg, exp_avg_sq)
+    g = grad.contiguous().float()
+    if param.dtype != torch.float32 or not param.is_contiguous():
+        raise RuntimeError("adam_step: parameters must be contiguous fp32")
+    _lib.check(_lib.load().s2p_adam_step(param.data_ptr(), g.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+                                         param.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
+                                         _stream()), "s2p_adam_step")

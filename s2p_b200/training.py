@@ -1,0 +1,130 @@
+"""GAN training step of train.py --netG=s2p (README.md:59): one generator step (L1 + hinge GAN +
+feature matching; rebuttal.md:71,131-135) then one discriminator step, SPADE Pix2PixTrainer order.
+Mirrors oracle/s2p_oracle.py `training_step` (ORACLE_SPEC v1.1) term by term.
+
+Multi-GPU (BASELINE configs[4]): one process per GPU, data parallel; after each backward the
+gradients are all-reduced (NCCL, flat buckets) and averaged.  Parameters are updated by the
+repo's fused Adam kernel (fp32 master weights, torch.optim.Adam arithmetic)."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from . import ops
+
+LAMBDA_FEAT = 10.0
+LAMBDA_L1 = 10.0
+
+
+class FusedAdam:
+    """Adam(lr, betas, eps) with torch.optim.Adam's update rule, one fused kernel per tensor."""
+
+    def __init__(self, params, lr=2e-4, betas=(0.0, 0.9), eps=1e-8):
+        self.params = [p for p in params if p.requires_grad]
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.step_count = 0
+        self.m = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
+        self.v = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
+
+    def zero_grad(self, set_to_none=True):
+        for p in self.params:
+            p.grad = None
+
+    @torch.no_grad()
+    def step(self):
+        self.step_count += 1
+        for p, m, v in zip(self.params, self.m, self.v):
+            if p.grad is None:
+                continue
+            ops.adam_step(p, p.grad, m, v, self.lr, self.betas[0], self.betas[1], self.eps, self.step_count)
+
+
+def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
+    """average .grad over ranks: flat fp32 buckets, one NCCL all-reduce each."""
+    import torch.distributed as dist
+    grads = [p.grad for p in params if p.grad is not None]
+    i = 0
+    while i < len(grads):
+        j, n = i, 0
+        while j < len(grads) and (n == 0 or n + grads[j].numel() <= bucket_elems):
+            n += grads[j].numel()
+            j += 1
+        flat = torch.cat([g.reshape(-1) for g in grads[i:j]])
+        dist.all_reduce(flat)
+        flat.mul_(1.0 / world_size)
+        off = 0
+        for g in grads[i:j]:
+            g.copy_(flat[off:off + g.numel()].view_as(g))
+            off += g.numel()
+        i = j
+
+
+def _split(pred):
+    fake = [[t[: t.shape[0] // 2] for t in p] for p in pred]
+    real = [[t[t.shape[0] // 2:] for t in p] for p in pred]
+    return fake, real
+
+
+def hinge_d_loss(pred_real, pred_fake):
+    loss = 0.0
+    for r, f in zip(pred_real, pred_fake):
+        loss = loss + F.relu(1.0 - r[-1].float()).mean() + F.relu(1.0 + f[-1].float()).mean()
+    return loss / len(pred_real)
+
+
+def generator_losses(pred_fake, pred_real, fake, real):
+    num_d = len(pred_fake)
+    gan = sum(-f[-1].float().mean() for f in pred_fake) / num_d
+    feat = 0.0
+    for f, r in zip(pred_fake, pred_real):
+        for a, b in zip(f[:-1], r[:-1]):
+            feat = feat + F.l1_loss(a.float(), b.detach().float()) * LAMBDA_FEAT / num_d
+    return {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+
+
+class S2PTrainer:
+    """run_generator_one_step / run_discriminator_one_step, as SPADE's Pix2PixTrainer."""
+
+    def __init__(self, netG, netD, lr=2e-4, betas=(0.0, 0.9), world_size=1):
+        self.netG, self.netD = netG, netD
+        self.optG = FusedAdam(netG.parameters(), lr, betas)
+        self.optD = FusedAdam(netD.parameters(), lr, betas)
+        self.world_size = world_size
+        self.fake = None
+
+    def _d(self, prev, fake, real):
+        return _split(self.netD(torch.cat([torch.cat([prev, fake], 1), torch.cat([prev, real], 1)], 0)))
+
+    def run_generator_one_step(self, prev_image, state, real_image):
+        self.netG.train()
+        fake = self.netG(prev_image, state)
+        pred_fake, pred_real = self._d(prev_image, fake, real_image)
+        losses = generator_losses(pred_fake, pred_real, fake, real_image)
+        self.optG.zero_grad()
+        self.optD.zero_grad()
+        sum(losses.values()).backward()
+        if self.world_size > 1:
+            allreduce_gradients(self.optG.params, self.world_size)
+        self.optG.step()
+        self.fake = fake.detach()
+        return losses
+
+    def run_discriminator_one_step(self, prev_image, state, real_image):
+        if self.fake is None:
+            with torch.no_grad():
+                self.netG.eval()
+                self.fake = self.netG(prev_image, state)
+        pred_fake, pred_real = self._d(prev_image, self.fake, real_image)
+        loss = hinge_d_loss(pred_real, pred_fake)
+        self.optD.zero_grad()
+        loss.backward()
+        if self.world_size > 1:
+            allreduce_gradients(self.optD.params, self.world_size)
+        self.optD.step()
+        self.fake = None
+        return loss
+
+    def train_step(self, prev_image, state, real_image):
+        g = self.run_generator_one_step(prev_image, state, real_image)
+        d = self.run_discriminator_one_step(prev_image, state, real_image)
+        return g, d
