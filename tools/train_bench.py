@@ -1,0 +1,77 @@
+"""Times the GAN training step (BASELINE configs[1]/[4]) on one GPU: this repo's S2PTrainer and,
+for context, the fp32 oracle through eager PyTorch (cuDNN/cuBLAS).
+usage: python tools/train_bench.py [--batch 16] [--steps 5] [--profile] [--no-oracle]"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    sys.path.insert(0, p)
+import torch
+
+import s2p_b200
+from s2p_b200 import _lib
+from s2p_b200.training import S2PTrainer
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--batch", type=int, default=16)
+ap.add_argument("--steps", type=int, default=5)
+ap.add_argument("--warmup", type=int, default=3)
+ap.add_argument("--env", type=str, default="walker")
+ap.add_argument("--profile", action="store_true")
+ap.add_argument("--no-oracle", action="store_true")
+a = ap.parse_args()
+B = a.batch
+torch.manual_seed(1234)
+opt = s2p_b200.make_options(env_type=a.env, gpu_ids="0", init_type="scaled")
+nG, nD = s2p_b200.define_G(opt), s2p_b200.define_D(opt)
+tr = S2PTrainer(nG, nD)
+g = torch.Generator().manual_seed(0)
+prev = (torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).cuda()
+real = (torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).cuda()
+state = torch.randn(B, opt.state_dim, generator=g).cuda()
+
+
+def timed(fn, steps, warm):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+l0 = _lib.launch_count()
+ms = timed(lambda: tr.train_step(prev, state, real), a.steps, a.warmup)
+launches = (_lib.launch_count() - l0) / (a.steps + a.warmup)
+print(f"s2p_b200 train step: batch={B} {ms:.2f} ms/step  {B / ms * 1e3:.1f} frames/s  ({launches:.0f} own kernel launches/step)")
+if a.profile:
+    from torch.profiler import profile, ProfilerActivity
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        tr.train_step(prev, state, real)
+        torch.cuda.synchronize()
+    print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=70))
+if not a.no_oracle:
+    import s2p_oracle as O
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    oG = O.define_G(O.make_options(env_type=a.env, init_type="scaled")).cuda().train()
+    oD = O.define_D(O.make_options(init_type="scaled")).cuda()
+    optG = torch.optim.Adam(oG.parameters(), **O.ADAM)
+    optD = torch.optim.Adam(oD.parameters(), **O.ADAM)
+    ms_o = timed(lambda: O.training_step(oG, oD, optG, optD, prev, state, real), max(2, a.steps // 2), 2)
+    print(f"oracle eager PyTorch (TF32 cuDNN): {ms_o:.2f} ms/step  {B / ms_o * 1e3:.1f} frames/s")
+
+    def amp_step():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            return O.training_step(oG, oD, optG, optD, prev, state, real)
+    try:
+        ms_a = timed(amp_step, max(2, a.steps // 2), 2)
+        print(f"oracle eager PyTorch (bf16 autocast): {ms_a:.2f} ms/step  {B / ms_a * 1e3:.1f} frames/s")
+    except Exception as e:  # noqa: BLE001
+        print("bf16 autocast oracle failed:", repr(e)[:200])
