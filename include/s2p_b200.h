@@ -152,9 +152,23 @@ int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S
 int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
                    int y_pitch, int B, int K, int N, int act, void* stream);
 
+/* packed weight of the data-gradient convolution: dst[ci][R-1-r][S-1-s][co] = w[co][ci][r][s]
+ * (bf16 rows of R*S*Cout), so dX = s2p_conv_igemm_fwd(dY (zero-inserted when stride 2), dst,
+ * pad = k-1-pad) -- replaces autograd's conv backward w.r.t. the input. */
+int s2p_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S, void* stream);
+/* dy_out = dy * act'(y) (act from the ACTIVATED output y; skipped when act == 0) and
+ * bias_grad[c] = sum over `rows` pixels of dy_out[:, c]; partial: fp32 scratch of
+ * s2p_act_bwd_bias_grad_chunks() * C floats; bias_grad/partial may both be NULL. */
+int s2p_act_bwd_bias_grad_chunks(void);
+int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y, int y_pitch, int act, void* dy_out,
+                          int out_pitch, float* bias_grad, float* partial, long long rows, int C, void* stream);
+
 /* ---- (a8) optimiser: torch.optim.Adam's update on fp32 tensors, one fused pass ------------ */
 int s2p_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);
+/* same update with the step count read from device memory (CUDA-graph replayable) */
+int s2p_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                      float beta1, float beta2, float eps, const int* step_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -39,6 +39,10 @@ SIGNATURES = {
     "s2p_torgb_tanh_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_torgb_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_adam_step": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _i, _vp]),
+    "s2p_adam_step_dev": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _vp, _vp]),
+    "s2p_pack_conv_weight_dgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_act_bwd_bias_grad_chunks": (_i, []),
+    "s2p_act_bwd_bias_grad": (_i, [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _vp, C.c_longlong, _i, _vp]),
     "s2p_pos_encode_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }

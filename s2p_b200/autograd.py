@@ -43,24 +43,22 @@ class ConvFn(torch.autograd.Function):
         x, weight, y = ctx.saved_tensors
         k, stride, act, has_bias, has_res, pad = ctx.cfg
         dy = dy.contiguous()
-        if act != ACT_NONE:
-            dy = _act_grad(dy, y, act)
-        dx = dw = db = dres = None
+        want_db = has_bias and ctx.needs_input_grad[2]
+        # activation gradient and bias gradient in one pass over dy
+        dy, db = ops.act_bwd_bias_grad(dy, y, act, want_db)
+        dx = dw = dres = None
         if ctx.needs_input_grad[0]:
             cout, cin = weight.shape[0], weight.shape[1]
             # dgrad = the same implicit GEMM with the filter flipped and in/out channels swapped
-            wt = weight.detach().flip(2, 3).transpose(0, 1).contiguous()
             g = dy
             if stride == 2:   # transposed conv: zero-insert the gradient, then a stride-1 conv
                 b, ho, wo, _ = dy.shape
                 g = torch.zeros(b, x.shape[1] + 2 * pad - k + 1, x.shape[2] + 2 * pad - k + 1, cout, dtype=dy.dtype,
                                 device=dy.device)
                 g[:, 0:2 * ho:2, 0:2 * wo:2] = dy
-            dx = ops.conv_igemm(g, ops.pack_conv_weight(wt), None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
+            dx = ops.conv_igemm(g, ops.pack_conv_weight_dgrad(weight), None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
         if ctx.needs_input_grad[1]:
             dw = ops.conv_wgrad(x, dy, k, stride, pad)
-        if has_bias and ctx.needs_input_grad[2]:
-            db = dy.float().sum(dim=(0, 1, 2))
         if has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None, None

@@ -1,0 +1,156 @@
+// Small training-path kernels: the pieces of the conv backward that are
+// not GEMMs, and the optimiser update.
+//   pack_conv_weight_dgrad : OIHW fp32 -> the packed weight of the data-gradient conv
+//                            (filter flipped, in/out channels swapped) in one pass
+//   act_bwd_bias_grad      : dy' = dy * act'(y) (ReLU / LeakyReLU(0.2), from the activated
+//                            output) and db[c] = sum_pixels dy'[pix, c], one read of dy / y,
+//                            fixed-order two-stage column reduction (bit-stable)
+//   adam_step (device step): torch.optim.Adam's update with the step count read from device
+//                            memory, so a captured CUDA graph of the whole step stays valid
+#include "ptx.cuh"
+#include "s2p_internal.h"
+
+namespace s2p {
+
+__global__ void pack_conv_weight_dgrad_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Cout,
+                                              int Cin, int R, int S) {
+  // dst[ci][r'][s'][co] = w[co][ci][R-1-r'][S-1-s']
+  const long long total = static_cast<long long>(Cout) * Cin * R * S;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int co = static_cast<int>(i % Cout);
+    long long t = i / Cout;
+    const int s = static_cast<int>(t % S); t /= S;
+    const int r = static_cast<int>(t % R);
+    const int ci = static_cast<int>(t / R);
+    dst[i] = __float2bfloat16_rn(w[((static_cast<long long>(co) * Cin + ci) * R + (R - 1 - r)) * S + (S - 1 - s)]);
+  }
+}
+
+__device__ __forceinline__ void unpack8f(const uint4& u, float (&f)[8]) {
+  f[0] = bf16_lo(u.x); f[1] = bf16_hi(u.x); f[2] = bf16_lo(u.y); f[3] = bf16_hi(u.y);
+  f[4] = bf16_lo(u.z); f[5] = bf16_hi(u.z); f[6] = bf16_lo(u.w); f[7] = bf16_hi(u.w);
+}
+
+// blockDim = (C/8, PY); grid = chunks of rows.  partial[chunk][C]
+__global__ void __launch_bounds__(256)
+act_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, const __nv_bfloat16* __restrict__ y,
+                      int y_pitch, int act, __nv_bfloat16* __restrict__ out, int out_pitch,
+                      float* __restrict__ partial, long long rows, int C, long long rows_per_cta) {
+  extern __shared__ float red[];   // [PY][C]
+  const int c0 = threadIdx.x * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  const long long r0 = blockIdx.x * rows_per_cta;
+  const long long r1 = (r0 + rows_per_cta < rows) ? r0 + rows_per_cta : rows;
+  for (long long r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
+    float d[8];
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(dy + r * dy_pitch + c0)), d);
+    if (act != 0) {
+      float v[8];
+      unpack8f(__ldg(reinterpret_cast<const uint4*>(y + r * y_pitch + c0)), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = v[j] > 0.f ? d[j] : (act == 2 ? 0.2f * d[j] : 0.f);
+      *reinterpret_cast<uint4*>(out + r * out_pitch + c0) =
+          make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]), pack_bf16x2(d[6], d[7]));
+      // the sum must be over the values as stored (bf16), like the tensor the wgrad kernel reads
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = __bfloat162float(__float2bfloat16_rn(d[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += d[j];
+  }
+  if (partial == nullptr) return;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y * C + c0 + j] = acc[j];
+  __syncthreads();
+  for (int c = threadIdx.y * blockDim.x + threadIdx.x; c < C; c += blockDim.x * blockDim.y) {
+    float s = 0.f;
+    for (int k = 0; k < static_cast<int>(blockDim.y); ++k) s += red[k * C + c];
+    partial[static_cast<size_t>(blockIdx.x) * C + c] = s;
+  }
+}
+
+__global__ void colsum_finalize_kernel(const float* __restrict__ partial, int chunks, float* __restrict__ out, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0;
+  for (int k = 0; k < chunks; ++k) s += static_cast<double>(partial[static_cast<size_t>(k) * C + c]);
+  out[c] = static_cast<float>(s);
+}
+
+__global__ void adam_step_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                     float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
+                                     const int* __restrict__ step_dev) {
+  const float step = static_cast<float>(*step_dev);
+  const float bc1 = 1.f - powf(b1, step);
+  const float bc2_sqrt = sqrtf(1.f - powf(b2, step));
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= (lr / bc1) * (mi / (sqrtf(vi) / bc2_sqrt + eps));
+  }
+}
+
+static const int kColsumMaxChunks = 592;
+
+}  // namespace s2p
+
+extern "C" int s2p_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S,
+                                          void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(w_oihw && dst && Cout > 0 && Cin > 0 && R > 0 && S > 0, "pack_conv_weight_dgrad: bad args");
+  const long long total = static_cast<long long>(Cout) * Cin * R * S;
+  const int blocks = static_cast<int>((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+  pack_conv_weight_dgrad_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w_oihw, static_cast<__nv_bfloat16*>(dst), Cout, Cin, R, S);
+  count_launch();
+  return check_launch("pack_conv_weight_dgrad_kernel");
+}
+
+extern "C" int s2p_act_bwd_bias_grad_chunks(void) { return s2p::kColsumMaxChunks; }
+
+extern "C" int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y, int y_pitch, int act,
+                                     void* dy_out, int out_pitch, float* bias_grad, float* partial,
+                                     long long rows, int C, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy && rows > 0 && C > 0 && C % 8 == 0 && C <= 2048, "act_bwd_bias_grad: bad dims");
+  S2P_CHECK_ARG(act >= 0 && act <= 2, "act_bwd_bias_grad: act=%d", act);
+  S2P_CHECK_ARG(act == 0 || (y && dy_out), "act_bwd_bias_grad: y and dy_out are needed when act != 0");
+  S2P_CHECK_ARG((bias_grad == nullptr) == (partial == nullptr), "act_bwd_bias_grad: bias_grad/partial together");
+  S2P_CHECK_ARG(dy_pitch % 8 == 0 && y_pitch % 8 == 0 && out_pitch % 8 == 0, "act_bwd_bias_grad: pitch");
+  const int groups = C / 8;
+  int py = 256 / groups;
+  if (py < 1) py = 1;
+  long long chunks = (rows + py * 8 - 1) / (py * 8);
+  if (chunks > kColsumMaxChunks) chunks = kColsumMaxChunks;
+  const long long rpc = (rows + chunks - 1) / chunks;
+  chunks = (rows + rpc - 1) / rpc;
+  const size_t smem = static_cast<size_t>(py) * C * sizeof(float);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  act_bwd_colsum_kernel<<<static_cast<unsigned>(chunks), dim3(groups, py), smem, st>>>(
+      static_cast<const __nv_bfloat16*>(dy), dy_pitch, static_cast<const __nv_bfloat16*>(y), y_pitch, act,
+      static_cast<__nv_bfloat16*>(dy_out), out_pitch, partial, rows, C, rpc);
+  count_launch();
+  int rc = check_launch("act_bwd_colsum_kernel");
+  if (rc != S2P_OK || bias_grad == nullptr) return rc;
+  colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, static_cast<int>(chunks), bias_grad, C);
+  count_launch();
+  return check_launch("colsum_finalize_kernel");
+}
+
+extern "C" int s2p_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                                 float lr, float beta1, float beta2, float eps, const int* step_dev, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && step_dev && n > 0, "adam_step_dev: bad args");
+  const int blocks = static_cast<int>((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+  adam_step_dev_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr,
+                                                                             beta1, beta2, eps, step_dev);
+  count_launch();
+  return check_launch("adam_step_dev_kernel");
+}

@@ -393,11 +393,26 @@ class S2PGeneratorB200(nn.Module):
             for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
                 hs[(bi, name)] = hsl
 
+        # state heads of all MATs as ONE linear (blend factors folded into the rows), then split
+        all_mats = [(bi, name, m) for bi, blk in enumerate(self.blocks()) for name, m in blk.mats()]
+        hw, hb = [], []
+        for _, _, m in all_mats:
+            a = torch.sigmoid(m.blend_gamma)
+            c = torch.sigmoid(m.blend_beta)
+            hw += [m.fc_gamma.weight * a, m.fc_beta.weight * c]
+            hb += [m.fc_gamma.bias * a, m.fc_beta.bias * c]
+        gsbs_all = A.linear(wlat, torch.cat(hw, dim=0), torch.cat(hb, dim=0))
+        gsbs = {}
+        off = 0
+        for bi, name, m in all_mats:
+            C = m.norm_nc
+            gsbs[(bi, name)] = (gsbs_all[:, off:off + C], gsbs_all[:, off + C:off + 2 * C])
+            off += 2 * C
+
         def mat(bi, name, m, xin, mr_in, up, act):
             a = torch.sigmoid(m.blend_gamma)
             c = torch.sigmoid(m.blend_beta)
-            gs = A.linear(wlat, m.fc_gamma.weight * a, m.fc_gamma.bias * a)
-            bs = A.linear(wlat, m.fc_beta.weight * c, m.fc_beta.bias * c)
+            gs, bs = gsbs[(bi, name)]
             gbw = torch.cat([m.mlp_gamma.weight * (1 - a), m.mlp_beta.weight * (1 - c)], dim=0)
             gbb = torch.cat([m.mlp_gamma.bias * (1 - a), m.mlp_beta.bias * (1 - c)], dim=0)
             gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb)

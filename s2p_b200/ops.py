@@ -342,3 +342,45 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):
     _lib.check(_lib.load().s2p_adam_step(param.data_ptr(), g.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
                                          param.numel(), float(lr), float(beta1), float(beta2), float(eps), int(step),
                                          _stream()), "s2p_adam_step")
+
+
+def adam_step_dev(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step_dev):
+    """Adam update with the step count in a device int32 tensor (graph-capturable)."""
+    _require_cuda(param, grad, exp_avg, exp_avg_sq, step_dev)
+    g = grad if (grad.is_contiguous() and grad.dtype == torch.float32) else grad.contiguous().float()
+    if param.dtype != torch.float32 or not param.is_contiguous() or step_dev.dtype != torch.int32:
+        raise RuntimeError("adam_step_dev: contiguous fp32 parameters and an int32 step tensor are required")
+    _lib.check(_lib.load().s2p_adam_step_dev(param.data_ptr(), g.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+                                             param.numel(), float(lr), float(beta1), float(beta2), float(eps),
+                                             step_dev.data_ptr(), _stream()), "s2p_adam_step_dev")
+
+
+def pack_conv_weight_dgrad(w_oihw):
+    """OIHW fp32 -> [Cin, R*S*Cout] bf16: the packed weight of the data-gradient conv."""
+    _require_cuda(w_oihw)
+    w = w_oihw.detach().contiguous().float()
+    co, ci, r, s = w.shape
+    out = torch.empty(ci, r * s * co, dtype=torch.bfloat16, device=w.device)
+    _lib.check(_lib.load().s2p_pack_conv_weight_dgrad(w.data_ptr(), out.data_ptr(), co, ci, r, s, _stream()),
+               "s2p_pack_conv_weight_dgrad")
+    return out
+
+
+def act_bwd_bias_grad(dy, y, act, want_bias_grad=True):
+    """(dy * act'(y), db): gradient through ReLU/LeakyReLU given the activated output, and the
+    bias gradient sum_{pixels} in the same pass.  dy, y NHWC bf16."""
+    _require_cuda(dy, y)
+    b, h, w, c = dy.shape
+    lib = _lib.load()
+    out = torch.empty(b, h, w, c, dtype=torch.bfloat16, device=dy.device) if act != ACT_NONE else dy
+    db = partial = None
+    if want_bias_grad:
+        db = torch.empty(c, dtype=torch.float32, device=dy.device)
+        partial = torch.empty(int(lib.s2p_act_bwd_bias_grad_chunks()) * c, dtype=torch.float32, device=dy.device)
+    elif act == ACT_NONE:
+        return dy, None
+    _lib.check(lib.s2p_act_bwd_bias_grad(dy.data_ptr(), _nhwc_pitch(dy, "dy"), _ptr(y) if act != ACT_NONE else 0,
+                                         _nhwc_pitch(y, "y") if act != ACT_NONE else 0, act,
+                                         out.data_ptr() if act != ACT_NONE else 0, c, _ptr(db), _ptr(partial),
+                                         b * h * w, c, _stream()), "s2p_act_bwd_bias_grad")
+    return out, db

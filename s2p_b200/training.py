@@ -17,14 +17,20 @@ LAMBDA_L1 = 10.0
 
 
 class FusedAdam:
-    """Adam(lr, betas, eps) with torch.optim.Adam's update rule, one fused kernel per tensor."""
+    """Adam(lr, betas, eps) with torch.optim.Adam's update rule, one fused kernel per tensor.  The
+    step count lives in device memory so that a captured CUDA graph of the step stays valid."""
 
     def __init__(self, params, lr=2e-4, betas=(0.0, 0.9), eps=1e-8):
         self.params = [p for p in params if p.requires_grad]
         self.lr, self.betas, self.eps = lr, betas, eps
-        self.step_count = 0
+        dev = self.params[0].device
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.m = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
         self.v = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
+
+    @property
+    def step_count(self):
+        return int(self.step_dev.item())
 
     def zero_grad(self, set_to_none=True):
         for p in self.params:
@@ -32,11 +38,11 @@ class FusedAdam:
 
     @torch.no_grad()
     def step(self):
-        self.step_count += 1
+        self.step_dev += 1
         for p, m, v in zip(self.params, self.m, self.v):
             if p.grad is None:
                 continue
-            ops.adam_step(p, p.grad, m, v, self.lr, self.betas[0], self.betas[1], self.eps, self.step_count)
+            ops.adam_step_dev(p, p.grad, m, v, self.lr, self.betas[0], self.betas[1], self.eps, self.step_dev)
 
 
 def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
@@ -128,3 +134,32 @@ class S2PTrainer:
         g = self.run_generator_one_step(prev_image, state, real_image)
         d = self.run_discriminator_one_step(prev_image, state, real_image)
         return g, d
+
+    # ------------------------------------------------------------------ CUDA graph of the whole step
+    def capture(self, prev_image, state, real_image, warmup=3):
+        """Capture one full G + D step (forward, backward, Adam) into a CUDA graph with static
+        input buffers.  At batch 16 the step is launch bound (~800 kernels of this library plus
+        the tape's glue); replaying the graph removes the host from the loop."""
+        if self.world_size > 1:
+            raise RuntimeError("capture(): single-process only (the NCCL all-reduce is issued eagerly)")
+        self._static = [t.clone() for t in (prev_image, state, real_image)]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self.train_step(*self._static)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.optG.zero_grad()
+        self.optD.zero_grad()
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            g, d = self.train_step(*self._static)
+            self._static_out = ({k: v.detach() for k, v in g.items()}, d.detach())
+        return self
+
+    def train_step_graphed(self, prev_image, state, real_image):
+        for dst, src in zip(self._static, (prev_image, state, real_image)):
+            dst.copy_(src, non_blocking=True)
+        self._graph.replay()
+        return self._static_out

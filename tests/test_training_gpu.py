@@ -224,3 +224,43 @@ def test_training_step_vs_oracle(pkg):
     # parameters moved, and by Adam-sized steps (|delta| <= lr / (1 - beta1) ...)
     moved = max((p - q).abs().max().item() for p, q in zip(nG.parameters(), oG.state_dict().values()))
     assert 0 < moved < 1e-2
+
+
+def test_act_bwd_bias_grad_kernel(pkg):
+    from s2p_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    for c, act in ((64, 2), (128, 1), (512, 0), (72, 2)):
+        dy = torch.randn(3, 37, 41, c, generator=g).cuda().to(torch.bfloat16)
+        y = torch.randn(3, 37, 41, c, generator=g).cuda().to(torch.bfloat16)
+        out, db = ops.act_bwd_bias_grad(dy, y, act, True)
+        ref = dy.float() if act == 0 else torch.where(y.float() > 0, dy.float(), dy.float() * (0.2 if act == 2 else 0.0))
+        ref = ref.to(torch.bfloat16)
+        assert torch.equal(out, ref)
+        assert torch.allclose(db, ref.float().sum(dim=(0, 1, 2)), rtol=1e-4, atol=1e-2)
+        assert torch.equal(ops.act_bwd_bias_grad(dy, y, act, True)[1], db)     # bit-stable
+
+
+def test_graphed_step_equals_eager(pkg):
+    """the CUDA-graph replay of the G + D step is the same computation as the eager step."""
+    from s2p_b200.training import S2PTrainer
+    image, states = common.make_inputs("cheetah", 2, 1)
+    g = torch.Generator().manual_seed(9)
+    real = (torch.rand(2, 3, 100, 100, generator=g) * 2 - 1).cuda()
+    image, st = image.cuda(), states[:, 0].cuda()
+    trainers = []
+    for _ in range(2):
+        torch.manual_seed(77)
+        nG = pkg.define_G(pkg.make_options(env_type="cheetah", gpu_ids="0", init_type="scaled"))
+        nD = pkg.define_D(pkg.make_options(gpu_ids="0"))
+        trainers.append(S2PTrainer(nG, nD))
+    eager, graphed = trainers
+    graphed.capture(image, st, real, warmup=2)
+    for _ in range(2):
+        eager.train_step(image, st, real)
+    g_e, d_e = eager.train_step(image, st, real)          # step 3
+    g_g, d_g = graphed.train_step_graphed(image, st, real)  # step 3 (2 warm-up steps + this replay)
+    torch.cuda.synchronize()
+    for k in g_e:
+        assert abs(float(g_e[k]) - float(g_g[k])) <= 1e-4 * abs(float(g_e[k])) + 1e-5, k
+    assert abs(float(d_e) - float(d_g)) <= 1e-4 * abs(float(d_e)) + 1e-5
+    assert graphed.optG.step_count == 3

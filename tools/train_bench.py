@@ -21,6 +21,7 @@ ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--env", type=str, default="walker")
 ap.add_argument("--profile", action="store_true")
 ap.add_argument("--no-oracle", action="store_true")
+ap.add_argument("--graph", action="store_true")
 a = ap.parse_args()
 B = a.batch
 torch.manual_seed(1234)
@@ -50,6 +51,11 @@ l0 = _lib.launch_count()
 ms = timed(lambda: tr.train_step(prev, state, real), a.steps, a.warmup)
 launches = (_lib.launch_count() - l0) / (a.steps + a.warmup)
 print(f"s2p_b200 train step: batch={B} {ms:.2f} ms/step  {B / ms * 1e3:.1f} frames/s  ({launches:.0f} own kernel launches/step)")
+if a.graph:
+    tr.capture(prev, state, real)
+    l0 = _lib.launch_count()
+    ms_g = timed(lambda: tr.train_step_graphed(prev, state, real), a.steps, a.warmup)
+    print(f"s2p_b200 train step (CUDA graph replay): batch={B} {ms_g:.2f} ms/step  {B / ms_g * 1e3:.1f} frames/s")
 if a.profile:
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
