@@ -43,6 +43,9 @@ def parse():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--batch", type=int, default=1024)
     p.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
+    p.add_argument("--workload", type=str, default="synthesis", choices=["synthesis", "train"],
+                   help="synthesis = BASELINE configs[2]/[3] (the metric's workload, default); "
+                        "train = configs[1]/[4], one G + D step per step (use --batch 16 / 256)")
     p.add_argument("--cpu-sample", type=int, default=16, help="frames per CPU-baseline forward")
     p.add_argument("--no-cpu-baseline", action="store_true")
     return p.parse_args()
@@ -337,9 +340,117 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     return roof, roof_norm, shares
 
 
+def run_train(args):
+    """BASELINE configs[1] (walker, batch 16, 1 GPU) / configs[4] (batch 256 per GPU, NCCL gradient
+    all-reduce): one step = one generator step + one discriminator step incl. Adam."""
+    import torch
+    import torch.distributed as dist
+    import s2p_b200
+    from s2p_b200 import _lib
+    from s2p_b200.training import S2PTrainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+    env = "walker"
+    torch.manual_seed(1234)                      # same initial weights on every rank
+    opt = s2p_b200.make_options(env_type=env, gpu_ids=str(local), init_type="scaled")
+    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt), world_size=world)
+    g = torch.Generator().manual_seed(100 + rank)
+    host = [(torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).pin_memory(),
+            torch.randn(B, opt.state_dim, generator=g).pin_memory(),
+            (torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).pin_memory()]
+    devt = [t.to(dev) for t in host]
+    use_graph = world == 1 and B <= 32           # launch-bound regime: replay a CUDA graph of the step
+    if use_graph:
+        tr.capture(*devt)
+        step = lambda: tr.train_step_graphed(*devt)   # noqa: E731
+    else:
+        step = lambda: tr.train_step(*devt)           # noqa: E731
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    with ClockSampler(local) as clk:
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+        launches = _lib.launch_count() - l0
+        ms_dev = max_over_ranks(e0.elapsed_time(e1))
+        # end to end: batch from pinned host memory in, loss scalars back out, every step
+        e0.record()
+        for _ in range(args.steps):
+            for d, h in zip(devt, host):
+                d.copy_(h, non_blocking=True)
+            gl, dl = step()
+            losses_host = [float(v) for v in gl.values()] + [float(dl)]
+        e1.record()
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    clocks = clk.summary()
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        frames = B * world * args.steps
+        # algorithmic flops per frame: generator forward 112.9 GFLOP (BASELINE.md section 4), its
+        # backward = dgrad + wgrad = 2x; discriminator (fake+real forward, backward) ~ 3 % on top
+        flops_frame = 3 * 112.9e9 * 1.03
+        ach = flops_frame * B / (ms_dev / args.steps / 1e3) / 1e12
+        h2d = sum(t.numel() * t.element_size() for t in host)
+        line = {"metric": "training_frames_per_sec", "value": frames / (ms_dev / 1e3), "unit": "frames/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": "GAN training step (BASELINE configs[1]/[4]): generator step (L1 + hinge GAN + "
+                                       f"feature matching) + discriminator step + Adam, {env}, batch {B} per GPU",
+                           "env_type": env, "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
+                           "cuda_graph": use_graph, "weights": "random init ('scaled'), VGG term off (ORACLE_SPEC v1.1)"},
+                "e2e": {"value": frames / (ms_e2e / 1e3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": 4 * len(losses_host), "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches) if not use_graph else None,
+                "gpu_launches_note": "CUDA-graph replay: the library's launches are inside the graph" if use_graph else None,
+                "clocks": clocks,
+                "roofline": {"kernel": "whole training step (conv fwd/dgrad/wgrad dominate)", "bound": "tensor",
+                             "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "traffic": None}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "train":
+        if a.batch == 1024:
+            a.batch = 16
+        run_train(a)
     else:
         run_b200(a)

@@ -104,10 +104,13 @@ class S2PTrainer:
     def run_generator_one_step(self, prev_image, state, real_image):
         self.netG.train()
         fake = self.netG(prev_image, state)
+        for p in self.optD.params:            # the G step needs D's data gradients only
+            p.requires_grad_(False)
         pred_fake, pred_real = self._d(prev_image, fake, real_image)
+        for p in self.optD.params:
+            p.requires_grad_(True)
         losses = generator_losses(pred_fake, pred_real, fake, real_image)
         self.optG.zero_grad()
-        self.optD.zero_grad()
         sum(losses.values()).backward()
         if self.world_size > 1:
             allreduce_gradients(self.optG.params, self.world_size)

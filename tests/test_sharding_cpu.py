@@ -72,3 +72,35 @@ def test_two_rank_sharding_gloo():
         assert p.exitcode == 0
     assert cover == [1] * 6 + [2] * 5       # every row owned by exactly one rank, contiguous
     assert tmax == 20.0
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from s2p_b200.training import allreduce_gradients
+    torch.manual_seed(0)
+    params = [torch.nn.Parameter(torch.zeros(s)) for s in ((3, 5), (7,), (2, 2, 2), (11,))]
+    for i, p in enumerate(params):
+        p.grad = torch.full_like(p, float((rank + 1) * (i + 1)))
+    params[1].grad = None                                   # a parameter without gradient is skipped
+    allreduce_gradients(params, world, bucket_elems=16)     # tiny buckets: several all-reduces
+    if rank == 0:
+        q.put([None if p.grad is None else p.grad.flatten()[0].item() for p in params])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_two_ranks_gloo():
+    """data-parallel training (BASELINE configs[4]): gradients are averaged over ranks in flat buckets."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_grad_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got == [1.5, None, 4.5, 6.0]       # mean over ranks of (rank+1)*(i+1)
