@@ -29,6 +29,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# rank 0 prints exactly ONE JSON line on stdout: keep NCCL's own banner ("NCCL version ...") out of it
+os.environ["NCCL_DEBUG"] = os.environ.get("S2P_NCCL_DEBUG", "WARN")
 
 METRIC = "generated_frames_per_sec"
 UNIT = "frames/s"
@@ -405,7 +407,7 @@ def run_train(args):
             for d, h in zip(devt, host):
                 d.copy_(h, non_blocking=True)
             gl, dl = step()
-            losses_host = [float(v) for v in gl.values()] + [float(dl)]
+            losses_host = [float(v.detach()) for v in gl.values()] + [float(dl.detach())]
         e1.record()
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1))
