@@ -50,6 +50,7 @@ def parse():
                         "train = configs[1]/[4], one G + D step per step (use --batch 16 / 256)")
     p.add_argument("--cpu-sample", type=int, default=16, help="frames per CPU-baseline forward")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-train", action="store_true", help="skip the configs[1] training-step side measurement")
     return p.parse_args()
 
 
@@ -238,6 +239,11 @@ def run_b200(args):
                     "d2h_bytes_per_step": synth.d2h_bytes // args.steps, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_norm": roof_norm,
             "kernel_time_share": shares}
+    if world == 1 and not args.no_train:
+        try:
+            line["training_step"] = train_side_measurement(torch, s2p_b200, dev)
+        except Exception as e:  # noqa: BLE001  (a side measurement must never cost the headline line)
+            line["training_step"] = {"error": repr(e)[:200]}
     if world == 1 and not args.no_cpu_baseline:
         best, mean, threads, times = cpu_oracle_fps(args.cpu_sample, 2)
         line["cpu_baseline"] = {"value": best, "unit": UNIT, "cores": threads, "kind": "port",
@@ -246,6 +252,34 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):
+    """BASELINE configs[1] (G + D training step, walker, batch 16, 1 GPU) timed beside the headline
+    generation workload: CUDA-graph replay of the whole step, CUDA events."""
+    from s2p_b200.training import S2PTrainer
+    torch.manual_seed(1234)
+    opt = s2p_b200.make_options(env_type="walker", gpu_ids=str(dev.index), init_type="scaled")
+    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt))
+    g = torch.Generator().manual_seed(7)
+    prev = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    real = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    state = torch.randn(batch, opt.state_dim, generator=g).to(dev)
+    tr.capture(prev, state, real)
+    for _ in range(warmup):
+        tr.train_step_graphed(prev, state, real)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        gl, dl = tr.train_step_graphed(prev, state, real)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"config": "BASELINE configs[1]: generator + multiscale-discriminator training step, walker, batch 16, 1 GPU "
+                      "(L1 + hinge GAN + feature matching, Adam; CUDA-graph replay)",
+            "ms_per_step": ms, "frames_per_sec": batch / ms * 1e3, "steps": steps, "warmup": warmup,
+            "losses": {k: float(v) for k, v in gl.items()} | {"D": float(dl)}}
 
 
 def instrumented_step(net, frames_d, states_d, ops, torch):
