@@ -28,6 +28,7 @@ struct WgradParams {
   int tile_w, tile_h, tiles_x, tiles_y;
   int kb_rows;              // tile_w * tile_h (multiple of 16)
   int num_pix_tiles;        // B * tiles_x * tiles_y
+  int stages;               // depth of the TMA -> MMA ring (2..8, as many as fit in shared memory)
   float* partial;           // [splits][Cout][R][S][Cin]
 };
 
@@ -47,7 +48,7 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(uint32_t M, uint32_t N
   return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
-constexpr int kWgStages = 2;
+constexpr int kWgMaxStages = 8;
 
 template <int BN, int TAPS>
 __global__ void __launch_bounds__(192, 1)
@@ -61,10 +62,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   const int atom_bytes = p.kb_rows * 128;                       // one 64-channel block of one tile
   const int atom_stride = (atom_bytes + 1023) & ~1023;          // keep every block 1024-B aligned
   const int stage_bytes = (kAtomsA + TAPS * kAtomsB) * atom_stride;
+  const int kWgStages = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * stage_bytes);
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + kWgStages;
-  uint64_t* done_bar = bars + 2 * kWgStages;
+  uint64_t* empty_bar = bars + kWgMaxStages;
+  uint64_t* done_bar = bars + 2 * kWgMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
@@ -196,11 +198,18 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __
 }
 
 // pixel tile for the K dimension: tile_w * tile_h a multiple of 16, <= 128 rows, fewest wasted rows
+static int wgrad_max_rows() {
+  static int r = 0;
+  if (r == 0) { const char* e = getenv("S2P_WGRAD_ROWS"); r = e ? atoi(e) : 128; if (r < 16) r = 16; if (r > 128) r = 128; }
+  return r;
+}
+
 static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out) {
+  const int max_rows = wgrad_max_rows();
   double best = -1.0;
   int btw = 16, bth = 1;
-  for (int tw = 1; tw <= W && tw <= 128; ++tw) {
-    for (int th = 1; th <= H && tw * th <= 128; ++th) {
+  for (int tw = 1; tw <= W && tw <= max_rows; ++tw) {
+    for (int th = 1; th <= H && tw * th <= max_rows; ++th) {
       if ((tw * th) % 16) continue;
       const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
       const double eff = static_cast<double>(H) * W / (tiles * static_cast<double>(tw * th));
@@ -248,15 +257,22 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
   p.num_pix_tiles = B * p.tiles_x * p.tiles_y;
   pl->taps = ksize;
   const int atom = p.kb_rows * 128;
-  pl->bn = (Cin % 128 == 0 && ksize * 128 <= 512 && kWgStages * (2 + ksize * 2) * atom <= 200 * 1024) ? 128 : 64;
+  pl->bn = (Cin % 128 == 0 && ksize * 128 <= 512 && 2 * (2 + ksize * 2) * atom <= 200 * 1024) ? 128 : 64;
   const int ctas = ((Cout + 127) / 128) * (Cin / pl->bn) * ksize;
-  int splits = (2 * num_sms() + ctas - 1) / ctas;
+  // split-K so that the grid is as close as possible to (but not above) ONE full wave: the kernel
+  // runs one CTA per SM, so 2.03 waves cost 3
+  int splits = num_sms() / ctas;
   if (splits > p.num_pix_tiles) splits = p.num_pix_tiles;
   if (splits < 1) splits = 1;
   pl->splits = splits;
   pl->grid = dim3((Cout + 127) / 128, (Cin / pl->bn) * ksize, splits);
   const int atom_stride = (p.kb_rows * 128 + 1023) & ~1023;
-  pl->smem_bytes = kWgStages * (2 + pl->taps * (pl->bn / 64)) * atom_stride + 1024 + 128;
+  const int stage_bytes = (2 + pl->taps * (pl->bn / 64)) * atom_stride;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > kWgMaxStages) stages = kWgMaxStages;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  pl->smem_bytes = stages * stage_bytes + 1024 + 256;
   return S2P_OK;
 }
 
