@@ -170,6 +170,34 @@ int s2p_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
 int s2p_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                       float beta1, float beta2, float eps, const int* step_dev, void* stream);
 
+/* ---- (f1) state-transition producer: the reference's Gaussian ensemble + rollout post-processing ----
+ * replaces, in ONE launch over the whole dataset, EnsembleTransition.forward
+ * (/root/reference/gaussian_ensemble.py:83-96; EnsembleLinear :37-48, Swish :9-11, soft_clamp :13-19;
+ * mode='local', with_reward=True, hidden_features=256 as constructed at
+ * state_transition_rollout.py:44-56) and the per-row arithmetic of the rollout loop
+ * (state_transition_rollout.py:149 normalisation, :192-195 member selection + de-normalisation,
+ * :199-204 disagreement / aleatoric uncertainty).  fp32 throughout.
+ *   obs [T][obs_dim] (raw when obs_mean/obs_std given, already normalised when both NULL), action [T][action_dim]
+ *   w_packed: n_members x s2p_transition_member_floats() floats, per member
+ *       W0 [32][256] (rows >= obs_dim+action_dim zero) | b0 [256] | (W_l [256][256] | b_l [256]) x (hidden_layers-1)
+ *       | W_out [256][64] (columns >= 2*(obs_dim+1) zero) | b_out [64]          ([in][out] = EnsembleLinear.weight[e])
+ *   mean_out / std_out [n_members][T][obs_dim+1]  (Normal.mean / .stddev of forward()), both or neither
+ *   member_idx [T] in [0, n_members): when given, also writes next_obs [T][obs_dim], reward [T],
+ *       disagreement [T], aleatoric [T]. */
+long long s2p_transition_member_floats(int obs_dim, int action_dim, int hidden_layers);
+int s2p_ensemble_transition_fwd(const float* obs, int obs_pitch, const float* action, int act_pitch,
+                                const float* obs_mean, const float* obs_std, const float* w_packed, int n_members,
+                                const float* min_logstd, const float* max_logstd, float* mean_out, float* std_out,
+                                const int* member_idx, const float* next_obs_mean, const float* next_obs_std,
+                                float reward_mean, float reward_std, float* next_obs, float* reward,
+                                float* disagreement, float* aleatoric, long long T, int obs_dim, int action_dim,
+                                int hidden_layers, void* stream);
+/* slac_observation_indices [N][num_seq+1] and slac_action_indices [N][num_seq] (int64) of
+ * generate_obs_act_indices, state_transition_rollout.py:105-132: row i of a trajectory starting at
+ * traj_start[i] gets i-num_seq+j, or `sentinel` (1e9) for the first num_seq rows of the trajectory. */
+int s2p_slac_indices(const long long* traj_start, long long* obs_idx, long long* act_idx, long long N, int num_seq,
+                     long long sentinel, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
