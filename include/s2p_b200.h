@@ -198,6 +198,16 @@ int s2p_ensemble_transition_fwd(const float* obs, int obs_pitch, const float* ac
 int s2p_slac_indices(const long long* traj_start, long long* obs_idx, long long* act_idx, long long N, int num_seq,
                      long long sentinel, void* stream);
 
+/* ---- (f2) SLAC window assembly: gather + HWC->CHW + uint8 -> float/255 in one pass --------------
+ * replaces the state half of ReplayBuffer.sample_latent / sample_sac / random_batch
+ * (/root/reference/rlkit/torch/slac/buffer.py:127-147: per-sample host copies of 9 LazyFrames, upload,
+ * .float().div_(255)) and the load-time np.transpose of rlkit/torch/slac/algo.py:174-175.
+ * frames / frames_tp1: [N][H][W][C] uint8 as stored on disk (image_observations, image_observations_tp1);
+ * codes [n_frames] int64 = 2*row + which (0: frames, 1: frames_tp1); out [n_frames][C][H][W] fp32
+ * (= [batch][num_seq+1][C][H][W] with n_frames = batch*(num_seq+1)).  C in {1, 3}. */
+int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes, float* out,
+                           long long n_frames, int H, int W, int C, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

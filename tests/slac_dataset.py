@@ -1,0 +1,45 @@
+"""Seeded synthetic dataset in the reference's on-disk schema, shared by the SLAC
+buffer golden generator and its tests (same recipe, so fixtures only hold results)."""
+import numpy as np
+
+import slac_buffer_oracle as SO
+import transition_oracle as TO
+
+H, W, C, A = 12, 10, 3, 6
+
+
+def make_dataset(seed, lengths, tail, h=H, w=W):
+    rs = np.random.RandomState(seed)
+    n = sum(lengths) + tail
+    d = {
+        "image_observations": rs.randint(0, 256, size=(n, h, w, C)).astype(np.uint8),
+        "image_observations_tp1": rs.randint(0, 256, size=(n, h, w, C)).astype(np.uint8),
+        "actions": rs.uniform(-1, 1, size=(n, A)).astype(np.float32),
+        "original_actions": rs.uniform(-1, 1, size=(n, A)).astype(np.float32),
+        "rewards": rs.randn(n).astype(np.float32),
+        "original_rewards": rs.randn(n).astype(np.float32),
+        "aleatoric_uncertainty": np.abs(rs.randn(n, 1)).astype(np.float32),
+        "disagreement_uncertainty": np.abs(rs.randn(n, 1)).astype(np.float32),
+        "timeouts": np.zeros(n, dtype=np.float32),
+    }
+    d["timeouts"][np.cumsum(lengths) - 1] = 1
+    obs_i, act_i, start = [], [], 0
+    for m in lengths:
+        o, a = TO.obs_act_indices(m, start)
+        obs_i.append(o); act_i.append(a); start += m
+    if tail:
+        o, a = TO.obs_act_indices(tail + 8, start)  # a trailing partial trajectory
+        obs_i.append(o[:tail]); act_i.append(a[:tail])
+    d["slac_observation_indices"] = np.concatenate(obs_i)
+    d["slac_action_indices"] = np.concatenate(act_i)
+    return d
+
+
+def loaded(d):
+    """what load_data_in_buffer holds after reading the file (algo.py:174-203): CHW frames, squeezed uncertainties"""
+    e = dict(d)
+    e["image_observations"] = SO.to_chw(d["image_observations"])
+    e["image_observations_tp1"] = SO.to_chw(d["image_observations_tp1"])
+    e["aleatoric_uncertainty"] = d["aleatoric_uncertainty"].squeeze(-1)
+    e["disagreement_uncertainty"] = d["disagreement_uncertainty"].squeeze(-1)
+    return e
