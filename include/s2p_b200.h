@@ -50,7 +50,7 @@ long long s2p_launch_count(void);
  * y = act(conv(x, w) + bias + residual); optionally emits per-image per-channel
  * (sum, sumsq) partials of the STORED bf16 values for the following instance norm:
  * stats_partial is [B][s2p_conv_stats_rows(Hout,Wout)][Cout][2] fp32.
- * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in 1..4 (3x3/1x1: generator; 4x4: discriminator),
+ * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in 1..5 (3x3/1x1: generator; 4x4: discriminator; 5x5: SLAC),
  * stride in {1,2}, explicit symmetric zero padding `pad` (nn.Conv2d padding). */
 int s2p_conv_stats_rows(int Hout, int Wout);
 int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
@@ -207,6 +207,17 @@ int s2p_slac_indices(const long long* traj_start, long long* obs_idx, long long*
  * (= [batch][num_seq+1][C][H][W] with n_frames = batch*(num_seq+1)).  C in {1, 3}. */
 int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes, float* out,
                            long long n_frames, int H, int W, int C, void* stream);
+
+/* ---- (f3) SLAC encoder, first layer from the resident uint8 dataset --------------------------------
+ * replaces nn.Conv2d(3, 32, 5, 2, 2) + nn.LeakyReLU(0.2) of Encoder.net
+ * (/root/reference/rlkit/torch/slac/network/latent.py:143-145 / :126-128) fused with the window gather and
+ * the /255 of ReplayBuffer.sample_latent (buffer.py:131-135): pass (frames, frames_tp1, codes) as for
+ * s2p_slac_window_gather, or x_nchw = float [n_frames][3][H][W] (the reference-facing forward(x)).
+ * y: NHWC bf16 [n_frames][Ho][Wo][y_pitch >= 64], channels 32..63 zero, ready for s2p_conv_igemm_fwd with
+ * Cin = 64 (the remaining encoder layers, latent.py:146-160, run on that kernel; ksize up to 5 there). */
+int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes, const float* x_nchw,
+                       const float* w_oihw, const float* bias, void* y, int y_pitch, long long n_frames, int H, int W,
+                       void* stream);
 
 #ifdef __cplusplus
 }

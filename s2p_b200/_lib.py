@@ -49,6 +49,7 @@ SIGNATURES = {
     "s2p_ensemble_transition_fwd": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f,
                                          _vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
     "s2p_slac_window_gather": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
+    "s2p_slac_conv1_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
     "s2p_slac_indices": (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_longlong, _vp]),
 }
 

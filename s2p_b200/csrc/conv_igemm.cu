@@ -641,7 +641,7 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
   S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
   S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
   S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
-  S2P_CHECK_ARG(ksize >= 1 && ksize <= 4, "conv: ksize=%d unsupported", ksize);
+  S2P_CHECK_ARG(ksize >= 1 && ksize <= 5, "conv: ksize=%d unsupported", ksize);
   S2P_CHECK_ARG(pad >= 0 && pad < ksize && Hin + 2 * pad >= ksize && Win + 2 * pad >= ksize, "conv: pad=%d", pad);
   S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
   S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
