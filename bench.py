@@ -260,7 +260,7 @@ def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):
     from s2p_b200.training import S2PTrainer
     torch.manual_seed(1234)
     opt = s2p_b200.make_options(env_type="walker", gpu_ids=str(dev.index), init_type="scaled")
-    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt))
+    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt), vgg=s2p_b200.VGG19FeaturesB200().to(dev))
     g = torch.Generator().manual_seed(7)
     prev = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
     real = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
@@ -277,7 +277,7 @@ def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     return {"config": "BASELINE configs[1]: generator + multiscale-discriminator training step, walker, batch 16, 1 GPU "
-                      "(L1 + hinge GAN + feature matching, Adam; CUDA-graph replay)",
+                      "(L1 + hinge GAN + feature matching + VGG19 perceptual with a random-init extractor, Adam; CUDA-graph replay)",
             "ms_per_step": ms, "frames_per_sec": batch / ms * 1e3, "steps": steps, "warmup": warmup,
             "losses": {k: float(v) for k, v in gl.items()} | {"D": float(dl)}}
 
@@ -396,7 +396,8 @@ def run_train(args):
     env = "walker"
     torch.manual_seed(1234)                      # same initial weights on every rank
     opt = s2p_b200.make_options(env_type=env, gpu_ids=str(local), init_type="scaled")
-    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt), world_size=world)
+    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt), world_size=world,
+                    vgg=s2p_b200.VGG19FeaturesB200().to(dev))
     g = torch.Generator().manual_seed(100 + rank)
     host = [(torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).pin_memory(),
             torch.randn(B, opt.state_dim, generator=g).pin_memory(),

@@ -219,6 +219,15 @@ int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, const l
                        const float* w_oihw, const float* bias, void* y, int y_pitch, long long n_frames, int H, int W,
                        void* stream);
 
+/* ---- (a8) 2x2 stride-2 max pool (floor mode) on NHWC bf16 and its backward -------------------------
+ * replaces nn.MaxPool2d(2, 2) of the VGG19 feature extractor behind the perceptual loss of the training step
+ * (/root/reference/rebuttal.md:71,131-135 "perceptual (VGG)"; oracle VGG19Features).  y: [B][H/2][W/2][C].
+ * backward: dx gets dy at the first maximum of each window (nn.MaxPool2d tie rule) and zeros elsewhere,
+ * including the row / column an odd H / W leaves uncovered.  C % 8 == 0. */
+int s2p_maxpool2_fwd(const void* x, int x_pitch, void* y, int y_pitch, int B, int H, int W, int C, void* stream);
+int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, void* dx, int dx_pitch, int B, int H,
+                     int W, int C, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -324,7 +324,8 @@ if __name__ == "__main__":
 #   losses: hinge GAN (D: mean relu(1 - D(real)) + mean relu(1 + D(fake)); G: -mean D(fake)),
 #       averaged over scales; feature matching L1 over the intermediate outputs (lambda 10,
 #       / num_D); L1(fake, real) * lambda_l1 (10).  The VGG19 perceptual term of the paper
-#       needs ImageNet weights (not available offline): lambda_vgg = 0 in this spec.
+#       needs ImageNet weights (not available offline): v1.1 had lambda_vgg = 0; v1.2 (below) adds the term with
+#       a seeded random-init extractor, enabled by passing `vgg=` to training_step.
 #   optimiser: Adam(lr 2e-4, betas (0.0, 0.9)) for G and for D (SPADE TTUR off).
 # ======================================================================================
 class NLayerDiscriminator(nn.Module):
@@ -374,7 +375,59 @@ def define_D(opt=None):
 
 LAMBDA_FEAT = 10.0
 LAMBDA_L1 = 10.0
+LAMBDA_VGG = 10.0
 ADAM = dict(lr=2e-4, betas=(0.0, 0.9))
+
+# ---- ORACLE_SPEC v1.2: VGG19 perceptual loss (rebuttal.md:71,131-135 "L1 + GAN + perceptual (VGG pretrained on
+# ImageNet)"; lineage NVlabs/SPADE VGGLoss).  The ImageNet weights cannot be fetched offline, so the extractor is
+# RANDOM-INIT under a fixed seed (SURVEY.md section 8 d, cfg 2: "VGG weights random-init (quality n/a)"): the
+# arithmetic of the training step is complete, the perceptual quality of the loss is not claimed.
+VGG19_CFG = [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512]  # ... conv5_1
+VGG_SLICE_ENDS = (2, 7, 12, 21, 30)            # torchvision vgg19.features indices: relu1_1 ... relu5_1
+VGG_WEIGHTS = (1.0 / 32, 1.0 / 16, 1.0 / 8, 1.0 / 4, 1.0)
+VGG_SEED = 4321
+
+
+class VGG19Features(nn.Module):
+    """features[0:30] of torchvision's vgg19 (same module indices, so a real checkpoint would load);
+    forward returns the five relu*_1 maps.  Inputs are the [-1,1] images as they are (SPADE does the same)."""
+
+    def __init__(self):
+        super().__init__()
+        layers, cin = [], 3
+        for v in VGG19_CFG:
+            if v == "M":
+                layers.append(nn.MaxPool2d(2, 2))
+            else:
+                layers += [nn.Conv2d(cin, v, 3, padding=1), nn.ReLU(inplace=False)]
+                cin = v
+        self.features = nn.Sequential(*layers)
+        assert len(self.features) == 30
+        gen = torch.Generator().manual_seed(VGG_SEED)
+        for m in self.features:
+            if isinstance(m, nn.Conv2d):       # torchvision's init: kaiming_normal_(fan_out, relu), zero bias
+                std = math.sqrt(2.0 / (m.out_channels * 9))
+                with torch.no_grad():
+                    m.weight.copy_(torch.randn(m.weight.shape, generator=gen) * std)
+                    m.bias.zero_()
+        for p in self.parameters():
+            p.requires_grad_(False)
+
+    def forward(self, x):
+        outs = []
+        for i, m in enumerate(self.features):
+            x = m(x)
+            if i + 1 in VGG_SLICE_ENDS:
+                outs.append(x)
+        return outs
+
+
+def vgg_loss(vgg, fake, real):
+    """SPADE VGGLoss: sum_i w_i * L1(vgg(fake)_i, vgg(real)_i.detach())"""
+    fx = vgg(fake)
+    with torch.no_grad():
+        fy = vgg(real)
+    return sum(w * F.l1_loss(a, b) for w, a, b in zip(VGG_WEIGHTS, fx, fy))
 
 
 def hinge_d_loss(pred_real, pred_fake):
@@ -384,7 +437,7 @@ def hinge_d_loss(pred_real, pred_fake):
     return loss / len(pred_real)
 
 
-def generator_losses(pred_fake, pred_real, fake, real):
+def generator_losses(pred_fake, pred_real, fake, real, vgg=None):
     """dict of the G-step loss terms (SPADE Pix2PixModel.compute_generator_loss shape)."""
     num_d = len(pred_fake)
     gan = sum(-f[-1].mean() for f in pred_fake) / num_d
@@ -392,16 +445,19 @@ def generator_losses(pred_fake, pred_real, fake, real):
     for f, r in zip(pred_fake, pred_real):
         for a, b in zip(f[:-1], r[:-1]):
             feat = feat + F.l1_loss(a, b.detach()) * LAMBDA_FEAT / num_d
-    return {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+    losses = {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+    if vgg is not None:
+        losses["VGG"] = vgg_loss(vgg, fake, real) * LAMBDA_VGG
+    return losses
 
 
-def training_step(netG, netD, optG, optD, prev_image, state, real_image):
+def training_step(netG, netD, optG, optD, prev_image, state, real_image, vgg=None):
     """one G step then one D step (SPADE Pix2PixTrainer order); returns (g_losses, d_loss, fake)."""
     fake = netG(prev_image, state)
     pred = netD(torch.cat([torch.cat([prev_image, fake], 1), torch.cat([prev_image, real_image], 1)], 0))
     pred_fake = [[t[: t.shape[0] // 2] for t in p] for p in pred]
     pred_real = [[t[t.shape[0] // 2:] for t in p] for p in pred]
-    g_losses = generator_losses(pred_fake, pred_real, fake, real_image)
+    g_losses = generator_losses(pred_fake, pred_real, fake, real_image, vgg)
     optG.zero_grad(set_to_none=True)
     sum(g_losses.values()).backward()
     optG.step()

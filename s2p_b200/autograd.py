@@ -120,6 +120,24 @@ def linear(x, weight, bias=None, act=ACT_NONE):
     return LinearFn.apply(x, weight, bias, act)
 
 
+class MaxPool2Fn(torch.autograd.Function):
+    """nn.MaxPool2d(2, 2) on NHWC bf16 (VGG19 feature extractor of the perceptual loss)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return ops.maxpool2(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        return ops.maxpool2_bwd(dy.contiguous(), x)
+
+
+def maxpool2(x):
+    return MaxPool2Fn.apply(x)
+
+
 def conv_stats(y_shape, device):
     """scratch for the conv epilogue's statistics partials of an output of shape [B,H,W,C]"""
     b, h, w, c = y_shape

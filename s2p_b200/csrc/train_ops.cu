@@ -154,3 +154,132 @@ extern "C" int s2p_adam_step_dev(float* param, const float* grad, float* exp_avg
   count_launch();
   return check_launch("adam_step_dev_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------
+// 2x2 stride-2 max pool (floor mode) on NHWC bf16 and its backward, for the VGG19 perceptual loss of the
+// training step (rebuttal.md:71,131-135).  HBM-bound: one read of x, a quarter-size
+// write.  The backward recomputes the argmax from x with nn.MaxPool2d's rule (first maximum in (dy, dx) scan
+// order wins; after a ReLU ties at 0 are common) and also zero-fills the row / column an odd input size
+// leaves uncovered, so dx needs no memset.
+namespace s2p {
+
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+__global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_pitch, __nv_bfloat16* __restrict__ y,
+                                    int y_pitch, int B, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, cv = C / 8;
+  const long long total = static_cast<long long>(B) * Ho * Wo * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % cv);
+    long long t = i / cv;
+    const int wo = static_cast<int>(t % Wo); t /= Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const long long b = t / Ho;
+    const __nv_bfloat16* px = x + ((b * H + 2 * ho) * W + 2 * wo) * static_cast<long long>(x_pitch) + c8 * 8;
+    const uint4 v00 = __ldg(reinterpret_cast<const uint4*>(px));
+    const uint4 v01 = __ldg(reinterpret_cast<const uint4*>(px + x_pitch));
+    const uint4 v10 = __ldg(reinterpret_cast<const uint4*>(px + static_cast<long long>(W) * x_pitch));
+    const uint4 v11 = __ldg(reinterpret_cast<const uint4*>(px + static_cast<long long>(W + 1) * x_pitch));
+    uint4 r;
+    __nv_bfloat162* rh = reinterpret_cast<__nv_bfloat162*>(&r);
+    const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
+    const __nv_bfloat162* bq = reinterpret_cast<const __nv_bfloat162*>(&v01);
+    const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
+    const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) rh[k] = __hmax2(__hmax2(a[k], bq[k]), __hmax2(c[k], d[k]));
+    *reinterpret_cast<uint4*>(y + ((b * Ho + ho) * Wo + wo) * static_cast<long long>(y_pitch) + c8 * 8) = r;
+  }
+}
+
+// one thread per 2x2 cell of the INPUT grid (ceil sizes) x 8 channels
+__global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, const __nv_bfloat16* __restrict__ x,
+                                    int x_pitch, __nv_bfloat16* __restrict__ dx, int dx_pitch, int B, int H, int W,
+                                    int C) {
+  const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, cv = C / 8;
+  const long long total = static_cast<long long>(B) * Hc * Wc * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % cv);
+    long long t = i / cv;
+    const int wc = static_cast<int>(t % Wc); t /= Wc;
+    const int hc = static_cast<int>(t % Hc);
+    const long long b = t / Hc;
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    if (hc >= Ho || wc >= Wo) {   // cells no pooling window covers (odd H / W)
+      for (int dyy = 0; dyy < 2; ++dyy)
+        for (int dxx = 0; dxx < 2; ++dxx) {
+          const int h = 2 * hc + dyy, w = 2 * wc + dxx;
+          if (h < H && w < W)
+            *reinterpret_cast<uint4*>(dx + ((b * H + h) * W + w) * static_cast<long long>(dx_pitch) + c8 * 8) = zero;
+        }
+      continue;
+    }
+    const __nv_bfloat16* px = x + ((b * H + 2 * hc) * W + 2 * wc) * static_cast<long long>(x_pitch) + c8 * 8;
+    float v[4][8], g[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(px)), v[0]);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(px + x_pitch)), v[1]);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(px + static_cast<long long>(W) * x_pitch)), v[2]);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(px + static_cast<long long>(W + 1) * x_pitch)), v[3]);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(dy + ((b * Ho + hc) * Wo + wc) * static_cast<long long>(dy_pitch) + c8 * 8)), g);
+    float o[4][8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      int arg = 0;
+      float m = v[0][k];
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (v[q][k] > m) { m = v[q][k]; arg = q; }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q][k] = (q == arg) ? g[k] : 0.f;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 r;
+      __nv_bfloat162* rh = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) rh[k] = __floats2bfloat162_rn(o[q][2 * k], o[q][2 * k + 1]);
+      const int h = 2 * hc + (q >> 1), w = 2 * wc + (q & 1);
+      *reinterpret_cast<uint4*>(dx + ((b * H + h) * W + w) * static_cast<long long>(dx_pitch) + c8 * 8) = r;
+    }
+  }
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_maxpool2_fwd(const void* x, int x_pitch, void* y, int y_pitch, int B, int H, int W, int C,
+                                void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && y && B > 0 && H >= 2 && W >= 2 && C > 0 && C % 8 == 0, "maxpool2_fwd: bad args");
+  S2P_CHECK_ARG(x_pitch >= C && x_pitch % 8 == 0 && y_pitch >= C && y_pitch % 8 == 0, "maxpool2_fwd: pitch");
+  const long long total = static_cast<long long>(B) * (H / 2) * (W / 2) * (C / 8);
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  maxpool2_fwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), x_pitch, static_cast<__nv_bfloat16*>(y), y_pitch, B, H, W, C);
+  count_launch();
+  return check_launch("maxpool2_fwd_kernel");
+}
+
+extern "C" int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, void* dx, int dx_pitch, int B,
+                                int H, int W, int C, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy && x && dx && B > 0 && H >= 2 && W >= 2 && C > 0 && C % 8 == 0, "maxpool2_bwd: bad args");
+  S2P_CHECK_ARG(x_pitch >= C && x_pitch % 8 == 0 && dy_pitch >= C && dy_pitch % 8 == 0 && dx_pitch >= C && dx_pitch % 8 == 0,
+                "maxpool2_bwd: pitch");
+  const long long total = static_cast<long long>(B) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  maxpool2_bwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), dy_pitch, static_cast<const __nv_bfloat16*>(x), x_pitch,
+      static_cast<__nv_bfloat16*>(dx), dx_pitch, B, H, W, C);
+  count_launch();
+  return check_launch("maxpool2_bwd_kernel");
+}

@@ -384,3 +384,24 @@ def act_bwd_bias_grad(dy, y, act, want_bias_grad=True):
                                          out.data_ptr() if act != ACT_NONE else 0, c, _ptr(db), _ptr(partial),
                                          b * h * w, c, _stream()), "s2p_act_bwd_bias_grad")
     return out, db
+
+
+def maxpool2(x, out=None):
+    """nn.MaxPool2d(2, 2) on NHWC bf16"""
+    _require_cuda(x, out)
+    b, h, w, c = x.shape
+    if out is None:
+        out = torch.empty(b, h // 2, w // 2, c, dtype=torch.bfloat16, device=x.device)
+    _lib.check(_lib.load().s2p_maxpool2_fwd(x.data_ptr(), _nhwc_pitch(x, "x"), out.data_ptr(), _nhwc_pitch(out, "out"),
+                                            b, h, w, c, _stream()), "s2p_maxpool2_fwd")
+    return out
+
+
+def maxpool2_bwd(dy, x):
+    """gradient of maxpool2 w.r.t. x (same shape as x, fully written)"""
+    _require_cuda(dy, x)
+    b, h, w, c = x.shape
+    dx = torch.empty(b, h, w, c, dtype=torch.bfloat16, device=x.device)
+    _lib.check(_lib.load().s2p_maxpool2_bwd(dy.data_ptr(), _nhwc_pitch(dy, "dy"), x.data_ptr(), _nhwc_pitch(x, "x"),
+                                            dx.data_ptr(), _nhwc_pitch(dx, "dx"), b, h, w, c, _stream()), "s2p_maxpool2_bwd")
+    return dx

@@ -1,5 +1,5 @@
 """GAN training step of train.py --netG=s2p (README.md:59): one generator step (L1 + hinge GAN +
-feature matching; rebuttal.md:71,131-135) then one discriminator step, SPADE Pix2PixTrainer order.
+feature matching + VGG19 perceptual when a `vgg` extractor is given; rebuttal.md:71,131-135) then one discriminator step, SPADE Pix2PixTrainer order.
 Mirrors oracle/s2p_oracle.py `training_step` (ORACLE_SPEC v1.1) term by term.
 
 Multi-GPU (BASELINE configs[4]): one process per GPU, data parallel; after each backward the
@@ -78,21 +78,25 @@ def hinge_d_loss(pred_real, pred_fake):
     return loss / len(pred_real)
 
 
-def generator_losses(pred_fake, pred_real, fake, real):
+def generator_losses(pred_fake, pred_real, fake, real, vgg=None):
     num_d = len(pred_fake)
     gan = sum(-f[-1].float().mean() for f in pred_fake) / num_d
     feat = 0.0
     for f, r in zip(pred_fake, pred_real):
         for a, b in zip(f[:-1], r[:-1]):
             feat = feat + F.l1_loss(a.float(), b.detach().float()) * LAMBDA_FEAT / num_d
-    return {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+    losses = {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
+    if vgg is not None:
+        from .networks.vgg import LAMBDA_VGG, vgg_loss
+        losses["VGG"] = vgg_loss(vgg, fake, real) * LAMBDA_VGG
+    return losses
 
 
 class S2PTrainer:
     """run_generator_one_step / run_discriminator_one_step, as SPADE's Pix2PixTrainer."""
 
-    def __init__(self, netG, netD, lr=2e-4, betas=(0.0, 0.9), world_size=1):
-        self.netG, self.netD = netG, netD
+    def __init__(self, netG, netD, lr=2e-4, betas=(0.0, 0.9), world_size=1, vgg=None):
+        self.netG, self.netD, self.vgg = netG, netD, vgg
         self.optG = FusedAdam(netG.parameters(), lr, betas)
         self.optD = FusedAdam(netD.parameters(), lr, betas)
         self.world_size = world_size
@@ -109,7 +113,7 @@ class S2PTrainer:
         pred_fake, pred_real = self._d(prev_image, fake, real_image)
         for p in self.optD.params:
             p.requires_grad_(True)
-        losses = generator_losses(pred_fake, pred_real, fake, real_image)
+        losses = generator_losses(pred_fake, pred_real, fake, real_image, self.vgg)
         self.optG.zero_grad()
         sum(losses.values()).backward()
         if self.world_size > 1:

@@ -22,12 +22,14 @@ ap.add_argument("--env", type=str, default="walker")
 ap.add_argument("--profile", action="store_true")
 ap.add_argument("--no-oracle", action="store_true")
 ap.add_argument("--graph", action="store_true")
+ap.add_argument("--no-vgg", action="store_true")
 a = ap.parse_args()
 B = a.batch
 torch.manual_seed(1234)
 opt = s2p_b200.make_options(env_type=a.env, gpu_ids="0", init_type="scaled")
 nG, nD = s2p_b200.define_G(opt), s2p_b200.define_D(opt)
-tr = S2PTrainer(nG, nD)
+nV = None if a.no_vgg else s2p_b200.VGG19FeaturesB200().cuda()
+tr = S2PTrainer(nG, nD, vgg=nV)
 g = torch.Generator().manual_seed(0)
 prev = (torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).cuda()
 real = (torch.rand(B, 3, 100, 100, generator=g) * 2 - 1).cuda()
@@ -70,12 +72,13 @@ if not a.no_oracle:
     oD = O.define_D(O.make_options(init_type="scaled")).cuda()
     optG = torch.optim.Adam(oG.parameters(), **O.ADAM)
     optD = torch.optim.Adam(oD.parameters(), **O.ADAM)
-    ms_o = timed(lambda: O.training_step(oG, oD, optG, optD, prev, state, real), max(2, a.steps // 2), 2)
+    oV = None if a.no_vgg else O.VGG19Features().cuda()
+    ms_o = timed(lambda: O.training_step(oG, oD, optG, optD, prev, state, real, vgg=oV), max(2, a.steps // 2), 2)
     print(f"oracle eager PyTorch (TF32 cuDNN): {ms_o:.2f} ms/step  {B / ms_o * 1e3:.1f} frames/s")
 
     def amp_step():
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            return O.training_step(oG, oD, optG, optD, prev, state, real)
+            return O.training_step(oG, oD, optG, optD, prev, state, real, vgg=oV)
     try:
         ms_a = timed(amp_step, max(2, a.steps // 2), 2)
         print(f"oracle eager PyTorch (bf16 autocast): {ms_a:.2f} ms/step  {B / ms_a * 1e3:.1f} frames/s")
