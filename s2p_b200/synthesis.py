@@ -108,3 +108,29 @@ class BulkSynthesizer:
         lo, hi = shard_range(frames.shape[0], rank, world)
         res = self.synthesize(frames[lo:hi], states[lo:hi], out)
         return lo, hi, res
+
+
+def synthesize_augmented_dataset(netG, transition_model, dataset, normalize_configs, act_low, act_high, rng=np.random,
+                                 batch: int = 1024):
+    """The whole "generation code" the reference leaves as a TODO (/root/reference/README.md:54), end to end on the
+    GPU: state-transition rollout (state_transition_rollout.py:134-229, ``transition.generate_rollout``) -> S2P
+    generator on (image_observations[i], predicted next_observations[i]) -> the ``..._dataset_augment.hdf5``
+    key set the SLAC loader reads (rlkit/torch/slac/algo.py:183-204).
+
+    ``dataset``: dict of host arrays in the real dataset's schema (observations, actions, rewards, timeouts,
+    image_observations uint8 HWC, ...).  Returns a dict of host arrays; rows after the last timeout are dropped
+    as in the reference's rollout script."""
+    from .transition import generate_rollout
+    roll = generate_rollout(transition_model, dataset["observations"], dataset["timeouts"], normalize_configs, act_low,
+                            act_high, rng)
+    n = roll["actions"].shape[0]
+    out = {k: np.asarray(v)[:n] for k, v in dataset.items()}
+    out["original_actions"] = np.asarray(dataset["actions"])[:n]       # state_transition_rollout.py:70-71
+    out["original_rewards"] = np.asarray(dataset["rewards"])[:n]
+    out.update(roll)                                                    # :222-229
+    frames = torch.from_numpy(np.ascontiguousarray(out["image_observations"]))
+    states = torch.from_numpy(np.ascontiguousarray(roll["next_observations"], dtype=np.float32))
+    tp1 = BulkSynthesizer(netG, batch=min(batch, n)).synthesize(frames, states)
+    torch.cuda.current_stream().synchronize()
+    out["image_observations_tp1"] = tp1.numpy()                         # what algo.py:175,190,336 consume
+    return out
