@@ -149,8 +149,13 @@ int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, cons
  * linear: y = act(x W^T + b), fp32 (oracle StateEncoder.layers, MAT.fc_gamma/fc_beta). */
 int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S, int n_freqs,
                        void* stream);
+/* K >= 1024 (only the backward of the batched state heads) runs split-K: partial sums in `workspace`
+ * (s2p_linear_workspace_floats floats, 0 when no split) combined in a fixed order; the split is a function of K
+ * only, so results never depend on the batch size.  workspace may be NULL when 0 floats are needed. */
+long long s2p_linear_workspace_floats(int B, int K, int N);
 int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
-                   int y_pitch, int B, int K, int N, int act, void* stream);
+                   int y_pitch, int B, int K, int N, int act, float* workspace, long long workspace_floats,
+                   void* stream);
 
 /* packed weight of the data-gradient convolution: dst[ci][R-1-r][S-1-s][co] = w[co][ci][r][s]
  * (bf16 rows of R*S*Cout), so dX = s2p_conv_igemm_fwd(dY (zero-inserted when stride 2), dst,
@@ -166,6 +171,12 @@ int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y, int y_pit
 /* ---- (a8) optimiser: torch.optim.Adam's update on fp32 tensors, one fused pass ------------ */
 int s2p_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);
+/* the same update for `count` (<= 64) tensors in ONE launch: param/grad/exp_avg/exp_avg_sq/n are HOST arrays of
+ * `count` device pointers / element counts (copied into the kernel's parameter space, so the call is
+ * CUDA-graph capturable); step count read from device memory. */
+int s2p_adam_step_multi(float* const* param, const float* const* grad, float* const* exp_avg, float* const* exp_avg_sq,
+                        const long long* n, int count, float lr, float beta1, float beta2, float eps,
+                        const int* step_dev, void* stream);
 /* same update with the step count read from device memory (CUDA-graph replayable) */
 int s2p_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                       float beta1, float beta2, float eps, const int* step_dev, void* stream);

@@ -44,7 +44,9 @@ SIGNATURES = {
     "s2p_act_bwd_bias_grad_chunks": (_i, []),
     "s2p_act_bwd_bias_grad": (_i, [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _vp, C.c_longlong, _i, _vp]),
     "s2p_pos_encode_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
-    "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2p_linear_workspace_floats": (C.c_longlong, [_i, _i, _i]),
+    "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.c_longlong, _vp]),
+    "s2p_adam_step_multi": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _vp]),
     "s2p_transition_member_floats": (C.c_longlong, [_i, _i, _i]),
     "s2p_ensemble_transition_fwd": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f,
                                          _vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),

@@ -29,7 +29,8 @@ __global__ void pos_encode_kernel(const float* __restrict__ state, float* __rest
 // y[B,N] = act(x[B,K] @ w[N,K]^T + bias).  64x64 tile, BK=16, 256 threads, 4x4 per thread.
 __global__ void __launch_bounds__(256)
 linear_kernel(const float* __restrict__ x, int x_pitch, const float* __restrict__ w,
-              const float* __restrict__ bias, float* __restrict__ y, int y_pitch, int B, int K, int N, int act) {
+              const float* __restrict__ bias, float* __restrict__ y, int y_pitch, int B, int K, int N, int act,
+              int k_per_split, float* __restrict__ partial) {
   __shared__ float xs[16][64 + 4];
   __shared__ float wsh[16][64 + 4];
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
@@ -39,12 +40,16 @@ linear_kernel(const float* __restrict__ x, int x_pitch, const float* __restrict_
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  for (int k0 = 0; k0 < K; k0 += 16) {
+  // split-K (gridDim.z > 1): this CTA sums k in [k_begin, k_end) into partial[z][B][N]; combined in a fixed
+  // order by linear_splitk_finalize_kernel (bit-stable, and the split depends on (K, N) only, never on B)
+  const int k_begin = blockIdx.z * k_per_split;
+  const int k_end = min(K, k_begin + k_per_split);
+  for (int k0 = k_begin; k0 < k_end; k0 += 16) {
     for (int i = threadIdx.x; i < 64 * 16; i += 256) {
       const int r = i / 16, kk = i % 16;
       const int k = k0 + kk;
-      xs[kk][r] = (m0 + r < B && k < K) ? x[static_cast<size_t>(m0 + r) * x_pitch + k] : 0.f;
-      wsh[kk][r] = (n0 + r < N && k < K) ? w[static_cast<size_t>(n0 + r) * K + k] : 0.f;
+      xs[kk][r] = (m0 + r < B && k < k_end) ? x[static_cast<size_t>(m0 + r) * x_pitch + k] : 0.f;
+      wsh[kk][r] = (n0 + r < N && k < k_end) ? w[static_cast<size_t>(n0 + r) * K + k] : 0.f;
     }
     __syncthreads();
 #pragma unroll
@@ -69,6 +74,10 @@ linear_kernel(const float* __restrict__ x, int x_pitch, const float* __restrict_
     for (int j = 0; j < 4; ++j) {
       const int n = n0 + tx * 4 + j;
       if (n >= N) continue;
+      if (partial != nullptr) {
+        partial[(static_cast<size_t>(blockIdx.z) * B + m) * N + n] = acc[i][j];
+        continue;
+      }
       float v = acc[i][j] + (bias ? bias[n] : 0.f);
       if (act == 2) v = v > 0.f ? v : 0.2f * v;
       else if (act == 1) v = fmaxf(v, 0.f);
@@ -76,6 +85,25 @@ linear_kernel(const float* __restrict__ x, int x_pitch, const float* __restrict_
     }
   }
 }
+
+__global__ void linear_splitk_finalize_kernel(const float* __restrict__ partial, int splits, const float* __restrict__ bias,
+                                             float* __restrict__ y, int y_pitch, int B, int N, int act) {
+  const long long total = static_cast<long long>(B) * N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = 0.f;
+    for (int z = 0; z < splits; ++z) v += partial[z * total + i];
+    const int n = static_cast<int>(i % N);
+    const long long m = i / N;
+    v += bias ? bias[n] : 0.f;
+    if (act == 2) v = v > 0.f ? v : 0.2f * v;
+    else if (act == 1) v = fmaxf(v, 0.f);
+    y[m * y_pitch + n] = v;
+  }
+}
+
+// split count: a function of (K, N) only, so a row's summation order never depends on the batch
+static inline int linear_splits(int K) { return K >= 1024 ? (K / 512 < 16 ? K / 512 : 16) : 1; }
 
 // OIHW fp32 -> [Cout][R][S][Cin] bf16
 __global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Cout,
@@ -135,16 +163,39 @@ extern "C" int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, i
   return check_launch("pos_encode_kernel");
 }
 
+extern "C" long long s2p_linear_workspace_floats(int B, int K, int N) {
+  if (B <= 0 || K <= 0 || N <= 0) return -1;
+  const int splits = s2p::linear_splits(K);
+  return splits > 1 ? static_cast<long long>(splits) * B * N : 0;
+}
+
 extern "C" int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
-                              int y_pitch, int B, int K, int N, int act, void* stream) {
+                              int y_pitch, int B, int K, int N, int act, float* workspace, long long workspace_floats,
+                              void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w && y, "linear: null pointer");
   S2P_CHECK_ARG(B > 0 && K > 0 && N > 0 && x_pitch >= K && y_pitch >= N, "linear: bad dims");
   S2P_CHECK_ARG(act >= 0 && act <= 2, "linear: act=%d", act);
-  dim3 grid((N + 63) / 64, (B + 63) / 64);
-  linear_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, x_pitch, w, bias, y, y_pitch, B, K, N, act);
+  const int splits = linear_splits(K);
+  const long long need = s2p_linear_workspace_floats(B, K, N);
+  S2P_CHECK_ARG(need == 0 || (workspace && workspace_floats >= need), "linear: workspace of %lld floats needed (K=%d)", need, K);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  dim3 grid((N + 63) / 64, (B + 63) / 64, splits);
+  if (splits == 1) {
+    linear_kernel<<<grid, 256, 0, st>>>(x, x_pitch, w, bias, y, y_pitch, B, K, N, act, K, nullptr);
+    count_launch();
+    return check_launch("linear_kernel");
+  }
+  const int kps = (((K + splits - 1) / splits) + 15) / 16 * 16;
+  linear_kernel<<<grid, 256, 0, st>>>(x, x_pitch, w, bias, y, y_pitch, B, K, N, act, kps, workspace);
   count_launch();
-  return check_launch("linear_kernel");
+  int rc = check_launch("linear_kernel");
+  if (rc != S2P_OK) return rc;
+  const long long total = static_cast<long long>(B) * N;
+  const int blocks = static_cast<int>((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+  linear_splitk_finalize_kernel<<<blocks, 256, 0, st>>>(workspace, splits, bias, y, y_pitch, B, N, act);
+  count_launch();
+  return check_launch("linear_splitk_finalize_kernel");
 }
 
 extern "C" int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S, float scale,

@@ -72,12 +72,55 @@ act_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, const 
   }
 }
 
-__global__ void colsum_finalize_kernel(const float* __restrict__ partial, int chunks, float* __restrict__ out, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// blockDim = (32 channels, 8 slices): slice k sums chunks k, k+8, ... in fp64, the 8 slices are then combined in
+// a fixed order (bit-stable; 8x the memory parallelism of one serial walk over up to 592 chunks)
+__global__ void __launch_bounds__(256)
+colsum_finalize_kernel(const float* __restrict__ partial, int chunks, float* __restrict__ out, int C) {
+  __shared__ double red[8][32];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   double s = 0.0;
-  for (int k = 0; k < chunks; ++k) s += static_cast<double>(partial[static_cast<size_t>(k) * C + c]);
-  out[c] = static_cast<float>(s);
+  if (c < C)
+    for (int k = threadIdx.y; k < chunks; k += 8) s += static_cast<double>(partial[static_cast<size_t>(k) * C + c]);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    out[c] = static_cast<float>(t);
+  }
+}
+
+// torch.optim.Adam's update for up to kAdamMulti tensors in one launch: blockIdx.y = tensor
+constexpr int kAdamMulti = 64;
+struct AdamMultiArgs {
+  float* p[kAdamMulti];
+  const float* g[kAdamMulti];
+  float* m[kAdamMulti];
+  float* v[kAdamMulti];
+  long long n[kAdamMulti];
+};
+
+__global__ void adam_step_multi_kernel(const __grid_constant__ AdamMultiArgs a, float lr, float b1, float b2, float eps,
+                                       const int* __restrict__ step_dev) {
+  const int t = blockIdx.y;
+  const float step = static_cast<float>(*step_dev);
+  const float bc1 = 1.f - powf(b1, step);
+  const float bc2_sqrt = sqrtf(1.f - powf(b2, step));
+  float* __restrict__ p = a.p[t];
+  const float* __restrict__ g = a.g[t];
+  float* __restrict__ m = a.m[t];
+  float* __restrict__ v = a.v[t];
+  const long long n = a.n[t];
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= (lr / bc1) * (mi / (sqrtf(vi) / bc2_sqrt + eps));
+  }
 }
 
 __global__ void adam_step_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
@@ -139,7 +182,7 @@ extern "C" int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y
   count_launch();
   int rc = check_launch("act_bwd_colsum_kernel");
   if (rc != S2P_OK || bias_grad == nullptr) return rc;
-  colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, static_cast<int>(chunks), bias_grad, C);
+  colsum_finalize_kernel<<<(C + 31) / 32, dim3(32, 8), 0, st>>>(partial, static_cast<int>(chunks), bias_grad, C);
   count_launch();
   return check_launch("colsum_finalize_kernel");
 }
@@ -282,4 +325,26 @@ extern "C" int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int
       static_cast<__nv_bfloat16*>(dx), dx_pitch, B, H, W, C);
   count_launch();
   return check_launch("maxpool2_bwd_kernel");
+}
+
+extern "C" int s2p_adam_step_multi(float* const* param, const float* const* grad, float* const* exp_avg,
+                                   float* const* exp_avg_sq, const long long* n, int count, float lr, float beta1,
+                                   float beta2, float eps, const int* step_dev, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && n && step_dev, "adam_step_multi: null pointer");
+  S2P_CHECK_ARG(count >= 1 && count <= kAdamMulti, "adam_step_multi: count=%d (1..%d)", count, kAdamMulti);
+  AdamMultiArgs a;
+  long long nmax = 0;
+  for (int i = 0; i < count; ++i) {
+    S2P_CHECK_ARG(param[i] && grad[i] && exp_avg[i] && exp_avg_sq[i] && n[i] > 0, "adam_step_multi: tensor %d", i);
+    a.p[i] = param[i]; a.g[i] = grad[i]; a.m[i] = exp_avg[i]; a.v[i] = exp_avg_sq[i]; a.n[i] = n[i];
+    if (n[i] > nmax) nmax = n[i];
+  }
+  for (int i = count; i < kAdamMulti; ++i) { a.p[i] = nullptr; a.g[i] = nullptr; a.m[i] = nullptr; a.v[i] = nullptr; a.n[i] = 0; }
+  int bx = static_cast<int>((nmax + 1023) / 1024);
+  if (bx > 64) bx = 64;
+  if (bx < 1) bx = 1;
+  adam_step_multi_kernel<<<dim3(bx, count), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, lr, beta1, beta2, eps, step_dev);
+  count_launch();
+  return check_launch("adam_step_multi_kernel");
 }

@@ -328,9 +328,37 @@ def linear(x, w, bias, act=ACT_NONE, out=None):
         out = torch.empty(b, n, dtype=torch.float32, device=x.device)
     if x.dtype != torch.float32 or w.dtype != torch.float32 or not w.is_contiguous() or x.stride(1) != 1:
         raise RuntimeError("linear: fp32 row-major operands required")
-    _lib.check(_lib.load().s2p_linear_fwd(x.data_ptr(), x.stride(0), w.data_ptr(), _ptr(bias), out.data_ptr(),
-                                          out.stride(0), b, k, n, act, _stream()), "s2p_linear_fwd")
+    lib = _lib.load()
+    need = int(lib.s2p_linear_workspace_floats(b, k, n))
+    ws = None
+    if need > 0:
+        ws = _linear_ws.get(x.device)
+        if ws is None or ws.numel() < need:
+            ws = torch.empty(need, dtype=torch.float32, device=x.device)
+            _linear_ws[x.device] = ws
+    _lib.check(lib.s2p_linear_fwd(x.data_ptr(), x.stride(0), w.data_ptr(), _ptr(bias), out.data_ptr(),
+                                  out.stride(0), b, k, n, act, _ptr(ws), need, _stream()), "s2p_linear_fwd")
     return out
+
+
+_linear_ws = {}
+
+
+def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps, step_dev):
+    """torch.optim.Adam update of many fp32 tensors, 64 per launch"""
+    import ctypes
+    lib = _lib.load()
+    for i in range(0, len(params), 64):
+        chunk = range(i, min(i + 64, len(params)))
+        cnt = len(chunk)
+        arr = lambda ts: (ctypes.c_void_p * cnt)(*[ts[j].data_ptr() for j in chunk])
+        ns = (ctypes.c_longlong * cnt)(*[params[j].numel() for j in chunk])
+        for j in chunk:
+            if grads[j].dtype != torch.float32 or not grads[j].is_contiguous() or not params[j].is_contiguous():
+                raise RuntimeError("adam_step_multi: contiguous fp32 tensors required")
+        _lib.check(lib.s2p_adam_step_multi(arr(params), arr(grads), arr(exp_avgs), arr(exp_avg_sqs), ns, cnt, float(lr),
+                                           float(beta1), float(beta2), float(eps), step_dev.data_ptr(), _stream()),
+                   "s2p_adam_step_multi")
 
 
 def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):

@@ -17,7 +17,7 @@ LAMBDA_L1 = 10.0
 
 
 class FusedAdam:
-    """Adam(lr, betas, eps) with torch.optim.Adam's update rule, one fused kernel per tensor.  The
+    """Adam(lr, betas, eps) with torch.optim.Adam's update rule, one fused launch per 64 tensors.  The
     step count lives in device memory so that a captured CUDA graph of the step stays valid."""
 
     def __init__(self, params, lr=2e-4, betas=(0.0, 0.9), eps=1e-8):
@@ -39,10 +39,11 @@ class FusedAdam:
     @torch.no_grad()
     def step(self):
         self.step_dev += 1
-        for p, m, v in zip(self.params, self.m, self.v):
-            if p.grad is None:
-                continue
-            ops.adam_step_dev(p, p.grad, m, v, self.lr, self.betas[0], self.betas[1], self.eps, self.step_dev)
+        live = [(p, p.grad if p.grad.is_contiguous() else p.grad.contiguous(), m, v)
+                for p, m, v in zip(self.params, self.m, self.v) if p.grad is not None]
+        if live:
+            ps, gs, ms, vs = zip(*live)
+            ops.adam_step_multi(ps, gs, ms, vs, self.lr, self.betas[0], self.betas[1], self.eps, self.step_dev)
 
 
 def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
