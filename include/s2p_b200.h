@@ -149,9 +149,10 @@ int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, cons
  * linear: y = act(x W^T + b), fp32 (oracle StateEncoder.layers, MAT.fc_gamma/fc_beta). */
 int s2p_pos_encode_fwd(const float* state, float* pe, int pe_pitch, int B, int S, int n_freqs,
                        void* stream);
-/* K >= 1024 (only the backward of the batched state heads) runs split-K: partial sums in `workspace`
- * (s2p_linear_workspace_floats floats, 0 when no split) combined in a fixed order; the split is a function of K
- * only, so results never depend on the batch size.  workspace may be NULL when 0 floats are needed. */
+/* K >= 256 runs split-K (4 ways; K/512 <= 16 ways from K = 1024, the backward of the batched state heads): the
+ * layers are skinny (batch x 512) and latency-bound on a serial K walk.  Partial sums go to `workspace`
+ * (s2p_linear_workspace_floats floats, 0 when no split) and are combined in a fixed order; the split is a
+ * function of K only, so results never depend on the batch size.  workspace may be NULL when 0 floats are needed. */
 long long s2p_linear_workspace_floats(int B, int K, int N);
 int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
                    int y_pitch, int B, int K, int N, int act, float* workspace, long long workspace_floats,

@@ -28,10 +28,11 @@ class ConvFn(torch.autograd.Function):
     """y = act(conv(x, W) + b + residual); x, residual, y NHWC bf16; W fp32 OIHW, b fp32."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, stride, act, stats, pad):
+    def forward(ctx, x, weight, bias, residual, stride, act, stats, pad, packed=None):
         cout, cin, k, _ = weight.shape
         pad = k // 2 if pad is None else pad
-        wp = ops.pack_conv_weight(weight)
+        ctx.packed = packed          # (fwd, dgrad) packed weights of a FROZEN layer, built once by the caller
+        wp = packed[0] if packed is not None else ops.pack_conv_weight(weight)
         y = ops.conv_igemm(x, wp, None if bias is None else bias.detach().float().contiguous(), cout, k, stride, act,
                            residual, None, stats, pad)
         ctx.save_for_backward(x, weight, y if act != ACT_NONE else None)
@@ -56,16 +57,17 @@ class ConvFn(torch.autograd.Function):
                 g = torch.zeros(b, x.shape[1] + 2 * pad - k + 1, x.shape[2] + 2 * pad - k + 1, cout, dtype=dy.dtype,
                                 device=dy.device)
                 g[:, 0:2 * ho:2, 0:2 * wo:2] = dy
-            dx = ops.conv_igemm(g, ops.pack_conv_weight_dgrad(weight), None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
+            wd = ctx.packed[1] if ctx.packed is not None else ops.pack_conv_weight_dgrad(weight)
+            dx = ops.conv_igemm(g, wd, None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
         if ctx.needs_input_grad[1]:
             dw = ops.conv_wgrad(x, dy, k, stride, pad)
         if has_res and ctx.needs_input_grad[3]:
             dres = dy
-        return dx, dw, db, dres, None, None, None, None
+        return dx, dw, db, dres, None, None, None, None, None
 
 
-def conv(x, weight, bias=None, residual=None, stride=1, act=ACT_NONE, stats=None, pad=None):
-    return ConvFn.apply(x, weight, bias, residual, stride, act, stats, pad)
+def conv(x, weight, bias=None, residual=None, stride=1, act=ACT_NONE, stats=None, pad=None, packed=None):
+    return ConvFn.apply(x, weight, bias, residual, stride, act, stats, pad, packed)
 
 
 class MatNormFn(torch.autograd.Function):

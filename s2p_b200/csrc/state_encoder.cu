@@ -103,7 +103,7 @@ __global__ void linear_splitk_finalize_kernel(const float* __restrict__ partial,
 }
 
 // split count: a function of (K, N) only, so a row's summation order never depends on the batch
-static inline int linear_splits(int K) { return K >= 1024 ? (K / 512 < 16 ? K / 512 : 16) : 1; }
+static inline int linear_splits(int K) { return K >= 1024 ? (K / 512 < 16 ? K / 512 : 16) : (K >= 256 ? 4 : 1); }
 
 // OIHW fp32 -> [Cout][R][S][Cin] bf16
 __global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Cout,

@@ -18,6 +18,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import autograd as A
+from .. import ops
 from ..ops import ACT_RELU
 
 VGG19_CFG = [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512]
@@ -47,6 +48,21 @@ class VGG19FeaturesB200(nn.Module):
                     m.bias.zero_()
         for p in self.parameters():
             p.requires_grad_(False)
+        self._packs, self._packs_key = None, None
+
+    def _packed(self):
+        """(padded weight, (fwd pack, dgrad pack)) per conv -- the extractor is frozen, so packed once per state_dict"""
+        convs = [m for m in self.features if isinstance(m, nn.Conv2d)]
+        key = tuple((c.weight.data_ptr(), c.weight._version) for c in convs)
+        if self._packs is None or key != self._packs_key:
+            packs = []
+            for c in convs:
+                w = c.weight.detach()
+                if w.shape[1] % 64:
+                    w = F.pad(w, (0, 0, 0, 0, 0, 64 - w.shape[1] % 64))
+                packs.append((w, (ops.pack_conv_weight(w), ops.pack_conv_weight_dgrad(w))))
+            self._packs, self._packs_key = packs, key
+        return self._packs
 
     def forward(self, image):
         """image: fp32 NCHW [B,3,H,W] in [-1,1] -> five NHWC bf16 feature maps (relu1_1 ... relu5_1)"""
@@ -56,6 +72,7 @@ class VGG19FeaturesB200(nn.Module):
         pad = torch.zeros(B, h, w, 64 - c, dtype=torch.bfloat16, device=image.device)
         x = torch.cat([image.permute(0, 2, 3, 1).to(torch.bfloat16), pad], dim=3)   # 3 -> 64 zero-padded channels
         outs = []
+        packs = iter(self._packed())
         i = 0
         while i < len(self.features):
             m = self.features[i]
@@ -63,10 +80,8 @@ class VGG19FeaturesB200(nn.Module):
                 x = A.maxpool2(x)
                 i += 1
             else:
-                wgt = m.weight
-                if wgt.shape[1] % 64:
-                    wgt = F.pad(wgt, (0, 0, 0, 0, 0, 64 - wgt.shape[1] % 64))
-                x = A.conv(x, wgt, m.bias, None, 1, ACT_RELU, None, 1)
+                wgt, pk = next(packs)
+                x = A.conv(x, wgt, m.bias, None, 1, ACT_RELU, None, 1, pk)
                 i += 2                                                             # conv + its ReLU
             if i in VGG_SLICE_ENDS:
                 outs.append(x)
