@@ -244,6 +244,11 @@ def run_b200(args):
             line["training_step"] = train_side_measurement(torch, s2p_b200, dev)
         except Exception as e:  # noqa: BLE001  (a side measurement must never cost the headline line)
             line["training_step"] = {"error": repr(e)[:200]}
+    if world == 1 and not args.no_train:
+        try:
+            line["adjacent_components"] = adjacent_side_measurements(torch, dev)
+        except Exception as e:  # noqa: BLE001
+            line["adjacent_components"] = {"error": repr(e)[:200]}
     if world == 1 and not args.no_cpu_baseline:
         best, mean, threads, times = cpu_oracle_fps(args.cpu_sample, 2)
         line["cpu_baseline"] = {"value": best, "unit": UNIT, "cores": threads, "kind": "port",
@@ -252,6 +257,70 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def adjacent_side_measurements(torch, dev):
+    """SURVEY.md section 8 f rows either side of the generator, timed with CUDA events beside the headline:
+    state-transition producer (1M rows, one launch), SLAC window gather (HBM roofline) and SLAC encoder straight
+    from the resident uint8 dataset."""
+    import numpy as np
+    from s2p_b200.networks.slac_encoder import SlacEncoderB200
+    from s2p_b200.slac_buffer import SlacReplayBufferB200
+    from s2p_b200.transition import EnsembleTransitionB200
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+
+    def timed(fn, reps=5, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    out = {}
+    T = 1_000_000
+    torch.manual_seed(0)
+    tm = EnsembleTransitionB200(17, 6, 256, 3).to(dev)
+    norm = dict(obs_mean=np.zeros(17, np.float32), obs_std=np.ones(17, np.float32), next_obs_mean=np.zeros(17, np.float32),
+                next_obs_std=np.ones(17, np.float32), reward_mean=0.0, reward_std=1.0)
+    obs, act = torch.randn(T, 17, device=dev), torch.rand(T, 6, device=dev) * 2 - 1
+    idx = torch.randint(0, 7, (T,), device=dev, dtype=torch.int32)
+    ms = timed(lambda: tm.rollout_rows(obs, act, idx, norm))
+    flops = 2.0 * T * 7 * (32 * 256 + 2 * 256 * 256 + 256 * 64)
+    out["state_transition_producer"] = {
+        "kernel": "ensemble_transition_kernel (7 x MLP 23-256-256-256-36 + selection + uncertainties, fp32 CUDA cores)",
+        "rows": T, "ms": ms, "rows_per_sec": T / ms * 1e3, "fp32_tflops": flops / ms / 1e9, "launches_per_call": 1}
+    del obs, act, idx
+    N, Bw = 40_000, 1024
+    buf = SlacReplayBufferB200(N, 8, (3, 100, 100), (6,), dev)
+    buf.frames = torch.randint(0, 256, (N, 100, 100, 3), dtype=torch.uint8, device=dev)
+    buf.frames_tp1 = torch.randint(0, 256, (N, 100, 100, 3), dtype=torch.uint8, device=dev)
+    rows = torch.arange(8, N, device=dev)
+    buf.codes = torch.cat([2 * (rows.unsqueeze(1) - 8 + torch.arange(8, device=dev)), (2 * (rows - 1) + 1).unsqueeze(1)], 1)
+    buf._n = buf.codes.shape[0]
+    pick = np.random.RandomState(0).randint(0, buf._n, size=Bw)
+    ms = timed(lambda: buf.gather_states(pick), reps=10)
+    byts = Bw * 9 * 30000 * 5
+    out["slac_window_gather"] = {
+        "kernel": "window_gather_quad_kernel (gather + HWC->CHW + uint8->float/255; whole sample call incl. index upload)",
+        "batch": Bw, "frames": Bw * 9, "ms": ms, "bound": "hbm", "achieved": byts / ms / 1e6, "peak": hbm_peak, "unit": "GB/s",
+        "frac": byts / ms / 1e6 / hbm_peak, "bytes_per_frame": 150000}
+    enc = SlacEncoderB200(3, 256, 100).to(dev)
+    pick = pick[:256]
+    ms = timed(lambda: enc.forward_from_buffer(buf, pick), reps=10)
+    out["slac_encoder"] = {"kernel": "slac_conv1_kernel (uint8 gather fused) + 5 x conv_igemm_kernel", "batch": 256,
+                           "frames": 256 * 9, "ms": ms, "frames_per_sec": 256 * 9 / ms * 1e3}
+    return out
 
 
 def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):
