@@ -527,16 +527,17 @@ def run_train(args):
         frames = B * world * args.steps
         # algorithmic flops per frame: generator forward 112.9 GFLOP, its
         # backward = dgrad + wgrad = 2x; discriminator (fake+real forward, backward) ~ 3 % on top
-        flops_frame = 3 * 112.9e9 * 1.03
+        # G fwd+dgrad+wgrad (x1.03 for D) + VGG19 to relu5_1 (3.503 GMAC per image): fwd(fake) + fwd(real) + dgrad(fake)
+        flops_frame = 3 * 112.9e9 * 1.03 + 3 * 7.006e9
         ach = flops_frame * B / (ms_dev / args.steps / 1e3) / 1e12
         h2d = sum(t.numel() * t.element_size() for t in host)
         line = {"metric": "training_frames_per_sec", "value": frames / (ms_dev / 1e3), "unit": "frames/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": {"workload": "GAN training step (BASELINE configs[1]/[4]): generator step (L1 + hinge GAN + "
-                                       f"feature matching) + discriminator step + Adam, {env}, batch {B} per GPU",
+                                       f"feature matching + VGG19 perceptual) + discriminator step + Adam, {env}, batch {B} per GPU",
                            "env_type": env, "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
-                           "cuda_graph": use_graph, "weights": "random init ('scaled'), VGG term off (ORACLE_SPEC v1.1)"},
+                           "cuda_graph": use_graph, "weights": "random init ('scaled'); VGG19 extractor seeded random init (ORACLE_SPEC v1.2)"},
                 "e2e": {"value": frames / (ms_e2e / 1e3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4 * len(losses_host), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches) if not use_graph else None,
