@@ -240,6 +240,18 @@ int s2p_maxpool2_fwd(const void* x, int x_pitch, void* y, int y_pitch, int B, in
 int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, void* dx, int dx_pitch, int B, int H,
                      int W, int C, void* stream);
 
+/* ---- (a8) multi-tensor scale: the MAT blend factors applied to parameter tensors, and its backward ----
+ * replaces the per-tensor `weight * sigmoid(blend)` of oracle MAT.forward and autograd's MulBackward for it.
+ * fwd: dst[i][:] = src[i][:] * scales[scale_idx[i]] for `count` (<= 64) fp32 tensors in one launch (dst may point
+ * into a concatenated operand buffer).  bwd: dsrc[i] = dout[i] * scale and partial[i][b] (b < s2p_multi_scale_blocks())
+ * = per-block sums of dout[i] * src[i] in a fixed order (sum over b = gradient contribution to scales[scale_idx[i]]).
+ * src/dst/dout/n/scale_idx are HOST arrays (copied into the kernel's parameter space: graph-capturable). */
+int s2p_multi_scale_blocks(void);
+int s2p_multi_scale_fwd(const float* const* src, float* const* dst, const long long* n, const int* scale_idx, int count,
+                        const float* scales, void* stream);
+int s2p_multi_scale_bwd(const float* const* dout, const float* const* src, float* const* dsrc, const long long* n,
+                        const int* scale_idx, int count, const float* scales, float* partial, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

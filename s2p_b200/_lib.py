@@ -54,6 +54,9 @@ SIGNATURES = {
     "s2p_slac_conv1_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
     "s2p_maxpool2_fwd": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2p_maxpool2_bwd": (_i, [_vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2p_multi_scale_blocks": (_i, []),
+    "s2p_multi_scale_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "s2p_multi_scale_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "s2p_slac_indices": (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_longlong, _vp]),
 }
 

@@ -122,6 +122,43 @@ def linear(x, weight, bias=None, act=ACT_NONE):
     return LinearFn.apply(x, weight, bias, act)
 
 
+class MultiScaleFn(torch.autograd.Function):
+    """Scaled copies of many fp32 parameter tensors written straight into concatenated operand buffers:
+    out[g][off_i : off_i + n_i] = src_i * scales[k_i].  `plan` = (group_shapes, [(group, elem_offset, k)] per source,
+    onehot [K, n_src] fp32 on the device).  Backward: one multi-tensor launch for the parameter gradients plus
+    fixed-order partial dot products for d scales (oracle MAT.forward's `weight * sigmoid(blend)` and its MulBackward)."""
+
+    @staticmethod
+    def forward(ctx, scales, plan, *srcs):
+        shapes, where, onehot = plan
+        dev = scales.device
+        outs = [torch.empty(sh, dtype=torch.float32, device=dev) for sh in shapes]
+        scales = scales.contiguous()
+        srcs_c = [t.detach().contiguous() for t in srcs]
+        ops.multi_scale_fwd([t.data_ptr() for t in srcs_c], [outs[g].data_ptr() + 4 * off for g, off, _ in where],
+                            [t.numel() for t in srcs_c], [k for _, _, k in where], scales)
+        ctx.save_for_backward(scales, *srcs_c)
+        ctx.plan = plan
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gouts):
+        scales, *srcs = ctx.saved_tensors
+        shapes, where, onehot = ctx.plan
+        gouts = [torch.zeros(sh, dtype=torch.float32, device=scales.device) if g is None else g.contiguous().float()
+                 for g, sh in zip(gouts, shapes)]
+        dsrcs = [torch.empty_like(t) for t in srcs]
+        partial = torch.empty(len(srcs), ops.multi_scale_blocks(), dtype=torch.float32, device=scales.device)
+        ops.multi_scale_bwd([gouts[g].data_ptr() + 4 * off for g, off, _ in where], [t.data_ptr() for t in srcs],
+                            [t.data_ptr() for t in dsrcs], [t.numel() for t in srcs], [k for _, _, k in where], scales, partial)
+        dscales = onehot @ partial.sum(dim=1)
+        return (dscales, None, *dsrcs)
+
+
+def multi_scale(scales, plan, srcs):
+    return MultiScaleFn.apply(scales, plan, *srcs)
+
+
 class MaxPool2Fn(torch.autograd.Function):
     """nn.MaxPool2d(2, 2) on NHWC bf16 (VGG19 feature extractor of the perceptual loss)."""
 

@@ -348,3 +348,103 @@ extern "C" int s2p_adam_step_multi(float* const* param, const float* const* grad
   count_launch();
   return check_launch("adam_step_multi_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Multi-tensor scale (training glue): the MAT blend factors a = sigmoid(blend) scale whole parameter tensors
+// (gamma/beta conv weights by 1-a, state-head rows by a; oracle MAT.forward).  Done tensor by tensor in torch
+// this was ~480 tiny kernels per step (mul / sum of the forward and of MulBackward); here the forward is one
+// launch per 64 tensors writing straight into the concatenated operand buffers, and the backward one launch
+// producing the parameter gradients and fixed-order per-block partial dot products for the scale gradients.
+namespace s2p {
+
+constexpr int kScaleMulti = 64;
+constexpr int kScaleBlocks = 32;
+struct MultiScaleArgs {
+  const float* src[kScaleMulti];   // parameter tensor
+  float* dst[kScaleMulti];         // fwd: scaled copy;  bwd: gradient w.r.t. the parameter
+  const float* dout[kScaleMulti];  // bwd: gradient w.r.t. the scaled copy
+  long long n[kScaleMulti];
+  int sidx[kScaleMulti];           // index into scales[]
+};
+
+__global__ void __launch_bounds__(256) multi_scale_fwd_kernel(const __grid_constant__ MultiScaleArgs a,
+                                                              const float* __restrict__ scales) {
+  const int t = blockIdx.y;
+  const float s = scales[a.sidx[t]];
+  const float* __restrict__ src = a.src[t];
+  float* __restrict__ dst = a.dst[t];
+  const long long n = a.n[t];
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) dst[i] = src[i] * s;
+}
+
+// dst = dout * s;  partial[t][block] = sum over the block's elements of dout * src   (fixed order)
+__global__ void __launch_bounds__(256) multi_scale_bwd_kernel(const __grid_constant__ MultiScaleArgs a,
+                                                              const float* __restrict__ scales, float* __restrict__ partial) {
+  __shared__ float red[8];
+  const int t = blockIdx.y;
+  const float s = scales[a.sidx[t]];
+  const float* __restrict__ src = a.src[t];
+  const float* __restrict__ dout = a.dout[t];
+  float* __restrict__ dst = a.dst[t];
+  const long long n = a.n[t];
+  float acc = 0.f;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) {
+    const float g = dout[i];
+    dst[i] = g * s;
+    acc = fmaf(g, src[i], acc);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[w];
+    partial[t * kScaleBlocks + blockIdx.x] = v;
+  }
+}
+
+}  // namespace s2p
+
+static int multi_scale_fill(s2p::MultiScaleArgs& a, const float* const* src, float* const* dst, const float* const* dout,
+                            const long long* n, const int* sidx, int count) {
+  using namespace s2p;
+  S2P_CHECK_ARG(src && dst && n && sidx && count >= 1 && count <= kScaleMulti, "multi_scale: bad args (count=%d)", count);
+  for (int i = 0; i < kScaleMulti; ++i) {
+    const bool live = i < count;
+    if (live) S2P_CHECK_ARG(src[i] && dst[i] && n[i] > 0 && sidx[i] >= 0 && (!dout || dout[i]), "multi_scale: tensor %d", i);
+    a.src[i] = live ? src[i] : nullptr;
+    a.dst[i] = live ? dst[i] : nullptr;
+    a.dout[i] = (live && dout) ? dout[i] : nullptr;
+    a.n[i] = live ? n[i] : 0;
+    a.sidx[i] = live ? sidx[i] : 0;
+  }
+  return S2P_OK;
+}
+
+extern "C" int s2p_multi_scale_blocks(void) { return s2p::kScaleBlocks; }
+
+extern "C" int s2p_multi_scale_fwd(const float* const* src, float* const* dst, const long long* n, const int* scale_idx,
+                                   int count, const float* scales, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(scales != nullptr, "multi_scale_fwd: scales");
+  MultiScaleArgs a;
+  const int rc = multi_scale_fill(a, src, dst, nullptr, n, scale_idx, count);
+  if (rc != S2P_OK) return rc;
+  multi_scale_fwd_kernel<<<dim3(kScaleBlocks, count), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, scales);
+  count_launch();
+  return check_launch("multi_scale_fwd_kernel");
+}
+
+extern "C" int s2p_multi_scale_bwd(const float* const* dout, const float* const* src, float* const* dsrc, const long long* n,
+                                   const int* scale_idx, int count, const float* scales, float* partial, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(scales && partial && dout, "multi_scale_bwd: null pointer");
+  MultiScaleArgs a;
+  const int rc = multi_scale_fill(a, src, dsrc, dout, n, scale_idx, count);
+  if (rc != S2P_OK) return rc;
+  multi_scale_bwd_kernel<<<dim3(kScaleBlocks, count), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, scales, partial);
+  count_launch();
+  return check_launch("multi_scale_bwd_kernel");
+}

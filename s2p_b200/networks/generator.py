@@ -393,28 +393,49 @@ class S2PGeneratorB200(nn.Module):
             for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
                 hs[(bi, name)] = hsl
 
-        # state heads of all MATs as ONE linear (blend factors folded into the rows), then split
+        # blend factors of all MATs at once: scales = [a_0, c_0, a_1, ... | 1-a_0, 1-c_0, ...]; every scaled parameter
+        # tensor (state-head rows by a / c, gamma/beta conv weights by 1-a / 1-c) is produced by ONE multi-tensor launch
+        # per 64 tensors, written straight into the concatenated operands (A.MultiScaleFn)
         all_mats = [(bi, name, m) for bi, blk in enumerate(self.blocks()) for name, m in blk.mats()]
-        hw, hb = [], []
+        nm = len(all_mats)
+        bl = torch.sigmoid(torch.stack([p for _, _, m in all_mats for p in (m.blend_gamma, m.blend_beta)]).float())
+        scales = torch.cat([bl, 1.0 - bl])
+        plan = getattr(self, "_blend_plan", None)
+        if plan is None or plan[2].device != dev:
+            shapes, where = [(sum(2 * m.norm_nc for _, _, m in all_mats), opt.w_dim), (sum(2 * m.norm_nc for _, _, m in all_mats),)], []
+            off = 0
+            for i, (_, _, m) in enumerate(all_mats):          # sources in the order built below
+                C = m.norm_nc
+                where += [(0, off * opt.w_dim, 2 * i), (0, (off + C) * opt.w_dim, 2 * i + 1), (1, off, 2 * i), (1, off + C, 2 * i + 1)]
+                off += 2 * C
+            for i, (_, _, m) in enumerate(all_mats):
+                C = m.norm_nc
+                wn = m.mlp_gamma.weight[0].numel()
+                g = len(shapes)
+                shapes += [(2 * C,) + tuple(m.mlp_gamma.weight.shape[1:]), (2 * C,)]
+                where += [(g, 0, 2 * nm + 2 * i), (g, C * wn, 2 * nm + 2 * i + 1), (g + 1, 0, 2 * nm + 2 * i), (g + 1, C, 2 * nm + 2 * i + 1)]
+            onehot = torch.zeros(4 * nm, len(where), dtype=torch.float32, device=dev)
+            onehot[torch.tensor([k for _, _, k in where], device=dev), torch.arange(len(where), device=dev)] = 1.0
+            plan = (shapes, where, onehot)
+            self._blend_plan = plan
+        srcs = []
         for _, _, m in all_mats:
-            a = torch.sigmoid(m.blend_gamma)
-            c = torch.sigmoid(m.blend_beta)
-            hw += [m.fc_gamma.weight * a, m.fc_beta.weight * c]
-            hb += [m.fc_gamma.bias * a, m.fc_beta.bias * c]
-        gsbs_all = A.linear(wlat, torch.cat(hw, dim=0), torch.cat(hb, dim=0))
-        gsbs = {}
+            srcs += [m.fc_gamma.weight, m.fc_beta.weight, m.fc_gamma.bias, m.fc_beta.bias]
+        for _, _, m in all_mats:
+            srcs += [m.mlp_gamma.weight, m.mlp_beta.weight, m.mlp_gamma.bias, m.mlp_beta.bias]
+        scaled = A.multi_scale(scales, plan, srcs)
+        gsbs_all = A.linear(wlat, scaled[0], scaled[1])
+        gsbs, gbwb = {}, {}
         off = 0
-        for bi, name, m in all_mats:
+        for i, (bi, name, m) in enumerate(all_mats):
             C = m.norm_nc
             gsbs[(bi, name)] = (gsbs_all[:, off:off + C], gsbs_all[:, off + C:off + 2 * C])
+            gbwb[(bi, name)] = (scaled[2 + 2 * i], scaled[3 + 2 * i])
             off += 2 * C
 
         def mat(bi, name, m, xin, mr_in, up, act):
-            a = torch.sigmoid(m.blend_gamma)
-            c = torch.sigmoid(m.blend_beta)
             gs, bs = gsbs[(bi, name)]
-            gbw = torch.cat([m.mlp_gamma.weight * (1 - a), m.mlp_beta.weight * (1 - c)], dim=0)
-            gbb = torch.cat([m.mlp_gamma.bias * (1 - a), m.mlp_beta.bias * (1 - c)], dim=0)
+            gbw, gbb = gbwb[(bi, name)]
             gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb)
             return A.mat_norm(xin, mr_in, gs, bs, gb, up, act)
 

@@ -433,3 +433,36 @@ def maxpool2_bwd(dy, x):
     _lib.check(_lib.load().s2p_maxpool2_bwd(dy.data_ptr(), _nhwc_pitch(dy, "dy"), x.data_ptr(), _nhwc_pitch(x, "x"),
                                             dx.data_ptr(), _nhwc_pitch(dx, "dx"), b, h, w, c, _stream()), "s2p_maxpool2_bwd")
     return dx
+
+
+def multi_scale_blocks() -> int:
+    return int(_lib.load().s2p_multi_scale_blocks())
+
+
+def _ptr_array(ptrs):
+    import ctypes
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)
+
+
+def multi_scale_fwd(src_ptrs, dst_ptrs, numels, scale_idx, scales):
+    """dst_i = src_i * scales[scale_idx[i]] for raw fp32 device pointers, 64 tensors per launch"""
+    import ctypes
+    lib = _lib.load()
+    for i in range(0, len(src_ptrs), 64):
+        j = min(i + 64, len(src_ptrs))
+        _lib.check(lib.s2p_multi_scale_fwd(_ptr_array(src_ptrs[i:j]), _ptr_array(dst_ptrs[i:j]),
+                                           (ctypes.c_longlong * (j - i))(*numels[i:j]), (ctypes.c_int * (j - i))(*scale_idx[i:j]),
+                                           j - i, scales.data_ptr(), _stream()), "s2p_multi_scale_fwd")
+
+
+def multi_scale_bwd(dout_ptrs, src_ptrs, dsrc_ptrs, numels, scale_idx, scales, partial):
+    """dsrc_i = dout_i * scale; partial[i, :] = per-block sums of dout_i * src_i (fp32 [count, multi_scale_blocks()])"""
+    import ctypes
+    lib = _lib.load()
+    nb = multi_scale_blocks()
+    for i in range(0, len(src_ptrs), 64):
+        j = min(i + 64, len(src_ptrs))
+        _lib.check(lib.s2p_multi_scale_bwd(_ptr_array(dout_ptrs[i:j]), _ptr_array(src_ptrs[i:j]), _ptr_array(dsrc_ptrs[i:j]),
+                                           (ctypes.c_longlong * (j - i))(*numels[i:j]), (ctypes.c_int * (j - i))(*scale_idx[i:j]),
+                                           j - i, scales.data_ptr(), partial.data_ptr() + i * nb * 4, _stream()),
+                   "s2p_multi_scale_bwd")
