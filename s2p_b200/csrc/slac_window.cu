@@ -142,58 +142,43 @@ __global__ void __launch_bounds__(256) slac_conv1_kernel(const Conv1Params p) {
     patch[i] = v;
   }
   __syncthreads();
-  // a thread owns TWO output pixels (same column, rows oy and oy + rows_per_cta/2) x 32 channels: every weight
-  // float4 read from shared memory feeds 8 FMAs instead of 4 (the one-pixel form was LDS-bound: 9 LDS per 32 FFMA)
-  const int half = p.rows_per_cta / 2;
   const int px = threadIdx.x;
   const int oy = px / p.Wo, ox = px % p.Wo;
-  if (oy >= half) return;
-  const bool v0 = oy0 + oy < p.Ho, v1 = oy0 + oy + half < p.Ho;
-  if (!v0) return;
-  float acc0[kC1Out], acc1[kC1Out];
+  if (oy >= p.rows_per_cta || oy0 + oy >= p.Ho) return;
+  float acc[kC1Out];
 #pragma unroll
-  for (int j = 0; j < kC1Out; ++j) acc0[j] = acc1[j] = p.bias[j];
+  for (int j = 0; j < kC1Out; ++j) acc[j] = p.bias[j];
   for (int r = 0; r < kC1K; ++r) {
-    const float* in0 = patch + ((2 * oy + r) * pcol + 2 * ox) * 3;
-    const float* in1 = in0 + 2 * half * pcol * 3;
+    const float* prow_ptr = patch + ((2 * oy + r) * pcol + 2 * ox) * 3;
 #pragma unroll
     for (int sc = 0; sc < kC1K * 3; ++sc) {
-      const float a0 = in0[sc], a1 = in1[sc];
+      const float v = prow_ptr[sc];
       const float4* wv = reinterpret_cast<const float4*>(wsm + (r * kC1K * 3 + sc) * kC1Out);
 #pragma unroll
       for (int j = 0; j < kC1Out / 4; ++j) {
         const float4 w4 = wv[j];
-        acc0[4 * j + 0] = fmaf(a0, w4.x, acc0[4 * j + 0]);
-        acc0[4 * j + 1] = fmaf(a0, w4.y, acc0[4 * j + 1]);
-        acc0[4 * j + 2] = fmaf(a0, w4.z, acc0[4 * j + 2]);
-        acc0[4 * j + 3] = fmaf(a0, w4.w, acc0[4 * j + 3]);
-        acc1[4 * j + 0] = fmaf(a1, w4.x, acc1[4 * j + 0]);
-        acc1[4 * j + 1] = fmaf(a1, w4.y, acc1[4 * j + 1]);
-        acc1[4 * j + 2] = fmaf(a1, w4.z, acc1[4 * j + 2]);
-        acc1[4 * j + 3] = fmaf(a1, w4.w, acc1[4 * j + 3]);
+        acc[4 * j + 0] = fmaf(v, w4.x, acc[4 * j + 0]);
+        acc[4 * j + 1] = fmaf(v, w4.y, acc[4 * j + 1]);
+        acc[4 * j + 2] = fmaf(v, w4.z, acc[4 * j + 2]);
+        acc[4 * j + 3] = fmaf(v, w4.w, acc[4 * j + 3]);
       }
     }
   }
+  __nv_bfloat16* o = p.out + ((f * p.Ho + oy0 + oy) * p.Wo + ox) * static_cast<long long>(p.out_pitch);
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    if (q == 1 && !v1) break;
-    const float* acc = q ? acc1 : acc0;
-    __nv_bfloat16* o = p.out + ((f * p.Ho + oy0 + oy + q * half) * p.Wo + ox) * static_cast<long long>(p.out_pitch);
+  for (int j = 0; j < kC1Out / 8; ++j) {
+    uint32_t pk[4];
 #pragma unroll
-    for (int j = 0; j < kC1Out / 8; ++j) {
-      uint32_t pk[4];
-#pragma unroll
-      for (int h = 0; h < 4; ++h) {
-        float a = acc[8 * j + 2 * h], b = acc[8 * j + 2 * h + 1];
-        a = a > 0.f ? a : 0.2f * a;
-        b = b > 0.f ? b : 0.2f * b;
-        const __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-        pk[h] = *reinterpret_cast<const uint32_t*>(&t);
-      }
-      reinterpret_cast<uint4*>(o)[j] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    for (int h = 0; h < 4; ++h) {
+      float a = acc[8 * j + 2 * h], b = acc[8 * j + 2 * h + 1];
+      a = a > 0.f ? a : 0.2f * a;
+      b = b > 0.f ? b : 0.2f * b;
+      const __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+      pk[h] = *reinterpret_cast<const uint32_t*>(&t);
     }
-    for (int j = kC1Out / 8; j < 8; ++j) reinterpret_cast<uint4*>(o)[j] = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(o)[j] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   }
+  for (int j = kC1Out / 8; j < 8; ++j) reinterpret_cast<uint4*>(o)[j] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 }  // namespace sw
@@ -241,7 +226,7 @@ extern "C" int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_t
   p.out = static_cast<__nv_bfloat16*>(y); p.out_pitch = y_pitch; p.H = H; p.W = W;
   p.Ho = (H + 4 - 5) / 2 + 1; p.Wo = (W + 4 - 5) / 2 + 1;
   S2P_CHECK_ARG(p.Wo <= 256, "slac_conv1: W=%d too wide", W);
-  p.rows_per_cta = 2 * (256 / p.Wo);   // two output pixels per thread
+  p.rows_per_cta = 256 / p.Wo;
   const size_t smem = (sw::kC1Taps * sw::kC1Out + static_cast<size_t>(2 * p.rows_per_cta + 3) * (W + 4) * 3) * 4;
   if (smem > 200 * 1024) return set_error(S2P_ERR_UNSUPPORTED, "slac_conv1: %zu B of shared memory needed", smem);
   static size_t configured = 48 * 1024;
