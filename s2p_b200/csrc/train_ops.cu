@@ -91,19 +91,26 @@ colsum_finalize_kernel(const float* __restrict__ partial, int chunks, float* __r
   }
 }
 
-// torch.optim.Adam's update for up to kAdamMulti tensors in one launch: blockIdx.y = tensor
+// torch.optim.Adam's update for up to kAdamMulti tensors in one launch.  Blocks are dealt out in proportion to
+// tensor size (one block per kAdamChunk elements; first_block[] is the prefix sum), so a 2.4 M-element conv weight
+// and a 64-element bias in the same launch both run at full memory parallelism.
 constexpr int kAdamMulti = 64;
+constexpr int kAdamChunk = 8192;
 struct AdamMultiArgs {
   float* p[kAdamMulti];
   const float* g[kAdamMulti];
   float* m[kAdamMulti];
   float* v[kAdamMulti];
   long long n[kAdamMulti];
+  int first_block[kAdamMulti + 1];
+  int count;
 };
 
-__global__ void adam_step_multi_kernel(const __grid_constant__ AdamMultiArgs a, float lr, float b1, float b2, float eps,
-                                       const int* __restrict__ step_dev) {
-  const int t = blockIdx.y;
+__global__ void __launch_bounds__(256)
+adam_step_multi_kernel(const __grid_constant__ AdamMultiArgs a, float lr, float b1, float b2, float eps,
+                       const int* __restrict__ step_dev) {
+  int t = 0;
+  while (t + 1 < a.count && static_cast<int>(blockIdx.x) >= a.first_block[t + 1]) ++t;   // <= 64 steps, block-uniform
   const float step = static_cast<float>(*step_dev);
   const float bc1 = 1.f - powf(b1, step);
   const float bc2_sqrt = sqrtf(1.f - powf(b2, step));
@@ -111,9 +118,9 @@ __global__ void adam_step_multi_kernel(const __grid_constant__ AdamMultiArgs a, 
   const float* __restrict__ g = a.g[t];
   float* __restrict__ m = a.m[t];
   float* __restrict__ v = a.v[t];
-  const long long n = a.n[t];
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  const long long i0 = static_cast<long long>(blockIdx.x - a.first_block[t]) * kAdamChunk;
+  const long long i1 = (i0 + kAdamChunk < a.n[t]) ? i0 + kAdamChunk : a.n[t];
+  for (long long i = i0 + threadIdx.x; i < i1; i += 256) {
     const float gi = g[i];
     const float mi = b1 * m[i] + (1.f - b1) * gi;
     const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
@@ -334,17 +341,19 @@ extern "C" int s2p_adam_step_multi(float* const* param, const float* const* grad
   S2P_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && n && step_dev, "adam_step_multi: null pointer");
   S2P_CHECK_ARG(count >= 1 && count <= kAdamMulti, "adam_step_multi: count=%d (1..%d)", count, kAdamMulti);
   AdamMultiArgs a;
-  long long nmax = 0;
+  int blocks = 0;
   for (int i = 0; i < count; ++i) {
     S2P_CHECK_ARG(param[i] && grad[i] && exp_avg[i] && exp_avg_sq[i] && n[i] > 0, "adam_step_multi: tensor %d", i);
     a.p[i] = param[i]; a.g[i] = grad[i]; a.m[i] = exp_avg[i]; a.v[i] = exp_avg_sq[i]; a.n[i] = n[i];
-    if (n[i] > nmax) nmax = n[i];
+    a.first_block[i] = blocks;
+    const long long nb = (n[i] + kAdamChunk - 1) / kAdamChunk;
+    S2P_CHECK_ARG(blocks + nb < (1ll << 30), "adam_step_multi: too many elements");
+    blocks += static_cast<int>(nb);
   }
-  for (int i = count; i < kAdamMulti; ++i) { a.p[i] = nullptr; a.g[i] = nullptr; a.m[i] = nullptr; a.v[i] = nullptr; a.n[i] = 0; }
-  int bx = static_cast<int>((nmax + 1023) / 1024);
-  if (bx > 64) bx = 64;
-  if (bx < 1) bx = 1;
-  adam_step_multi_kernel<<<dim3(bx, count), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, lr, beta1, beta2, eps, step_dev);
+  for (int i = count; i < kAdamMulti; ++i) { a.p[i] = nullptr; a.g[i] = nullptr; a.m[i] = nullptr; a.v[i] = nullptr; a.n[i] = 0; a.first_block[i] = blocks; }
+  a.first_block[kAdamMulti] = blocks;
+  a.count = count;
+  adam_step_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a, lr, beta1, beta2, eps, step_dev);
   count_launch();
   return check_launch("adam_step_multi_kernel");
 }
