@@ -49,3 +49,36 @@ def encoder_forward(sd, x, image_size=100):
         y = F.conv2d(y, torch.as_tensor(sd[f"net.{2 * i}.weight"]), torch.as_tensor(sd[f"net.{2 * i}.bias"]), st, pad)
         y = F.leaky_relu(y, 0.2)
     return y.reshape(B, S, -1).numpy()
+
+
+# ---------------------------------------------------------------------------------------------------
+# Decoder (latent.py:55-115): ConvTranspose2d + LeakyReLU(0.2) stack, [B,S,latent] -> ([B,S,3,H,W], std * ones)
+def decoder_specs(image_size=100, input_dim=288, output_dim=3):
+    """(cin, cout, k, stride, pad, output_padding), latent.py:63-101"""
+    if image_size == 64:
+        return [(input_dim, 256, 4, 1, 0, 0), (256, 128, 3, 2, 1, 1), (128, 64, 3, 2, 1, 1), (64, 32, 3, 2, 1, 1),
+                (32, output_dim, 5, 2, 2, 1)]
+    return [(input_dim, 256, 4, 1, 0, 0), (256, 256, 3, 2, 1, 0), (256, 128, 3, 2, 1, 0), (128, 64, 3, 2, 1, 0),
+            (64, 32, 3, 2, 1, 1), (32, output_dim, 5, 2, 2, 1)]
+
+
+def make_decoder_weights(image_size=100, seed=0, input_dim=288):
+    rs = np.random.RandomState(seed)
+    sd = {}
+    for i, (cin, cout, k, _, _, _) in enumerate(decoder_specs(image_size, input_dim)):
+        bound = np.sqrt(6.0 / ((cin + cout) * k * k))
+        sd[f"net.{2 * i}.weight"] = rs.uniform(-bound, bound, size=(cin, cout, k, k)).astype(np.float32)  # ConvTranspose2d layout
+        sd[f"net.{2 * i}.bias"] = (rs.randn(cout) * 0.05).astype(np.float32)
+    return sd
+
+
+def decoder_forward(sd, z, image_size=100, std=1.0):
+    """z: [B,S,latent] -> (mean [B,S,3,H,W], std [B,S,3,H,W])  (latent.py:105-115)"""
+    z = torch.as_tensor(z, dtype=torch.float32)
+    B, S, L = z.shape
+    y = z.reshape(B * S, L, 1, 1)
+    for i, (_, _, _, st, pad, op) in enumerate(decoder_specs(image_size, L)):
+        y = F.conv_transpose2d(y, torch.as_tensor(sd[f"net.{2 * i}.weight"]), torch.as_tensor(sd[f"net.{2 * i}.bias"]), st, pad, op)
+        y = F.leaky_relu(y, 0.2)
+    y = y.reshape(B, S, *y.shape[1:])
+    return y.numpy(), np.full(y.shape, std, dtype=np.float32)

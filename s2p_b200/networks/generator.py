@@ -318,10 +318,14 @@ class S2PGeneratorB200(nn.Module):
             B, H, W = image.shape[0], image.shape[2], image.shape[3]
         else:
             raise RuntimeError(f"image dtype {image.dtype} unsupported (fp32 NCHW or uint8 NHWC)")
+        if state.dim() != 2 or state.shape[0] != B or state.shape[1] != self.opt.state_dim:
+            raise RuntimeError(f"state must be [{B}, {self.opt.state_dim}] for this batch and env_type, got {tuple(state.shape)}")
         image = image.contiguous()
         state = state.contiguous().float()
         out_f32 = torch.empty(B, 3, H, W, dtype=torch.float32, device=image.device) if want_f32 else None
         out_u8 = torch.empty(B, H, W, 3, dtype=torch.uint8, device=image.device) if want_u8 else None
+        if B == 0:                       # empty batch: nothing to launch (nn.Module semantics of the oracle)
+            return out_f32, out_u8
         mb = self.max_microbatch
         gsbs = self._state_path(state)
         for s in range(0, B, mb):

@@ -116,3 +116,88 @@ class SlacEncoderB200(nn.Module):
         c, h, w = buffer.state_shape
         y = self._conv1(b * s, h, w, frames=buffer.frames, frames_tp1=buffer.frames_tp1, codes=codes)
         return self._tail(y, b * s).view(b, s, -1)
+
+
+def _decoder_specs(image_size, input_dim, output_dim):
+    """(cin, cout, k, stride, pad, output_padding) per ConvTranspose2d, latent.py:63-101"""
+    if image_size == 64:
+        return [(input_dim, 256, 4, 1, 0, 0), (256, 128, 3, 2, 1, 1), (128, 64, 3, 2, 1, 1), (64, 32, 3, 2, 1, 1),
+                (32, output_dim, 5, 2, 2, 1)]
+    if image_size == 100:
+        return [(input_dim, 256, 4, 1, 0, 0), (256, 256, 3, 2, 1, 0), (256, 128, 3, 2, 1, 0), (128, 64, 3, 2, 1, 0),
+                (64, 32, 3, 2, 1, 1), (32, output_dim, 5, 2, 2, 1)]
+    raise RuntimeError(f"SlacDecoderB200: image_size={image_size} (the reference defines 64 and 100)")
+
+
+def _pad64(n):
+    return (n + 63) // 64 * 64
+
+
+class SlacDecoderB200(nn.Module):
+    """Mirror of ``Decoder`` (/root/reference/rlkit/torch/slac/network/latent.py:55-115): same constructor and
+    parameter names (ConvTranspose2d weights [Cin, Cout, k, k]), ``forward(x[B,S,latent]) -> (mean [B,S,3,H,W], std)``.
+
+    Every transposed conv runs on the generator's tcgen05 implicit-GEMM kernel in its data-gradient form: the input is
+    zero-inserted (stride 2; output_padding = extra zero rows/columns at the far edge), the filter is flipped with
+    in/out channels swapped, padding k-1-p; the first layer (4x4 on a 1x1 map) is a 1x1 conv latent -> 4*4*256.
+    Channel counts are zero-padded to multiples of 64 (288 -> 320, 32 -> 64, 3 -> 64).  Inference only."""
+
+    def __init__(self, input_dim=288, output_dim=3, std=1.0, image_size=64):
+        super().__init__()
+        _lib.load()
+        self.image_size, self.std, self.output_dim = image_size, std, output_dim
+        self.specs = _decoder_specs(image_size, input_dim, output_dim)
+        mods = []
+        for cin, cout, k, st, pad, op in self.specs:
+            m = nn.ConvTranspose2d(cin, cout, k, st, pad, op)
+            nn.init.xavier_uniform_(m.weight, gain=1.0)
+            nn.init.constant_(m.bias, 0)
+            mods += [m, nn.LeakyReLU(0.2, inplace=True)]
+        self.net = nn.Sequential(*mods)
+        self._packed, self._key = None, None
+
+    def _pack(self):
+        convs = [m for m in self.net if isinstance(m, nn.ConvTranspose2d)]
+        key = tuple((c.weight._version, c.bias._version, c.weight.data_ptr()) for c in convs)
+        if self._packed is not None and key == self._key:
+            return self._packed
+        packed = []
+        for i, c in enumerate(convs):
+            w = c.weight.detach().float()                    # [Cin, Cout, k, k]
+            b = c.bias.detach().float()
+            cin, cout, k, _ = w.shape
+            if i == 0:
+                # y[n, r, s, co] = sum_ci x[n, ci] * w[ci, co, r, s]: a 1x1 conv with Cout' = k*k*Cout in (r, s, co) order
+                w1 = w.permute(2, 3, 1, 0).reshape(k * k * cout, cin, 1, 1)
+                w1 = torch.nn.functional.pad(w1, (0, 0, 0, 0, 0, _pad64(cin) - cin))
+                packed.append((ops.pack_conv_weight(w1.contiguous()), b.repeat(k * k).contiguous()))
+                continue
+            weq = w.permute(1, 0, 2, 3).flip(2, 3)           # equivalent regular conv weight [Cout, Cin, k, k]
+            weq = torch.nn.functional.pad(weq, (0, 0, 0, 0, 0, _pad64(cin) - cin, 0, _pad64(cout) - cout))
+            packed.append((ops.pack_conv_weight(weq.contiguous()), torch.nn.functional.pad(b, (0, _pad64(cout) - cout)).contiguous()))
+        self._packed, self._key = packed, key
+        return packed
+
+    @torch.no_grad()
+    def forward(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("SlacDecoderB200 needs CUDA tensors: there is no CPU path")
+        B, S, L = x.shape
+        if L != self.specs[0][0]:
+            raise RuntimeError(f"SlacDecoderB200: latent dim {L} != {self.specs[0][0]}")
+        n = B * S
+        packed = self._pack()
+        dev = x.device
+        cin0, cout0, k0 = self.specs[0][0], self.specs[0][1], self.specs[0][2]
+        z = torch.zeros(1, 1, n, _pad64(cin0), dtype=torch.bfloat16, device=dev)
+        z[0, 0, :, :cin0] = x.reshape(n, L)
+        y = ops.conv_igemm(z, packed[0][0], packed[0][1], k0 * k0 * cout0, 1, stride=1, act=ACT_LRELU, pad=0)
+        y = y.reshape(n, k0, k0, cout0)
+        for i in range(1, len(self.specs)):
+            cin, cout, k, st, pad, op = self.specs[i]
+            h = y.shape[1]
+            g = torch.zeros(n, (h - 1) * st + 1 + op, (h - 1) * st + 1 + op, y.shape[3], dtype=torch.bfloat16, device=dev)
+            g[:, 0:(h - 1) * st + 1:st, 0:(h - 1) * st + 1:st] = y
+            y = ops.conv_igemm(g, packed[i][0], packed[i][1], _pad64(cout), k, stride=1, act=ACT_LRELU, pad=k - 1 - pad)
+        mean = y[..., :self.output_dim].permute(0, 3, 1, 2).float().reshape(B, S, self.output_dim, y.shape[1], y.shape[2])
+        return mean, torch.ones_like(mean).mul_(self.std)

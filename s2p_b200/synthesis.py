@@ -134,3 +134,27 @@ def synthesize_augmented_dataset(netG, transition_model, dataset, normalize_conf
     torch.cuda.current_stream().synchronize()
     out["image_observations_tp1"] = tp1.numpy()                         # what algo.py:175,190,336 consume
     return out
+
+
+# ---------------------------------------------------------------------------------------- flat-file twin of the HDF5 schema
+def save_dataset_dir(path: str, dataset: dict) -> None:
+    """Write every key of a dataset dict as `<path>/<key>.npy` -- a flat binary twin of the reference's HDF5 files
+    (state_transition_rollout.py:232-243 writes the same keys with h5py, which this image does not have).  The
+    arrays keep the on-disk schema of SURVEY.md Appendix B (frames uint8 HWC)."""
+    import os
+    os.makedirs(path, exist_ok=True)
+    for k, v in dataset.items():
+        np.save(os.path.join(path, f"{k}.npy"), np.ascontiguousarray(v))
+
+
+def load_dataset_dir(path: str, keys=None, data_num=None, mmap: bool = True) -> dict:
+    """Read a dataset written by save_dataset_dir; `data_num` is the row limit of load_data_in_buffer
+    (rlkit/torch/slac/algo.py:183-204), `mmap` maps the big frame arrays instead of reading them, so every rank of a
+    sharded synthesis run can open the same files and touch only its own rows (BulkSynthesizer.synthesize_shard)."""
+    import os
+    out = {}
+    names = sorted(f[:-4] for f in os.listdir(path) if f.endswith(".npy")) if keys is None else list(keys)
+    for k in names:
+        a = np.load(os.path.join(path, f"{k}.npy"), mmap_mode="r" if mmap else None)
+        out[k] = a if data_num is None else a[:data_num]
+    return out

@@ -136,6 +136,8 @@ class EnsembleTransitionB200(nn.Module):
                        torch.empty(T, dtype=torch.float32, device=dev),
                        torch.empty(T, 1, dtype=torch.float32, device=dev),
                        torch.empty(T, 1, dtype=torch.float32, device=dev))
+        if T == 0:                      # empty batch: nothing to launch (the reference returns empty tensors)
+            return mean_out, std_out, sel_out
         lo, hi = self.min_logstd.detach().float().contiguous(), self.max_logstd.detach().float().contiguous()
         rc = _lib.load().s2p_ensemble_transition_fwd(
             obs.data_ptr(), obs.stride(0), action.data_ptr(), action.stride(0), _ptr(obs_mean), _ptr(obs_std),

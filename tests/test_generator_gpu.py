@@ -149,3 +149,25 @@ def test_state_changes_output(pkg):
     a = net(image.cuda(), states[:, 0].cuda())
     b = net(image.cuda(), states[:, 1].cuda())
     assert (a - b).abs().max().item() > 1e-3
+
+
+def test_edge_cases_empty_ragged_and_bad_shapes(pkg):
+    """empty batch, a batch that is not a multiple of the micro-batch (ragged last micro-batch), and shape errors"""
+    net = pkg.define_G(pkg.make_options(gpu_ids="0", init_type="scaled")).eval()
+    dev = torch.device("cuda", 0)
+    out = net(torch.zeros(0, 3, 100, 100, device=dev), torch.zeros(0, 17, device=dev))
+    assert tuple(out.shape) == (0, 3, 100, 100)
+    assert tuple(net.forward_u8(torch.zeros(0, 100, 100, 3, dtype=torch.uint8, device=dev), torch.zeros(0, 17, device=dev)).shape) == (0, 100, 100, 3)
+    g = torch.Generator().manual_seed(3)
+    n = net.max_microbatch + 3                                  # one full micro-batch + a ragged one of 3 rows
+    frames = torch.randint(0, 256, (n, 100, 100, 3), dtype=torch.uint8, generator=g).to(dev)
+    states = torch.randn(n, 17, generator=g).to(dev)
+    whole = net.forward_u8(frames, states)
+    tail = net.forward_u8(frames[-3:], states[-3:])
+    assert torch.equal(whole[-3:], tail)                        # rows do not depend on how the batch is cut
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(2, 3, 100, 100, device=dev), torch.zeros(2, 24, device=dev))      # walker state into a cheetah net
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(2, 3, 100, 100, device=dev), torch.zeros(3, 17, device=dev))
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(2, 3, 100, 100, dtype=torch.float16, device=dev), torch.zeros(2, 17, device=dev))

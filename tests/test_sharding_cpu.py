@@ -104,3 +104,23 @@ def test_gradient_allreduce_two_ranks_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert got == [1.5, None, 4.5, 6.0]       # mean over ranks of (rank+1)*(i+1)
+
+
+def test_flat_dataset_dir_roundtrip(tmp_path):
+    """the .npy-per-key twin of the HDF5 schema: exact round trip, row limit, memory-mapped frames"""
+    import numpy as np
+    from s2p_b200.synthesis import load_dataset_dir, save_dataset_dir, shard_range
+    rs = np.random.RandomState(0)
+    d = {"image_observations": rs.randint(0, 256, size=(10, 100, 100, 3)).astype(np.uint8),
+         "next_observations": rs.randn(10, 17).astype(np.float32), "timeouts": np.zeros(10, np.float32),
+         "slac_observation_indices": rs.randint(0, 10, size=(10, 9)).astype(np.int64)}
+    save_dataset_dir(str(tmp_path / "ds"), d)
+    back = load_dataset_dir(str(tmp_path / "ds"))
+    assert set(back) == set(d)
+    for k in d:
+        assert back[k].dtype == d[k].dtype and np.array_equal(np.asarray(back[k]), d[k])
+    assert isinstance(back["image_observations"], np.memmap)
+    part = load_dataset_dir(str(tmp_path / "ds"), keys=["image_observations", "next_observations"], data_num=7, mmap=False)
+    assert part["image_observations"].shape[0] == 7 and set(part) == {"image_observations", "next_observations"}
+    lo, hi = shard_range(10, 1, 3)
+    assert np.array_equal(np.asarray(back["image_observations"][lo:hi]), d["image_observations"][lo:hi])

@@ -72,3 +72,18 @@ def test_no_cpu_path():
         SlacEncoderB200(3, 256, 100)(torch.zeros(1, 1, 3, 100, 100))
     with pytest.raises(RuntimeError):
         SlacEncoderB200(3, 256, 84)
+
+
+@pytest.mark.parametrize("size", [100, 64])
+def test_decoder_vs_reference_vectors(size):
+    """ConvTranspose stack on the implicit-GEMM kernel's data-gradient form vs the reference's own Decoder."""
+    from s2p_b200.networks.slac_encoder import SlacDecoderB200
+    g = load_golden("slac_encoder")
+    b, s = (int(v) for v in g[f"dec_shape_{size}"])
+    dec = SlacDecoderB200(288, 3, 1.0, size)
+    dec.load_state_dict({k: torch.from_numpy(v) for k, v in EO.make_decoder_weights(size, seed=200 + size).items()})
+    dec = dec.cuda()
+    z = torch.from_numpy(np.random.RandomState(300 + size).randn(b, s, 288).astype(np.float32)).cuda()
+    mean, std = dec(z)
+    assert mean.shape == (b, s, 3, size, size) and float(std.min()) == float(std.max()) == 1.0
+    _close(mean.cpu().numpy(), g[f"dec_mean_{size}"])

@@ -105,6 +105,12 @@ def test_rollout_rows_large_and_bit_stable():
         np.testing.assert_allclose(got[sl].cpu().numpy(), want, rtol=5e-6, atol=2e-5)
 
 
+def test_empty_batch():
+    _, _, sd = _golden()
+    dist = _model(sd)(torch.zeros(0, 23, device="cuda"))
+    assert dist.mean.shape == (7, 0, 18) and dist.stddev.shape == (7, 0, 18)
+
+
 def test_no_cpu_path():
     _, _, sd = _golden()
     from s2p_b200.transition import EnsembleTransitionB200
