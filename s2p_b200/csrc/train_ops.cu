@@ -147,7 +147,7 @@ __global__ void adam_step_dev_kernel(float* __restrict__ p, const float* __restr
   }
 }
 
-static const int kColsumMaxChunks = 592;
+static const int kColsumMaxChunks = 1184;   // 8 CTAs of 256 threads per SM: full occupancy for the streaming pass
 
 }  // namespace s2p
 
