@@ -252,6 +252,17 @@ int s2p_multi_scale_fwd(const float* const* src, float* const* dst, const long l
 int s2p_multi_scale_bwd(const float* const* dout, const float* const* src, float* const* dsrc, const long long* n,
                         const int* scale_idx, int count, const float* scales, float* partial, void* stream);
 
+/* ---- (a8) mean |a - b| over NHWC bf16 feature maps and its backward ----------------------------------
+ * replaces F.l1_loss(a.float(), b.float()) and its autograd backward in the feature-matching and VGG perceptual
+ * terms (oracle generator_losses / vgg_loss).  a, b: [rows][pitch] bf16 with C live channels; out[0] = mean;
+ * partial: fp32 scratch of s2p_l1_mean_chunks() floats (fixed-order reduction).  backward: da = sign(a - b) * gout[0]
+ * / (rows * C) in bf16, gout read from device memory. */
+int s2p_l1_mean_chunks(void);
+int s2p_l1_mean_fwd(const void* a, int a_pitch, const void* b, int b_pitch, long long rows, int C, float* partial,
+                    float* out, void* stream);
+int s2p_l1_mean_bwd(const void* a, int a_pitch, const void* b, int b_pitch, const float* gout, long long rows, int C,
+                    void* da, int da_pitch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

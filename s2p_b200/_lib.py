@@ -57,6 +57,9 @@ SIGNATURES = {
     "s2p_multi_scale_blocks": (_i, []),
     "s2p_multi_scale_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "s2p_multi_scale_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "s2p_l1_mean_chunks": (_i, []),
+    "s2p_l1_mean_fwd": (_i, [_vp, _i, _vp, _i, C.c_longlong, _i, _vp, _vp, _vp]),
+    "s2p_l1_mean_bwd": (_i, [_vp, _i, _vp, _i, _vp, C.c_longlong, _i, _vp, _i, _vp]),
     "s2p_slac_indices": (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_longlong, _vp]),
 }
 

@@ -159,6 +159,41 @@ def multi_scale(scales, plan, srcs):
     return MultiScaleFn.apply(scales, plan, *srcs)
 
 
+class L1MeanFn(torch.autograd.Function):
+    """mean |a - b| over NHWC bf16 feature maps; b is a constant (detached target)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return ops.l1_mean(a, b)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        return ops.l1_mean_bwd(a, b, g), None
+
+
+def _as_nhwc(t):
+    """the NHWC bf16 tensor behind `t` (itself, or an NCHW-permuted view of one), else None"""
+    if t.dtype != torch.bfloat16 or t.dim() != 4:
+        return None
+    for cand in (t, t.permute(0, 2, 3, 1)):
+        b, h, w, c = cand.shape
+        p = cand.stride(2)
+        if cand.stride(3) == 1 and c % 8 == 0 and p % 8 == 0 and cand.stride(1) == p * w and (b == 1 or cand.stride(0) == p * w * h) \
+                and cand.data_ptr() % 16 == 0:
+            return cand
+    return None
+
+
+def l1_mean(a, b):
+    """F.l1_loss(a.float(), b.float()) for bf16 feature maps on the fused kernel; other inputs take the torch path"""
+    an, bn = _as_nhwc(a), _as_nhwc(b.detach())
+    if an is None or bn is None or an.shape != bn.shape:
+        return torch.nn.functional.l1_loss(a.float(), b.detach().float())
+    return L1MeanFn.apply(an, bn)
+
+
 class MaxPool2Fn(torch.autograd.Function):
     """nn.MaxPool2d(2, 2) on NHWC bf16 (VGG19 feature extractor of the perceptual loss)."""
 

@@ -44,22 +44,38 @@ act_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, const 
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   const long long r0 = blockIdx.x * rows_per_cta;
   const long long r1 = (r0 + rows_per_cta < rows) ? r0 + rows_per_cta : rows;
-  for (long long r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-    float d[8];
-    unpack8f(__ldg(reinterpret_cast<const uint4*>(dy + r * dy_pitch + c0)), d);
+  // two rows per iteration with all loads issued first: the single-row loop kept one 16-B load pair in flight per
+  // thread and ran at 48 % of HBM peak
+  const long long stride = blockDim.y;
+  for (long long r = r0 + threadIdx.y; r < r1; r += 2 * stride) {
+    const long long rb = r + stride;
+    const bool has_b = rb < r1;
+    uint4 da = __ldg(reinterpret_cast<const uint4*>(dy + r * dy_pitch + c0)), db = make_uint4(0u, 0u, 0u, 0u);
+    uint4 ya = make_uint4(0u, 0u, 0u, 0u), yb = ya;
+    if (has_b) db = __ldg(reinterpret_cast<const uint4*>(dy + rb * dy_pitch + c0));
     if (act != 0) {
-      float v[8];
-      unpack8f(__ldg(reinterpret_cast<const uint4*>(y + r * y_pitch + c0)), v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = v[j] > 0.f ? d[j] : (act == 2 ? 0.2f * d[j] : 0.f);
-      *reinterpret_cast<uint4*>(out + r * out_pitch + c0) =
-          make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]), pack_bf16x2(d[6], d[7]));
-      // the sum must be over the values as stored (bf16), like the tensor the wgrad kernel reads
-#pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = __bfloat162float(__float2bfloat16_rn(d[j]));
+      ya = __ldg(reinterpret_cast<const uint4*>(y + r * y_pitch + c0));
+      if (has_b) yb = __ldg(reinterpret_cast<const uint4*>(y + rb * y_pitch + c0));
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] += d[j];
+    for (int q = 0; q < 2; ++q) {
+      if (q == 1 && !has_b) break;
+      float d[8];
+      unpack8f(q ? db : da, d);
+      if (act != 0) {
+        float v[8];
+        unpack8f(q ? yb : ya, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = v[j] > 0.f ? d[j] : (act == 2 ? 0.2f * d[j] : 0.f);
+        *reinterpret_cast<uint4*>(out + (q ? rb : r) * out_pitch + c0) =
+            make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]), pack_bf16x2(d[6], d[7]));
+        // the sum must be over the values as stored (bf16), like the tensor the wgrad kernel reads
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = __bfloat162float(__float2bfloat16_rn(d[j]));
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += d[j];
+    }
   }
   if (partial == nullptr) return;
 #pragma unroll
@@ -456,4 +472,121 @@ extern "C" int s2p_multi_scale_bwd(const float* const* dout, const float* const*
   multi_scale_bwd_kernel<<<dim3(kScaleBlocks, count), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, scales, partial);
   count_launch();
   return check_launch("multi_scale_bwd_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------------
+// mean |a - b| over NHWC bf16 feature maps and its backward (feature-matching and VGG perceptual terms of the
+// generator loss, oracle generator_losses / vgg_loss: F.l1_loss on fp32 copies).  One read of a and b, fp32 math,
+// fixed-order two-stage reduction (bit-stable); the backward writes sign(a - b) * g / N in bf16 with the upstream
+// gradient g read from device memory (no host sync, graph-capturable).
+namespace s2p {
+
+constexpr int kL1MaxChunks = 1184;
+
+__global__ void __launch_bounds__(256)
+l1_sum_kernel(const __nv_bfloat16* __restrict__ a, int a_pitch, const __nv_bfloat16* __restrict__ b, int b_pitch,
+              long long rows, int groups, long long vec_per_cta, float* __restrict__ partial) {
+  __shared__ float red[8];
+  const long long total = rows * groups;                 // 8-channel vectors
+  const long long v0 = blockIdx.x * vec_per_cta;
+  const long long v1 = (v0 + vec_per_cta < total) ? v0 + vec_per_cta : total;
+  float acc = 0.f;
+  for (long long v = v0 + threadIdx.x; v < v1; v += 256) {
+    const long long r = v / groups;
+    const int c0 = static_cast<int>(v - r * groups) * 8;
+    float x[8], y[8];
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(a + r * a_pitch + c0)), x);
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(b + r * b_pitch + c0)), y);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += fabsf(x[j] - y[j]);
+    acc += s;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w];
+    partial[blockIdx.x] = t;
+  }
+}
+
+__global__ void l1_finalize_kernel(const float* __restrict__ partial, int chunks, double inv_n, float* __restrict__ out) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int k = threadIdx.x; k < chunks; k += 32) s += static_cast<double>(partial[k]);
+  red[threadIdx.x] = s;
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int k = 0; k < 32; ++k) t += red[k];
+    out[0] = static_cast<float>(t * inv_n);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+l1_bwd_kernel(const __nv_bfloat16* __restrict__ a, int a_pitch, const __nv_bfloat16* __restrict__ b, int b_pitch,
+              const float* __restrict__ gout, float inv_n, long long rows, int groups, __nv_bfloat16* __restrict__ da,
+              int da_pitch) {
+  const float g = gout[0] * inv_n;
+  const long long total = rows * groups;
+  for (long long v = blockIdx.x * 256ll + threadIdx.x; v < total; v += static_cast<long long>(gridDim.x) * 256) {
+    const long long r = v / groups;
+    const int c0 = static_cast<int>(v - r * groups) * 8;
+    float x[8], y[8], o[8];
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(a + r * a_pitch + c0)), x);
+    unpack8f(__ldg(reinterpret_cast<const uint4*>(b + r * b_pitch + c0)), y);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = x[j] - y[j];
+      o[j] = d > 0.f ? g : (d < 0.f ? -g : 0.f);
+    }
+    *reinterpret_cast<uint4*>(da + r * da_pitch + c0) =
+        make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+  }
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_l1_mean_chunks(void) { return s2p::kL1MaxChunks; }
+
+extern "C" int s2p_l1_mean_fwd(const void* a, int a_pitch, const void* b, int b_pitch, long long rows, int C,
+                               float* partial, float* out, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(a && b && partial && out && rows > 0 && C > 0 && C % 8 == 0, "l1_mean_fwd: bad args");
+  S2P_CHECK_ARG(a_pitch >= C && a_pitch % 8 == 0 && b_pitch >= C && b_pitch % 8 == 0, "l1_mean_fwd: pitch");
+  const int groups = C / 8;
+  const long long total = rows * groups;
+  long long chunks = (total + 2047) / 2048;
+  if (chunks > kL1MaxChunks) chunks = kL1MaxChunks;
+  const long long vpc = (total + chunks - 1) / chunks;
+  chunks = (total + vpc - 1) / vpc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  l1_sum_kernel<<<static_cast<unsigned>(chunks), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a), a_pitch,
+                                                              static_cast<const __nv_bfloat16*>(b), b_pitch, rows, groups, vpc, partial);
+  count_launch();
+  int rc = check_launch("l1_sum_kernel");
+  if (rc != S2P_OK) return rc;
+  l1_finalize_kernel<<<1, 32, 0, st>>>(partial, static_cast<int>(chunks), 1.0 / (static_cast<double>(rows) * C), out);
+  count_launch();
+  return check_launch("l1_finalize_kernel");
+}
+
+extern "C" int s2p_l1_mean_bwd(const void* a, int a_pitch, const void* b, int b_pitch, const float* gout, long long rows,
+                               int C, void* da, int da_pitch, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(a && b && gout && da && rows > 0 && C > 0 && C % 8 == 0, "l1_mean_bwd: bad args");
+  S2P_CHECK_ARG(a_pitch >= C && a_pitch % 8 == 0 && b_pitch >= C && b_pitch % 8 == 0 && da_pitch >= C && da_pitch % 8 == 0,
+                "l1_mean_bwd: pitch");
+  const int groups = C / 8;
+  const long long total = rows * groups;
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  l1_bwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(a), a_pitch, static_cast<const __nv_bfloat16*>(b), b_pitch, gout,
+      static_cast<float>(1.0 / (static_cast<double>(rows) * C)), rows, groups, static_cast<__nv_bfloat16*>(da), da_pitch);
+  count_launch();
+  return check_launch("l1_bwd_kernel");
 }

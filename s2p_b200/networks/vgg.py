@@ -93,4 +93,4 @@ def vgg_loss(vgg, fake, real):
     fx = vgg(fake)
     with torch.no_grad():
         fy = vgg(real)
-    return sum(w * F.l1_loss(a.float(), b.float()) for w, a, b in zip(VGG_WEIGHTS, fx, fy))
+    return sum(w * A.l1_mean(a, b) for w, a, b in zip(VGG_WEIGHTS, fx, fy))

@@ -466,3 +466,28 @@ def multi_scale_bwd(dout_ptrs, src_ptrs, dsrc_ptrs, numels, scale_idx, scales, p
                                            (ctypes.c_longlong * (j - i))(*numels[i:j]), (ctypes.c_int * (j - i))(*scale_idx[i:j]),
                                            j - i, scales.data_ptr(), partial.data_ptr() + i * nb * 4, _stream()),
                    "s2p_multi_scale_bwd")
+
+
+def l1_mean(a, b):
+    """mean |a - b| of two NHWC bf16 tensors (channel slices allowed) -> fp32 scalar tensor"""
+    _require_cuda(a, b)
+    if a.shape != b.shape:
+        raise RuntimeError("l1_mean: shape mismatch")
+    bb, h, w, c = a.shape
+    lib = _lib.load()
+    partial = torch.empty(int(lib.s2p_l1_mean_chunks()), dtype=torch.float32, device=a.device)
+    out = torch.empty((), dtype=torch.float32, device=a.device)
+    _lib.check(lib.s2p_l1_mean_fwd(a.data_ptr(), _nhwc_pitch(a, "a"), b.data_ptr(), _nhwc_pitch(b, "b"), bb * h * w, c,
+                                   partial.data_ptr(), out.data_ptr(), _stream()), "s2p_l1_mean_fwd")
+    return out
+
+
+def l1_mean_bwd(a, b, gout):
+    """gradient of l1_mean w.r.t. a: sign(a - b) * gout / numel, NHWC bf16"""
+    _require_cuda(a, b, gout)
+    bb, h, w, c = a.shape
+    da = torch.empty(bb, h, w, c, dtype=torch.bfloat16, device=a.device)
+    g = gout.detach().float().contiguous()
+    _lib.check(_lib.load().s2p_l1_mean_bwd(a.data_ptr(), _nhwc_pitch(a, "a"), b.data_ptr(), _nhwc_pitch(b, "b"), g.data_ptr(),
+                                           bb * h * w, c, da.data_ptr(), _nhwc_pitch(da, "da"), _stream()), "s2p_l1_mean_bwd")
+    return da

@@ -10,6 +10,7 @@ from __future__ import annotations
 import torch
 import torch.nn.functional as F
 
+from . import autograd as A
 from . import ops
 
 LAMBDA_FEAT = 10.0
@@ -85,7 +86,7 @@ def generator_losses(pred_fake, pred_real, fake, real, vgg=None):
     feat = 0.0
     for f, r in zip(pred_fake, pred_real):
         for a, b in zip(f[:-1], r[:-1]):
-            feat = feat + F.l1_loss(a.float(), b.detach().float()) * LAMBDA_FEAT / num_d
+            feat = feat + A.l1_mean(a, b) * LAMBDA_FEAT / num_d
     losses = {"GAN": gan, "GAN_Feat": feat, "L1": F.l1_loss(fake, real) * LAMBDA_L1}
     if vgg is not None:
         from .networks.vgg import LAMBDA_VGG, vgg_loss

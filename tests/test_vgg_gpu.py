@@ -116,3 +116,23 @@ def test_training_step_with_vgg_vs_oracle(pkg):
         print(f"G loss {k}: {a:.5f} vs oracle {b:.5f}")
         assert abs(a - b) <= 2e-2 * abs(b) + 2e-3
     assert abs(float(d_out.detach()) - float(d_ref.detach())) <= 2e-2 * abs(float(d_ref.detach())) + 2e-3
+
+
+def test_l1_mean_kernels_vs_torch(pkg):
+    """fused mean|a-b| on NHWC bf16 (channel-sliced and NCHW-permuted views included) and its sign backward"""
+    from s2p_b200 import autograd as A
+    g = torch.Generator().manual_seed(11)
+    for shape, sl in (((3, 25, 25, 256), 256), ((2, 50, 50, 128), 64), ((4, 6, 6, 512), 512)):
+        a = torch.randn(shape, generator=g).cuda().to(torch.bfloat16)
+        b = torch.randn(shape, generator=g).cuda().to(torch.bfloat16)
+        b[0, 0, 0, :8] = a[0, 0, 0, :8]                               # exact ties -> zero gradient
+        a.requires_grad_()
+        av, bv = a[..., :sl].permute(0, 3, 1, 2), b[..., :sl].permute(0, 3, 1, 2)     # the discriminator's NCHW views
+        out = A.l1_mean(av, bv)
+        a2 = a.detach().clone().requires_grad_()
+        ref = F.l1_loss(a2[..., :sl].float(), b[..., :sl].float())
+        assert abs(out.item() - ref.item()) <= 1e-6 * abs(ref.item()) + 1e-7
+        (out * 3.0).backward()
+        (ref * 3.0).backward()
+        assert torch.equal(a.grad, a2.grad)
+        assert torch.equal(A.l1_mean(av, bv), out.detach())           # bit-stable
