@@ -60,7 +60,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int atom_bytes = p.kb_rows * 128;                       // one 64-channel block of one tile
-  const int atom_stride = (atom_bytes + 1023) & ~1023;          // keep every block 1024-B aligned
+  const int atom_stride = ((p.kb_rows + 15) / 16) * 16 * 128;   // whole K steps per 64-channel block (1024-B aligned)
   const int stage_bytes = (kAtomsA + TAPS * kAtomsB) * atom_stride;
   const int kWgStages = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * stage_bytes);
@@ -71,6 +71,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
+  if (p.kb_rows % 16) {
+    // pixel tiles whose row count is not a multiple of the UMMA K (16), e.g. 25 x 5 = 125: the K loop runs to the next
+    // multiple and the rows TMA never writes must read as zeros in BOTH operands -> clear the ring once (generic
+    // proxy), then make it visible to the async proxy before the first TMA / MMA
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = kWgStages * stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async();
+  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_dy);
     tma_prefetch_desc(&tmap_x);
@@ -122,7 +131,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     const uint32_t lbo = static_cast<uint32_t>(atom_stride), sbo = 1024u;
     int stage = 0;
     uint32_t phase = 0;
-    const int ksteps = p.kb_rows / 16;
+    const int ksteps = (p.kb_rows + 15) / 16;
     for (int t = t_begin; t < t_end; ++t) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
@@ -204,17 +213,28 @@ static int wgrad_max_rows() {
   return r;
 }
 
+static int wgrad_pad16() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("S2P_WGRAD_PAD16"); v = e ? atoi(e) : 1; }
+  return v;
+}
+
+// Pixel tile (the GEMM K block): tile_w * tile_h <= 128 rows.  The MMA consumes K in steps of 16, so a tile costs
+// ceil16(rows) rows of tensor time; rows need not be a multiple of 16 (the kernel zero-fills the slack), which is what
+// lets 25 x 5 = 125 -> 128 tile 100^2, 50^2 and 25^2 maps at 97.7 % instead of 80-row tiles at 78-100 %.
 static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out) {
   const int max_rows = wgrad_max_rows();
+  const bool pad_ok = wgrad_pad16() != 0;
   double best = -1.0;
   int btw = 16, bth = 1;
   for (int tw = 1; tw <= W && tw <= max_rows; ++tw) {
     for (int th = 1; th <= H && tw * th <= max_rows; ++th) {
-      if ((tw * th) % 16) continue;
+      if (!pad_ok && (tw * th) % 16) continue;
+      const int cost = (tw * th + 15) / 16 * 16;
       const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
-      const double eff = static_cast<double>(H) * W / (tiles * static_cast<double>(tw * th));
+      const double eff = static_cast<double>(H) * W / (tiles * static_cast<double>(cost));
       // prefer efficiency, then bigger tiles (fewer pipeline turns)
-      const double score = eff + 1e-4 * tw * th;
+      const double score = eff + 1e-4 * cost;
       if (score > best) { best = score; btw = tw; bth = th; }
     }
   }
@@ -256,7 +276,7 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
   p.kb_rows = p.tile_w * p.tile_h;
   p.num_pix_tiles = B * p.tiles_x * p.tiles_y;
   pl->taps = ksize;
-  const int atom = p.kb_rows * 128;
+  const int atom = ((p.kb_rows + 15) / 16) * 16 * 128;
   pl->bn = (Cin % 128 == 0 && ksize * 128 <= 512 && 2 * (2 + ksize * 2) * atom <= 200 * 1024) ? 128 : 64;
   const int ctas = ((Cout + 127) / 128) * (Cin / pl->bn) * ksize;
   // split-K so that the grid is as close as possible to (but not above) ONE full wave: the kernel
@@ -266,7 +286,7 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
   if (splits < 1) splits = 1;
   pl->splits = splits;
   pl->grid = dim3((Cout + 127) / 128, (Cin / pl->bn) * ksize, splits);
-  const int atom_stride = (p.kb_rows * 128 + 1023) & ~1023;
+  const int atom_stride = ((p.kb_rows + 15) / 16) * 16 * 128;
   const int stage_bytes = (2 + pl->taps * (pl->bn / 64)) * atom_stride;
   int stages = (200 * 1024) / stage_bytes;
   if (stages > kWgMaxStages) stages = kWgMaxStages;
