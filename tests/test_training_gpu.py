@@ -264,3 +264,63 @@ def test_graphed_step_equals_eager(pkg):
         assert abs(float(g_e[k]) - float(g_g[k])) <= 1e-4 * abs(float(g_e[k])) + 1e-5, k
     assert abs(float(d_e) - float(d_g)) <= 1e-4 * abs(float(d_e)) + 1e-5
     assert graphed.optG.step_count == 3
+
+
+def test_linear_splitk_vs_torch_and_batch_invariant(pkg):
+    """K >= 256 runs split-K: same values as torch (fp32 reorder only), and a row's result never depends on the batch"""
+    from s2p_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    for (b, k, n) in ((16, 9600, 512), (16, 512, 512), (70, 357, 512), (3, 200, 9600)):
+        x = torch.randn(b, k, generator=g).cuda()
+        w = (torch.randn(n, k, generator=g) / k ** 0.5).cuda()
+        bias = torch.randn(n, generator=g).cuda()
+        y = ops.linear(x, w, bias, 2)
+        ref = F.leaky_relu(x.double() @ w.double().t() + bias.double(), 0.2).float()
+        assert (y - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
+        assert torch.equal(ops.linear(x[:1].contiguous(), w, bias, 2), y[:1])      # batch-invariant bits
+        assert torch.equal(ops.linear(x, w, bias, 2), y)                           # run-to-run
+
+
+def test_adam_multi_tensor_matches_torch(pkg):
+    from s2p_b200.training import FusedAdam
+    g = torch.Generator().manual_seed(12)
+    shapes = [(64,), (512, 128, 3, 3), (1,), (9600, 512), (8193,)] + [(33, 7)] * 70      # > 64 tensors: two launches
+    a = [torch.nn.Parameter(torch.randn(s, generator=g).cuda()) for s in shapes]
+    b = [torch.nn.Parameter(p.detach().clone()) for p in a]
+    mine, ref = FusedAdam(a, 2e-4, (0.0, 0.9)), torch.optim.Adam(b, lr=2e-4, betas=(0.0, 0.9))
+    for _ in range(3):
+        for p, q in zip(a, b):
+            gr = torch.randn(p.shape, generator=g).cuda()
+            p.grad, q.grad = gr.clone(), gr.clone()
+        a[5].grad = None                                        # a parameter without a gradient is skipped
+        b[5].grad = None
+        mine.step()
+        ref.step()
+    for p, q in zip(a, b):
+        assert (p - q).abs().max().item() < 1e-6
+
+
+def test_multi_scale_fn_vs_torch(pkg):
+    """blend scaling of many parameter tensors into concatenated operands, forward and backward"""
+    from s2p_b200 import autograd as A
+    g = torch.Generator().manual_seed(13)
+    dev = torch.device("cuda")
+    srcs = [torch.randn(s, generator=g).to(dev).requires_grad_() for s in ((64, 128, 3, 3), (32, 128, 3, 3), (64,), (32,), (10, 7))]
+    scales = torch.rand(3, generator=g).to(dev).requires_grad_()
+    shapes = [(96, 128, 3, 3), (96,), (10, 7)]
+    where = [(0, 0, 0), (0, 64 * 128 * 9, 1), (1, 0, 0), (1, 64, 1), (2, 0, 2)]
+    onehot = torch.zeros(3, 5, device=dev)
+    onehot[torch.tensor([k for _, _, k in where]), torch.arange(5)] = 1.0
+    outs = A.multi_scale(scales, (shapes, where, onehot), srcs)
+    srcs2 = [t.detach().clone().requires_grad_() for t in srcs]
+    scales2 = scales.detach().clone().requires_grad_()
+    ref = [torch.cat([srcs2[0] * scales2[0], srcs2[1] * scales2[1]]), torch.cat([srcs2[2] * scales2[0], srcs2[3] * scales2[1]]),
+           srcs2[4] * scales2[2]]
+    gs = [torch.randn(o.shape, generator=g).to(dev) for o in ref]
+    for o, r in zip(outs, ref):
+        assert torch.equal(o, r)
+    torch.autograd.backward(list(outs), gs)
+    torch.autograd.backward(ref, gs)
+    for t, t2 in zip(srcs, srcs2):
+        assert torch.equal(t.grad, t2.grad)
+    assert torch.allclose(scales.grad, scales2.grad, rtol=1e-4, atol=1e-4)
