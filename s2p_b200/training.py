@@ -37,6 +37,16 @@ class FusedAdam:
         for p in self.params:
             p.grad = None
 
+    def state_dict(self):
+        return {"step": self.step_dev.clone(), "exp_avg": [t.clone() for t in self.m], "exp_avg_sq": [t.clone() for t in self.v]}
+
+    def load_state_dict(self, sd):
+        self.step_dev.copy_(sd["step"])
+        for dst, src in zip(self.m, sd["exp_avg"]):
+            dst.copy_(src)
+        for dst, src in zip(self.v, sd["exp_avg_sq"]):
+            dst.copy_(src)
+
     @torch.no_grad()
     def step(self):
         self.step_dev += 1
@@ -139,6 +149,17 @@ class S2PTrainer:
         self.fake = None
         return loss
 
+    def state_dict(self):
+        """everything a resumed run needs (SPADE's `--continue_train`): G, D, both optimiser states"""
+        return {"netG": self.netG.state_dict(), "netD": self.netD.state_dict(), "optG": self.optG.state_dict(),
+                "optD": self.optD.state_dict()}
+
+    def load_state_dict(self, sd):
+        self.netG.load_state_dict(sd["netG"])
+        self.netD.load_state_dict(sd["netD"])
+        self.optG.load_state_dict(sd["optG"])
+        self.optD.load_state_dict(sd["optD"])
+
     def train_step(self, prev_image, state, real_image):
         g = self.run_generator_one_step(prev_image, state, real_image)
         d = self.run_discriminator_one_step(prev_image, state, real_image)
@@ -152,6 +173,11 @@ class S2PTrainer:
         if self.world_size > 1:
             raise RuntimeError("capture(): single-process only (the NCCL all-reduce is issued eagerly)")
         self._static = [t.clone() for t in (prev_image, state, real_image)]
+        # the warm-up steps below are real optimiser steps: snapshot and restore, so capture() leaves weights, Adam
+        # moments and the step count exactly as it found them
+        snap = {"netG": {k: v.clone() for k, v in self.netG.state_dict().items()},
+                "netD": {k: v.clone() for k, v in self.netD.state_dict().items()},
+                "optG": self.optG.state_dict(), "optD": self.optD.state_dict()}
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -159,6 +185,9 @@ class S2PTrainer:
                 self.train_step(*self._static)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
+        with torch.no_grad():
+            self.load_state_dict(snap)
+        self.fake = None
         self.optG.zero_grad()
         self.optD.zero_grad()
         self._graph = torch.cuda.CUDAGraph()

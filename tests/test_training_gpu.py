@@ -254,11 +254,14 @@ def test_graphed_step_equals_eager(pkg):
         nD = pkg.define_D(pkg.make_options(gpu_ids="0"))
         trainers.append(S2PTrainer(nG, nD))
     eager, graphed = trainers
-    graphed.capture(image, st, real, warmup=2)
+    graphed.capture(image, st, real, warmup=2)              # warm-up steps are rolled back: still at step 0
+    assert graphed.optG.step_count == 0
     for _ in range(2):
         eager.train_step(image, st, real)
+        graphed.train_step_graphed(image, st, real)
     g_e, d_e = eager.train_step(image, st, real)          # step 3
-    g_g, d_g = graphed.train_step_graphed(image, st, real)  # step 3 (2 warm-up steps + this replay)
+    g_g, d_g = graphed.train_step_graphed(image, st, real)  # step 3
+    g_g, d_g = {k: v.clone() for k, v in g_g.items()}, d_g.clone()
     torch.cuda.synchronize()
     for k in g_e:
         assert abs(float(g_e[k]) - float(g_g[k])) <= 1e-4 * abs(float(g_e[k])) + 1e-5, k
