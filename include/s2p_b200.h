@@ -214,11 +214,12 @@ int s2p_slac_indices(const long long* traj_start, long long* obs_idx, long long*
  * replaces the state half of ReplayBuffer.sample_latent / sample_sac / random_batch
  * (/root/reference/rlkit/torch/slac/buffer.py:127-147: per-sample host copies of 9 LazyFrames, upload,
  * .float().div_(255)) and the load-time np.transpose of rlkit/torch/slac/algo.py:174-175.
- * frames / frames_tp1: [N][H][W][C] uint8 as stored on disk (image_observations, image_observations_tp1);
+ * frames / frames_tp1: [n_rows][H][W][C] uint8 as stored on disk (image_observations, image_observations_tp1; a code
+ * whose row is outside [0, n_rows) reads row 0 instead of faulting -- the host mirror validates its tables);
  * codes [n_frames] int64 = 2*row + which (0: frames, 1: frames_tp1); out [n_frames][C][H][W] fp32
  * (= [batch][num_seq+1][C][H][W] with n_frames = batch*(num_seq+1)).  C in {1, 3}. */
-int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes, float* out,
-                           long long n_frames, int H, int W, int C, void* stream);
+int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, long long n_rows, const long long* codes,
+                           float* out, long long n_frames, int H, int W, int C, void* stream);
 
 /* ---- (f3) SLAC encoder, first layer from the resident uint8 dataset --------------------------------
  * replaces nn.Conv2d(3, 32, 5, 2, 2) + nn.LeakyReLU(0.2) of Encoder.net
@@ -227,7 +228,7 @@ int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, con
  * s2p_slac_window_gather, or x_nchw = float [n_frames][3][H][W] (the reference-facing forward(x)).
  * y: NHWC bf16 [n_frames][Ho][Wo][y_pitch >= 64], channels 32..63 zero, ready for s2p_conv_igemm_fwd with
  * Cin = 64 (the remaining encoder layers, latent.py:146-160, run on that kernel; ksize up to 5 there). */
-int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes, const float* x_nchw,
+int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, long long n_rows, const long long* codes, const float* x_nchw,
                        const float* w_oihw, const float* bias, void* y, int y_pitch, long long n_frames, int H, int W,
                        void* stream);
 

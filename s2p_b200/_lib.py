@@ -50,8 +50,8 @@ SIGNATURES = {
     "s2p_transition_member_floats": (C.c_longlong, [_i, _i, _i]),
     "s2p_ensemble_transition_fwd": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f,
                                          _vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
-    "s2p_slac_window_gather": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
-    "s2p_slac_conv1_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
+    "s2p_slac_window_gather": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
+    "s2p_slac_conv1_fwd": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
     "s2p_maxpool2_fwd": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2p_maxpool2_bwd": (_i, [_vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2p_multi_scale_blocks": (_i, []),

@@ -20,10 +20,11 @@ constexpr int kThreads = 256;
 template <int C>
 __global__ void __launch_bounds__(kThreads)
 window_gather_kernel(const uint8_t* __restrict__ frames, const uint8_t* __restrict__ frames_tp1,
-                     const long long* __restrict__ codes, float* __restrict__ out, int HW) {
+                     const long long* __restrict__ codes, float* __restrict__ out, int HW, long long n_rows) {
   __shared__ __align__(16) uint8_t tile[kPix * C];
   const long long f = blockIdx.y;
-  const long long code = codes[f];
+  long long code = codes[f];
+  if (code < 0 || (code >> 1) >= n_rows) code = 0;   // never read outside the dataset (row 0 instead; host validates)
   const uint8_t* src = ((code & 1) ? frames_tp1 : frames) + (code >> 1) * static_cast<long long>(HW) * C;
   const int p0 = blockIdx.x * kPix;
   const int npix = min(kPix, HW - p0);
@@ -67,11 +68,12 @@ window_gather_kernel(const uint8_t* __restrict__ frames, const uint8_t* __restri
 // 128-bit streaming store per colour plane.
 __global__ void __launch_bounds__(kThreads)
 window_gather_quad_kernel(const uint8_t* __restrict__ frames, const uint8_t* __restrict__ frames_tp1,
-                          const long long* __restrict__ codes, float* __restrict__ out, int HW) {
+                          const long long* __restrict__ codes, float* __restrict__ out, int HW, long long n_rows) {
   const int q = blockIdx.x * kThreads + threadIdx.x;  // quad of pixels
   if (q * 4 >= HW) return;
   const long long f = blockIdx.y;
-  const long long code = __ldg(codes + f);
+  long long code = __ldg(codes + f);
+  if (code < 0 || (code >> 1) >= n_rows) code = 0;
   const uint8_t* src = ((code & 1) ? frames_tp1 : frames) + (code >> 1) * static_cast<long long>(HW) * 3;
   const uint32_t* s = reinterpret_cast<const uint32_t*>(src) + q * 3;
   const uint32_t w0 = __ldg(s), w1 = __ldg(s + 1), w2 = __ldg(s + 2);  // r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
@@ -105,6 +107,7 @@ constexpr int kC1Out = 32, kC1K = 5, kC1Taps = kC1K * kC1K * 3;
 
 struct Conv1Params {
   const uint8_t* frames; const uint8_t* frames_tp1; const long long* codes;   // uint8 HWC source (codes != NULL)
+  long long n_rows;                                                            // rows of frames / frames_tp1
   const float* x_nchw;                                                         // or float [n][3][H][W] in [0,1]
   const float* w;      // [32][3][5][5] (nn.Conv2d layout)
   const float* bias;   // [32]
@@ -128,7 +131,8 @@ __global__ void __launch_bounds__(256) slac_conv1_kernel(const Conv1Params p) {
   const long long HW = static_cast<long long>(p.H) * p.W;
   const uint8_t* src8 = nullptr;
   if (p.codes) {
-    const long long code = p.codes[f];
+    long long code = p.codes[f];
+    if (code < 0 || (code >> 1) >= p.n_rows) code = 0;
     src8 = ((code & 1) ? p.frames_tp1 : p.frames) + (code >> 1) * HW * 3;
   }
   for (int i = threadIdx.x; i < prow * pcol * 3; i += 256) {
@@ -184,11 +188,12 @@ __global__ void __launch_bounds__(256) slac_conv1_kernel(const Conv1Params p) {
 }  // namespace sw
 }  // namespace s2p
 
-extern "C" int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes,
-                                      float* out, long long n_frames, int H, int W, int C, void* stream) {
+extern "C" int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* frames_tp1, long long n_rows,
+                                      const long long* codes, float* out, long long n_frames, int H, int W, int C,
+                                      void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(frames && frames_tp1 && codes && out, "slac_window_gather: null pointer");
-  S2P_CHECK_ARG(n_frames > 0 && n_frames <= 65535ll * 1024 && H > 0 && W > 0, "slac_window_gather: bad dims");
+  S2P_CHECK_ARG(n_frames > 0 && n_frames <= 65535ll * 1024 && H > 0 && W > 0 && n_rows > 0, "slac_window_gather: bad dims");
   S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 15) == 0, "slac_window_gather: out not 16-B aligned");
   const int HW = H * W;
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -201,9 +206,9 @@ extern "C" int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* fram
     const bool quad = C == 3 && HW % 4 == 0 && ((reinterpret_cast<uintptr_t>(frames) | reinterpret_cast<uintptr_t>(frames_tp1)) & 3) == 0;
     if (quad) {
       const dim3 qgrid((HW / 4 + sw::kThreads - 1) / sw::kThreads, static_cast<unsigned>(nf));
-      sw::window_gather_quad_kernel<<<qgrid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW);
-    } else if (C == 3) sw::window_gather_kernel<3><<<grid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW);
-    else if (C == 1) sw::window_gather_kernel<1><<<grid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW);
+      sw::window_gather_quad_kernel<<<qgrid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW, n_rows);
+    } else if (C == 3) sw::window_gather_kernel<3><<<grid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW, n_rows);
+    else if (C == 1) sw::window_gather_kernel<1><<<grid, sw::kThreads, 0, st>>>(frames, frames_tp1, codes + f0, o, HW, n_rows);
     else return set_error(S2P_ERR_UNSUPPORTED, "slac_window_gather: C=%d (1 or 3)", C);
     count_launch();
     const int rc = check_launch("window_gather_kernel");
@@ -212,17 +217,17 @@ extern "C" int s2p_slac_window_gather(const uint8_t* frames, const uint8_t* fram
   return S2P_OK;
 }
 
-extern "C" int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, const long long* codes,
+extern "C" int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, long long n_rows, const long long* codes,
                                   const float* x_nchw, const float* w_oihw, const float* bias, void* y, int y_pitch,
                                   long long n_frames, int H, int W, void* stream) {
   using namespace s2p;
-  S2P_CHECK_ARG((codes && frames && frames_tp1 && !x_nchw) || (!codes && x_nchw), "slac_conv1: pass either "
+  S2P_CHECK_ARG((codes && frames && frames_tp1 && n_rows > 0 && !x_nchw) || (!codes && x_nchw), "slac_conv1: pass either "
                 "(frames, frames_tp1, codes) or x_nchw");
   S2P_CHECK_ARG(w_oihw && bias && y, "slac_conv1: null pointer");
   S2P_CHECK_ARG(n_frames > 0 && n_frames <= 65535 && H >= 5 && W >= 5, "slac_conv1: bad dims");
   S2P_CHECK_ARG(y_pitch >= 64 && y_pitch % 8 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0, "slac_conv1: y_pitch / alignment");
   sw::Conv1Params p;
-  p.frames = frames; p.frames_tp1 = frames_tp1; p.codes = codes; p.x_nchw = x_nchw; p.w = w_oihw; p.bias = bias;
+  p.frames = frames; p.frames_tp1 = frames_tp1; p.codes = codes; p.n_rows = n_rows; p.x_nchw = x_nchw; p.w = w_oihw; p.bias = bias;
   p.out = static_cast<__nv_bfloat16*>(y); p.out_pitch = y_pitch; p.H = H; p.W = W;
   p.Ho = (H + 4 - 5) / 2 + 1; p.Wo = (W + 4 - 5) / 2 + 1;
   S2P_CHECK_ARG(p.Wo <= 256, "slac_conv1: W=%d too wide", W);

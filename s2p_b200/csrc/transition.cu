@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) ensemble_transition_kernel(const 
   dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, 16));
   const long long row = row0 + r;
   if (lane < 8 && row < p.T) {
-    const int sel = p.member_idx[row];
+    const int sel = min(max(p.member_idx[row], 0), E - 1);   // a bad index must not read outside the tile's shared memory
     const float* msel = s.mus + (static_cast<size_t>(sel) * kTileRows + r) * od;
     for (int d = 0; d < p.obs_dim; ++d)
       p.next_obs[row * p.obs_dim + d] = msel[d] * p.next_obs_std[d] + p.next_obs_mean[d];  // :194

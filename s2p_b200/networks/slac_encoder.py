@@ -91,7 +91,7 @@ class SlacEncoderB200(nn.Module):
         ho, wo = (h + 4 - 5) // 2 + 1, (w + 4 - 5) // 2 + 1
         y = torch.empty(n, ho, wo, 64, dtype=torch.bfloat16, device=dev)
         p = lambda t: 0 if t is None else t.data_ptr()
-        _lib.check(_lib.load().s2p_slac_conv1_fwd(p(frames), p(frames_tp1), p(codes), p(x), w1.data_ptr(), b1.data_ptr(),
+        _lib.check(_lib.load().s2p_slac_conv1_fwd(p(frames), p(frames_tp1), 0 if frames is None else frames.shape[0], p(codes), p(x), w1.data_ptr(), b1.data_ptr(),
                                                   y.data_ptr(), 64, n, h, w, _stream()), "s2p_slac_conv1_fwd")
         return y
 

@@ -165,7 +165,7 @@ class SlacReplayBufferB200:
         c, h, w = self.state_shape
         b, s = codes.shape
         out = torch.empty(b, s, c, h, w, dtype=torch.float32, device=self.device)
-        _lib.check(_lib.load().s2p_slac_window_gather(self.frames.data_ptr(), self.frames_tp1.data_ptr(), codes.data_ptr(),
+        _lib.check(_lib.load().s2p_slac_window_gather(self.frames.data_ptr(), self.frames_tp1.data_ptr(), self.frames.shape[0], codes.data_ptr(),
                                                       out.data_ptr(), b * s, h, w, c, _stream()), "s2p_slac_window_gather")
         return out
 
