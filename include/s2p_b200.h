@@ -162,6 +162,11 @@ int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bia
  * (bf16 rows of R*S*Cout), so dX = s2p_conv_igemm_fwd(dY (zero-inserted when stride 2), dst,
  * pad = k-1-pad) -- replaces autograd's conv backward w.r.t. the input. */
 int s2p_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S, void* stream);
+/* both packed forms (s2p_pack_conv_weight with scale 1, s2p_pack_conv_weight_dgrad) of `count` (<= 48) weight
+ * tensors in ONE launch; every argument is a HOST array of `count` entries, dst_dgrad[i] may be NULL when the layer
+ * needs no data gradient.  Replaces the per-layer re-pack after each optimiser step of train.py (README.md:59). */
+int s2p_pack_conv_weights_multi(const float* const* w_oihw, void* const* dst_fwd, void* const* dst_dgrad,
+                                const int* Cout, const int* Cin, const int* R, const int* S, int count, void* stream);
 /* dy_out = dy * act'(y) (act from the ACTIVATED output y; skipped when act == 0) and
  * bias_grad[c] = sum over `rows` pixels of dy_out[:, c]; partial: fp32 scratch of
  * s2p_act_bwd_bias_grad_chunks() * C floats; bias_grad/partial may both be NULL. */
@@ -240,6 +245,25 @@ int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, long lo
 int s2p_maxpool2_fwd(const void* x, int x_pitch, void* y, int y_pitch, int B, int H, int W, int C, void* stream);
 int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, void* dx, int dx_pitch, int B, int H,
                      int W, int C, void* stream);
+
+/* ---- (a8) image layout for the tensor-core convs of the training step -------------------------------------------
+ * fp32 NCHW [B][C][H][W] with C <= 8 (an image, or the discriminator's 6-channel image pair) -> bf16 NHWC
+ * [B][H][W][64] with channels >= C zero, and the backward (the first C channels of a bf16 NHWC gradient -> fp32
+ * NCHW).  Replaces the `permute + zero-pad` (torch.cat along the 3+61 channel axis) in front of the oracle's first
+ * Conv2d of generator, discriminator and VGG19 extractor and autograd's slice / permute backward of it. */
+int s2p_nchw_to_nhwc64(const float* x_nchw, void* y_nhwc64, int B, int C, int H, int W, void* stream);
+int s2p_nhwc64_to_nchw(const void* dy_nhwc, int dy_pitch, float* dx_nchw, int B, int C, int H, int W, void* stream);
+/* the generator's output head in training: y_nchw[b][c][h][w] = tanh(x_nhwc[b][h][w][c]) for the first C (<= 8)
+ * channels of the padded ToRGB conv output, and its backward dx_nhwc64 = pad64(dy * (1 - y^2)) in bf16.  Replaces
+ * slice + float + tanh + permute/contiguous (and autograd's backward of each) of `tanh(conv_img(x))`. */
+int s2p_tanh_nhwc_to_nchw(const void* x_nhwc, int x_pitch, float* y_nchw, int B, int C, int H, int W, void* stream);
+int s2p_tanh_bwd_nchw_to_nhwc64(const float* dy_nchw, const float* y_nchw, void* dx_nhwc64, int B, int C, int H, int W,
+                                void* stream);
+
+/* zero insertion in front of the data-gradient conv of a stride-2 layer: out [B][Hout][Wout][C] (contiguous) gets
+ * dy[b][i][j] at (2i, 2j) and zeros elsewhere; Hout >= 2*Ho-1, Wout >= 2*Wo-1, C % 8 == 0. */
+int s2p_zero_insert2(const void* dy, int dy_pitch, void* out, int B, int Ho, int Wo, int Hout, int Wout, int C,
+                     void* stream);
 
 /* ---- (a8) multi-tensor scale: the MAT blend factors applied to parameter tensors, and its backward ----
  * replaces the per-tensor `weight * sigmoid(blend)` of oracle MAT.forward and autograd's MulBackward for it.

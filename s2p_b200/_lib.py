@@ -41,6 +41,7 @@ SIGNATURES = {
     "s2p_adam_step": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _i, _vp]),
     "s2p_adam_step_dev": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _vp, _vp]),
     "s2p_pack_conv_weight_dgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_pack_conv_weights_multi": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "s2p_act_bwd_bias_grad_chunks": (_i, []),
     "s2p_act_bwd_bias_grad": (_i, [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _vp, C.c_longlong, _i, _vp]),
     "s2p_pos_encode_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
@@ -53,6 +54,11 @@ SIGNATURES = {
     "s2p_slac_window_gather": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
     "s2p_slac_conv1_fwd": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
     "s2p_maxpool2_fwd": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2p_zero_insert2": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2p_tanh_nhwc_to_nchw": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_tanh_bwd_nchw_to_nhwc64": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_nchw_to_nhwc64": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2p_nhwc64_to_nchw": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp]),
     "s2p_maxpool2_bwd": (_i, [_vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2p_multi_scale_blocks": (_i, []),
     "s2p_multi_scale_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),

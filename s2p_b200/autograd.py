@@ -53,11 +53,8 @@ class ConvFn(torch.autograd.Function):
             # dgrad = the same implicit GEMM with the filter flipped and in/out channels swapped
             g = dy
             if stride == 2:   # transposed conv: zero-insert the gradient, then a stride-1 conv
-                b, ho, wo, _ = dy.shape
-                g = torch.zeros(b, x.shape[1] + 2 * pad - k + 1, x.shape[2] + 2 * pad - k + 1, cout, dtype=dy.dtype,
-                                device=dy.device)
-                g[:, 0:2 * ho:2, 0:2 * wo:2] = dy
-            wd = ctx.packed[1] if ctx.packed is not None else ops.pack_conv_weight_dgrad(weight)
+                g = ops.zero_insert2(dy, x.shape[1] + 2 * pad - k + 1, x.shape[2] + 2 * pad - k + 1)
+            wd = ctx.packed[1] if ctx.packed is not None and ctx.packed[1] is not None else ops.pack_conv_weight_dgrad(weight)
             dx = ops.conv_igemm(g, wd, None, cin, k, 1, ACT_NONE, pad=k - 1 - pad)
         if ctx.needs_input_grad[1]:
             dw = ops.conv_wgrad(x, dy, k, stride, pad)
@@ -210,6 +207,44 @@ class MaxPool2Fn(torch.autograd.Function):
 
 def maxpool2(x):
     return MaxPool2Fn.apply(x)
+
+
+class PadChannelsFn(torch.autograd.Function):
+    """fp32 NCHW image (<= 8 channels) -> bf16 NHWC with 64 zero-padded channels, the layout of every first conv"""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.c = x.shape[1]
+        return ops.nchw_to_nhwc64(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return ops.nhwc64_to_nchw(dy if dy.stride(-1) == 1 else dy.contiguous(), ctx.c)
+
+
+def pad_channels(x):
+    return PadChannelsFn.apply(x)
+
+
+class TanhOutFn(torch.autograd.Function):
+    """image = tanh(rgb[..., :c]) as fp32 NCHW from the 64-channel-padded bf16 NHWC output of the ToRGB conv"""
+
+    @staticmethod
+    def forward(ctx, rgb, c):
+        if rgb.shape[-1] != 64:
+            raise RuntimeError("tanh_out: expects the 64-channel padded ToRGB output")
+        y = ops.tanh_nhwc_to_nchw(rgb, c)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return ops.tanh_bwd_nchw_to_nhwc64(dy, y), None
+
+
+def tanh_out(rgb, c=3):
+    return TanhOutFn.apply(rgb, c)
 
 
 def conv_stats(y_shape, device):

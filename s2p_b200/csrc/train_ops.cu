@@ -27,6 +27,49 @@ __global__ void pack_conv_weight_dgrad_kernel(const float* __restrict__ w, __nv_
   }
 }
 
+// Both packed forms of up to kPackMulti weight tensors in ONE launch: a training step re-packs every conv weight
+// after the optimiser step, and tensor by tensor that was ~105 launches of 7-8 us each (0.8 ms of a 14 ms batch-16
+// step).  The pointer table travels in kernel parameter space (graph-capturable); blocks are dealt out by tensor size.
+constexpr int kPackMulti = 48;
+constexpr int kPackChunk = 4096;   // elements of ONE packed form per block
+struct PackMultiArgs {
+  const float* src[kPackMulti];
+  __nv_bfloat16* fwd[kPackMulti];      // [Cout][R][S][Cin]
+  __nv_bfloat16* dgrad[kPackMulti];    // [Cin][R][S][Cout], filter flipped; nullptr = not wanted
+  int cout[kPackMulti], cin[kPackMulti], r[kPackMulti], s[kPackMulti];
+  int first_block[kPackMulti + 1];
+  int count;
+};
+
+__global__ void __launch_bounds__(256) pack_conv_weights_multi_kernel(const __grid_constant__ PackMultiArgs a) {
+  int t = 0;
+  while (t + 1 < a.count && static_cast<int>(blockIdx.x) >= a.first_block[t + 1]) ++t;   // block-uniform
+  const float* __restrict__ w = a.src[t];
+  const int Cout = a.cout[t], Cin = a.cin[t], R = a.r[t], S = a.s[t];
+  const long long total = static_cast<long long>(Cout) * Cin * R * S;
+  const long long i0 = static_cast<long long>(blockIdx.x - a.first_block[t]) * kPackChunk;
+  const long long i1 = (i0 + kPackChunk < total) ? i0 + kPackChunk : total;
+  __nv_bfloat16* __restrict__ fwd = a.fwd[t];
+  for (long long i = i0 + threadIdx.x; i < i1; i += 256) {
+    const int ci = static_cast<int>(i % Cin);
+    long long q = i / Cin;
+    const int s = static_cast<int>(q % S); q /= S;
+    const int r = static_cast<int>(q % R);
+    const int co = static_cast<int>(q / R);
+    fwd[i] = __float2bfloat16_rn(__ldg(w + ((static_cast<long long>(co) * Cin + ci) * R + r) * S + s));
+  }
+  __nv_bfloat16* __restrict__ dg = a.dgrad[t];
+  if (dg == nullptr) return;
+  for (long long i = i0 + threadIdx.x; i < i1; i += 256) {
+    const int co = static_cast<int>(i % Cout);
+    long long q = i / Cout;
+    const int s = static_cast<int>(q % S); q /= S;
+    const int r = static_cast<int>(q % R);
+    const int ci = static_cast<int>(q / R);
+    dg[i] = __float2bfloat16_rn(__ldg(w + ((static_cast<long long>(co) * Cin + ci) * R + (R - 1 - r)) * S + (S - 1 - s)));
+  }
+}
+
 __device__ __forceinline__ void unpack8f(const uint4& u, float (&f)[8]) {
   f[0] = bf16_lo(u.x); f[1] = bf16_hi(u.x); f[2] = bf16_lo(u.y); f[3] = bf16_hi(u.y);
   f[4] = bf16_lo(u.z); f[5] = bf16_hi(u.z); f[6] = bf16_lo(u.w); f[7] = bf16_hi(u.w);
@@ -179,6 +222,39 @@ extern "C" int s2p_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int Co
   return check_launch("pack_conv_weight_dgrad_kernel");
 }
 
+extern "C" int s2p_pack_conv_weights_multi(const float* const* w_oihw, void* const* dst_fwd, void* const* dst_dgrad,
+                                           const int* Cout, const int* Cin, const int* R, const int* S, int count,
+                                           void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(w_oihw && dst_fwd && dst_dgrad && Cout && Cin && R && S, "pack_conv_weights_multi: null table");
+  S2P_CHECK_ARG(count > 0 && count <= kPackMulti, "pack_conv_weights_multi: count=%d (1..%d)", count, kPackMulti);
+  PackMultiArgs a;
+  int blocks = 0;
+  for (int i = 0; i < count; ++i) {
+    S2P_CHECK_ARG(w_oihw[i] && dst_fwd[i] && Cout[i] > 0 && Cin[i] > 0 && R[i] > 0 && S[i] > 0,
+                  "pack_conv_weights_multi: tensor %d", i);
+    a.src[i] = w_oihw[i];
+    a.fwd[i] = static_cast<__nv_bfloat16*>(dst_fwd[i]);
+    a.dgrad[i] = static_cast<__nv_bfloat16*>(dst_dgrad[i]);
+    a.cout[i] = Cout[i]; a.cin[i] = Cin[i]; a.r[i] = R[i]; a.s[i] = S[i];
+    a.first_block[i] = blocks;
+    const long long total = static_cast<long long>(Cout[i]) * Cin[i] * R[i] * S[i];
+    const long long nb = (total + kPackChunk - 1) / kPackChunk;
+    S2P_CHECK_ARG(blocks + nb < (1ll << 30), "pack_conv_weights_multi: too many elements");
+    blocks += static_cast<int>(nb);
+  }
+  for (int i = count; i < kPackMulti; ++i) {
+    a.src[i] = nullptr; a.fwd[i] = nullptr; a.dgrad[i] = nullptr;
+    a.cout[i] = a.cin[i] = a.r[i] = a.s[i] = 0;
+    a.first_block[i] = blocks;
+  }
+  a.first_block[kPackMulti] = blocks;
+  a.count = count;
+  pack_conv_weights_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  count_launch();
+  return check_launch("pack_conv_weights_multi_kernel");
+}
+
 extern "C" int s2p_act_bwd_bias_grad_chunks(void) { return s2p::kColsumMaxChunks; }
 
 extern "C" int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y, int y_pitch, int act,
@@ -318,6 +394,70 @@ __global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int dy
       *reinterpret_cast<uint4*>(dx + ((b * H + h) * W + w) * static_cast<long long>(dx_pitch) + c8 * 8) = r;
     }
   }
+}
+
+// Zero-insertion in front of the data-gradient conv of a stride-2 layer (transposed convolution):
+// out[b][2i][2j][:] = dy[b][i][j][:], everything else 0, in one write-only pass (was a fill plus a strided copy).
+__global__ void __launch_bounds__(256)
+zero_insert2_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, __nv_bfloat16* __restrict__ out, int B, int Ho,
+                    int Wo, int Hout, int Wout, int C8) {
+  const long long total = static_cast<long long>(B) * Hout * Wout * C8;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int c8 = static_cast<int>(i % C8);
+    long long q = i / C8;
+    const int w = static_cast<int>(q % Wout); q /= Wout;
+    const int h = static_cast<int>(q % Hout);
+    const long long b = q / Hout;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (!(h & 1) && !(w & 1) && (h >> 1) < Ho && (w >> 1) < Wo)
+      v = __ldg(reinterpret_cast<const uint4*>(dy + ((b * Ho + (h >> 1)) * Wo + (w >> 1)) * dy_pitch + c8 * 8));
+    reinterpret_cast<uint4*>(out)[i] = v;
+  }
+}
+
+// fp32 NCHW [B][c][H][W] (c <= 8: images, image pairs) -> bf16 NHWC [B][H][W][64], channels >= c zero: the operand
+// the tensor-core convs take for a 3- or 6-channel input.  8 threads per pixel, one 16-byte store each (a warp
+// writes 512 contiguous bytes); only the first thread of a pixel reads.  HBM-bound on the 128 B per pixel it writes.
+// `t` (optional, same layout as x): the tanh output whose backward this is -> x * (1 - t^2) is what gets stored
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc64_kernel(const float* __restrict__ x, const float* __restrict__ t, __nv_bfloat16* __restrict__ y,
+                      long long total_pix, int c, int HW) {
+  const long long gid = blockIdx.x * 256ll + threadIdx.x;
+  const long long pix = gid >> 3;
+  const int part = static_cast<int>(gid & 7);
+  if (pix >= total_pix) return;
+  uint4 v = make_uint4(0u, 0u, 0u, 0u);
+  if (part == 0) {
+    const long long n = pix / HW;
+    const int p = static_cast<int>(pix - n * HW);
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[j] = j < c ? __ldg(x + (n * c + j) * HW + p) : 0.f;
+      if (t != nullptr && j < c) {
+        const float tv = __ldg(t + (n * c + j) * HW + p);
+        f[j] *= 1.f - tv * tv;
+      }
+    }
+    v = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+  }
+  *reinterpret_cast<uint4*>(y + pix * 64 + part * 8) = v;
+}
+
+// its backward: dx[n][j][h][w] = float(dy[n][h][w][j]) for j < c (the padded channels carry no gradient)
+__global__ void __launch_bounds__(256)
+nhwc64_to_nchw_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, float* __restrict__ dx, long long total_pix,
+                      int c, int HW, int apply_tanh) {
+  const long long pix = blockIdx.x * 256ll + threadIdx.x;
+  if (pix >= total_pix) return;
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(dy + pix * dy_pitch));
+  float f[8];
+  unpack8f(u, f);
+  const long long n = pix / HW;
+  const int p = static_cast<int>(pix - n * HW);
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < c) dx[(n * c + j) * HW + p] = apply_tanh ? tanhf(f[j]) : f[j];
 }
 
 }  // namespace s2p
@@ -589,4 +729,70 @@ extern "C" int s2p_l1_mean_bwd(const void* a, int a_pitch, const void* b, int b_
       static_cast<float>(1.0 / (static_cast<double>(rows) * C)), rows, groups, static_cast<__nv_bfloat16*>(da), da_pitch);
   count_launch();
   return check_launch("l1_bwd_kernel");
+}
+
+static int nchw_to_nhwc64_impl(const float* x_nchw, const float* tanh_out, void* y_nhwc64, int B, int C, int H, int W,
+                               void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x_nchw && y_nhwc64 && B > 0 && H > 0 && W > 0, "nchw_to_nhwc64: bad args");
+  S2P_CHECK_ARG(C >= 1 && C <= 8, "nchw_to_nhwc64: C=%d (1..8 channels are padded to 64)", C);
+  S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(y_nhwc64) & 15) == 0, "nchw_to_nhwc64: 16-byte alignment");
+  const long long total = static_cast<long long>(B) * H * W;
+  const long long blocks = (total * 8 + 255) / 256;
+  S2P_CHECK_ARG(blocks < (1ll << 31), "nchw_to_nhwc64: too many pixels");
+  nchw_to_nhwc64_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x_nchw, tanh_out, static_cast<__nv_bfloat16*>(y_nhwc64), total, C, H * W);
+  count_launch();
+  return check_launch("nchw_to_nhwc64_kernel");
+}
+
+extern "C" int s2p_nchw_to_nhwc64(const float* x_nchw, void* y_nhwc64, int B, int C, int H, int W, void* stream) {
+  return nchw_to_nhwc64_impl(x_nchw, nullptr, y_nhwc64, B, C, H, W, stream);
+}
+
+extern "C" int s2p_tanh_bwd_nchw_to_nhwc64(const float* dy_nchw, const float* y_nchw, void* dx_nhwc64, int B, int C, int H,
+                                           int W, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(y_nchw != nullptr, "tanh_bwd_nchw_to_nhwc64: null tanh output");
+  return nchw_to_nhwc64_impl(dy_nchw, y_nchw, dx_nhwc64, B, C, H, W, stream);
+}
+
+static int nhwc64_to_nchw_impl(const void* dy_nhwc, int dy_pitch, float* dx_nchw, int B, int C, int H, int W,
+                               int apply_tanh, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy_nhwc && dx_nchw && B > 0 && H > 0 && W > 0, "nhwc64_to_nchw: bad args");
+  S2P_CHECK_ARG(C >= 1 && C <= 8 && dy_pitch >= 8 && dy_pitch % 8 == 0, "nhwc64_to_nchw: C=%d pitch=%d", C, dy_pitch);
+  S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(dy_nhwc) & 15) == 0, "nhwc64_to_nchw: 16-byte alignment");
+  const long long total = static_cast<long long>(B) * H * W;
+  const long long blocks = (total + 255) / 256;
+  S2P_CHECK_ARG(blocks < (1ll << 31), "nhwc64_to_nchw: too many pixels");
+  nhwc64_to_nchw_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy_nhwc), dy_pitch, dx_nchw, total, C, H * W, apply_tanh);
+  count_launch();
+  return check_launch("nhwc64_to_nchw_kernel");
+}
+
+extern "C" int s2p_nhwc64_to_nchw(const void* dy_nhwc, int dy_pitch, float* dx_nchw, int B, int C, int H, int W,
+                                  void* stream) {
+  return nhwc64_to_nchw_impl(dy_nhwc, dy_pitch, dx_nchw, B, C, H, W, 0, stream);
+}
+
+extern "C" int s2p_tanh_nhwc_to_nchw(const void* x_nhwc, int x_pitch, float* y_nchw, int B, int C, int H, int W,
+                                     void* stream) {
+  return nhwc64_to_nchw_impl(x_nhwc, x_pitch, y_nchw, B, C, H, W, 1, stream);
+}
+
+extern "C" int s2p_zero_insert2(const void* dy, int dy_pitch, void* out, int B, int Ho, int Wo, int Hout, int Wout, int C,
+                                void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy && out && B > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 8 == 0, "zero_insert2: bad args");
+  S2P_CHECK_ARG(Hout >= 2 * Ho - 1 && Wout >= 2 * Wo - 1, "zero_insert2: output %dx%d too small for %dx%d", Hout, Wout, Ho, Wo);
+  S2P_CHECK_ARG(dy_pitch >= C && dy_pitch % 8 == 0, "zero_insert2: pitch");
+  S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, "zero_insert2: 16-byte alignment");
+  const long long total = static_cast<long long>(B) * Hout * Wout * (C / 8);
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  zero_insert2_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), dy_pitch, static_cast<__nv_bfloat16*>(out), B, Ho, Wo, Hout, Wout, C / 8);
+  count_launch();
+  return check_launch("zero_insert2_kernel");
 }

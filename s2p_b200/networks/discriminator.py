@@ -29,10 +29,9 @@ class _NLayerParams(nn.Module):
             # nn.Sequential with the conv at index 0: parameter names "model{i}.0.weight" as in the oracle
             self.add_module(f"model{i}", nn.Sequential(nn.Conv2d(ci, co, 4, st, 2)))
 
-    def forward(self, x_nhwc):
-        feats = []
-        x = x_nhwc
-        last = len(self.specs) - 1
+    def padded_params(self):
+        """[(weight, bias)] with in / out channels zero-padded to multiples of 64 (what the kernels run on)"""
+        out = []
         for i, (ci, co, st, norm) in enumerate(self.specs):
             conv = getattr(self, f"model{i}")[0]
             w, b = conv.weight, conv.bias
@@ -41,14 +40,25 @@ class _NLayerParams(nn.Module):
             if co % 64:
                 w = F.pad(w, (0, 0, 0, 0, 0, 0, 0, 64 - co % 64))
                 b = F.pad(b, (0, 64 - co % 64))
+            out.append((w, b))
+        return out
+
+    def forward(self, x_nhwc, params=None, packs=None):
+        feats = []
+        x = x_nhwc
+        last = len(self.specs) - 1
+        params = self.padded_params() if params is None else params
+        for i, (ci, co, st, norm) in enumerate(self.specs):
+            w, b = params[i]
+            pk = None if packs is None else packs[i]
             B, h, wd, _ = x.shape
             ho, wo = (h + 4 - 4) // st + 1, (wd + 4 - 4) // st + 1
             if norm:
                 stt = A.conv_stats((B, ho, wo, w.shape[0]), x.device)
-                y = A.conv(x, w, b, None, st, ACT_NONE, stt, 2)
+                y = A.conv(x, w, b, None, st, ACT_NONE, stt, 2, packed=pk)
                 x = A.mat_norm(y, ops.in_stats_finalize(stt, ho * wo))
             else:
-                x = A.conv(x, w, b, None, st, ACT_NONE if i == last else ACT_LRELU, None, 2)
+                x = A.conv(x, w, b, None, st, ACT_NONE if i == last else ACT_LRELU, None, 2, packed=pk)
             feats.append(x[..., :co].permute(0, 3, 1, 2))      # NCHW view, like the oracle's outputs
         return feats
 
@@ -70,11 +80,16 @@ class MultiscaleDiscriminatorB200(nn.Module):
         if not x.is_cuda:
             raise RuntimeError("MultiscaleDiscriminatorB200 needs CUDA tensors; there is no CPU fallback")
         out = []
+        # both packed forms of every conv weight of every scale in one launch (the first layer's data gradient only
+        # when the input carries one: the generator step)
+        nets = [getattr(self, f"discriminator_{i}") for i in range(self.num_D)]
+        params = [n.padded_params() for n in nets]
+        flat = [(w, x.requires_grad or li > 0) for ps in params for li, (w, _) in enumerate(ps)]
+        packed = ops.pack_conv_weights_multi([w for w, _ in flat], [d for _, d in flat])
         for i in range(self.num_D):
-            B, c, h, w = x.shape
-            x0 = torch.zeros(B, h, w, 64, dtype=torch.bfloat16, device=x.device)
-            x0[..., :c] = x.permute(0, 2, 3, 1)
-            out.append(getattr(self, f"discriminator_{i}")(x0))
+            x0 = A.pad_channels(x.float())
+            nl = len(params[i])
+            out.append(nets[i](x0, params[i], packed[i * nl:(i + 1) * nl]))
             if i + 1 < self.num_D:
                 x = F.avg_pool2d(x, 3, 2, 1, count_include_pad=False)
         return out

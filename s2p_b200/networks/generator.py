@@ -357,14 +357,14 @@ class S2PGeneratorB200(nn.Module):
         dev = image.device
         bf = torch.bfloat16
 
-        def conv_in(x, conv, stride=1, act=ACT_NONE, residual=None, want_stats=True, weight=None, bias=None):
+        def conv_in(x, conv, stride=1, act=ACT_NONE, residual=None, want_stats=True, weight=None, bias=None, packed=None):
             w = conv.weight if weight is None else weight
             b = conv.bias if bias is None else bias
             k = w.shape[2]
             ho = (x.shape[1] + 2 * (k // 2) - k) // stride + 1
             wo = (x.shape[2] + 2 * (k // 2) - k) // stride + 1
             st = A.conv_stats((B, ho, wo, w.shape[0]), dev) if want_stats else None
-            y = A.conv(x, w, b, residual, stride, act, st)
+            y = A.conv(x, w, b, residual, stride, act, st, packed=packed)
             mr = ops.in_stats_finalize(st, ho * wo) if want_stats else None
             return y, mr
 
@@ -375,27 +375,12 @@ class S2PGeneratorB200(nn.Module):
         wlat = h
         # ---- image encoder; the 3-channel image is zero-padded to 64 channels so the stem is a
         # regular tensor-core conv with a regular weight gradient
-        x0 = torch.zeros(B, H, W, 64, dtype=bf, device=dev)
-        x0[..., :3] = image.permute(0, 2, 3, 1)
+        x0 = A.pad_channels(image.float())
         enc = self.image_encoder
-        e1, mr = conv_in(x0, enc.conv1, weight=F.pad(enc.conv1.weight, (0, 0, 0, 0, 0, 61)))
-        f = {1: A.mat_norm(e1, mr)}
-        e2, mr = conv_in(f[1], enc.conv2, stride=2)
-        f[2] = A.mat_norm(e2, mr)
-        e3, mr = conv_in(f[2], enc.conv3, stride=2)
-        f[4] = A.mat_norm(e3, mr)
-        # ---- merged mlp_shared convs
         groups = {4: [], 2: [], 1: []}
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
             for name, m in blk.mats():
                 groups[ds].append((bi, name, m))
-        hs = {}
-        for ds, mats in groups.items():
-            sw = torch.cat([m.mlp_shared.weight for _, _, m in mats], dim=0)
-            sb = torch.cat([m.mlp_shared.bias for _, _, m in mats], dim=0)
-            hcat, _ = conv_in(f[ds], None, act=ACT_RELU, want_stats=False, weight=sw, bias=sb)
-            for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
-                hs[(bi, name)] = hsl
 
         # blend factors of all MATs at once: scales = [a_0, c_0, a_1, ... | 1-a_0, 1-c_0, ...]; every scaled parameter
         # tensor (state-head rows by a / c, gamma/beta conv weights by 1-a / 1-c) is produced by ONE multi-tensor launch
@@ -430,20 +415,49 @@ class S2PGeneratorB200(nn.Module):
         scaled = A.multi_scale(scales, plan, srcs)
         gsbs_all = A.linear(wlat, scaled[0], scaled[1])
         gsbs, gbwb = {}, {}
-        off = 0
         for i, (bi, name, m) in enumerate(all_mats):
-            C = m.norm_nc
-            gsbs[(bi, name)] = (gsbs_all[:, off:off + C], gsbs_all[:, off + C:off + 2 * C])
             gbwb[(bi, name)] = (scaled[2 + 2 * i], scaled[3 + 2 * i])
-            off += 2 * C
+        # one split (its backward is one cat) instead of 2 slices per MAT (each a zero-fill + copy + accumulate)
+        parts = torch.split(gsbs_all, [m.norm_nc for _, _, m in all_mats for _ in (0, 1)], dim=1)
+        for i, (bi, name, m) in enumerate(all_mats):
+            gsbs[(bi, name)] = (parts[2 * i], parts[2 * i + 1])
+
+        # ---- both packed bf16 forms (forward / data-gradient) of EVERY conv weight of this step in one launch per 48
+        w_e1 = F.pad(enc.conv1.weight, (0, 0, 0, 0, 0, 61))
+        w_rgb = F.pad(self.conv_img.weight, (0, 0, 0, 0, 0, 0, 0, 61))
+        w_sh = {ds: torch.cat([m.mlp_shared.weight for _, _, m in mats], dim=0) for ds, mats in groups.items()}
+        named = [("e1", w_e1, False), ("e2", enc.conv2.weight, True), ("e3", enc.conv3.weight, True),
+                 ("head", self.head.weight, True), ("rgb", w_rgb, True)]
+        named += [(("sh", ds), w, True) for ds, w in w_sh.items()]
+        named += [(("gb", bi, name), gbwb[(bi, name)][0], True) for bi, name, _ in all_mats]
+        for bi, blk in enumerate(self.blocks()):
+            named += [(("c0", bi), blk.conv_0.weight, True), (("c1", bi), blk.conv_1.weight, True)]
+            if blk.learned_shortcut:
+                named.append((("cs", bi), blk.conv_s.weight, True))
+        pk = dict(zip([k for k, _, _ in named], ops.pack_conv_weights_multi([w for _, w, _ in named], [d for _, _, d in named])))
+
+        # ---- image encoder
+        e1, mr = conv_in(x0, enc.conv1, weight=w_e1, packed=pk["e1"])
+        f = {1: A.mat_norm(e1, mr)}
+        e2, mr = conv_in(f[1], enc.conv2, stride=2, packed=pk["e2"])
+        f[2] = A.mat_norm(e2, mr)
+        e3, mr = conv_in(f[2], enc.conv3, stride=2, packed=pk["e3"])
+        f[4] = A.mat_norm(e3, mr)
+        # ---- merged mlp_shared convs
+        hs = {}
+        for ds, mats in groups.items():
+            sb = torch.cat([m.mlp_shared.bias for _, _, m in mats], dim=0)
+            hcat, _ = conv_in(f[ds], None, act=ACT_RELU, want_stats=False, weight=w_sh[ds], bias=sb, packed=pk[("sh", ds)])
+            for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
+                hs[(bi, name)] = hsl
 
         def mat(bi, name, m, xin, mr_in, up, act):
             gs, bs = gsbs[(bi, name)]
             gbw, gbb = gbwb[(bi, name)]
-            gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb)
+            gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb, packed=pk[("gb", bi, name)])
             return A.mat_norm(xin, mr_in, gs, bs, gb, up, act)
 
-        x, mr_x = conv_in(f[4], self.head)
+        x, mr_x = conv_in(f[4], self.head, packed=pk["head"])
         cur = 4
         nblk = len(self.RES_OF_BLOCK)
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
@@ -452,18 +466,18 @@ class S2PGeneratorB200(nn.Module):
             last = bi == nblk - 1
             if blk.learned_shortcut:
                 t = mat(bi, "norm_s", blk.norm_s, x, mr_x, up, ACT_NONE)
-                xs, _ = conv_in(t, blk.conv_s, want_stats=False)
+                xs, _ = conv_in(t, blk.conv_s, want_stats=False, packed=pk[("cs", bi)])
             else:
                 xs = x
             t = mat(bi, "norm_0", blk.norm_0, x, mr_x, up, ACT_LRELU)
-            dx, mr_dx = conv_in(t, blk.conv_0)
+            dx, mr_dx = conv_in(t, blk.conv_0, packed=pk[("c0", bi)])
             t = mat(bi, "norm_1", blk.norm_1, dx, mr_dx, 1, ACT_LRELU)
-            x, mr_x = conv_in(t, blk.conv_1, act=ACT_LRELU if last else ACT_NONE, residual=xs, want_stats=not last)
+            x, mr_x = conv_in(t, blk.conv_1, act=ACT_LRELU if last else ACT_NONE, residual=xs, want_stats=not last,
+                              packed=pk[("c1", bi)])
         # ToRGB: 3 output channels zero-padded to 64 so it runs (and differentiates) on the igemm kernels
-        wi = F.pad(self.conv_img.weight, (0, 0, 0, 0, 0, 0, 0, 61))
         bi_ = F.pad(self.conv_img.bias, (0, 61))
-        rgb, _ = conv_in(x, None, want_stats=False, weight=wi, bias=bi_)
-        return torch.tanh(rgb[..., :3].float()).permute(0, 3, 1, 2).contiguous()
+        rgb, _ = conv_in(x, None, want_stats=False, weight=w_rgb, bias=bi_, packed=pk["rgb"])
+        return A.tanh_out(rgb, 3)
 
     def forward_u8(self, frames_u8_nhwc, state):
         """dataset-facing variant: uint8 HWC frames in, uint8 HWC frames out

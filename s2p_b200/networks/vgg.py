@@ -68,9 +68,7 @@ class VGG19FeaturesB200(nn.Module):
         """image: fp32 NCHW [B,3,H,W] in [-1,1] -> five NHWC bf16 feature maps (relu1_1 ... relu5_1)"""
         if not image.is_cuda:
             raise RuntimeError("VGG19FeaturesB200 needs CUDA tensors; there is no CPU fallback")
-        B, c, h, w = image.shape
-        pad = torch.zeros(B, h, w, 64 - c, dtype=torch.bfloat16, device=image.device)
-        x = torch.cat([image.permute(0, 2, 3, 1).to(torch.bfloat16), pad], dim=3)   # 3 -> 64 zero-padded channels
+        x = A.pad_channels(image.float())   # NHWC bf16, 3 -> 64 zero-padded channels, one kernel (and one for its backward)
         outs = []
         packs = iter(self._packed())
         i = 0

@@ -383,6 +383,44 @@ def adam_step_dev(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step_
                                              step_dev.data_ptr(), _stream()), "s2p_adam_step_dev")
 
 
+def pack_conv_weights_multi(weights, want_dgrad):
+    """[(fwd, dgrad | None)] for a list of OIHW fp32 conv weights: pack_conv_weight / pack_conv_weight_dgrad of all of
+    them in one launch per 48 tensors, into ONE bf16 allocation (views are 256-byte aligned)."""
+    import ctypes
+    lib = _lib.load()
+    ws = []
+    for w in weights:
+        _require_cuda(w)
+        w = w.detach()
+        if w.dtype != torch.float32 or not w.is_contiguous():
+            w = w.contiguous().float()
+        ws.append(w)
+    if not ws:
+        return []
+    al = lambda n: (n + 127) // 128 * 128  # noqa: E731
+    total = sum(al(w.numel()) * (2 if d else 1) for w, d in zip(ws, want_dgrad))
+    flat = torch.empty(total, dtype=torch.bfloat16, device=ws[0].device)
+    out, off = [], 0
+    for w, d in zip(ws, want_dgrad):
+        co, ci, r, s = w.shape
+        f = flat[off:off + w.numel()].view(co, r * s * ci)
+        off += al(w.numel())
+        g = None
+        if d:
+            g = flat[off:off + w.numel()].view(ci, r * s * co)
+            off += al(w.numel())
+        out.append((f, g))
+    for i in range(0, len(ws), 48):
+        ch = range(i, min(i + 48, len(ws)))
+        n = len(ch)
+        vp = lambda xs: (ctypes.c_void_p * n)(*xs)  # noqa: E731
+        ia = lambda k: (ctypes.c_int * n)(*[ws[j].shape[k] for j in ch])  # noqa: E731
+        _lib.check(lib.s2p_pack_conv_weights_multi(vp([ws[j].data_ptr() for j in ch]), vp([out[j][0].data_ptr() for j in ch]),
+                                                   vp([out[j][1].data_ptr() if out[j][1] is not None else None for j in ch]),
+                                                   ia(0), ia(1), ia(2), ia(3), n, _stream()), "s2p_pack_conv_weights_multi")
+    return out
+
+
 def pack_conv_weight_dgrad(w_oihw):
     """OIHW fp32 -> [Cin, R*S*Cout] bf16: the packed weight of the data-gradient conv."""
     _require_cuda(w_oihw)
@@ -433,6 +471,64 @@ def maxpool2_bwd(dy, x):
     _lib.check(_lib.load().s2p_maxpool2_bwd(dy.data_ptr(), _nhwc_pitch(dy, "dy"), x.data_ptr(), _nhwc_pitch(x, "x"),
                                             dx.data_ptr(), _nhwc_pitch(dx, "dx"), b, h, w, c, _stream()), "s2p_maxpool2_bwd")
     return dx
+
+
+def zero_insert2(dy, hout, wout):
+    """[B,Ho,Wo,C] bf16 -> [B,hout,wout,C] with dy at the even positions and zeros elsewhere (stride-2 dgrad input)"""
+    _require_cuda(dy)
+    b, ho, wo, c = dy.shape
+    out = torch.empty(b, hout, wout, c, dtype=torch.bfloat16, device=dy.device)
+    if b:
+        _lib.check(_lib.load().s2p_zero_insert2(dy.data_ptr(), _nhwc_pitch(dy, "dy"), out.data_ptr(), b, ho, wo, hout, wout, c,
+                                                _stream()), "s2p_zero_insert2")
+    return out
+
+
+def nchw_to_nhwc64(x):
+    """fp32 NCHW [B,c<=8,H,W] -> bf16 NHWC [B,H,W,64], zero-padded channels"""
+    _require_cuda(x)
+    if x.dtype != torch.float32 or x.dim() != 4:
+        raise RuntimeError("nchw_to_nhwc64: fp32 NCHW tensor required")
+    x = x.contiguous()
+    b, c, h, w = x.shape
+    out = torch.empty(b, h, w, 64, dtype=torch.bfloat16, device=x.device)
+    if b:
+        _lib.check(_lib.load().s2p_nchw_to_nhwc64(x.data_ptr(), out.data_ptr(), b, c, h, w, _stream()), "s2p_nchw_to_nhwc64")
+    return out
+
+
+def nhwc64_to_nchw(dy, c):
+    """the first c channels of a bf16 NHWC tensor as fp32 NCHW (backward of nchw_to_nhwc64)"""
+    _require_cuda(dy)
+    b, h, w, _ = dy.shape
+    out = torch.empty(b, c, h, w, dtype=torch.float32, device=dy.device)
+    if b:
+        _lib.check(_lib.load().s2p_nhwc64_to_nchw(dy.data_ptr(), _nhwc_pitch(dy, "dy"), out.data_ptr(), b, c, h, w, _stream()),
+                   "s2p_nhwc64_to_nchw")
+    return out
+
+
+def tanh_nhwc_to_nchw(x, c):
+    """tanh of the first c channels of a bf16 NHWC tensor, as fp32 NCHW"""
+    _require_cuda(x)
+    b, h, w, _ = x.shape
+    out = torch.empty(b, c, h, w, dtype=torch.float32, device=x.device)
+    if b:
+        _lib.check(_lib.load().s2p_tanh_nhwc_to_nchw(x.data_ptr(), _nhwc_pitch(x, "x"), out.data_ptr(), b, c, h, w, _stream()),
+                   "s2p_tanh_nhwc_to_nchw")
+    return out
+
+
+def tanh_bwd_nchw_to_nhwc64(dy, y):
+    """dy * (1 - y^2) (fp32 NCHW, <= 8 channels) as bf16 NHWC with 64 zero-padded channels"""
+    _require_cuda(dy, y)
+    dy, y = dy.contiguous().float(), y.contiguous()
+    b, c, h, w = dy.shape
+    out = torch.empty(b, h, w, 64, dtype=torch.bfloat16, device=dy.device)
+    if b:
+        _lib.check(_lib.load().s2p_tanh_bwd_nchw_to_nhwc64(dy.data_ptr(), y.data_ptr(), out.data_ptr(), b, c, h, w, _stream()),
+                   "s2p_tanh_bwd_nchw_to_nhwc64")
+    return out
 
 
 def multi_scale_blocks() -> int:

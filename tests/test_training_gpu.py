@@ -327,3 +327,74 @@ def test_multi_scale_fn_vs_torch(pkg):
     for t, t2 in zip(srcs, srcs2):
         assert torch.equal(t.grad, t2.grad)
     assert torch.allclose(scales.grad, scales2.grad, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.gpu
+def test_pack_conv_weights_multi_matches_single_tensor_packs():
+    """one launch for many tensors == the per-tensor pack kernels, bit for bit (incl. > 48 tensors, odd shapes, no-dgrad)"""
+    from s2p_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    shapes = [(64, 64, 3, 3), (128, 64, 1, 1), (8, 64, 4, 4), (512, 128, 3, 3), (64, 320, 1, 1)] + [(64, 64, 3, 3)] * 50
+    ws = [torch.randn(*s, generator=g).cuda() for s in shapes]
+    want = [i % 3 != 1 for i in range(len(ws))]
+    out = ops.pack_conv_weights_multi(ws, want)
+    assert len(out) == len(ws)
+    for w, d, (f, gq) in zip(ws, want, out):
+        assert f.data_ptr() % 256 == 0
+        assert torch.equal(f, ops.pack_conv_weight(w))
+        if d:
+            assert gq.data_ptr() % 256 == 0 and torch.equal(gq, ops.pack_conv_weight_dgrad(w))
+        else:
+            assert gq is None
+    assert ops.pack_conv_weights_multi([], []) == []
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(3, 3, 100, 100), (2, 6, 50, 50), (1, 1, 7, 5), (2, 8, 9, 9)])
+def test_pad_channels_fwd_bwd(shape):
+    """NCHW fp32 -> NHWC bf16 (64 zero-padded channels) and its backward, bit-exact vs the torch expression it replaces"""
+    from s2p_b200 import autograd as A
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(*shape, generator=g).cuda().requires_grad_(True)
+    y = A.pad_channels(x)
+    b, c, h, w = shape
+    ref = torch.zeros(b, h, w, 64, dtype=torch.bfloat16, device="cuda")
+    ref[..., :c] = x.detach().permute(0, 2, 3, 1)
+    assert y.shape == ref.shape and torch.equal(y, ref)
+    dy = torch.randn(b, h, w, 64, generator=g).to(torch.bfloat16).cuda()
+    (dx,) = torch.autograd.grad(y, x, dy)
+    assert torch.equal(dx, dy[..., :c].float().permute(0, 3, 1, 2))
+    with pytest.raises(RuntimeError):
+        A.pad_channels(torch.zeros(1, 9, 4, 4, device="cuda"))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("b,ho,wo,c,hout,wout", [(2, 51, 51, 64, 101, 101), (1, 3, 4, 8, 6, 9), (3, 13, 13, 128, 25, 25)])
+def test_zero_insert2(b, ho, wo, c, hout, wout):
+    from s2p_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    dy = torch.randn(b, ho, wo, c, generator=g).to(torch.bfloat16).cuda()
+    ref = torch.zeros(b, hout, wout, c, dtype=torch.bfloat16, device="cuda")
+    ref[:, 0:2 * ho:2, 0:2 * wo:2] = dy
+    assert torch.equal(ops.zero_insert2(dy, hout, wout), ref)
+    wide = torch.randn(b, ho, wo, c + 8, generator=g).to(torch.bfloat16).cuda()
+    ref[:, 0:2 * ho:2, 0:2 * wo:2] = wide[..., :c]
+    assert torch.equal(ops.zero_insert2(wide[..., :c], hout, wout), ref)      # channel-sliced (pitched) source
+
+
+@pytest.mark.gpu
+def test_tanh_out_fwd_bwd():
+    """generator output head: tanh + NHWC(64) -> NCHW(3), forward and backward vs the torch expression it replaces"""
+    from s2p_b200 import autograd as A
+    g = torch.Generator().manual_seed(13)
+    rgb = (torch.randn(3, 20, 12, 64, generator=g) * 2).to(torch.bfloat16).cuda().requires_grad_(True)
+    y = A.tanh_out(rgb, 3)
+    ref_in = rgb.detach().clone().requires_grad_(True)
+    ref = torch.tanh(ref_in[..., :3].float()).permute(0, 3, 1, 2).contiguous()
+    assert y.shape == ref.shape and (y - ref).abs().max().item() < 2e-6
+    dy = torch.randn(3, 3, 20, 12, generator=g).cuda()
+    (dx,) = torch.autograd.grad(y, rgb, dy)
+    (dref,) = torch.autograd.grad(ref, ref_in, dy)
+    assert dx.shape == dref.shape and dx.dtype == torch.bfloat16
+    assert torch.equal(dx[..., 3:], torch.zeros_like(dx[..., 3:]))
+    assert (dx.float() - dref.float()).abs().max().item() <= 2 ** -7 * dref.float().abs().max().item()

@@ -60,10 +60,17 @@ if a.graph:
     print(f"s2p_b200 train step (CUDA graph replay): batch={B} {ms_g:.2f} ms/step  {B / ms_g * 1e3:.1f} frames/s")
 if a.profile:
     from torch.profiler import profile, ProfilerActivity
-    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_shapes=True) as prof:
         tr.train_step(prev, state, real)
         torch.cuda.synchronize()
     print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=70))
+    # the torch glue between this repo's kernels, by op and input shape (what is left to fuse away)
+    rows = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startswith("aten::") and e.self_device_time_total > 0]
+    rows.sort(key=lambda e: -e.self_device_time_total)
+    print("aten ops by self CUDA time (us), calls, input shapes")
+    for e in rows[:45]:
+        print(f"{e.key:28s} {e.self_device_time_total:9.0f} {e.count:4d}  {str(e.input_shapes)[:150]}")
+    print("aten total self CUDA us:", sum(e.self_device_time_total for e in rows))
 if not a.no_oracle:
     import s2p_oracle as O
     torch.backends.cudnn.allow_tf32 = True
