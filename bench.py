@@ -109,7 +109,7 @@ def run_reference(args):
 # ---------------------------------------------------------------------------- clocks
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw,power.limit")
 
     def __init__(self, index):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
@@ -141,8 +141,14 @@ class ClockSampler:
         sm = sorted(float(s[0]) for s in self.samples)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
-                "samples": len(sm)}
+        out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+               "samples": len(sm)}
+        try:   # board power under load next to its limit: says whether the clock is where the power cap puts it
+            pw = sorted(float(s[6]) for s in self.samples if len(s) >= 8)
+            out["power_w"], out["power_limit_w"] = pw[len(pw) // 2], float(self.samples[0][7])
+        except (ValueError, IndexError):
+            pass
+        return out
 
 
 # ---------------------------------------------------------------------------- GPU arm
