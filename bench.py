@@ -6,8 +6,9 @@ One "step" = one pass of the generator over one batch of B synthetic dataset row
 per rank (uint8 HWC frame + fp32 state -> uint8 HWC next frame): the unit of work of
 BASELINE.json configs[3] (bulk synthesis, batch-sharded over 1/2/4/8 GPUs, weak
 scaling: B rows per rank per step) and, per frame, the same forward as configs[2]
-(the 5-step rollout at batch 1024).  configs[1]/[4] (GAN training) are not built yet
-(DESIGN.md "out of scope this round").
+(the 5-step rollout at batch 1024, also timed as a side measurement `rollout`).  configs[1]
+(GAN training step, batch 16) is timed beside it as `training_step`; `--workload train` makes
+the training step the headline line (configs[4]: batch 256 per GPU, NCCL gradient all-reduce).
   value : frames/s, inputs resident in HBM, CUDA-event timed, max over ranks.
   e2e   : frames/s through s2p_b200.synthesis.BulkSynthesizer with pinned HOST
           buffers: H2D of every row and D2H of every result inside the timed region.
@@ -252,6 +253,11 @@ def run_b200(args):
             line["training_step"] = {"error": repr(e)[:200]}
     if world == 1 and not args.no_train:
         try:
+            line["rollout"] = rollout_side_measurement(torch, net, dev)
+        except Exception as e:  # noqa: BLE001
+            line["rollout"] = {"error": repr(e)[:200]}
+    if world == 1 and not args.no_train:
+        try:
             line["adjacent_components"] = adjacent_side_measurements(torch, dev)
         except Exception as e:  # noqa: BLE001
             line["adjacent_components"] = {"error": repr(e)[:200]}
@@ -328,6 +334,27 @@ def adjacent_side_measurements(torch, dev):
     out["slac_encoder"] = {"kernel": "slac_conv1_kernel (uint8 gather fused) + 5 x conv_igemm_kernel", "batch": 256,
                            "frames": 256 * 9, "ms": ms, "frames_per_sec": 256 * 9 / ms * 1e3}
     return out
+
+
+def rollout_side_measurement(torch, net, dev, batch=1024, seq_len=5, steps=3, warmup=1):
+    """BASELINE configs[2]: N-step autoregressive rollout, seq_len 5, 1024 start frames, through the public
+    `rollout(image, states)` call (fp32 NCHW frames fed back unquantised, all 5 frames of every row returned)."""
+    g = torch.Generator().manual_seed(11)
+    image = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    states = torch.randn(batch, seq_len, net.opt.state_dim, generator=g).to(dev)
+    for _ in range(warmup):
+        out = net.rollout(image, states)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = net.rollout(image, states)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"config": f"BASELINE configs[2]: {seq_len}-step autoregressive rollout of {batch} start frames, cheetah, 1 GPU",
+            "ms_per_rollout": ms, "frames_per_sec": batch * seq_len / ms * 1e3, "steps": steps, "warmup": warmup,
+            "output": list(out.shape), "finite": bool(torch.isfinite(out).all())}
 
 
 def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):

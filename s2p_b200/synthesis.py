@@ -50,8 +50,9 @@ class BulkSynthesizer:
                 frames=torch.empty(b, h, w, 3, dtype=torch.uint8, device=self.device),
                 states=torch.empty(b, s, dtype=torch.float32, device=self.device),
                 out=torch.empty(b, h, w, 3, dtype=torch.uint8, device=self.device),
-                loaded=torch.cuda.Event(), computed=torch.cuda.Event(), drained=torch.cuda.Event()))
+                loaded=torch.cuda.Event(), computed=torch.cuda.Event(), drained=torch.cuda.Event(), used=False))
         self._slots = (slots, (h, w, s))
+        self._tick = 0
 
     @staticmethod
     def _as_host_tensor(a, dtype):
@@ -80,16 +81,20 @@ class BulkSynthesizer:
         for i in range(nb):
             lo, hi = i * self.batch, min(n, (i + 1) * self.batch)
             m = hi - lo
-            sl = slots[i % 2]
+            # slots alternate across calls too: back-to-back synthesize() calls (no host sync in between) keep the
+            # copy / compute overlap and never reuse a slot whose previous batch is still in flight
+            sl = slots[self._tick % 2]
+            self._tick += 1
             with torch.cuda.stream(self._copy_in):
-                if i >= 2:
+                if sl["used"]:
                     self._copy_in.wait_event(sl["computed"])      # slot's inputs consumed
                 sl["frames"][:m].copy_(frames[lo:hi], non_blocking=True)
                 sl["states"][:m].copy_(states[lo:hi], non_blocking=True)
                 sl["loaded"].record(self._copy_in)
             compute.wait_event(sl["loaded"])
-            if i >= 2:
+            if sl["used"]:
                 compute.wait_event(sl["drained"])                  # slot's output copied out
+            sl["used"] = True
             res = self.net.forward_u8(sl["frames"][:m], sl["states"][:m])
             sl["out"][:m].copy_(res)
             sl["computed"].record(compute)

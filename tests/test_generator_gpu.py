@@ -171,3 +171,28 @@ def test_edge_cases_empty_ragged_and_bad_shapes(pkg):
         net(torch.zeros(2, 3, 100, 100, device=dev), torch.zeros(3, 17, device=dev))
     with pytest.raises(RuntimeError):
         net(torch.zeros(2, 3, 100, 100, dtype=torch.float16, device=dev), torch.zeros(2, 17, device=dev))
+
+
+def test_bulk_synthesizer_back_to_back_calls_and_ragged_tail(pkg):
+    """BulkSynthesizer (pinned host buffers, copy streams, two device slots): calls issued back to back WITHOUT a host
+    sync in between must not reuse a slot whose previous batch is still in flight; a ragged last batch and a
+    caller-provided output buffer are covered too.  Every result equals forward_u8 on the same rows, bit for bit."""
+    from s2p_b200.synthesis import BulkSynthesizer
+    _, net = _pair(pkg, "cheetah", "scaled")
+    g = torch.Generator().manual_seed(21)
+    synth = BulkSynthesizer(net, batch=48)
+    jobs = []
+    for n in (200, 48, 131):
+        frames = torch.randint(0, 256, (n, 100, 100, 3), dtype=torch.uint8, generator=g).pin_memory()
+        states = torch.randn(n, 17, generator=g).pin_memory()
+        jobs.append((frames, states, torch.empty_like(frames).pin_memory()))
+    for frames, states, out in jobs:                     # queued back to back
+        assert synth.synthesize(frames, states, out) is out
+    torch.cuda.synchronize()
+    for frames, states, out in jobs:
+        ref = torch.cat([net.forward_u8(frames[i:i + 64].cuda(), states[i:i + 64].cuda()).cpu() for i in range(0, frames.shape[0], 64)])
+        assert torch.equal(out, ref)
+    assert synth.h2d_bytes == sum(f.numel() + s.numel() * 4 for f, s, _ in jobs)
+    assert synth.d2h_bytes == sum(f.numel() for f, _, _ in jobs)
+    with pytest.raises(RuntimeError):
+        synth.synthesize(jobs[0][0], jobs[1][1])         # row counts disagree
