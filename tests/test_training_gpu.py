@@ -398,3 +398,36 @@ def test_tanh_out_fwd_bwd():
     assert dx.shape == dref.shape and dx.dtype == torch.bfloat16
     assert torch.equal(dx[..., 3:], torch.zeros_like(dx[..., 3:]))
     assert (dx.float() - dref.float()).abs().max().item() <= 2 ** -7 * dref.float().abs().max().item()
+
+
+@pytest.mark.gpu
+def test_training_fits_a_fixed_batch_like_the_oracle(pkg):
+    """Functional check over MANY steps (per-op parity cannot catch a sign or a stale-pack error that only shows after
+    the optimiser has moved the weights): 30 G + D steps on one fixed batch.  The L1 term must fall, stay finite, and
+    end within a few percent of where the eager fp32 oracle ends from the same weights on the same batch."""
+    import s2p_oracle as O
+    from s2p_b200.training import S2PTrainer
+    oG = common.build_oracle("walker", "scaled").cuda().train()
+    torch.manual_seed(6)
+    oD = O.define_D(O.make_options(init_type="scaled")).cuda()
+    nG = pkg.define_G(pkg.make_options(env_type="walker", gpu_ids="0"))
+    nD = pkg.define_D(pkg.make_options(gpu_ids="0"))
+    nG.load_state_dict(oG.state_dict())
+    nD.load_state_dict(oD.state_dict())
+    image, states = common.make_inputs("walker", 4, 1)
+    g = torch.Generator().manual_seed(10)
+    real = (torch.rand(4, 3, 100, 100, generator=g) * 0.6 - 0.3).cuda()
+    image, st = image.cuda(), states[:, 0].cuda()
+    optG = torch.optim.Adam(oG.parameters(), **O.ADAM)
+    optD = torch.optim.Adam(oD.parameters(), **O.ADAM)
+    tr = S2PTrainer(nG, nD, O.ADAM["lr"], O.ADAM["betas"])
+    ours, ref = [], []
+    for _ in range(30):
+        g_out, d_out = tr.train_step(image, st, real)
+        g_ref, d_ref, _ = O.training_step(oG, oD, optG, optD, image, st, real)
+        ours.append(float(g_out["L1"].detach()))
+        ref.append(float(g_ref["L1"].detach()))
+        assert all(torch.isfinite(v).all() for v in g_out.values()) and torch.isfinite(d_out).all()
+    print(f"L1 ours {ours[0]:.4f} -> {ours[-1]:.4f}; oracle {ref[0]:.4f} -> {ref[-1]:.4f}")
+    assert ours[-1] < 0.8 * ours[0] and ref[-1] < 0.8 * ref[0]
+    assert abs(ours[-1] - ref[-1]) <= 0.10 * ref[-1]
