@@ -398,36 +398,39 @@ __global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int dy
 
 // Zero-insertion in front of the data-gradient conv of a stride-2 layer (transposed convolution):
 // out[b][2i][2j][:] = dy[b][i][j][:], everything else 0, in one write-only pass (was a fill plus a strided copy).
+// One CTA per output row (b, h): 32-bit index arithmetic only, odd rows are pure zero fills.
 __global__ void __launch_bounds__(256)
-zero_insert2_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, __nv_bfloat16* __restrict__ out, int B, int Ho,
-                    int Wo, int Hout, int Wout, int C8) {
-  const long long total = static_cast<long long>(B) * Hout * Wout * C8;
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
-    const int c8 = static_cast<int>(i % C8);
-    long long q = i / C8;
-    const int w = static_cast<int>(q % Wout); q /= Wout;
-    const int h = static_cast<int>(q % Hout);
-    const long long b = q / Hout;
+zero_insert2_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, __nv_bfloat16* __restrict__ out, int Ho, int Wo,
+                    int Hout, int Wout, int C8) {
+  const int h = blockIdx.x % Hout;
+  const long long b = blockIdx.x / Hout;
+  uint4* __restrict__ row = reinterpret_cast<uint4*>(out) + (b * Hout + h) * static_cast<long long>(Wout) * C8;
+  const int n = Wout * C8;
+  const bool live = !(h & 1) && (h >> 1) < Ho;
+  const __nv_bfloat16* __restrict__ src = dy + (b * Ho + (h >> 1)) * static_cast<long long>(Wo) * dy_pitch;
+  for (int i = threadIdx.x; i < n; i += 256) {
     uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (!(h & 1) && !(w & 1) && (h >> 1) < Ho && (w >> 1) < Wo)
-      v = __ldg(reinterpret_cast<const uint4*>(dy + ((b * Ho + (h >> 1)) * Wo + (w >> 1)) * dy_pitch + c8 * 8));
-    reinterpret_cast<uint4*>(out)[i] = v;
+    if (live) {
+      const int w = i / C8, c8 = i - w * C8;
+      if (!(w & 1) && (w >> 1) < Wo)
+        v = __ldg(reinterpret_cast<const uint4*>(src + static_cast<long long>(w >> 1) * dy_pitch + c8 * 8));
+    }
+    row[i] = v;
   }
 }
 
 // fp32 NCHW [B][c][H][W] (c <= 8: images, image pairs) -> bf16 NHWC [B][H][W][64], channels >= c zero: the operand
-// the tensor-core convs take for a 3- or 6-channel input.  8 threads per pixel, one 16-byte store each (a warp
-// writes 512 contiguous bytes); only the first thread of a pixel reads.  HBM-bound on the 128 B per pixel it writes.
-// `t` (optional, same layout as x): the tanh output whose backward this is -> x * (1 - t^2) is what gets stored
+// the tensor-core convs take for a 3- or 6-channel input.  A CTA takes 256 pixels: every thread reads the c planes of
+// ONE pixel (coalesced along the plane) and parks the packed 8 channels in shared memory; then the CTA writes its
+// 256 x 128 B of output as consecutive 16-byte stores (7 of every 8 are zeros).  HBM-bound on the 128 B per pixel it
+// writes.  `t` (optional, same layout as x): the tanh output whose backward this is -> x * (1 - t^2) is stored.
 __global__ void __launch_bounds__(256)
 nchw_to_nhwc64_kernel(const float* __restrict__ x, const float* __restrict__ t, __nv_bfloat16* __restrict__ y,
                       long long total_pix, int c, int HW) {
-  const long long gid = blockIdx.x * 256ll + threadIdx.x;
-  const long long pix = gid >> 3;
-  const int part = static_cast<int>(gid & 7);
-  if (pix >= total_pix) return;
-  uint4 v = make_uint4(0u, 0u, 0u, 0u);
-  if (part == 0) {
+  __shared__ uint4 head[256];
+  const long long pix0 = blockIdx.x * 256ll;
+  const long long pix = pix0 + threadIdx.x;
+  if (pix < total_pix) {
     const long long n = pix / HW;
     const int p = static_cast<int>(pix - n * HW);
     float f[8];
@@ -439,9 +442,13 @@ nchw_to_nhwc64_kernel(const float* __restrict__ x, const float* __restrict__ t, 
         f[j] *= 1.f - tv * tv;
       }
     }
-    v = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+    head[threadIdx.x] = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
   }
-  *reinterpret_cast<uint4*>(y + pix * 64 + part * 8) = v;
+  __syncthreads();
+  const long long left = total_pix - pix0;
+  const int items = static_cast<int>(left < 256 ? left : 256) * 8;
+  uint4* __restrict__ dst = reinterpret_cast<uint4*>(y + pix0 * 64);
+  for (int i = threadIdx.x; i < items; i += 256) dst[i] = (i & 7) ? make_uint4(0u, 0u, 0u, 0u) : head[i >> 3];
 }
 
 // its backward: dx[n][j][h][w] = float(dy[n][h][w][j]) for j < c (the padded channels carry no gradient)
@@ -738,7 +745,7 @@ static int nchw_to_nhwc64_impl(const float* x_nchw, const float* tanh_out, void*
   S2P_CHECK_ARG(C >= 1 && C <= 8, "nchw_to_nhwc64: C=%d (1..8 channels are padded to 64)", C);
   S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(y_nhwc64) & 15) == 0, "nchw_to_nhwc64: 16-byte alignment");
   const long long total = static_cast<long long>(B) * H * W;
-  const long long blocks = (total * 8 + 255) / 256;
+  const long long blocks = (total + 255) / 256;
   S2P_CHECK_ARG(blocks < (1ll << 31), "nchw_to_nhwc64: too many pixels");
   nchw_to_nhwc64_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       x_nchw, tanh_out, static_cast<__nv_bfloat16*>(y_nhwc64), total, C, H * W);
@@ -789,10 +796,10 @@ extern "C" int s2p_zero_insert2(const void* dy, int dy_pitch, void* out, int B, 
   S2P_CHECK_ARG(Hout >= 2 * Ho - 1 && Wout >= 2 * Wo - 1, "zero_insert2: output %dx%d too small for %dx%d", Hout, Wout, Ho, Wo);
   S2P_CHECK_ARG(dy_pitch >= C && dy_pitch % 8 == 0, "zero_insert2: pitch");
   S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, "zero_insert2: 16-byte alignment");
-  const long long total = static_cast<long long>(B) * Hout * Wout * (C / 8);
-  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-  zero_insert2_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), dy_pitch, static_cast<__nv_bfloat16*>(out), B, Ho, Wo, Hout, Wout, C / 8);
+  const long long rows = static_cast<long long>(B) * Hout;
+  S2P_CHECK_ARG(rows < (1ll << 31) && static_cast<long long>(Wout) * (C / 8) < (1ll << 31), "zero_insert2: too large");
+  zero_insert2_kernel<<<static_cast<unsigned>(rows), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), dy_pitch, static_cast<__nv_bfloat16*>(out), Ho, Wo, Hout, Wout, C / 8);
   count_launch();
   return check_launch("zero_insert2_kernel");
 }
