@@ -112,8 +112,10 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw,power.limit")
 
-    def __init__(self, index):
-        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+    def __init__(self, index, enabled=True):
+        # only rank 0 samples: eight ranks each forking nvidia-smi five times a second compete with the ranks' own
+        # launch threads for the host cores
+        self.index, self.samples, self._stop, self._t, self.enabled = index, [], threading.Event(), None, enabled
 
     def _loop(self):
         while not self._stop.is_set():
@@ -128,13 +130,15 @@ class ClockSampler:
             self._stop.wait(0.2)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._loop, daemon=True)
-        self._t.start()
+        if self.enabled:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
         return self
 
     def __exit__(self, *a):
         self._stop.set()
-        self._t.join(timeout=6)
+        if self._t is not None:
+            self._t.join(timeout=6)
 
     def summary(self):
         if not self.samples:
@@ -199,7 +203,7 @@ def run_b200(args):
     for _ in range(args.warmup):
         net.forward_u8(frames_d, states_d)
     barrier()
-    with ClockSampler(local) as clk:
+    with ClockSampler(local, enabled=rank == 0) as clk:
         l0 = _lib.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -529,7 +533,7 @@ def run_train(args):
     for _ in range(args.warmup):
         step()
     barrier()
-    with ClockSampler(local) as clk:
+    with ClockSampler(local, enabled=rank == 0) as clk:
         l0 = _lib.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
