@@ -96,7 +96,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   const int co0 = blockIdx.x * 128;
   const int ci_tiles = p.Cin / BN;
   const int ci0 = (blockIdx.y % ci_tiles) * BN;
-  const int r = blockIdx.y / ci_tiles;            // filter row of this CTA
+  // a CTA owns filter row r and TAPS consecutive taps of it starting at s_base (TAPS == S: the whole row)
+  const int s_groups = p.S / TAPS;
+  const int rs = blockIdx.y / ci_tiles;
+  const int r = rs / s_groups;
+  const int s_base = (rs % s_groups) * TAPS;
   const int split = blockIdx.z, splits = gridDim.z;
   const int t_begin = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * split / splits);
   const int t_end = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * (split + 1) / splits);
@@ -121,7 +125,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 #pragma unroll
           for (int b = 0; b < kAtomsB; ++b)
             tma_load_4d(s0 + (kAtomsA + s * kAtomsB + b) * atom_stride, &tmap_x, &full_bar[stage], ci0 + 64 * b,
-                        w0 * p.stride - p.pad + s, h0 * p.stride - p.pad + r, img);
+                        w0 * p.stride - p.pad + s_base + s, h0 * p.stride - p.pad + r, img);
       }
       __syncwarp();
       if (++stage == kWgStages) { stage = 0; phase ^= 1; }
@@ -174,7 +178,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         }
         if (co < p.Cout) {
           float4* dst = reinterpret_cast<float4*>(
-              p.partial + (((static_cast<size_t>(split) * p.Cout + co) * p.R + r) * p.S + s) * p.Cin + ci0 + c * 32);
+              p.partial + (((static_cast<size_t>(split) * p.Cout + co) * p.R + r) * p.S + s_base + s) * p.Cin + ci0 + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             dst[j] = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]),
@@ -211,6 +215,12 @@ static int wgrad_max_rows() {
   static int r = 0;
   if (r == 0) { const char* e = getenv("S2P_WGRAD_ROWS"); r = e ? atoi(e) : 128; if (r < 16) r = 16; if (r > 128) r = 128; }
   return r;
+}
+
+static int wgrad_tap_split() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("S2P_WGRAD_TAP_SPLIT"); v = e ? atoi(e) : 1; }
+  return v;
 }
 
 static int wgrad_pad16() {
@@ -278,14 +288,18 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
   pl->taps = ksize;
   const int atom = ((p.kb_rows + 15) / 16) * 16 * 128;
   pl->bn = (Cin % 128 == 0 && ksize * 128 <= 512 && 2 * (2 + ksize * 2) * atom <= 200 * 1024) ? 128 : 64;
-  const int ctas = ((Cout + 127) / 128) * (Cin / pl->bn) * ksize;
+  // big pixel tiles (25 x 5 = 125 rows, 16 KB per 64-channel block) leave no room for a 128-wide ci tile of all
+  // three taps; a 128 x 64 MMA is operand-bound at ~46 % of the tensor pipe, so such layers run ONE tap per CTA
+  // with the 128-wide tile instead (dY is then fetched once per tap, from L2)
+  if (pl->bn == 64 && Cin % 128 == 0 && ksize == 3 && wgrad_tap_split()) { pl->bn = 128; pl->taps = 1; }
+  const int ctas = ((Cout + 127) / 128) * (Cin / pl->bn) * ksize * (ksize / pl->taps);
   // split-K so that the grid is as close as possible to (but not above) ONE full wave: the kernel
   // runs one CTA per SM, so 2.03 waves cost 3
   int splits = num_sms() / ctas;
   if (splits > p.num_pix_tiles) splits = p.num_pix_tiles;
   if (splits < 1) splits = 1;
   pl->splits = splits;
-  pl->grid = dim3((Cout + 127) / 128, (Cin / pl->bn) * ksize, splits);
+  pl->grid = dim3((Cout + 127) / 128, (Cin / pl->bn) * ksize * (ksize / pl->taps), splits);
   const int atom_stride = ((p.kb_rows + 15) / 16) * 16 * 128;
   const int stage_bytes = (2 + pl->taps * (pl->bn / 64)) * atom_stride;
   int stages = (200 * 1024) / stage_bytes;
@@ -368,14 +382,14 @@ extern "C" int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc;
   if (pl.bn == 128) {
-    switch (ksize) {
+    switch (pl.taps) {
       case 1: rc = launch_wgrad<128, 1>(tdy, tx, pl, st); break;
       case 3: rc = launch_wgrad<128, 3>(tdy, tx, pl, st); break;
       case 4: rc = launch_wgrad<128, 4>(tdy, tx, pl, st); break;
       default: return set_error(S2P_ERR_UNSUPPORTED, "wgrad: ksize=%d", ksize);
     }
   } else {
-    switch (ksize) {
+    switch (pl.taps) {
       case 1: rc = launch_wgrad<64, 1>(tdy, tx, pl, st); break;
       case 3: rc = launch_wgrad<64, 3>(tdy, tx, pl, st); break;
       case 4: rc = launch_wgrad<64, 4>(tdy, tx, pl, st); break;

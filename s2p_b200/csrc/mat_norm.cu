@@ -189,6 +189,7 @@ extern "C" int s2p_in_stats_finalize(const float* stats_partial, int rows, float
   using namespace s2p;
   S2P_CHECK_ARG(stats_partial && mean_rstd, "stats_finalize: null pointer");
   S2P_CHECK_ARG(rows > 0 && B > 0 && C > 0 && HW > 0, "stats_finalize: bad dims");
+  S2P_CHECK_ARG(B <= 65535, "stats_finalize: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 grid((C + 31) / 32, B), block(32, 8);
   in_stats_finalize_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float2*>(stats_partial), rows, reinterpret_cast<float2*>(mean_rstd), B, C,
@@ -205,6 +206,7 @@ extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float
   S2P_CHECK_ARG(rows > 0 && B > 0 && C > 0 && HW > 0, "mat_prepare: bad dims");
   S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_prepare: gs and bs must both be given or both null");
   S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(mod_table) & 15) == 0, "mat_prepare: table must be 16-byte aligned");
+  S2P_CHECK_ARG(B <= 65535, "mat_prepare: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 grid((C + 31) / 32, B), block(32, 8);
   mat_prepare_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float2*>(stats_partial), rows, gs, bs, gsbs_pitch, bias_gb,
@@ -245,6 +247,7 @@ extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float*
   if (chunks < 1) chunks = 1;
   p.pix_per_cta = (HW + chunks - 1) / chunks;
   chunks = (HW + p.pix_per_cta - 1) / p.pix_per_cta;
+  S2P_CHECK_ARG(B <= 65535, "mat_norm: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 block(groups, py), grid(chunks, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (gb_spatial) {
@@ -491,6 +494,7 @@ extern "C" int s2p_mat_norm_bwd(const void* dy, int dy_pitch, const void* x, int
   p.B = B; p.H = H; p.W = W; p.C = C; p.up = up; p.act = act;
   int py;
   norm_bwd_geometry(B, H, W, C, &py, &p.chunks, &p.pix_per_cta);
+  S2P_CHECK_ARG(B <= 65535, "mat_norm_bwd: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 block(C / 8, py), grid(p.chunks, B);
   const size_t smem = static_cast<size_t>(py) * C * sizeof(float4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -216,6 +216,7 @@ extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* 
   const int rows = s2p_stem_stats_rows(H, W);
   const int slots = 256 / (Cout / 8);
   const size_t smem = (27 * Cout + 3 * (kStemRows + 2) * (W + 2) + slots * Cout * 2) * sizeof(float);
+  S2P_CHECK_ARG(B <= 65535, "stem: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 grid(rows, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   static size_t smem_configured = 48 * 1024;
