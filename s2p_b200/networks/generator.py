@@ -133,8 +133,16 @@ class S2PGeneratorB200(nn.Module):
 
     def _apply(self, fn, *a, **k):
         self._packed = None
+        self._plist = None
         self._ws = {}
         return super()._apply(fn, *a, **k)
+
+    def _pack_key(self):
+        """what the packed bf16 weights were built from: torch's version counter of every parameter (in-place
+        updates by torch code) and the library's parameter epoch (fused Adam / graph replay update through raw pointers)"""
+        if getattr(self, "_plist", None) is None:
+            self._plist = list(self.parameters())
+        return ops.param_epoch(), tuple(p._version for p in self._plist)
 
     @torch.no_grad()
     def pack(self):
@@ -191,6 +199,7 @@ class S2PGeneratorB200(nn.Module):
                 d["cs_w"] = ops.pack_conv_weight(blk.conv_s.weight)
             P["blk"].append(d)
         self._packed = P
+        self._packed_key = self._pack_key()
         return self
 
     # ------------------------------------------------------------------ workspace
@@ -310,8 +319,8 @@ class S2PGeneratorB200(nn.Module):
         if not image.is_cuda or not state.is_cuda:
             raise RuntimeError("S2PGeneratorB200.forward needs CUDA tensors; there is no CPU fallback "
                                "(the CPU restatement lives in oracle/ and is test infrastructure)")
-        if self._packed is None:
-            self.pack()
+        if self._packed is None or self._packed_key != self._pack_key():
+            self.pack()                  # first use, or the parameters moved since the last pack (training in between)
         if image.dtype == torch.uint8:
             B, H, W = image.shape[0], image.shape[1], image.shape[2]
         elif image.dtype == torch.float32:

@@ -344,6 +344,20 @@ def linear(x, w, bias, act=ACT_NONE, out=None):
 _linear_ws = {}
 
 
+# Kernels of this library update parameters through raw pointers (fused Adam, a replayed CUDA graph of the whole
+# training step), which torch's per-tensor version counters do not see.  Every such update bumps this epoch, and the
+# modules that cache packed bf16 weights (the generator's inference schedule) key their cache on it.
+_PARAM_EPOCH = [0]
+
+
+def bump_param_epoch():
+    _PARAM_EPOCH[0] += 1
+
+
+def param_epoch() -> int:
+    return _PARAM_EPOCH[0]
+
+
 def adam_step_multi(params, grads, exp_avgs, exp_avg_sqs, lr, beta1, beta2, eps, step_dev):
     """torch.optim.Adam update of many fp32 tensors, 64 per launch"""
     import ctypes

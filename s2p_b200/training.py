@@ -55,6 +55,7 @@ class FusedAdam:
         if live:
             ps, gs, ms, vs = zip(*live)
             ops.adam_step_multi(ps, gs, ms, vs, self.lr, self.betas[0], self.betas[1], self.eps, self.step_dev)
+            ops.bump_param_epoch()      # packed-weight caches keyed on the parameters are stale now
 
 
 def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
@@ -200,4 +201,5 @@ class S2PTrainer:
         for dst, src in zip(self._static, (prev_image, state, real_image)):
             dst.copy_(src, non_blocking=True)
         self._graph.replay()
+        ops.bump_param_epoch()          # the replayed graph moved the weights without touching their version counters
         return self._static_out

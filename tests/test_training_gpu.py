@@ -431,3 +431,42 @@ def test_training_fits_a_fixed_batch_like_the_oracle(pkg):
     print(f"L1 ours {ours[0]:.4f} -> {ours[-1]:.4f}; oracle {ref[0]:.4f} -> {ref[-1]:.4f}")
     assert ours[-1] < 0.8 * ours[0] and ref[-1] < 0.8 * ref[0]
     assert abs(ours[-1] - ref[-1]) <= 0.10 * ref[-1]
+
+
+@pytest.mark.gpu
+def test_inference_after_training_uses_the_updated_weights(pkg):
+    """the inference schedule caches packed bf16 weights; a fused-Adam step, a replayed graph step and a plain in-place
+    torch update must each invalidate that cache (the first two move the weights through raw pointers)"""
+    from s2p_b200.training import S2PTrainer
+    torch.manual_seed(3)
+    opt = pkg.make_options(env_type="walker", gpu_ids="0", init_type="scaled")
+    nG, nD = pkg.define_G(opt), pkg.define_D(opt)
+    image, states = common.make_inputs("walker", 2, 1)
+    g = torch.Generator().manual_seed(2)
+    real = (torch.rand(2, 3, 100, 100, generator=g) * 2 - 1).cuda()
+    image, st = image.cuda(), states[:, 0].cuda()
+
+    def fresh_eval():
+        ref = pkg.define_G(opt)
+        ref.load_state_dict(nG.state_dict())
+        return ref.eval()(image, st)
+
+    def own_eval():
+        nG.eval()
+        with torch.no_grad():
+            out = nG(image, st)
+        nG.train()
+        return out
+
+    before = own_eval()                                  # builds the cache
+    tr = S2PTrainer(nG, nD, lr=1e-2)                     # a step large enough to change the output visibly
+    tr.train_step(image, st, real)
+    after = own_eval()
+    assert not torch.equal(after, before)
+    assert torch.equal(after, fresh_eval())
+    tr.capture(image, st, real)
+    tr.train_step_graphed(image, st, real)
+    assert torch.equal(own_eval(), fresh_eval())
+    with torch.no_grad():
+        nG.head.weight.mul_(1.5)
+    assert torch.equal(own_eval(), fresh_eval())
