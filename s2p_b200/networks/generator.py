@@ -204,12 +204,15 @@ class S2PGeneratorB200(nn.Module):
 
     # ------------------------------------------------------------------ workspace
     def _buf(self, name, shape, dtype):
-        key = (name, tuple(shape), dtype)
+        """workspace tensor of `shape` (leading dimension = frames of the micro-batch).  One allocation per name, sized
+        for the largest micro-batch seen so far; smaller (ragged-tail, variable-size serving) batches get a leading
+        slice of it, so the set of buffers never grows with the number of distinct batch sizes."""
+        key = (name, tuple(shape[1:]), dtype)
         t = self._ws.get(key)
-        if t is None:
+        if t is None or t.shape[0] < shape[0]:
             t = torch.empty(shape, dtype=dtype, device=self.head.weight.device)
             self._ws[key] = t
-        return t
+        return t[:shape[0]]
 
     def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False,
               finalize=True):

@@ -196,3 +196,22 @@ def test_bulk_synthesizer_back_to_back_calls_and_ragged_tail(pkg):
     assert synth.d2h_bytes == sum(f.numel() for f, _, _ in jobs)
     with pytest.raises(RuntimeError):
         synth.synthesize(jobs[0][0], jobs[1][1])         # row counts disagree
+
+
+def test_workspace_does_not_grow_with_distinct_batch_sizes(pkg):
+    """variable-size serving: after the largest batch has been seen, smaller batches reuse its workspace (leading
+    slices) and give the same bytes as when run first on a fresh module"""
+    ora, net = _pair(pkg, "cheetah", "scaled")
+    image, states = common.make_inputs("cheetah", 5, 1)
+    image, st = image.cuda(), states[:, 0].cuda()
+    full = net(image, st)
+    torch.cuda.synchronize()
+    n_bufs, mem = len(net._ws), torch.cuda.memory_allocated()
+    outs = [net(image[:b], st[:b]) for b in (3, 1, 4, 2)]
+    torch.cuda.synchronize()
+    assert len(net._ws) == n_bufs
+    del outs[1:]
+    assert torch.cuda.memory_allocated() <= mem + 8 * 3 * 100 * 100 * 4 + (1 << 20)
+    assert torch.equal(outs[0], full[:3])
+    _, fresh = _pair(pkg, "cheetah", "scaled")
+    assert torch.equal(fresh(image[:3], st[:3]), outs[0])
