@@ -94,6 +94,20 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
 
 
 _wgrad_ws = {}
+_retired_ws = []
+
+
+def _grow_workspace(cache, device, need, dtype, floor=1):
+    """per-device scratch shared by successive launches on one stream.  It only ever grows (at least doubling), and
+    an outgrown buffer is kept alive instead of freed: a captured CUDA graph of the training step holds its raw
+    pointer, and freed memory handed to another tensor would be scribbled on by the next replay."""
+    ws = cache.get(device)
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _retired_ws.append(ws)
+        ws = torch.empty(max(need, floor, 2 * ws.numel() if ws is not None else 0), dtype=dtype, device=device)
+        cache[device] = ws
+    return ws
 
 
 def conv_wgrad(x, dy, ksize, stride=1, pad=None, out=None, accumulate=False):
@@ -111,11 +125,7 @@ def conv_wgrad(x, dy, ksize, stride=1, pad=None, out=None, accumulate=False):
     need = int(lib.s2p_conv_wgrad_workspace_bytes(b, hin, win, cin, cout, ksize, stride, pad))
     if need < 0:
         raise RuntimeError("conv_wgrad: unsupported shape")
-    key = x.device.index
-    ws = _wgrad_ws.get(key)
-    if ws is None or ws.numel() < need:
-        ws = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
-        _wgrad_ws[key] = ws
+    ws = _grow_workspace(_wgrad_ws, x.device, need, torch.uint8, 1 << 20)
     _lib.check(lib.s2p_conv_wgrad(x.data_ptr(), _nhwc_pitch(x, "x"), dy.data_ptr(), _nhwc_pitch(dy, "dy"), out.data_ptr(),
                                   ws.data_ptr(), ws.numel(), b, hin, win, cin, cout, ksize, stride, pad,
                                   1 if accumulate else 0, _stream()), "s2p_conv_wgrad")
@@ -330,12 +340,7 @@ def linear(x, w, bias, act=ACT_NONE, out=None):
         raise RuntimeError("linear: fp32 row-major operands required")
     lib = _lib.load()
     need = int(lib.s2p_linear_workspace_floats(b, k, n))
-    ws = None
-    if need > 0:
-        ws = _linear_ws.get(x.device)
-        if ws is None or ws.numel() < need:
-            ws = torch.empty(need, dtype=torch.float32, device=x.device)
-            _linear_ws[x.device] = ws
+    ws = _grow_workspace(_linear_ws, x.device, need, torch.float32) if need > 0 else None
     _lib.check(lib.s2p_linear_fwd(x.data_ptr(), x.stride(0), w.data_ptr(), _ptr(bias), out.data_ptr(),
                                   out.stride(0), b, k, n, act, _ptr(ws), need, _stream()), "s2p_linear_fwd")
     return out
