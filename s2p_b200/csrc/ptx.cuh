@@ -114,8 +114,12 @@ __device__ __forceinline__ uint32_t map_to_cta(const void* smem_ptr, uint32_t ra
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(smem_u32(smem_ptr)), "r"(rank));
   return r;
 }
+// Arrive on a (possibly remote) CTA's barrier.  Default semantics (.release at CTA scope), NOT .release.cluster: the
+// cluster-scope form compiles to MEMBAR.ALL.GPU, which makes the arriving warp wait for every global store it has
+// in flight -- in the conv epilogue that exposed a full store round trip per tile (top stall "membar" in ncu).  The
+// accumulator hand-off needs no memory ordering: TMEM reuse is ordered by tcgen05.wait::ld + tcgen05.fence.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(bar_cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(bar_cluster_addr) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
