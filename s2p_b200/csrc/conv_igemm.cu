@@ -84,15 +84,36 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 // 32 different lines with 16 B each (LSU-bound on wide outputs).  The rows are transposed
 // through a warp-private, XOR-swizzled (bank-conflict-free) shared-memory tile instead, and
 // written back with NCH lanes per pixel: whole 32 B sectors, 32/NCH pixels per instruction.
+// The reading side of warp_store_rows stores row rr = i * (32 / NCH) + lane / NCH in its i-th instruction: the
+// destination pixel and validity of those rows are fetched from their owner lanes ONCE per tile (they are the same
+// for every column chunk of the tile), not once per store instruction.
 template <int NCH>
-__device__ __forceinline__ void warp_store_rows(uint8_t* stg, const uint32_t* packed, __nv_bfloat16* out_col,
-                                                int out_pitch, uint32_t pix, bool valid, int lane) {
+struct StoreRows {
+  uint32_t pix[NCH];
+  uint32_t valid_mask;
+};
+template <int NCH>
+__device__ __forceinline__ StoreRows<NCH> store_rows_prepare(uint32_t pix, bool valid, int lane) {
+  StoreRows<NCH> r;
+  r.valid_mask = 0u;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int rr = i * (32 / NCH) + lane / NCH;
+    r.pix[i] = __shfl_sync(0xffffffffu, pix, rr);
+    r.valid_mask |= static_cast<uint32_t>(__shfl_sync(0xffffffffu, static_cast<int>(valid), rr)) << i;
+  }
+  return r;
+}
+
+template <int NCH>
+__device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* packed, __nv_bfloat16* out_col,
+                                                int out_pitch, const StoreRows<NCH>& rows, int lane) {
   constexpr int kRow = NCH * 16;
   const int wkey = (NCH == 4) ? (lane >> 1) : (lane >> 2);
 #pragma unroll
   for (int j = 0; j < NCH; ++j)
-    *reinterpret_cast<uint4*>(stg + lane * kRow + ((j ^ wkey) & (NCH - 1)) * 16) =
-        make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+    sts128(stg + lane * kRow + ((j ^ wkey) & (NCH - 1)) * 16, packed[4 * j], packed[4 * j + 1], packed[4 * j + 2],
+           packed[4 * j + 3]);
   __syncwarp();
   constexpr int kRowsPerInst = 32 / NCH;
   const int j = lane % NCH;
@@ -100,10 +121,9 @@ __device__ __forceinline__ void warp_store_rows(uint8_t* stg, const uint32_t* pa
   for (int i = 0; i < NCH; ++i) {
     const int rr = i * kRowsPerInst + lane / NCH;
     const int rkey = (NCH == 4) ? (rr >> 1) : (rr >> 2);
-    const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * kRow + ((j ^ rkey) & (NCH - 1)) * 16);
-    const uint32_t rpix = __shfl_sync(0xffffffffu, pix, rr);
-    const int rvalid = __shfl_sync(0xffffffffu, static_cast<int>(valid), rr);
-    if (rvalid) *reinterpret_cast<uint4*>(out_col + static_cast<size_t>(rpix) * out_pitch + j * 8) = v;
+    const uint4 v = lds128(stg + rr * kRow + ((j ^ rkey) & (NCH - 1)) * 16);
+    if ((rows.valid_mask >> i) & 1u)
+      *reinterpret_cast<uint4*>(out_col + static_cast<size_t>(rows.pix[i]) * out_pitch + j * 8) = v;
   }
   __syncwarp();
 }
@@ -275,6 +295,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
       const int n0 = n_tile * BLOCK_N;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
+      const uint32_t stg_s = smem_u32(store_smem + (warp - 2) * 2048);   // this warp's staging tile
 
       auto release_acc = [&]() {
         tc_fence_before();
@@ -296,6 +317,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           xpix = pix;
         }
         const int ch0 = n_tile * CT;
+        const StoreRows<2> rows2 = store_rows_prepare<2>(static_cast<uint32_t>(pix), valid, lane);
         float4* tab_s = tab_smem + acc * 128;
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
         const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0 + cw);
@@ -344,8 +366,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
             ow_out[0] = ow[0]; ow_out[1] = ow[1]; ow_out[2] = ow[2]; ow_out[3] = ow[3];
             ow_out[4] = ow[4]; ow_out[5] = ow[5]; ow_out[6] = ow[6]; ow_out[7] = ow[7];
           }
-          warp_store_rows<2>(store_smem + (warp - 2) * 2048, ow_out, p.out + ch0 + cw + sidx * 16, p.out_pitch,
-                             static_cast<uint32_t>(pix), valid, lane);
+          warp_store_rows<2>(stg_s, ow_out, p.out + ch0 + cw + sidx * 16, p.out_pitch, rows2, lane);
         }
       } else if constexpr (EPI == kEpiToRGB) {
         mbar_wait(&tmem_full[acc], acc_phase);
@@ -379,6 +400,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         constexpr int kChunks = BLOCK_N / 64;          // 32-column chunks per warp
         const int cbeg = half * kChunks;
         const bool has_res = (p.residual != nullptr) && valid;
+        const StoreRows<4> rows4 = store_rows_prepare<4>(static_cast<uint32_t>(pix), valid, lane);
         const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + n0 + cbeg * 32);
         uint4 rn[4];
         if (has_res) {
@@ -440,8 +462,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
           for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
           if (!(p.debug & 1))
-            warp_store_rows<4>(store_smem + (warp - 2) * 2048, packed, p.out + ch, p.out_pitch,
-                               static_cast<uint32_t>(pix), valid, lane);
+            warp_store_rows<4>(stg_s, packed, p.out + ch, p.out_pitch, rows4, lane);
           if (p.stats_partial != nullptr && live) {
             // statistics of the values as stored (bf16-rounded), fixed reduction order
             float s1[32], s2[32];
