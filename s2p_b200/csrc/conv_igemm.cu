@@ -414,6 +414,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll 1
         for (int i = 0; i < kChunks; ++i) {
           const int c = cbeg + i;
+          // the chunk's bias values leave shared memory before the accumulator wait, not after it
+          float4 bb[8];
+          if (bias_s != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(bias_s + n0 + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bb[j] = b4[j];
+          }
           tmem_ld_wait();
           float v[32];
 #pragma unroll
@@ -434,11 +441,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           const int ch = n0 + c * 32;
           if (bias_s != nullptr) {
-            const float4* b4 = reinterpret_cast<const float4*>(bias_s + ch);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 bb = b4[j];
-              v[4 * j + 0] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+              v[4 * j + 0] += bb[j].x; v[4 * j + 1] += bb[j].y; v[4 * j + 2] += bb[j].z; v[4 * j + 3] += bb[j].w;
             }
           }
           if (has_res) {
