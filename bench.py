@@ -420,7 +420,8 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
         b, h, w, cin = x.shape
         ho = (h + 2 * (ksize // 2) - ksize) // stride + 1
         wo = (w + 2 * (ksize // 2) - ksize) // stride + 1
-        return 2.0 * b * ho * wo * cout * cin * ksize * ksize
+        cin2 = k["x2"].shape[3] if k.get("x2") is not None else 0     # the 1x1 shortcut riding along as a second operand
+        return 2.0 * b * ho * wo * cout * (cin * ksize * ksize + cin2)
 
     def norm_bytes(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=2, out=None):
         b, hx, wx, c = x.shape

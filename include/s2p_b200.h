@@ -57,6 +57,16 @@ int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const f
                        const void* residual, int res_pitch, void* y, int y_pitch,
                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
                        int stride, int pad, int act, void* stream);
+/* the same convolution with a SECOND operand accumulated into it: y = act(conv(x, W[:, :k*k*Cin]) +
+ * x2 . W[:, k*k*Cin:] + bias + residual), x2 NHWC bf16 [B][Hout][Wout][Cin2] (a 1x1 convolution over a tensor of the
+ * output's size; stride 1, 'same' padding).  w_packed is [Cout][k*k*Cin + Cin2]: s2p_pack_conv_weight of the two
+ * weights concatenated along the row.  Replaces `conv_1(h) + conv_s(x_s)` of the oracle's res-block (SPADEResnetBlock
+ * lineage: learned shortcut) in one launch, without the bf16 round trip of the shortcut through HBM.  x2 == NULL: the
+ * plain call. */
+int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2, const void* w_packed,
+                        const float* bias, const void* residual, int res_pitch, void* y, int y_pitch,
+                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize, int stride,
+                        int pad, int act, void* stream);
 
 /* ---- (a8) weight gradient of the convolution (training) -----------------------------
  * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]

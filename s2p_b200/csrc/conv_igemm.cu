@@ -44,6 +44,10 @@ struct ConvParams {
   float* rgb_f32;
   uint8_t* rgb_u8;
   int debug;   // S2P_CONV_DEBUG (timing experiments only): 1 = skip the plain epilogue's global stores
+  // second operand (plain epilogue, stride 1): kb2 extra 64-channel k-blocks taken from a second NHWC tensor of the
+  // output's spatial size through tmap_a2 -- a 1x1 convolution accumulated into the same tile, which is how a
+  // res-block's learned shortcut rides along with its last 3x3 conv (weights concatenated along K)
+  int kb2;
 };
 
 enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
@@ -130,8 +134,8 @@ __device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* pa
 
 template <int BLOCK_N, int EPI, int CL>
 __global__ void __launch_bounds__(320, 1)
-conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                  const __grid_constant__ CUtensorMap tmap_b, const ConvParams p) {
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_a2, const ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -149,6 +153,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
+    if (p.kb2 > 0) tma_prefetch_desc(&tmap_a2);
     tma_prefetch_desc(&tmap_b);
     for (int i = 0; i < Cfg::kStages; ++i) {
       mbar_init(&full_bar[i], 1);
@@ -182,7 +187,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const int tile_first = blockIdx.x / CL, tile_step = gridDim.x / CL;
   const int tiles_per_img = p.tiles_x * p.tiles_y;
   const int cchunks = p.Cin / Cfg::kBlockK;
-  const int num_kb = p.R * p.S * cchunks;
+  const int num_kb_main = p.R * p.S * cchunks;
+  const int num_kb = num_kb_main + p.kb2;      // the second operand's k-blocks follow the filter taps
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
 
@@ -209,11 +215,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
             constexpr int kPart = BLOCK_N / CL;
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
             const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
-            tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            if (kb < num_kb_main) tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
             tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-            tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            if (kb < num_kb_main) tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            else tma_load_4d(sa, &tmap_a2, &full_bar[stage], (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
             tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
           }
         }
@@ -537,7 +545,8 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
 }
 
 template <int BLOCK_N, int EPI, int CL>
-static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
+static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const ConvParams& p,
+                          cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
   static bool configured = false;
   if (!configured) {
@@ -560,7 +569,7 @@ static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const Co
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, p));
+  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, ta2, p));
   count_launch();
   return check_launch("conv_igemm_kernel");
 }
@@ -576,9 +585,10 @@ int conv_cluster_size() {
 }
 
 template <int BLOCK_N, int EPI>
-static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, cudaStream_t st) {
-  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, p, st);
-  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, p, st);
+static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const ConvParams& p,
+                       cudaStream_t st) {
+  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, ta2, p, st);
+  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, ta2, p, st);
 }
 
 }  // namespace s2p
@@ -594,7 +604,8 @@ namespace s2p {
 // Shared host path of the two conv entry points: validates the GEMM geometry, builds the
 // two tensor maps and launches.  `p` arrives with the epilogue fields already filled.
 static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B, int Hin, int Win, int Cin,
-                         int Cout, int ksize, int stride, int pad, int block_n, int epi, ConvParams p, void* stream) {
+                         int Cout, int ksize, int stride, int pad, int block_n, int epi, ConvParams p, void* stream,
+                         const void* x2 = nullptr, int x2_pitch = 0, int Cin2 = 0) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   {
@@ -614,7 +625,8 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
   p.num_m_tiles = B * p.tiles_x * p.tiles_y;
   p.num_n_tiles = Cout / block_n;
 
-  CUtensorMap ta, tb;
+  p.kb2 = x2 != nullptr ? Cin2 / 64 : 0;
+  CUtensorMap ta, tb, ta2;
   {
     cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)B};
     cuuint64_t strides[3] = {(cuuint64_t)x_pitch * 2, (cuuint64_t)x_pitch * 2 * Win,
@@ -627,7 +639,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: activation tensor map encode failed (CUresult %d)", (int)r);
   }
   {
-    const int K = ksize * ksize * Cin;
+    const int K = ksize * ksize * Cin + (x2 != nullptr ? Cin2 : 0);
     cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Cout};
     cuuint64_t strides[1] = {(cuuint64_t)K * 2};
     cuuint32_t box[2] = {64, (cuuint32_t)(block_n / conv_cluster_size())};   // each CTA loads its share
@@ -637,20 +649,32 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: weight tensor map encode failed (CUresult %d)", (int)r);
   }
+  ta2 = ta;
+  if (x2 != nullptr) {   // same spatial size as the output (stride 1 only), 1x1 taps
+    cuuint64_t dims[4] = {(cuuint64_t)Cin2, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)x2_pitch * 2, (cuuint64_t)x2_pitch * 2 * p.W,
+                             (cuuint64_t)x2_pitch * 2 * p.W * p.H};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(&ta2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x2), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: second operand tensor map encode failed (CUresult %d)", (int)r);
+  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, p, st);
+  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, ta2, p, st);
   if (epi == kEpiMat) {
     switch (block_n) {
-      case 256: return launch_conv<256, kEpiMat>(ta, tb, p, st);
-      case 128: return launch_conv<128, kEpiMat>(ta, tb, p, st);
-      default: return launch_conv<64, kEpiMat>(ta, tb, p, st);
+      case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, p, st);
+      case 128: return launch_conv<128, kEpiMat>(ta, tb, ta2, p, st);
+      default: return launch_conv<64, kEpiMat>(ta, tb, ta2, p, st);
     }
   }
   switch (block_n) {
-    case 256: return launch_conv<256, kEpiPlain>(ta, tb, p, st);
-    case 192: return launch_conv<192, kEpiPlain>(ta, tb, p, st);
-    case 128: return launch_conv<128, kEpiPlain>(ta, tb, p, st);
-    default: return launch_conv<64, kEpiPlain>(ta, tb, p, st);
+    case 256: return launch_conv<256, kEpiPlain>(ta, tb, ta2, p, st);
+    case 192: return launch_conv<192, kEpiPlain>(ta, tb, ta2, p, st);
+    case 128: return launch_conv<128, kEpiPlain>(ta, tb, ta2, p, st);
+    default: return launch_conv<64, kEpiPlain>(ta, tb, ta2, p, st);
   }
 }
 
@@ -662,8 +686,22 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
                                   const void* residual, int res_pitch, void* y, int y_pitch,
                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
                                   int ksize, int stride, int pad, int act, void* stream) {
+  return s2p_conv_igemm_fwd2(x, x_pitch, nullptr, 0, 0, w_packed, bias, residual, res_pitch, y, y_pitch, stats_partial, B,
+                             Hin, Win, Cin, Cout, ksize, stride, pad, act, stream);
+}
+
+extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2,
+                                   const void* w_packed, const float* bias, const void* residual, int res_pitch,
+                                   void* y, int y_pitch, float* stats_partial, int B, int Hin, int Win, int Cin,
+                                   int Cout, int ksize, int stride, int pad, int act, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
+  if (x2 != nullptr) {
+    S2P_CHECK_ARG(stride == 1 && 2 * pad == ksize - 1, "conv: a second operand needs a stride-1 'same' convolution");
+    S2P_CHECK_ARG(Cin2 > 0 && Cin2 % 64 == 0, "conv: Cin2=%d must be a multiple of 64", Cin2);
+    S2P_CHECK_ARG(x2_pitch >= Cin2 && x2_pitch % 8 == 0, "conv: x2_pitch=%d", x2_pitch);
+    S2P_CHECK_ARG((reinterpret_cast<uintptr_t>(x2) & 15) == 0, "conv: pointers must be 16-byte aligned");
+  }
   S2P_CHECK_ARG(B > 0 && Hin > 0 && Win > 0, "conv: bad dims B=%d H=%d W=%d", B, Hin, Win);
   S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv: Cin=%d must be a multiple of 64", Cin);
   S2P_CHECK_ARG(Cout > 0 && Cout % 64 == 0, "conv: Cout=%d must be a multiple of 64", Cout);
@@ -683,7 +721,8 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
   p.out = static_cast<__nv_bfloat16*>(y);
   p.stats_partial = stats_partial;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
-  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream);
+  return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream,
+                       x2, x2_pitch, Cin2);
 }
 
 extern "C" int s2p_mat_fused_ct(int C) { return C >= 128 ? 128 : C; }

@@ -196,7 +196,8 @@ class S2PGeneratorB200(nn.Module):
             d = dict(c0_w=ops.pack_conv_weight(blk.conv_0.weight), c0_b=f32(blk.conv_0.bias),
                      c1_w=ops.pack_conv_weight(blk.conv_1.weight), c1_b=f32(blk.conv_1.bias))
             if blk.learned_shortcut:
-                d["cs_w"] = ops.pack_conv_weight(blk.conv_s.weight)
+                # conv_1 and the 1x1 learned shortcut as ONE launch: weights side by side along K
+                d["c1s_w"] = torch.cat([d["c1_w"], ops.pack_conv_weight(blk.conv_s.weight)], dim=1).contiguous()
             P["blk"].append(d)
         self._packed = P
         self._packed_key = self._pack_key()
@@ -215,7 +216,7 @@ class S2PGeneratorB200(nn.Module):
         return t[:shape[0]]
 
     def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False,
-              finalize=True):
+              finalize=True, x2=None):
         """returns (y, stats) where stats is the finalized (mean, rstd) table when `finalize`,
         else the raw (partials, HW) pair consumed by ops.mat_prepare."""
         B, hin, win, _ = x.shape
@@ -226,7 +227,7 @@ class S2PGeneratorB200(nn.Module):
         st = None
         if want_stats:
             st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
-        ops.conv_igemm(x, w, b, cout, k, stride, act, residual, y, st)
+        ops.conv_igemm(x, w, b, cout, k, stride, act, residual, y, st, x2=x2)
         if want_stats:
             if not finalize:
                 return y, (st, ho * wo)
@@ -301,9 +302,11 @@ class S2PGeneratorB200(nn.Module):
                 ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
                 return ops.mat_norm(xin, mr_in, gs, bs, gbuf, up_, act, self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
 
+            ts = None
             if blk.learned_shortcut:
-                t = mat("norm_s", x, mr_x, up, ACT_NONE, "s")
-                xs, _ = self._conv(f"xs{bi}", t, pb["cs_w"], None, blk.fout, 1, 1)
+                # conv_s(norm_s(x)) is not a launch of its own: it rides along with conv_1 below as a second operand
+                ts = mat("norm_s", x, mr_x, up, ACT_NONE, "s")
+                xs = None
             else:
                 if up != 1:
                     raise RuntimeError("identity shortcut across an upsample is not part of ORACLE_SPEC v1")
@@ -313,9 +316,9 @@ class S2PGeneratorB200(nn.Module):
                                    finalize=not fuse)
             t = mat("norm_1", dx, mr_dx, 1, ACT_LRELU, "b")
             # the last block's output is only ever read through LeakyReLU (ToRGB): apply it here
-            x, mr_x = self._conv(f"x{bi}", t, pb["c1_w"], pb["c1_b"], blk.fout, 3, 1,
+            x, mr_x = self._conv(f"x{bi}", t, pb["c1s_w"] if ts is not None else pb["c1_w"], pb["c1_b"], blk.fout, 3, 1,
                                  act=ACT_LRELU if last else ACT_NONE, residual=xs,
-                                 want_stats=not last, finalize=not fuse)
+                                 want_stats=not last, finalize=not fuse, x2=ts)
         ops.torgb_igemm(x, P["img_w"], P["img_b"], out_f32, out_u8)
 
     def _run(self, image, state, want_f32=True, want_u8=False):

@@ -59,10 +59,13 @@ def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scal
     return out
 
 
-def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None, pad=None):
+def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None, pad=None,
+               x2=None):
     """y = act(conv(x) + bias + residual); returns y.  ``stats`` (fp32
-    [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given."""
-    _require_cuda(x, w_packed, bias, residual, out, stats)
+    [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given.  ``x2`` (NHWC bf16 of the output's
+    spatial size): a second operand whose 1x1 convolution is accumulated into the same tile; ``w_packed`` is then
+    [Cout, k*k*Cin + Cin2] (the two packed weights concatenated along the row)."""
+    _require_cuda(x, w_packed, bias, residual, out, stats, x2)
     b, hin, win, cin = x.shape
     pad = ksize // 2 if pad is None else pad
     hout = (hin + 2 * pad - ksize) // stride + 1
@@ -71,7 +74,12 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
         out = torch.empty(b, hout, wout, cout, dtype=torch.bfloat16, device=x.device)
     if tuple(out.shape) != (b, hout, wout, cout):
         raise RuntimeError(f"conv_igemm: out shape {tuple(out.shape)} != {(b, hout, wout, cout)}")
-    if w_packed.dtype != torch.bfloat16 or w_packed.numel() != cout * ksize * ksize * cin or not w_packed.is_contiguous():
+    cin2 = 0
+    if x2 is not None:
+        cin2 = x2.shape[3]
+        if tuple(x2.shape[:3]) != (b, hout, wout):
+            raise RuntimeError(f"conv_igemm: x2 must have the output's spatial size, got {tuple(x2.shape)}")
+    if w_packed.dtype != torch.bfloat16 or w_packed.numel() != cout * (ksize * ksize * cin + cin2) or not w_packed.is_contiguous():
         raise RuntimeError("conv_igemm: packed weight has the wrong size/dtype")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout or not bias.is_contiguous()):
         raise RuntimeError("conv_igemm: bias must be contiguous fp32 [Cout]")
@@ -85,11 +93,12 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
             raise RuntimeError("conv_igemm: residual shape mismatch")
         res_pitch = _nhwc_pitch(residual, "residual")
     _lib.check(
-        _lib.load().s2p_conv_igemm_fwd(
-            x.data_ptr(), _nhwc_pitch(x, "x"), w_packed.data_ptr(), _ptr(bias), _ptr(residual), res_pitch,
+        _lib.load().s2p_conv_igemm_fwd2(
+            x.data_ptr(), _nhwc_pitch(x, "x"), _ptr(x2), _nhwc_pitch(x2, "x2") if x2 is not None else 0, cin2,
+            w_packed.data_ptr(), _ptr(bias), _ptr(residual), res_pitch,
             out.data_ptr(), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout, ksize, stride, pad, act,
             _stream()),
-        "s2p_conv_igemm_fwd")
+        "s2p_conv_igemm_fwd2")
     return out
 
 

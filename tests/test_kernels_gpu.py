@@ -84,6 +84,32 @@ def test_conv_channel_sliced_views(ops):
     assert out_wide[..., :256].abs().max().item() == 0
 
 
+@pytest.mark.parametrize("b,h,cin,cin2,cout,act,stats", [(2, 25, 512, 512, 256, 0, True), (3, 50, 128, 256, 128, 0, True),
+                                                      (2, 100, 64, 128, 64, 2, False), (1, 20, 64, 64, 192, 0, True)])
+def test_conv_second_operand(ops, b, h, cin, cin2, cout, act, stats):
+    """3x3 conv with a 1x1 conv over a second tensor accumulated into the same tile (the res-block's learned
+    shortcut riding along with conv_1) == the two convolutions summed in fp32."""
+    g = torch.Generator().manual_seed(cin + cin2 + cout)
+    xb = torch.randn(b, h, h, cin, generator=g).cuda().to(torch.bfloat16)
+    x2 = torch.randn(b, h, h, 2 * cin2, generator=g).cuda().to(torch.bfloat16)[..., cin2:]      # channel-sliced view
+    w3 = (torch.randn(cout, cin, 3, 3, generator=g) / (9 * cin) ** 0.5).cuda()
+    w1 = (torch.randn(cout, cin2, 1, 1, generator=g) / cin2 ** 0.5).cuda()
+    bs = torch.randn(cout, generator=g).cuda()
+    wp = torch.cat([ops.pack_conv_weight(w3), ops.pack_conv_weight(w1)], dim=1).contiguous()
+    st = torch.full((b, ops.conv_stats_rows(h, h), cout, 2), float("nan"), device="cuda") if stats else None
+    y = ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, None, None, st, x2=x2)
+    ref = F.conv2d(xb.float().permute(0, 3, 1, 2), w3.to(torch.bfloat16).float(), bs, 1, 1) \
+        + F.conv2d(x2.float().permute(0, 3, 1, 2), w1.to(torch.bfloat16).float(), None, 1, 0)
+    ref = nhwc(ref)
+    ref = F.leaky_relu(ref, 0.2) if act == 2 else ref
+    assert (y.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 1e-3
+    if stats:
+        mr = ops.in_stats_finalize(st, h * h)
+        assert torch.allclose(mr[..., 0], y.float().mean(dim=(1, 2)), atol=1e-4)
+    with pytest.raises(RuntimeError):      # second operand of the wrong spatial size
+        ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, None, None, None, x2=x2[:, 1:])
+
+
 def test_conv_bit_stable(ops):
     g = torch.Generator().manual_seed(5)
     x = torch.randn(4, 50, 50, 128, generator=g).cuda().to(torch.bfloat16)
