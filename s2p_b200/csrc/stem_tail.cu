@@ -17,7 +17,7 @@ constexpr int kStemMaxW = 256;
 // converted to fp32 once into shared memory; a thread owns 8 output channels x 4 consecutive
 // pixels of a row, so every weight float4 read from shared memory feeds 16 FMAs.
 template <bool U8>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oihw,
                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int y_pitch,
                  float2* __restrict__ stats, int H, int W, int Cout, int rows) {
@@ -34,29 +34,39 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
   const int h0 = blockIdx.x * kStemRows;
   const int nrows = min(kStemRows, H - h0);
   const int HW = H * W;
+  // weights: coalesced global read, transposed into [tap][Cout]
   for (int i = threadIdx.x; i < 27 * Cout; i += blockDim.x) {
-    const int tap = i / Cout, co = i % Cout;
-    ws[i] = w_oihw[co * 27 + tap];
+    const int co = i / 27, tap = i - co * 27;
+    ws[tap * Cout + co] = __ldg(w_oihw + i);
   }
-  for (int i = threadIdx.x; i < 3 * (kStemRows + 2) * PW; i += blockDim.x) {
-    const int pw = i % PW;
-    const int pr = (i / PW) % (kStemRows + 2);
-    const int ci = i / (PW * (kStemRows + 2));
-    const int hh = h0 + pr - 1, ww = pw - 1;
-    float v = 0.f;
-    if (hh >= 0 && hh < H && ww >= 0 && ww < W) {
-      if (U8) {
-        const uint8_t* im = static_cast<const uint8_t*>(image);
-        // two separately rounded steps (no FMA contraction): bit-identical to the driver-side
-        // `u.float() * (1/127.5) - 1` conversion, so the uint8 and fp32 entries agree exactly
-        v = __fadd_rn(__fmul_rn(static_cast<float>(__ldg(im + (static_cast<size_t>(n) * HW + hh * W + ww) * 3 + ci)),
-                                1.0f / 127.5f), -1.0f);
-      } else {
-        const float* im = static_cast<const float*>(image);
-        v = __ldg(im + (static_cast<size_t>(n) * 3 + ci) * HW + hh * W + ww);
+  // patch: one (channel, row) line per warp pass, lanes along the row -- no per-element divisions, and the
+  // row's loads are independent of each other (they are issued together, not one L2 round trip at a time)
+  {
+    const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int line = wid; line < 3 * (kStemRows + 2); line += nwarps) {
+      const int ci = line / (kStemRows + 2), pr = line - ci * (kStemRows + 2);
+      const int hh = h0 + pr - 1;
+      const bool row_ok = hh >= 0 && hh < H;
+      float* dst = patch + line * PW;
+#pragma unroll 4
+      for (int pw = ln; pw < PW; pw += 32) {
+        const int ww = pw - 1;
+        float v = 0.f;
+        if (row_ok && ww >= 0 && ww < W) {
+          if (U8) {
+            const uint8_t* im = static_cast<const uint8_t*>(image);
+            // two separately rounded steps (no FMA contraction): bit-identical to the driver-side
+            // `u.float() * (1/127.5) - 1` conversion, so the uint8 and fp32 entries agree exactly
+            v = __fadd_rn(__fmul_rn(static_cast<float>(__ldg(im + (static_cast<size_t>(n) * HW + hh * W + ww) * 3 + ci)),
+                                    1.0f / 127.5f), -1.0f);
+          } else {
+            const float* im = static_cast<const float*>(image);
+            v = __ldg(im + (static_cast<size_t>(n) * 3 + ci) * HW + hh * W + ww);
+          }
+        }
+        dst[pw] = v;
       }
     }
-    patch[i] = v;
   }
   __syncthreads();
   float bv[8];
@@ -74,9 +84,12 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[i][j] = bv[j];
-#pragma unroll
+    // ci / r stay rolled: fully unrolled, the compiler keeps all 27 x 8 weights of the thread in registers
+    // (249 registers, one CTA per SM, nothing to overlap the patch fill with); rolled, the 24 weights of a
+    // filter row come from shared memory per iteration and two CTAs share an SM
+#pragma unroll 1
     for (int ci = 0; ci < 3; ++ci) {
-#pragma unroll
+#pragma unroll 1
       for (int r = 0; r < 3; ++r) {
         const float* prow = patch + (ci * (kStemRows + 2) + lr + r) * PW + w0;
         float in[6];
