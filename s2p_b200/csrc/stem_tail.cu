@@ -5,6 +5,7 @@
 //  tail: LeakyReLU -> 3x3 conv Cin->3 -> tanh -> fp32 NCHW and/or uint8 HWC.  N = 3 is
 //        too thin for UMMA: each pixel is owned by Cin/8 lanes (8 channels each, one
 //        128-bit load per tap), reduced with warp shuffles.
+#include <algorithm>
 #include "ptx.cuh"
 #include "s2p_internal.h"
 
@@ -14,15 +15,15 @@ constexpr int kStemRows = 8;      // output rows per CTA = one statistics partia
 constexpr int kStemMaxW = 256;
 
 // CTA = kStemRows full-width output rows of one image.  The (rows+2) x (W+2) x 3 input patch is
-// converted to fp32 once into shared memory; a thread owns 8 output channels x 4 consecutive
-// pixels of a row, so every weight float4 read from shared memory feeds 16 FMAs.
+// converted to fp32 once into shared memory; a thread owns 8 output channels x 8 consecutive
+// pixels of a row, so every weight float4 read from shared memory feeds 32 FMAs.
 template <bool U8>
 __global__ void __launch_bounds__(256, 2)
 stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oihw,
                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int y_pitch,
                  float2* __restrict__ stats, int H, int W, int Cout, int rows) {
-  extern __shared__ float sm[];
-  const int PW = W + 2;
+  extern __shared__ __align__(16) float sm[];
+  const int PW = (W + 2 + 8 + 3) & ~3;              // patch row pitch: halo + the last 8-pixel group's overhang, 16-B rows
   float* ws = sm;                                   // [27][Cout], tap = ci*9 + r*3 + s
   float* patch = ws + 27 * Cout;                    // [3][kStemRows+2][PW]
   float* red = patch + 3 * (kStemRows + 2) * PW;    // [slots][Cout][2]
@@ -76,31 +77,37 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
 
-  const int gpr = (W + 3) / 4;                      // 4-pixel groups per row
+  const int gpr = (W + 7) / 8;                      // 8-pixel groups per row
   for (int pg = slot; pg < nrows * gpr; pg += slots) {
-    const int lr = pg / gpr, w0 = (pg - lr * gpr) * 4;
-    float acc[4][8];
+    const int lr = pg / gpr, w0 = (pg - lr * gpr) * 8;
+    float acc[8][8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 8; ++i)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[i][j] = bv[j];
     // ci / r stay rolled: fully unrolled, the compiler keeps all 27 x 8 weights of the thread in registers
     // (249 registers, one CTA per SM, nothing to overlap the patch fill with); rolled, the 24 weights of a
-    // filter row come from shared memory per iteration and two CTAs share an SM
+    // filter row come from shared memory per iteration (each float4 feeds 32 FMAs) and two CTAs share an SM
 #pragma unroll 1
     for (int ci = 0; ci < 3; ++ci) {
 #pragma unroll 1
       for (int r = 0; r < 3; ++r) {
         const float* prow = patch + (ci * (kStemRows + 2) + lr + r) * PW + w0;
-        float in[6];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) in[i] = (w0 + i < PW) ? prow[i] : 0.f;
+        float in[10];
+        {
+          const float4 p0 = *reinterpret_cast<const float4*>(prow);
+          const float4 p1 = *reinterpret_cast<const float4*>(prow + 4);
+          const float2 p2 = *reinterpret_cast<const float2*>(prow + 8);
+          in[0] = p0.x; in[1] = p0.y; in[2] = p0.z; in[3] = p0.w;
+          in[4] = p1.x; in[5] = p1.y; in[6] = p1.z; in[7] = p1.w;
+          in[8] = p2.x; in[9] = p2.y;
+        }
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
           const float4 wa = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0);
           const float4 wb = *reinterpret_cast<const float4*>(ws + (ci * 9 + r * 3 + s) * Cout + c0 + 4);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
+          for (int i = 0; i < 8; ++i) {
             const float v = in[i + s];
             acc[i][0] = fmaf(v, wa.x, acc[i][0]); acc[i][1] = fmaf(v, wa.y, acc[i][1]);
             acc[i][2] = fmaf(v, wa.z, acc[i][2]); acc[i][3] = fmaf(v, wa.w, acc[i][3]);
@@ -112,7 +119,7 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
     }
     const size_t pix0 = static_cast<size_t>(n) * HW + static_cast<size_t>(h0 + lr) * W + w0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
       if (w0 + i >= W) break;
       uint4 ov = make_uint4(pack_bf16x2(acc[i][0], acc[i][1]), pack_bf16x2(acc[i][2], acc[i][3]),
                             pack_bf16x2(acc[i][4], acc[i][5]), pack_bf16x2(acc[i][6], acc[i][7]));
@@ -228,7 +235,15 @@ extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* 
   S2P_CHECK_ARG(image_fmt == S2P_IMG_F32_NCHW || image_fmt == S2P_IMG_U8_NHWC, "stem: image_fmt=%d", image_fmt);
   const int rows = s2p_stem_stats_rows(H, W);
   const int slots = 256 / (Cout / 8);
-  const size_t smem = (27 * Cout + 3 * (kStemRows + 2) * (W + 2) + slots * Cout * 2) * sizeof(float);
+  const int pw_pitch = (W + 2 + 8 + 3) & ~3;      // the kernel's padded patch row
+  const size_t smem = (27 * Cout + 3 * (kStemRows + 2) * pw_pitch + slots * Cout * 2) * sizeof(float);
+  // threads: the fewest 8-channel x 8-pixel slots that finish a CTA's rows in the same number of passes, so the
+  // last pass is not mostly idle (100 px wide, 8 rows: 104 groups = 4 passes of 26 slots, not 3.25 passes of 32)
+  const int groups = Cout / 8;
+  const int pgs = kStemRows * ((W + 7) / 8);
+  const int passes = (pgs + slots - 1) / slots;
+  const int slots_used = (pgs + passes - 1) / passes;
+  const unsigned threads = static_cast<unsigned>(std::min(256, (slots_used * groups + 31) & ~31));
   S2P_CHECK_ARG(B <= 65535, "stem: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 grid(rows, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -240,10 +255,10 @@ extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* 
     smem_configured = smem;
   }
   if (image_fmt == S2P_IMG_U8_NHWC)
-    stem_conv_kernel<true><<<grid, 256, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
+    stem_conv_kernel<true><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
                                                     reinterpret_cast<float2*>(stats_partial), H, W, Cout, rows);
   else
-    stem_conv_kernel<false><<<grid, 256, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
+    stem_conv_kernel<false><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
                                                      reinterpret_cast<float2*>(stats_partial), H, W, Cout, rows);
   count_launch();
   return check_launch("stem_conv_kernel");
