@@ -298,6 +298,32 @@ int s2p_l1_mean_fwd(const void* a, int a_pitch, const void* b, int b_pitch, long
 int s2p_l1_mean_bwd(const void* a, int a_pitch, const void* b, int b_pitch, const float* gout, long long rows, int C,
                     void* da, int da_pitch, void* stream);
 
+/* ---- (f4) RAD image augmentations, one pass per call --------------------------------------------------
+ * replaces /root/reference/examples/iql/data_augs.py (imported as `rad` by
+ * rlkit/launchers/experiments/awac/finetune_rl.py:34): random_crop :8-23, random_translate :244-254,
+ * random_cutout :71-89, random_cutout_color :91-113 (per-image host loops over numpy arrays) and random_flip
+ * :117-146, random_rotation :150-187 (flip / rot90 copies of the whole batch blended with 0/1 masks).
+ * in: [N][C][H][W], out: [N][C][Ho][Wo], elements uint8 (elem_bytes 1) or float32 (4); the per-image draws
+ * are int32 DEVICE arrays of N entries, made on the host with np.random in the reference's order:
+ *   S2P_RAD_CROP       p0 = h1, p1 = w1: out[y][x] = in[y+h1][x+w1]              (Ho <= H, Wo <= W)
+ *   S2P_RAD_TRANSLATE  p0 = h1, p1 = w1: out[h1+y][w1+x] = in[y][x], else zero   (Ho >= H, Wo >= W)
+ *   S2P_RAD_CUTOUT     p0 = h1, p1 = w1: rows [h1,2*h1) x columns [w1,2*w1) (the reference's slice, clipped to the
+ *                      image) = fill[n][c] (same element type, DEVICE) or zero when fill == NULL; the rest copied
+ *   S2P_RAD_FLIP       p0 = flag: flag ? in[y][W-1-x] : in[y][x]; p1 unused
+ *   S2P_RAD_ROT90      p0 = quarter turns 0..3 as torch.rot90(k, [2,3]); square images; p1 unused
+ * out must not alias in. */
+#define S2P_RAD_CROP 0
+#define S2P_RAD_TRANSLATE 1
+#define S2P_RAD_CUTOUT 2
+#define S2P_RAD_FLIP 3
+#define S2P_RAD_ROT90 4
+int s2p_rad_augment(const void* in, void* out, int elem_bytes, long long N, int C, int H, int W, int Ho, int Wo, int op,
+                    const int* p0, const int* p1, const void* fill, void* stream);
+/* random_grayscale (data_augs.py:26-66) with the reference's roundings: u8 = trunc(x*255); per frame (3 channels)
+ * gray = trunc(u8_r*0.2989f + u8_g*0.587f + u8_b*0.114f); out = (mask[n] ? gray : u8) / 255.
+ * in/out: float32 [N][frames*3][H][W]; mask: int32 DEVICE [N]. */
+int s2p_rad_grayscale(const float* in, float* out, long long N, int frames, int H, int W, const int* mask, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libs2p_sm100.so")
 
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 IMG_F32_NCHW, IMG_U8_NHWC = 0, 1
+RAD_CROP, RAD_TRANSLATE, RAD_CUTOUT, RAD_FLIP, RAD_ROT90 = 0, 1, 2, 3, 4
 
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
 
@@ -68,6 +69,8 @@ SIGNATURES = {
     "s2p_l1_mean_fwd": (_i, [_vp, _i, _vp, _i, C.c_longlong, _i, _vp, _vp, _vp]),
     "s2p_l1_mean_bwd": (_i, [_vp, _i, _vp, _i, _vp, C.c_longlong, _i, _vp, _i, _vp]),
     "s2p_slac_indices": (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_longlong, _vp]),
+    "s2p_rad_augment": (_i, [_vp, _vp, _i, C.c_longlong, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "s2p_rad_grayscale": (_i, [_vp, _vp, C.c_longlong, _i, _i, _i, _vp, _vp]),
 }
 
 _lib = None

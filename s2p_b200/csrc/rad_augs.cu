@@ -1,0 +1,342 @@
+// RAD image augmentations (SURVEY.md section 8 f, rank 4): the "naive augmentation" comparator of S2P
+// (/root/reference/examples/iql/data_augs.py; imported as `rad` by
+// rlkit/launchers/experiments/awac/finetune_rl.py:34).  The reference runs the index-moving ones
+// (random_crop :8-23, random_cutout :71-89, random_cutout_color :91-113, random_translate :244-254) as a
+// per-image Python loop over numpy arrays on the host, and random_flip :117-146 / random_rotation :150-187 /
+// random_grayscale :41-66 as 4-10 full-size torch passes (flip / rot90 copies of the whole batch, mask
+// broadcasts, multiply-adds).  Here every function is ONE pass: an output element computes where it comes
+// from out of the per-image draw (offset, box, flag, quarter turns), so the batch is read once and written once.
+// Byte work, HBM-bound: algorithmic bytes per image = (C*H*W read + C*Ho*Wo written) * sizeof(element).
+// The random draws stay on the host (np.random, same order as the reference: s2p_b200/data_augs.py) and arrive
+// as int32 arrays, so a seeded run moves the same pixels.
+#include <stdint.h>
+
+#include "s2p_internal.h"
+
+namespace s2p {
+namespace rad {
+
+constexpr int kThreads = 256;
+
+template <typename T> struct Quad;
+template <> struct Quad<uint8_t> { using type = uint32_t; };
+template <> struct Quad<float> { using type = float4; };
+
+__device__ __forceinline__ uint32_t pack4(const uint8_t* v) {
+  return static_cast<uint32_t>(v[0]) | (static_cast<uint32_t>(v[1]) << 8) | (static_cast<uint32_t>(v[2]) << 16) |
+         (static_cast<uint32_t>(v[3]) << 24);
+}
+__device__ __forceinline__ float4 pack4(const float* v) { return make_float4(v[0], v[1], v[2], v[3]); }
+
+// One thread = four consecutive output elements of one row (x0..x0+3) of image blockIdx.y.
+template <typename T, int OP>
+__global__ void __launch_bounds__(kThreads)
+augment_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W, int Ho, int Wo,
+               const int* __restrict__ p0, const int* __restrict__ p1, const T* __restrict__ fill, int vec_store) {
+  const unsigned quads_per_row = static_cast<unsigned>(Wo + 3) >> 2;
+  const unsigned q = blockIdx.x * kThreads + threadIdx.x;   // < 2^31 (checked by the host): 32-bit divisions only
+  if (q >= static_cast<unsigned>(C) * Ho * quads_per_row) return;
+  const int xq = static_cast<int>(q % quads_per_row);
+  const unsigned cy = q / quads_per_row;
+  const int y = static_cast<int>(cy % Ho), c = static_cast<int>(cy / Ho);
+  const long long n = blockIdx.y;
+  int a = __ldg(p0 + n);
+  int b = p1 ? __ldg(p1 + n) : 0;
+  const T* src = in + (n * C + c) * static_cast<long long>(H) * W;
+  T* dst = out + ((n * C + c) * static_cast<long long>(Ho) + y) * Wo;
+  const int x0 = xq << 2;
+  T v[4];
+  if (OP == S2P_RAD_CROP) {            // out[y][x] = in[y + h1][x + w1]; offsets clamped: never read outside
+    a = min(max(a, 0), H - Ho);
+    b = min(max(b, 0), W - Wo);
+    const T* row = src + static_cast<long long>(y + a) * W + b;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = (x0 + i < Wo) ? __ldg(row + x0 + i) : T(0);
+  } else if (OP == S2P_RAD_TRANSLATE) { // out[h1 + y][w1 + x] = in[y][x], zero elsewhere
+    const int sy = y - a;
+    const bool row_in = sy >= 0 && sy < H;
+    const T* row = src + static_cast<long long>(row_in ? sy : 0) * W;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int sx = x0 + i - b;
+      v[i] = (row_in && sx >= 0 && sx < W) ? __ldg(row + sx) : T(0);
+    }
+  } else if (OP == S2P_RAD_CUTOUT) {    // box rows [h1, 2*h1) x columns [w1, 2*w1) (the reference's slice), numpy-clipped
+    const bool row_in = y >= a && y < 2 * a;
+    const T f = fill ? __ldg(fill + n * C + c) : T(0);
+    const T* row = src + static_cast<long long>(y) * W;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int x = x0 + i;
+      const bool boxed = row_in && x >= b && x < 2 * b;
+      v[i] = boxed ? f : ((x < W) ? __ldg(row + x) : T(0));
+    }
+  } else if (OP == S2P_RAD_FLIP) {      // flag ? in[y][W-1-x] : in[y][x]
+    const T* row = src + static_cast<long long>(y) * W;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int x = x0 + i;
+      v[i] = (x < W) ? __ldg(row + (a ? W - 1 - x : x)) : T(0);
+    }
+  } else {                              // S2P_RAD_ROT90: a quarter turns counter-clockwise (torch.rot90(k, [2, 3])), H == W
+    a &= 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int x = x0 + i;
+      int sy = y, sx = x;
+      if (a == 1) { sy = x; sx = W - 1 - y; }
+      else if (a == 2) { sy = H - 1 - y; sx = W - 1 - x; }
+      else if (a == 3) { sy = H - 1 - x; sx = y; }
+      v[i] = (x < W) ? __ldg(src + static_cast<long long>(sy) * W + sx) : T(0);
+    }
+  }
+  if (vec_store) {
+    *reinterpret_cast<typename Quad<T>::type*>(dst + x0) = pack4(v);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (x0 + i < Wo) dst[x0 + i] = v[i];
+  }
+}
+
+// random_grayscale (data_augs.py:26-66) in one pass, with the reference's roundings: u8 = trunc(x * 255);
+// gray = trunc(u8_r * 0.2989f + u8_g * 0.587f + u8_b * 0.114f) (separately rounded fp32 products and sums);
+// out = (flag ? gray : u8) / 255.
+__global__ void __launch_bounds__(kThreads)
+grayscale_kernel(const float* __restrict__ in, float* __restrict__ out, int frames, int HW, const int* __restrict__ mask) {
+  const long long t = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x;
+  if (t >= static_cast<long long>(frames) * HW) return;
+  const int p = static_cast<int>(t % HW), f = static_cast<int>(t / HW);
+  const long long n = blockIdx.y;
+  const long long base = ((n * frames + f) * 3) * static_cast<long long>(HW) + p;
+  const float r = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base), 255.f)));
+  const float g = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base + HW), 255.f)));
+  const float b = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base + 2ll * HW), 255.f)));
+  float o0 = r, o1 = g, o2 = b;
+  if (__ldg(mask + n)) {
+    const float s = __fadd_rn(__fadd_rn(__fmul_rn(r, 0.2989f), __fmul_rn(g, 0.587f)), __fmul_rn(b, 0.114f));
+    o0 = o1 = o2 = static_cast<float>(static_cast<uint8_t>(s));
+  }
+  __stcs(out + base, __fdiv_rn(o0, 255.f));
+  __stcs(out + base + HW, __fdiv_rn(o1, 255.f));
+  __stcs(out + base + 2ll * HW, __fdiv_rn(o2, 255.f));
+}
+
+// uint8 fast path (rows of whole 32-bit words, 4-B aligned buffers): one thread = 16 consecutive output bytes of a
+// row.  The source run of a crop / translate / cutout / flip / half turn is contiguous in memory at an arbitrary byte
+// offset: five ALIGNED 32-bit loads cover it and funnel shifts realign it (a byte-reversing permute for the mirrored
+// cases), so a thread issues 5 loads + 1..4 stores per 16 bytes instead of 16 byte loads.  Words outside the input
+// buffer are not loaded (they can only feed bytes the op masks or never stores).  Quarter turns walk a column: byte loads.
+template <int OP>
+__global__ void __launch_bounds__(kThreads)
+augment_u8_words_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int C, int H, int W, int Ho, int Wo,
+                        const int* __restrict__ p0, const int* __restrict__ p1, const uint8_t* __restrict__ fill,
+                        long long in_bytes, long long n_base) {
+  const unsigned segs = static_cast<unsigned>(Wo + 15) >> 4;
+  const unsigned t = blockIdx.x * kThreads + threadIdx.x;
+  if (t >= static_cast<unsigned>(C) * Ho * segs) return;
+  const unsigned seg = t % segs, cy = t / segs;
+  const int y = static_cast<int>(cy % Ho), c = static_cast<int>(cy / Ho);
+  const long long n = n_base + blockIdx.y;
+  int a = __ldg(p0 + n);
+  int b = p1 ? __ldg(p1 + n) : 0;
+  const long long plane = (n * C + c) * static_cast<long long>(H) * W;   // byte offset of this channel plane
+  const int x0 = static_cast<int>(seg) << 4;
+  const int nw = min(4, (Wo - x0) >> 2);
+  int srow = y, off = 0;
+  bool reversed = false, column = false, row_in = true;
+  if (OP == S2P_RAD_CROP) {
+    a = min(max(a, 0), H - Ho);
+    b = min(max(b, 0), W - Wo);
+    srow = y + a; off = b;
+  } else if (OP == S2P_RAD_TRANSLATE) {
+    srow = y - a; off = -b;
+    row_in = srow >= 0 && srow < H;
+    if (!row_in) srow = 0;
+  } else if (OP == S2P_RAD_FLIP) {
+    reversed = a != 0;
+  } else if (OP == S2P_RAD_ROT90) {
+    a &= 3;
+    if (a == 2) { srow = H - 1 - y; reversed = true; }
+    column = (a & 1) != 0;
+  }
+  uint32_t o[4];
+  if (!column) {
+    const long long s = plane + static_cast<long long>(srow) * W + (reversed ? (W - x0 - 16) : (off + x0));
+    const int sh = static_cast<int>(s & 3) << 3;
+    const long long sa = s - (s & 3);
+    uint32_t w[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const long long wa = sa + 4 * k;
+      w[k] = (wa >= 0 && wa + 4 <= in_bytes) ? __ldg(reinterpret_cast<const uint32_t*>(in + wa)) : 0u;
+    }
+    uint32_t run[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) run[j] = __funnelshift_r(w[j], w[j + 1], sh);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = reversed ? __byte_perm(run[3 - j], 0u, 0x0123) : run[j];
+    if (OP == S2P_RAD_TRANSLATE || OP == S2P_RAD_CUTOUT) {
+      // bytes [lo, hi) of the row: kept (translate: the pasted image) or replaced (cutout: the box)
+      int lo, hi;
+      uint32_t fw = 0u;
+      if (OP == S2P_RAD_TRANSLATE) { lo = row_in ? b : 0; hi = row_in ? b + W : 0; }
+      else {
+        const bool boxed_row = y >= a && y < 2 * a;
+        lo = boxed_row ? b : 0; hi = boxed_row ? 2 * b : 0;
+        fw = fill ? static_cast<uint32_t>(__ldg(fill + n * C + c)) * 0x01010101u : 0u;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t m = 0u;   // bytes inside [lo, hi)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int x = x0 + 4 * j + i;
+          m |= (x >= lo && x < hi) ? (0xffu << (8 * i)) : 0u;
+        }
+        o[j] = (OP == S2P_RAD_TRANSLATE) ? (o[j] & m) : ((o[j] & ~m) | (fw & m));
+      }
+    }
+  } else {
+    const uint8_t* src = in + plane;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t v = 0u;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int x = x0 + 4 * j + i;
+        if (x < W) {
+          const int sy = (a == 1) ? x : H - 1 - x, sx = (a == 1) ? W - 1 - y : y;
+          v |= static_cast<uint32_t>(__ldg(src + static_cast<long long>(sy) * W + sx)) << (8 * i);
+        }
+      }
+      o[j] = v;
+    }
+  }
+  uint8_t* dst = out + ((n * C + c) * static_cast<long long>(Ho) + y) * Wo + x0;
+  if (nw == 4 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (j < nw) reinterpret_cast<uint32_t*>(dst)[j] = o[j];
+  }
+}
+
+template <int OP>
+int launch_u8_words(const uint8_t* in, uint8_t* out, long long N, int C, int H, int W, int Ho, int Wo, const int* p0,
+                    const int* p1, const uint8_t* fill, cudaStream_t st) {
+  const long long threads = static_cast<long long>(C) * Ho * ((Wo + 15) >> 4);
+  const unsigned gx = static_cast<unsigned>((threads + kThreads - 1) / kThreads);
+  const long long in_bytes = N * C * static_cast<long long>(H) * W;
+  for (long long n0 = 0; n0 < N; n0 += 65535) {
+    const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
+    augment_u8_words_kernel<OP><<<dim3(gx, ny), kThreads, 0, st>>>(in, out, C, H, W, Ho, Wo, p0, p1, fill, in_bytes, n0);
+    count_launch();
+    const int rc = check_launch("rad augment_u8_words_kernel");
+    if (rc != S2P_OK) return rc;
+  }
+  return S2P_OK;
+}
+
+template <typename T>
+int launch(const T* in, T* out, long long N, int C, int H, int W, int Ho, int Wo, int op, const int* p0, const int* p1,
+           const T* fill, cudaStream_t st) {
+  const long long quads = static_cast<long long>(C) * Ho * ((Wo + 3) >> 2);
+  const unsigned gx = static_cast<unsigned>((quads + kThreads - 1) / kThreads);
+  const int vec = (Wo % 4 == 0) && (reinterpret_cast<uintptr_t>(out) % (4 * sizeof(T)) == 0);
+  for (long long n0 = 0; n0 < N; n0 += 65535) {   // gridDim.y limit
+    const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
+    const dim3 grid(gx, ny);
+    const T* i = in + n0 * C * static_cast<long long>(H) * W;
+    T* o = out + n0 * C * static_cast<long long>(Ho) * Wo;
+    const int* q0 = p0 + n0;
+    const int* q1 = p1 ? p1 + n0 : nullptr;
+    const T* fl = fill ? fill + n0 * C : nullptr;
+    switch (op) {
+      case S2P_RAD_CROP: augment_kernel<T, S2P_RAD_CROP><<<grid, kThreads, 0, st>>>(i, o, C, H, W, Ho, Wo, q0, q1, fl, vec); break;
+      case S2P_RAD_TRANSLATE: augment_kernel<T, S2P_RAD_TRANSLATE><<<grid, kThreads, 0, st>>>(i, o, C, H, W, Ho, Wo, q0, q1, fl, vec); break;
+      case S2P_RAD_CUTOUT: augment_kernel<T, S2P_RAD_CUTOUT><<<grid, kThreads, 0, st>>>(i, o, C, H, W, Ho, Wo, q0, q1, fl, vec); break;
+      case S2P_RAD_FLIP: augment_kernel<T, S2P_RAD_FLIP><<<grid, kThreads, 0, st>>>(i, o, C, H, W, Ho, Wo, q0, q1, fl, vec); break;
+      default: augment_kernel<T, S2P_RAD_ROT90><<<grid, kThreads, 0, st>>>(i, o, C, H, W, Ho, Wo, q0, q1, fl, vec); break;
+    }
+    count_launch();
+    const int rc = check_launch("rad augment_kernel");
+    if (rc != S2P_OK) return rc;
+  }
+  return S2P_OK;
+}
+
+}  // namespace rad
+}  // namespace s2p
+
+extern "C" int s2p_rad_augment(const void* in, void* out, int elem_bytes, long long N, int C, int H, int W, int Ho, int Wo,
+                               int op, const int* p0, const int* p1, const void* fill, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(in && out && p0, "rad_augment: null pointer");
+  S2P_CHECK_ARG(in != out, "rad_augment: in-place is not supported (every op reads other pixels than it writes)");
+  S2P_CHECK_ARG(N > 0 && C > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0, "rad_augment: bad dims");
+  S2P_CHECK_ARG(static_cast<long long>(C) * Ho * ((Wo + 3) / 4) < (1ll << 31), "rad_augment: image too large");
+  if (elem_bytes != 1 && elem_bytes != 4) return set_error(S2P_ERR_UNSUPPORTED, "rad_augment: elem_bytes=%d (1: uint8, 4: float32)", elem_bytes);
+  switch (op) {
+    case S2P_RAD_CROP:
+      S2P_CHECK_ARG(p1 && Ho <= H && Wo <= W, "rad_augment(crop): needs p1 and Ho <= H, Wo <= W");
+      break;
+    case S2P_RAD_TRANSLATE:
+      S2P_CHECK_ARG(p1 && Ho >= H && Wo >= W, "rad_augment(translate): needs p1 and Ho >= H, Wo >= W");
+      break;
+    case S2P_RAD_CUTOUT:
+      S2P_CHECK_ARG(p1 && Ho == H && Wo == W, "rad_augment(cutout): needs p1 and Ho == H, Wo == W");
+      break;
+    case S2P_RAD_FLIP:
+      S2P_CHECK_ARG(Ho == H && Wo == W, "rad_augment(flip): needs Ho == H, Wo == W");
+      break;
+    case S2P_RAD_ROT90:
+      S2P_CHECK_ARG(Ho == H && Wo == W && H == W, "rad_augment(rot90): needs square images and Ho == H, Wo == W");
+      break;
+    default:
+      return set_error(S2P_ERR_UNSUPPORTED, "rad_augment: op=%d", op);
+  }
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (elem_bytes == 1) {
+    const uint8_t* i8 = static_cast<const uint8_t*>(in);
+    uint8_t* o8 = static_cast<uint8_t*>(out);
+    const uint8_t* f8 = static_cast<const uint8_t*>(fill);
+    const bool words = Wo % 4 == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 3) == 0 &&
+                       (N * C * static_cast<long long>(H) * W) % 4 == 0;
+    if (words) {
+      switch (op) {
+        case S2P_RAD_CROP: return rad::launch_u8_words<S2P_RAD_CROP>(i8, o8, N, C, H, W, Ho, Wo, p0, p1, f8, st);
+        case S2P_RAD_TRANSLATE: return rad::launch_u8_words<S2P_RAD_TRANSLATE>(i8, o8, N, C, H, W, Ho, Wo, p0, p1, f8, st);
+        case S2P_RAD_CUTOUT: return rad::launch_u8_words<S2P_RAD_CUTOUT>(i8, o8, N, C, H, W, Ho, Wo, p0, p1, f8, st);
+        case S2P_RAD_FLIP: return rad::launch_u8_words<S2P_RAD_FLIP>(i8, o8, N, C, H, W, Ho, Wo, p0, p1, f8, st);
+        default: return rad::launch_u8_words<S2P_RAD_ROT90>(i8, o8, N, C, H, W, Ho, Wo, p0, p1, f8, st);
+      }
+    }
+    return rad::launch<uint8_t>(static_cast<const uint8_t*>(in), static_cast<uint8_t*>(out), N, C, H, W, Ho, Wo, op, p0, p1,
+                                static_cast<const uint8_t*>(fill), st);
+  }
+  S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 3) == 0, "rad_augment: float buffers not 4-B aligned");
+  return rad::launch<float>(static_cast<const float*>(in), static_cast<float*>(out), N, C, H, W, Ho, Wo, op, p0, p1,
+                            static_cast<const float*>(fill), st);
+}
+
+extern "C" int s2p_rad_grayscale(const float* in, float* out, long long N, int frames, int H, int W, const int* mask,
+                                 void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(in && out && mask, "rad_grayscale: null pointer");
+  S2P_CHECK_ARG(N > 0 && frames > 0 && H > 0 && W > 0, "rad_grayscale: bad dims");
+  const int HW = H * W;
+  const long long per = static_cast<long long>(frames) * HW;
+  S2P_CHECK_ARG(per < (1ll << 31) * rad::kThreads, "rad_grayscale: image too large");
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned gx = static_cast<unsigned>((per + rad::kThreads - 1) / rad::kThreads);
+  for (long long n0 = 0; n0 < N; n0 += 65535) {
+    const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
+    rad::grayscale_kernel<<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per * 3, out + n0 * per * 3, frames, HW, mask + n0);
+    count_launch();
+    const int rc = check_launch("rad grayscale_kernel");
+    if (rc != S2P_OK) return rc;
+  }
+  return S2P_OK;
+}

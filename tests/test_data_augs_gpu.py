@@ -1,0 +1,143 @@
+"""GPU: s2p_b200.data_augs (rad augment_kernel / grayscale_kernel through the C ABI) against
+(1) the outputs of the REFERENCE'S OWN functions on the same np.random seed (tests/golden/data_augs.npz),
+(2) the numpy oracle at the repo's frame shape (9 x 100 x 100 stacks, uint8 and float32) and on ragged sizes that take
+    the scalar-store path, and (3) size-independent properties at a large batch (crop undoes translate, flip and a
+    full turn are involutions).  Index moves and the grayscale's uint8 roundings are bit-exact: array_equal."""
+import numpy as np
+import pytest
+import torch
+
+import data_augs_oracle as DO
+from common import load_golden
+from test_data_augs_oracle import golden_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def rad():
+    import s2p_b200.data_augs as R
+    return R
+
+
+def _np(t):
+    return t.cpu().numpy() if isinstance(t, torch.Tensor) else t
+
+
+GOLD = [("crop", "u8", lambda R, x: R.random_crop(x, out=32)), ("crop", "f32", lambda R, x: R.random_crop(x, out=32)),
+        ("cutout", "u8", lambda R, x: R.random_cutout(x, 10, 30)), ("cutout", "f32", lambda R, x: R.random_cutout(x, 10, 30)),
+        ("cutout_color", "u8", lambda R, x: R.random_cutout_color(x, 10, 30)),
+        ("cutout_color", "f32", lambda R, x: R.random_cutout_color(x, 10, 30)),
+        ("translate", "u8", lambda R, x: R.random_translate(x, 52)), ("translate", "f32", lambda R, x: R.random_translate(x, 52)),
+        ("flip", "f32", lambda R, x: R.random_flip(x, p=.5)), ("rotation", "f32", lambda R, x: R.random_rotation(x, p=.7)),
+        ("grayscale", "f32", lambda R, x: R.random_grayscale(x, p=.5))]
+
+
+@pytest.mark.parametrize("name,tag,fn", GOLD, ids=[f"{g[0]}_{g[1]}" for g in GOLD])
+@pytest.mark.parametrize("host", [False, True], ids=["cuda_tensor", "numpy_in_out"])
+def test_matches_reference_outputs(name, tag, fn, host):
+    g = load_golden("data_augs")
+    u8, f32 = golden_inputs(g)
+    x = u8 if tag == "u8" else f32
+    np.random.seed(int(g["seed_draw"]))
+    out = fn(rad(), x if host else torch.from_numpy(x).cuda())
+    assert isinstance(out, np.ndarray) == host
+    ref = g[f"{name}_{tag}"]
+    out = _np(out)
+    assert out.dtype == ref.dtype and out.shape == ref.shape
+    assert np.array_equal(out, ref)
+
+
+def _imgs(shape, dtype, seed):
+    rng = np.random.RandomState(seed)
+    if dtype == np.uint8:
+        return rng.randint(0, 256, size=shape).astype(np.uint8)
+    return rng.rand(*shape).astype(np.float32)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.float32], ids=["u8", "f32"])
+@pytest.mark.parametrize("shape,out,size", [((16, 9, 100, 100), 84, 108), ((5, 3, 37, 37), 30, 41), ((3, 1, 7, 7), 7, 7)],
+                         ids=["frames100", "ragged37", "tiny7"])
+def test_every_op_vs_oracle(dtype, shape, out, size):
+    R = rad()
+    x = _imgs(shape, dtype, 5)
+    xc = torch.from_numpy(x).cuda()
+    lo, hi = (10, 30) if shape[2] >= 37 else (1, 6)
+    calls = [("random_crop", dict(out=out)), ("random_cutout", dict(min_cut=lo, max_cut=hi)),
+             ("random_cutout_color", dict(min_cut=lo, max_cut=hi)), ("random_translate", dict(size=size)),
+             ("random_flip", dict(p=.5)), ("random_rotation", dict(p=.8))]
+    for k, (name, kw) in enumerate(calls):
+        np.random.seed(100 + k)
+        got = getattr(R, name)(xc, **kw)
+        np.random.seed(100 + k)
+        want = getattr(DO, name)(x, **kw)
+        assert got.dtype == xc.dtype and tuple(got.shape) == want.shape, name
+        assert np.array_equal(_np(got), want), name
+    assert np.array_equal(_np(xc), x)   # inputs untouched
+
+
+def test_grayscale_vs_oracle_and_rounding_edges():
+    R = rad()
+    # every k/255 (trunc(x*255) sits on an integer edge for some k) and random values, 3 frames of 100 x 100
+    rng = np.random.RandomState(9)
+    x = rng.rand(8, 9, 100, 100).astype(np.float32)
+    x[0] = (rng.randint(0, 256, size=(9, 100, 100)) / 255.).astype(np.float32)
+    x[1, :, 0, :] = 1.0
+    x[2, :, 0, :] = 0.0
+    for p in (0.0, 0.5, 1.0):
+        np.random.seed(4)
+        got = R.random_grayscale(torch.from_numpy(x).cuda(), p=p)
+        np.random.seed(4)
+        want = DO.random_grayscale(x, p=p)
+        bad = int((_np(got) != want).sum())
+        assert bad == 0, (p, bad)
+    # and against torch's own device arithmetic for the reference's gray expression (no fused multiply-add); the last
+    # division is done on the host: torch's CUDA `x / 255.` multiplies by the reciprocal, the reference's CPU path divides
+    xc = torch.from_numpy(x).cuda()
+    u8 = (xc * 255.).type(torch.uint8).view(8, 3, 3, 100, 100)
+    gray = (u8[:, :, 0] * 0.2989 + u8[:, :, 1] * 0.587 + u8[:, :, 2] * 0.114).type(torch.uint8).float()
+    np.random.seed(4)
+    got = R.random_grayscale(xc, p=1.0)
+    assert torch.equal(got.view(8, 3, 3, 100, 100)[:, :, 1].cpu(), gray.cpu() / 255.)
+
+
+def test_properties_large_batch():
+    R = rad()
+    x = torch.randint(0, 256, (2048, 9, 100, 100), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+    np.random.seed(8)
+    t, idx = R.random_translate(x, 108, return_random_idxs=True)
+    assert t.shape == (2048, 9, 108, 108)
+    # crop undoes translate (same offsets): feed the translate draws to the crop kernel through the C ABI path
+    from s2p_b200 import _lib
+    back = R._augment(t, _lib.RAD_CROP, 100, 100, idx["h1s"], idx["w1s"])
+    assert torch.equal(back, x)
+    assert int(t.sum(dtype=torch.int64)) == int(x.sum(dtype=torch.int64))   # everything outside the paste is zero
+    ones = np.ones(2048, dtype=np.int32)
+    f = R._augment(x, _lib.RAD_FLIP, 100, 100, ones)
+    assert not torch.equal(f, x) and torch.equal(R._augment(f, _lib.RAD_FLIP, 100, 100, ones), x)
+    assert torch.equal(f, x.flip([3]))
+    r = R._augment(x, _lib.RAD_ROT90, 100, 100, ones)
+    assert torch.equal(r, x.rot90(1, [2, 3]))
+    assert torch.equal(R._augment(r, _lib.RAD_ROT90, 100, 100, 3 * ones), x)
+
+
+def test_errors_and_empty():
+    R = rad()
+    from s2p_b200 import _lib
+    with pytest.raises(RuntimeError):
+        R.random_flip(torch.zeros(2, 3, 8, 8))                      # CPU tensor: no fallback
+    with pytest.raises(RuntimeError):
+        R.random_crop(torch.zeros(2, 3, 8, 8, dtype=torch.float64, device="cuda"), out=4)
+    with pytest.raises(ValueError):
+        R.random_rotation(torch.zeros(2, 3, 8, 6, device="cuda"))
+    x = torch.zeros(2, 3, 8, 8, device="cuda")
+    d = torch.zeros(2, dtype=torch.int32, device="cuda")
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.s2p_rad_augment(x.data_ptr(), x.data_ptr(), 4, 2, 3, 8, 8, 8, 8, _lib.RAD_FLIP, d.data_ptr(), 0, 0, st) == -1  # aliasing
+    y = torch.empty_like(x)
+    assert lib.s2p_rad_augment(x.data_ptr(), y.data_ptr(), 2, 2, 3, 8, 8, 8, 8, _lib.RAD_FLIP, d.data_ptr(), 0, 0, st) == -3  # elem size
+    assert lib.s2p_rad_augment(x.data_ptr(), y.data_ptr(), 4, 2, 3, 8, 8, 9, 9, _lib.RAD_CROP, d.data_ptr(), d.data_ptr(), 0, st) == -1
+    assert lib.s2p_rad_augment(x.data_ptr(), y.data_ptr(), 4, 2, 3, 8, 8, 8, 8, 7, d.data_ptr(), 0, 0, st) == -3
+    assert b"rad_augment" in lib.s2p_last_error_string()
+    e = R.random_cutout(torch.zeros(0, 3, 8, 8, dtype=torch.uint8, device="cuda"))
+    assert e.shape == (0, 3, 8, 8)
