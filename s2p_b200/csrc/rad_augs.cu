@@ -91,7 +91,7 @@ augment_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int 
     }
   }
   if (vec_store) {
-    *reinterpret_cast<typename Quad<T>::type*>(dst + x0) = pack4(v);
+    __stcs(reinterpret_cast<typename Quad<T>::type*>(dst + x0), pack4(v));   // written once, not re-read: evict first
   } else {
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -102,24 +102,45 @@ augment_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int 
 // random_grayscale (data_augs.py:26-66) in one pass, with the reference's roundings: u8 = trunc(x * 255);
 // gray = trunc(u8_r * 0.2989f + u8_g * 0.587f + u8_b * 0.114f) (separately rounded fp32 products and sums);
 // out = (flag ? gray : u8) / 255.
+__device__ __forceinline__ void gray_px(float r, float g, float b, bool on, float& o0, float& o1, float& o2) {
+  r = static_cast<float>(static_cast<uint8_t>(__fmul_rn(r, 255.f)));
+  g = static_cast<float>(static_cast<uint8_t>(__fmul_rn(g, 255.f)));
+  b = static_cast<float>(static_cast<uint8_t>(__fmul_rn(b, 255.f)));
+  if (on) {
+    const float s = __fadd_rn(__fadd_rn(__fmul_rn(r, 0.2989f), __fmul_rn(g, 0.587f)), __fmul_rn(b, 0.114f));
+    r = g = b = static_cast<float>(static_cast<uint8_t>(s));
+  }
+  o0 = __fdiv_rn(r, 255.f); o1 = __fdiv_rn(g, 255.f); o2 = __fdiv_rn(b, 255.f);
+}
+
+// VEC = 4: H*W % 4 == 0 and 16-B aligned buffers, a thread owns four pixels of one frame (3 x 128-bit loads / stores)
+template <int VEC>
 __global__ void __launch_bounds__(kThreads)
 grayscale_kernel(const float* __restrict__ in, float* __restrict__ out, int frames, int HW, const int* __restrict__ mask) {
-  const long long t = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x;
-  if (t >= static_cast<long long>(frames) * HW) return;
-  const int p = static_cast<int>(t % HW), f = static_cast<int>(t / HW);
+  const unsigned per_frame = static_cast<unsigned>(HW) / VEC;
+  const unsigned t = blockIdx.x * kThreads + threadIdx.x;
+  if (t >= static_cast<unsigned>(frames) * per_frame) return;
+  const unsigned f = t / per_frame, p = (t - f * per_frame) * VEC;
   const long long n = blockIdx.y;
   const long long base = ((n * frames + f) * 3) * static_cast<long long>(HW) + p;
-  const float r = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base), 255.f)));
-  const float g = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base + HW), 255.f)));
-  const float b = static_cast<float>(static_cast<uint8_t>(__fmul_rn(__ldg(in + base + 2ll * HW), 255.f)));
-  float o0 = r, o1 = g, o2 = b;
-  if (__ldg(mask + n)) {
-    const float s = __fadd_rn(__fadd_rn(__fmul_rn(r, 0.2989f), __fmul_rn(g, 0.587f)), __fmul_rn(b, 0.114f));
-    o0 = o1 = o2 = static_cast<float>(static_cast<uint8_t>(s));
+  const bool on = __ldg(mask + n) != 0;
+  if (VEC == 4) {
+    const float4 r = __ldcs(reinterpret_cast<const float4*>(in + base));
+    const float4 g = __ldcs(reinterpret_cast<const float4*>(in + base + HW));
+    const float4 b = __ldcs(reinterpret_cast<const float4*>(in + base + 2ll * HW));
+    float4 o0, o1, o2;
+    gray_px(r.x, g.x, b.x, on, o0.x, o1.x, o2.x);
+    gray_px(r.y, g.y, b.y, on, o0.y, o1.y, o2.y);
+    gray_px(r.z, g.z, b.z, on, o0.z, o1.z, o2.z);
+    gray_px(r.w, g.w, b.w, on, o0.w, o1.w, o2.w);
+    __stcs(reinterpret_cast<float4*>(out + base), o0);
+    __stcs(reinterpret_cast<float4*>(out + base + HW), o1);
+    __stcs(reinterpret_cast<float4*>(out + base + 2ll * HW), o2);
+  } else {
+    float o0, o1, o2;
+    gray_px(__ldg(in + base), __ldg(in + base + HW), __ldg(in + base + 2ll * HW), on, o0, o1, o2);
+    out[base] = o0; out[base + HW] = o1; out[base + 2ll * HW] = o2;
   }
-  __stcs(out + base, __fdiv_rn(o0, 255.f));
-  __stcs(out + base + HW, __fdiv_rn(o1, 255.f));
-  __stcs(out + base + 2ll * HW, __fdiv_rn(o2, 255.f));
 }
 
 // uint8 fast path (rows of whole 32-bit words, 4-B aligned buffers): one thread = 16 consecutive output bytes of a
@@ -165,11 +186,19 @@ augment_u8_words_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ ou
     const long long s = plane + static_cast<long long>(srow) * W + (reversed ? (W - x0 - 16) : (off + x0));
     const int sh = static_cast<int>(s & 3) << 3;
     const long long sa = s - (s & 3);
-    uint32_t w[5];
+    // a translate's segment outside the pasted image is all zero: no loads
+    const bool live = OP != S2P_RAD_TRANSLATE || (row_in && x0 + 16 > b && x0 < b + W);
+    uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};
+    if (live) {
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(in + sa);
+      if (sa >= 0 && sa + 20 <= in_bytes) {   // the usual case: one range check for the five words
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-      const long long wa = sa + 4 * k;
-      w[k] = (wa >= 0 && wa + 4 <= in_bytes) ? __ldg(reinterpret_cast<const uint32_t*>(in + wa)) : 0u;
+        for (int k = 0; k < 5; ++k) w[k] = __ldg(wp + k);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+          if (sa + 4 * k >= 0 && sa + 4 * k + 4 <= in_bytes) w[k] = __ldg(wp + k);
+      }
     }
     uint32_t run[4];
 #pragma unroll
@@ -188,12 +217,10 @@ augment_u8_words_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ ou
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        uint32_t m = 0u;   // bytes inside [lo, hi)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int x = x0 + 4 * j + i;
-          m |= (x >= lo && x < hi) ? (0xffu << (8 * i)) : 0u;
-        }
+        // bytes of word j inside [lo, hi): byte positions [s0, s1) of the word
+        const int xj = x0 + 4 * j;
+        const int s0 = min(max(lo - xj, 0), 4), s1 = min(max(hi - xj, 0), 4);
+        const uint32_t m = s1 > s0 ? ((0xffffffffu >> (8 * (4 - (s1 - s0)))) << (8 * s0)) : 0u;
         o[j] = (OP == S2P_RAD_TRANSLATE) ? (o[j] & m) : ((o[j] & ~m) | (fw & m));
       }
     }
@@ -215,11 +242,11 @@ augment_u8_words_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ ou
   }
   uint8_t* dst = out + ((n * C + c) * static_cast<long long>(Ho) + y) * Wo + x0;
   if (nw == 4 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+    __stcs(reinterpret_cast<uint4*>(dst), make_uint4(o[0], o[1], o[2], o[3]));
   } else {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (j < nw) reinterpret_cast<uint32_t*>(dst)[j] = o[j];
+      if (j < nw) __stcs(reinterpret_cast<uint32_t*>(dst) + j, o[j]);
   }
 }
 
@@ -328,12 +355,15 @@ extern "C" int s2p_rad_grayscale(const float* in, float* out, long long N, int f
   S2P_CHECK_ARG(N > 0 && frames > 0 && H > 0 && W > 0, "rad_grayscale: bad dims");
   const int HW = H * W;
   const long long per = static_cast<long long>(frames) * HW;
-  S2P_CHECK_ARG(per < (1ll << 31) * rad::kThreads, "rad_grayscale: image too large");
+  S2P_CHECK_ARG(per < (1ll << 31), "rad_grayscale: image too large");
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const unsigned gx = static_cast<unsigned>((per + rad::kThreads - 1) / rad::kThreads);
+  const bool vec = HW % 4 == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  const long long threads = vec ? per / 4 : per;
+  const unsigned gx = static_cast<unsigned>((threads + rad::kThreads - 1) / rad::kThreads);
   for (long long n0 = 0; n0 < N; n0 += 65535) {
     const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
-    rad::grayscale_kernel<<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per * 3, out + n0 * per * 3, frames, HW, mask + n0);
+    if (vec) rad::grayscale_kernel<4><<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per * 3, out + n0 * per * 3, frames, HW, mask + n0);
+    else rad::grayscale_kernel<1><<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per * 3, out + n0 * per * 3, frames, HW, mask + n0);
     count_launch();
     const int rc = check_launch("rad grayscale_kernel");
     if (rc != S2P_OK) return rc;

@@ -90,6 +90,11 @@ def test_grayscale_vs_oracle_and_rounding_edges():
         want = DO.random_grayscale(x, p=p)
         bad = int((_np(got) != want).sum())
         assert bad == 0, (p, bad)
+    xr = rng.rand(5, 6, 7, 9).astype(np.float32)     # H*W % 4 != 0: the scalar kernel
+    np.random.seed(6)
+    got = R.random_grayscale(torch.from_numpy(xr).cuda(), p=.6)
+    np.random.seed(6)
+    assert np.array_equal(_np(got), DO.random_grayscale(xr, p=.6))
     # and against torch's own device arithmetic for the reference's gray expression (no fused multiply-add); the last
     # division is done on the host: torch's CUDA `x / 255.` multiplies by the reciprocal, the reference's CPU path divides
     xc = torch.from_numpy(x).cuda()
