@@ -337,6 +337,20 @@ def adjacent_side_measurements(torch, dev):
     ms = timed(lambda: enc.forward_from_buffer(buf, pick), reps=10)
     out["slac_encoder"] = {"kernel": "slac_conv1_kernel (uint8 gather fused) + 5 x conv_igemm_kernel", "batch": 256,
                            "frames": 256 * 9, "ms": ms, "frames_per_sec": 256 * 9 / ms * 1e3}
+    del buf, enc
+    # RAD augmentations through the reference-named calls (draws on the host + upload + one launch)
+    from s2p_b200 import data_augs as rad
+    np.random.seed(0)
+    stacks = torch.randint(0, 256, (Bw, 9, 100, 100), dtype=torch.uint8, device=dev)
+    ms_crop = timed(lambda: rad.random_crop(stacks, out=84), reps=10)
+    stacks_f = torch.rand(Bw, 9, 100, 100, device=dev)
+    ms_gray = timed(lambda: rad.random_grayscale(stacks_f, p=.3), reps=10)
+    b_crop, b_gray = Bw * 9 * (84 * 84 * 2), Bw * 9 * 10000 * 8
+    out["rad_augmentations"] = {
+        "kernel": "augment_u8_words_kernel<crop> (uint8) / grayscale_kernel<4> (float32); whole call incl. host draws + upload",
+        "stacks": Bw, "shape": "9x100x100", "bound": "hbm", "peak": hbm_peak, "unit": "GB/s",
+        "random_crop_u8": {"ms": ms_crop, "achieved": b_crop / ms_crop / 1e6, "frac": b_crop / ms_crop / 1e6 / hbm_peak},
+        "random_grayscale_f32": {"ms": ms_gray, "achieved": b_gray / ms_gray / 1e6, "frac": b_gray / ms_gray / 1e6 / hbm_peak}}
     return out
 
 
