@@ -55,8 +55,9 @@ def _imgs(shape, dtype, seed):
 
 
 @pytest.mark.parametrize("dtype", [np.uint8, np.float32], ids=["u8", "f32"])
-@pytest.mark.parametrize("shape,out,size", [((16, 9, 100, 100), 84, 108), ((5, 3, 37, 37), 30, 41), ((3, 1, 7, 7), 7, 7)],
-                         ids=["frames100", "ragged37", "tiny7"])
+@pytest.mark.parametrize("shape,out,size", [((16, 9, 100, 100), 84, 108), ((5, 3, 37, 37), 30, 41), ((3, 1, 7, 7), 7, 7),
+                                             ((4, 3, 37, 37), 32, 40), ((6, 2, 52, 52), 36, 64)],
+                         ids=["frames100", "ragged37", "tiny7", "unaligned_rows37", "words52"])
 def test_every_op_vs_oracle(dtype, shape, out, size):
     R = rad()
     x = _imgs(shape, dtype, 5)
@@ -123,6 +124,26 @@ def test_properties_large_batch():
     r = R._augment(x, _lib.RAD_ROT90, 100, 100, ones)
     assert torch.equal(r, x.rot90(1, [2, 3]))
     assert torch.equal(R._augment(r, _lib.RAD_ROT90, 100, 100, 3 * ones), x)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.float32], ids=["u8", "f32"])
+def test_more_images_than_one_grid(dtype):
+    """N > 65535 (gridDim.y): the launch loop's second chunk starts at the right image, draws and fill included."""
+    R = rad()
+    from s2p_b200 import _lib
+    n = 70000
+    x = _imgs((n, 2, 8, 8), dtype, 3)
+    xc = torch.from_numpy(x).cuda()
+    rng = np.random.RandomState(1)
+    h1, w1 = rng.randint(0, 5, n), rng.randint(0, 5, n)
+    assert np.array_equal(_np(R._augment(xc, _lib.RAD_CROP, 4, 4, h1, w1)), DO.crop_at(x, h1, w1, 4))
+    assert np.array_equal(_np(R._augment(xc, _lib.RAD_TRANSLATE, 12, 12, h1, w1)), DO.translate_at(x, h1, w1, 12))
+    fill = _imgs((n, 2), dtype, 4)
+    got = R._augment(xc, _lib.RAD_CUTOUT, 8, 8, h1, w1, torch.from_numpy(fill).cuda())
+    assert np.array_equal(_np(got), DO.cutout_at(x, h1, w1, fill))
+    turns = rng.randint(0, 4, n)
+    assert np.array_equal(_np(R._augment(xc, _lib.RAD_ROT90, 8, 8, turns)), DO.rot90_at(x, turns))
+    assert np.array_equal(_np(R._augment(xc, _lib.RAD_FLIP, 8, 8, turns & 1)), DO.flip_at(x, turns & 1))
 
 
 def test_errors_and_empty():
