@@ -44,8 +44,10 @@ def _leave(t, was_np):
     return t.cpu().numpy() if was_np else t
 
 
-def _draws(a, dev):
-    return torch.from_numpy(np.ascontiguousarray(np.asarray(a).astype(np.int32))).to(dev, non_blocking=False)
+def _draws(dev, *arrays):
+    """One host->device copy for all per-image draws of a call: int32 [len(arrays), n], row k = arrays[k]."""
+    host = np.ascontiguousarray(np.stack([np.asarray(a).astype(np.int32) for a in arrays]))
+    return torch.from_numpy(host).to(dev)
 
 
 def _augment(x, op, ho, wo, p0, p1=None, fill=None):
@@ -54,10 +56,9 @@ def _augment(x, op, ho, wo, p0, p1=None, fill=None):
     if n == 0:
         return out
     with torch.cuda.device(x.device):
-        d0 = _draws(p0, x.device)
-        d1 = _draws(p1, x.device) if p1 is not None else None
+        d = _draws(x.device, p0) if p1 is None else _draws(x.device, p0, p1)
         _lib.check(_lib.load().s2p_rad_augment(x.data_ptr(), out.data_ptr(), _ELEM[x.dtype], n, c, h, w, ho, wo, op,
-                                               d0.data_ptr(), 0 if d1 is None else d1.data_ptr(),
+                                               d[0].data_ptr(), 0 if p1 is None else d[1].data_ptr(),
                                                0 if fill is None else fill.data_ptr(), _stream()), "s2p_rad_augment")
     return out
 
@@ -125,7 +126,7 @@ def random_grayscale(images, p=.3, device=None):
     out = torch.empty_like(x)
     if n:
         with torch.cuda.device(x.device):
-            m = _draws(flags, x.device)
+            m = _draws(x.device, flags)
             _lib.check(_lib.load().s2p_rad_grayscale(x.data_ptr(), out.data_ptr(), n, c // 3, h, w, m.data_ptr(), _stream()),
                        "s2p_rad_grayscale")
     return _leave(out, was_np)
