@@ -32,6 +32,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 # rank 0 prints exactly ONE JSON line on stdout: keep NCCL's own banner ("NCCL version ...") out of it
 os.environ["NCCL_DEBUG"] = os.environ.get("S2P_NCCL_DEBUG", "WARN")
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL prints its version banner at WARN level too: to stderr
 
 METRIC = "generated_frames_per_sec"
 UNIT = "frames/s"
