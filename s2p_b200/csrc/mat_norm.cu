@@ -8,6 +8,8 @@
 // HBM-bound: algorithmic bytes per output element = 2 (x, /up^2 when upsampled)
 // + 4 (gI,bI) + 2 (y) in bf16.
 #include "ptx.cuh"
+#include <stdlib.h>
+
 #include "s2p_internal.h"
 
 namespace s2p {
@@ -241,7 +243,12 @@ extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float*
   if (py < 1) py = 1;
   const int HW = H * W;
   // ~8 CTAs per SM in flight at large batch; each CTA walks >= 4*py*4 pixels
-  int chunks = (HW + py * 16 - 1) / (py * 16);
+  static const int pix_per_thread = [] {   // diagnostic override: S2P_NORM_PIX_PER_THREAD
+    const char* e = getenv("S2P_NORM_PIX_PER_THREAD");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : 16;
+  }();
+  int chunks = (HW + py * pix_per_thread - 1) / (py * pix_per_thread);
   const int max_chunks = (num_sms() * 16 + B - 1) / B;
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
@@ -447,7 +454,12 @@ static void norm_bwd_geometry(int B, int H, int W, int C, int* py_out, int* chun
   int py = 256 / groups;
   if (py < 1) py = 1;
   const int HW = H * W;
-  int chunks = (HW + py * 16 - 1) / (py * 16);
+  static const int pix_per_thread = [] {   // diagnostic override: S2P_NORM_PIX_PER_THREAD
+    const char* e = getenv("S2P_NORM_PIX_PER_THREAD");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : 16;
+  }();
+  int chunks = (HW + py * pix_per_thread - 1) / (py * pix_per_thread);
   const int max_chunks = (num_sms() * 8 + B - 1) / B;
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
