@@ -12,6 +12,10 @@
  *     (a cudaStream_t passed as void*), so every call is CUDA-graph capturable;
  *   - activations: NHWC bf16, `pitch` = elements between consecutive pixels
  *     (>= C, multiple of 8) so channel slices of a wider tensor can be passed;
+ *   - WIDE activations: a tensor that an instance norm or a residual add reads (the residual stream,
+ *     a block's inner activation, the encoder's pre-norm maps) may be stored as a bf16 PAIR
+ *     hi + lo (lo = bf16(v - hi): ~16 mantissa bits); the `*_lo` pointers below take the low halves
+ *     (same pitch as the high halves; NULL = plain bf16).  Tensor-core operands are always bf16;
  *   - statistics / modulation vectors / state path: fp32;
  *   - conv weights: pre-packed [Cout][R][S][Cin] bf16 (s2p_pack_conv_weight);
  *   - return 0 on success, a negative S2P_ERR_* otherwise, text via
@@ -62,11 +66,12 @@ int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const f
  * output's size; stride 1, 'same' padding).  w_packed is [Cout][k*k*Cin + Cin2]: s2p_pack_conv_weight of the two
  * weights concatenated along the row.  Replaces `conv_1(h) + conv_s(x_s)` of the oracle's res-block (SPADEResnetBlock
  * lineage: learned shortcut) in one launch, without the bf16 round trip of the shortcut through HBM.  x2 == NULL: the
- * plain call. */
+ * plain call.  residual_lo / y_lo: low halves of a wide residual / output (see Conventions); with y_lo the statistics
+ * partials are those of the fp32 values. */
 int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2, const void* w_packed,
-                        const float* bias, const void* residual, int res_pitch, void* y, int y_pitch,
-                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize, int stride,
-                        int pad, int act, void* stream);
+                        const float* bias, const void* residual, const void* residual_lo, int res_pitch, void* y,
+                        void* y_lo, int y_pitch, float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
+                        int ksize, int stride, int pad, int act, void* stream);
 
 /* ---- (a8) weight gradient of the convolution (training) -----------------------------
  * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]
@@ -91,12 +96,16 @@ int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int 
  * F.leaky_relu that follows it (and F.interpolate(nearest x2) in front when up==2).
  *   y[n,h,w,c] = act( (x[n,h/up,w/up,c]-mean)*rstd * (1 + gs[n,c] + gI[n,h,w,c]) + bs[n,c] + bI[n,h,w,c] )
  * gb_spatial holds gI in channels [0,C) and bI in [C,2C) of each pixel; gs/bs/gb_spatial
- * may be NULL (plain IN + act, oracle ImageEncoder).  C % 8 == 0. */
+ * may be NULL (plain IN + act, oracle ImageEncoder).  C % 8 == 0.
+ * x_lo: low halves of a wide x.  y_lo: the output is stored wide; y_dup: a second copy of the output's high
+ * halves -- with y, y_lo, y_dup = three channel slices of one tensor the result is the operand layout
+ * [hi | lo | hi] of the split-precision convolution (weights [W_hi | W_hi | W_lo] along Cin: the three
+ * significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core pass, used for the encoder's convs). */
 int s2p_in_stats_finalize(const float* stats_partial, int rows, float* mean_rstd, int B, int C,
                           int HW, float eps, void* stream);
-int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd, const float* gs,
-                     const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y,
-                     int y_pitch, int B, int H, int W, int C, int act, void* stream);
+int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd, const float* gs,
+                     const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y, void* y_lo,
+                     void* y_dup, int y_pitch, int B, int H, int W, int C, int act, void* stream);
 
 /* ---- (a3 fused into a4) gamma/beta conv with the MAT norm applied in its epilogue ----
  * replaces, in ONE kernel, oracle MAT.mlp_gamma + MAT.mlp_beta (nn.Conv2d 3x3) and the
@@ -110,12 +119,13 @@ int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd,
  * [2*ct*j, 2*ct*j+ct) are gamma channels [ct*j, ct*(j+1)) and the next ct rows the beta
  * channels of the same range (so one accumulator tile holds both for its channels).
  * bias_gb in s2p_mat_prepare is in plain [gamma(C) | beta(C)] order.
+ * x_lo: low halves of a wide x (NULL = plain bf16).
  * Requires Cin % 64 == 0, C in {32, 64} or C % 128 == 0. */
 int s2p_mat_fused_ct(int C);
 int s2p_mat_prepare(const float* stats_partial, int rows, const float* gs, const float* bs, int gsbs_pitch,
                     const float* bias_gb, float* mod_table, int B, int C, int HW, float eps, void* stream);
-int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, const void* x, int x_pitch,
-                           int up, const float* mod_table, void* y, int y_pitch, int B, int H, int W,
+int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, const void* x, const void* x_lo,
+                           int x_pitch, int up, const float* mod_table, void* y, int y_pitch, int B, int H, int W,
                            int Cin, int C, int ksize, int act, void* stream);
 
 /* backward of s2p_mat_norm_fwd (training; replaces autograd through F.instance_norm, the MAT
@@ -139,7 +149,7 @@ int s2p_mat_norm_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, i
  * (floor((y+1)*127.5+0.5) clamped), oracle S2PGenerator.conv_img + to_uint8_hwc. */
 int s2p_stem_stats_rows(int H, int W);
 int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* w_oihw, const float* bias,
-                      void* y, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
+                      void* y, void* y_lo, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
                       void* stream);
 int s2p_torgb_tanh_fwd(const void* x, int x_pitch, const float* w_oihw, const float* bias,
                        float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,

@@ -59,7 +59,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-SPEC_VERSION = "ORACLE_SPEC v1"
+SPEC_VERSION = "ORACLE_SPEC v1"   # v1.3 added the 'trained_like' init only (no change to the forward)
 
 # state dimensionality per --env_type.  cheetah=17 is pinned by the reference
 # (normalize_configs_dict.pkl, state_transition_rollout.py:44); walker=24 is the
@@ -230,14 +230,15 @@ def init_weights(net, init_type="xavier", gain=0.02):
     """SPADE BaseNetwork.init_weights flavour: xavier_normal_(gain) on conv/linear
     weights, zero bias.  'scaled' is a variance-preserving (He-style, fan_in) init
     used by the parity tests so that activations and outputs are O(1) and the bf16
-    path is actually exercised (gain-0.02 nets emit ~0 everywhere)."""
+    path is actually exercised (gain-0.02 nets emit ~0 everywhere).  'trained_like'
+    (v1.3) = 'scaled' with a non-saturating output head and blend scalars away from 0."""
     for m in net.modules():
         if isinstance(m, (nn.Conv2d, nn.Linear)):
             if init_type == "xavier":
                 nn.init.xavier_normal_(m.weight, gain=gain)
                 if m.bias is not None:
                     nn.init.zeros_(m.bias)
-            elif init_type == "scaled":
+            elif init_type in ("scaled", "trained_like"):
                 fan_in = m.weight[0].numel()
                 nn.init.normal_(m.weight, 0.0, math.sqrt(1.0 / fan_in))
                 if m.bias is not None:
@@ -249,6 +250,22 @@ def init_weights(net, init_type="xavier", gain=0.02):
             if isinstance(m, MAT):
                 nn.init.normal_(m.blend_gamma, 0.0, 1.0)
                 nn.init.normal_(m.blend_beta, 0.0, 1.0)
+    if init_type == "trained_like":
+        # ORACLE_SPEC v1.3: the third parity init.  'scaled' weights, but (i) the ToRGB conv is
+        # scaled by 0.3 so that tanh works in its near-linear range (output std ~0.3, nothing saturated: every
+        # upstream rounding error reaches the output undamped), and (ii) every MAT blend scalar sits well away from
+        # sigmoid = 0.5: |blend| ~ U(1, 2.5) with a random sign, i.e. a state-dominated or an image-dominated mix.
+        for m in net.modules():
+            if isinstance(m, MAT):
+                for p in (m.blend_gamma, m.blend_beta):
+                    mag = 1.0 + 1.5 * torch.rand(())
+                    sign = 1.0 if torch.rand(()) < 0.5 else -1.0
+                    with torch.no_grad():
+                        p.fill_(float(mag * sign))
+        conv_img = getattr(net, "conv_img", None)
+        if conv_img is not None:
+            with torch.no_grad():
+                conv_img.weight.mul_(0.3)
 
 
 def define_G(opt):

@@ -11,11 +11,18 @@
 // Replaces the cuDNN convs behind nn.Conv2d in the (absent) reference generator
 // (oracle/s2p_oracle.py MATResBlk / MAT / ImageEncoder / head).
 //
-// Warp roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer
-// (warp 1 owns the TMEM allocation), warps 2..5 = epilogue (TMEM lane quarter = warp % 4).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer and owner of the TMEM
+// allocation (both loops run warp-converged and elect one lane around the asynchronous issue),
+// warps 2..9 = epilogue (TMEM lane quarter = warp % 4, two warps per quarter split the columns).
+// CTA pairs (cta_group::2): two CTAs of a cluster walk two adjacent m-tiles of one n-tile as one
+// M=256 UMMA, each loading its own activation rows and half of the weight tile.
 // Persistent: grid = min(#tiles, #SMs); static round-robin tile schedule, n-tile fastest so
 // CTAs running together share the activation tile in L2.  Accumulators are double
 // buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+//
+// Wide activations: a tensor the following instance norm / residual add reads (the residual stream x,
+// the block-internal dx, the encoder's pre-norm e) can be stored as a bf16 PAIR hi + lo (lo = bf16(v - hi),
+// ~16 mantissa bits) instead of one bf16: `out_lo`, `residual_lo`, `mat_x_lo`.  Conv operands stay bf16.
 #include <stdlib.h>
 
 #include "ptx.cuh"
@@ -33,17 +40,19 @@ struct ConvParams {
   int act;                // 0 none, 1 relu, 2 lrelu(0.2)
   const float* bias;
   const __nv_bfloat16* residual;
+  const __nv_bfloat16* residual_lo;   // low halves of a wide residual (same pitch) or null
   __nv_bfloat16* out;
+  __nv_bfloat16* out_lo;              // low halves of a wide output (same pitch) or null
   float* stats_partial;   // [B][tiles_per_img*4][Cout][2] (sum, sumsq) or null
   // fused MAT epilogue (conv_mat_fused): the accumulators are the spatial gamma|beta maps,
   // the stored value is act((x*A + Bc) * (G1 + gamma) + (B0 + beta)) with (A,Bc,G1,B0) = mat_tab[n][c]
   const __nv_bfloat16* mat_x;   // pre-norm activation [B][H/up][W/up][mat_x_pitch]
+  const __nv_bfloat16* mat_x_lo; // its low halves when it is stored wide (same pitch) or null
   const float4* mat_tab;        // [B][mat_C]
   int mat_x_pitch, mat_up, mat_C;
   // ToRGB epilogue (BLOCK_N = 16, 3 live columns): tanh(acc + bias) -> fp32 NCHW and/or uint8 NHWC
   float* rgb_f32;
   uint8_t* rgb_u8;
-  int debug;   // S2P_CONV_DEBUG (timing experiments only): 1 = skip the plain epilogue's global stores
   // second operand (plain epilogue, stride 1): kb2 extra 64-channel k-blocks taken from a second NHWC tensor of the
   // output's spatial size through tmap_a2 -- a 1x1 convolution accumulated into the same tile, which is how a
   // res-block's learned shortcut rides along with its last 3x3 conv (weights concatenated along K)
@@ -329,8 +338,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         float4* tab_s = tab_smem + acc * 128;
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
         const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0 + cw);
-        uint4 xn[2];
+        const bool wide_x = p.mat_x_lo != nullptr;
+        const uint4* xl4 = reinterpret_cast<const uint4*>(p.mat_x_lo + xpix * p.mat_x_pitch + ch0 + cw);
+        uint4 xn[2], xln[2];
         if (valid) { xn[0] = __ldg(x4); xn[1] = __ldg(x4 + 1); }
+        if (valid && wide_x) { xln[0] = __ldg(xl4); xln[1] = __ldg(xl4 + 1); }
         asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
@@ -344,16 +356,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int k = 0; k < 16; ++k) { g[k] = __uint_as_float(rg[k]); bt[k] = __uint_as_float(rb[k]); }
           const uint4 xr0 = xn[0], xr1 = xn[1];
+          const uint4 xq0 = xln[0], xq1 = xln[1];
           if (sidx + 1 < kSteps) {
             tmem_ld16(t_row + cw + (sidx + 1) * 16, rg);
             tmem_ld16(t_row + CT + cw + (sidx + 1) * 16, rb);
             if (valid) { xn[0] = __ldg(x4 + (sidx + 1) * 2); xn[1] = __ldg(x4 + (sidx + 1) * 2 + 1); }
+            if (valid && wide_x) { xln[0] = __ldg(xl4 + (sidx + 1) * 2); xln[1] = __ldg(xl4 + (sidx + 1) * 2 + 1); }
           } else {
             release_acc();
           }
           uint32_t ow_out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
           if (valid) {
             const uint32_t xw[8] = {xr0.x, xr0.y, xr0.z, xr0.w, xr1.x, xr1.y, xr1.z, xr1.w};
+            const uint32_t xlw[8] = {xq0.x, xq0.y, xq0.z, xq0.w, xq1.x, xq1.y, xq1.z, xq1.w};
             uint32_t ow[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -362,7 +377,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               for (int hlf = 0; hlf < 2; ++hlf) {
                 const int k = 2 * e + hlf;
                 const float4 tb = tab_s[cw + sidx * 16 + k];
-                const float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
+                float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
+                if (wide_x) xv += hlf ? bf16_hi(xlw[e]) : bf16_lo(xlw[e]);
                 const float xh = fmaf(xv, tb.x, tb.y);
                 float v = fmaf(xh, tb.z + g[k], tb.w + bt[k]);
                 if (p.act == 2) v = v > 0.f ? v : 0.2f * v;
@@ -409,6 +425,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const int cbeg = half * kChunks;
         const bool has_res = (p.residual != nullptr) && valid;
         const StoreRows<4> rows4 = store_rows_prepare<4>(static_cast<uint32_t>(pix), valid, lane);
+        const bool wide_res = has_res && (p.residual_lo != nullptr);
+        const bool wide_out = p.out_lo != nullptr;
         const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + pix * p.res_pitch + n0 + cbeg * 32);
         uint4 rn[4];
         if (has_res) {
@@ -464,6 +482,21 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               v[8 * j + 6] += bf16_lo(rr.w); v[8 * j + 7] += bf16_hi(rr.w);
             }
           }
+          if (wide_res) {
+            // low halves of a wide residual: loaded at the point of use (not pipelined like the high halves) -- the
+            // only launches that take this branch are the identity-shortcut blocks at 25x25, K = 4608 per tile,
+            // whose epilogue has slack, and the registers of a second prefetch set spill in the wide tiles
+            // (address = the high halves' + a launch-uniform distance: no second per-thread pointer)
+            const uint4* rl4 = r4 + (reinterpret_cast<const uint4*>(p.residual_lo) - reinterpret_cast<const uint4*>(p.residual));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 rr = __ldg(rl4 + i * 4 + j);
+              v[8 * j + 0] += bf16_lo(rr.x); v[8 * j + 1] += bf16_hi(rr.x);
+              v[8 * j + 2] += bf16_lo(rr.y); v[8 * j + 3] += bf16_hi(rr.y);
+              v[8 * j + 4] += bf16_lo(rr.z); v[8 * j + 5] += bf16_hi(rr.z);
+              v[8 * j + 6] += bf16_lo(rr.w); v[8 * j + 7] += bf16_hi(rr.w);
+            }
+          }
           if (p.act == 1) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -474,20 +507,30 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           uint32_t packed[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-          if (!(p.debug & 1))
-            warp_store_rows<4>(stg_s, packed, p.out + ch, p.out_pitch, rows4, lane);
-          if (p.stats_partial != nullptr && live) {
-            // statistics of the values as stored (bf16-rounded), fixed reduction order
-            float s1[32], s2[32];
+          warp_store_rows<4>(stg_s, packed, p.out + ch, p.out_pitch, rows4, lane);
+          if (wide_out) {
+            // low halves of the wide store: v - hi is exact in fp32, its bf16 rounding leaves ~2^-17 relative
+            uint32_t plo[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const float a = valid ? bf16_lo(packed[j]) : 0.f;
-              const float b = valid ? bf16_hi(packed[j]) : 0.f;
-              s1[2 * j] = a; s1[2 * j + 1] = b;
-              s2[2 * j] = a * a; s2[2 * j + 1] = b * b;
+            for (int j = 0; j < 16; ++j)
+              plo[j] = pack_bf16x2(v[2 * j] - bf16_lo(packed[j]), v[2 * j + 1] - bf16_hi(packed[j]));
+            warp_store_rows<4>(stg_s, plo, p.out_lo + ch, p.out_pitch, rows4, lane);
+          }
+          if (p.stats_partial != nullptr && live) {
+            // statistics of the values as stored (bf16-rounded; the fp32 values when stored wide), fixed reduction order
+            // (sum first, then sum of squares, each through one 32-register butterfly: both arrays live at once
+            // next to the fp32 values of a wide store spill)
+            if (!wide_out) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { v[2 * j] = bf16_lo(packed[j]); v[2 * j + 1] = bf16_hi(packed[j]); }
             }
+            float s1[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s1[j] = valid ? v[j] : 0.f;
             const float cs = warp_colsum32(s1, lane);
-            const float cq = warp_colsum32(s2, lane);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s1[j] = valid ? v[j] * v[j] : 0.f;
+            const float cq = warp_colsum32(s1, lane);
             const size_t prow = (static_cast<size_t>(img) * tiles_per_img + t) * 4 + q;
             float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + ch + lane;
             *dst = make_float2(cs, cq);
@@ -548,11 +591,12 @@ template <int BLOCK_N, int EPI, int CL>
 static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const ConvParams& p,
                           cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};   // the attribute is per device
+  const int dev = current_device();
+  if (!configured[dev]) {
     S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI, CL>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured = true;
+    configured[dev] = true;
   }
   const int super_tiles = ((p.num_m_tiles + CL - 1) / CL) * p.num_n_tiles;
   const int max_clusters = num_sms() / CL;
@@ -608,11 +652,6 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
                          const void* x2 = nullptr, int x2_pitch = 0, int Cin2 = 0) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-  {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("S2P_CONV_DEBUG"); dbg = e ? atoi(e) : 0; }
-    p.debug = dbg;
-  }
   p.B = B;
   p.H = (Hin + 2 * pad - ksize) / stride + 1;
   p.W = (Win + 2 * pad - ksize) / stride + 1;
@@ -686,16 +725,19 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
                                   const void* residual, int res_pitch, void* y, int y_pitch,
                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
                                   int ksize, int stride, int pad, int act, void* stream) {
-  return s2p_conv_igemm_fwd2(x, x_pitch, nullptr, 0, 0, w_packed, bias, residual, res_pitch, y, y_pitch, stats_partial, B,
-                             Hin, Win, Cin, Cout, ksize, stride, pad, act, stream);
+  return s2p_conv_igemm_fwd2(x, x_pitch, nullptr, 0, 0, w_packed, bias, residual, nullptr, res_pitch, y, nullptr, y_pitch,
+                             stats_partial, B, Hin, Win, Cin, Cout, ksize, stride, pad, act, stream);
 }
 
 extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2,
-                                   const void* w_packed, const float* bias, const void* residual, int res_pitch,
-                                   void* y, int y_pitch, float* stats_partial, int B, int Hin, int Win, int Cin,
-                                   int Cout, int ksize, int stride, int pad, int act, void* stream) {
+                                   const void* w_packed, const float* bias, const void* residual,
+                                   const void* residual_lo, int res_pitch, void* y, void* y_lo, int y_pitch,
+                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
+                                   int stride, int pad, int act, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
+  S2P_CHECK_ARG(!residual_lo || residual, "conv: residual_lo without residual");
+  S2P_CHECK_ARG(aligned16(residual_lo) && aligned16(y_lo), "conv: pointers must be 16-byte aligned");
   if (x2 != nullptr) {
     S2P_CHECK_ARG(stride == 1 && 2 * pad == ksize - 1, "conv: a second operand needs a stride-1 'same' convolution");
     S2P_CHECK_ARG(Cin2 > 0 && Cin2 % 64 == 0, "conv: Cin2=%d must be a multiple of 64", Cin2);
@@ -718,7 +760,9 @@ extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, i
   p.out_pitch = y_pitch; p.res_pitch = res_pitch; p.act = act;
   p.bias = bias;
   p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.residual_lo = static_cast<const __nv_bfloat16*>(residual_lo);
   p.out = static_cast<__nv_bfloat16*>(y);
+  p.out_lo = static_cast<__nv_bfloat16*>(y_lo);
   p.stats_partial = stats_partial;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
   return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream,
@@ -728,8 +772,9 @@ extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, i
 extern "C" int s2p_mat_fused_ct(int C) { return C >= 128 ? 128 : C; }
 
 extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_packed_gb, const void* x,
-                                      int x_pitch, int up, const float* mod_table, void* y, int y_pitch, int B,
-                                      int H, int W, int Cin, int C, int ksize, int act, void* stream) {
+                                      const void* x_lo, int x_pitch, int up, const float* mod_table, void* y,
+                                      int y_pitch, int B, int H, int W, int Cin, int C, int ksize, int act,
+                                      void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(h && w_packed_gb && x && mod_table && y, "conv_mat_fused: null pointer");
   S2P_CHECK_ARG(B > 0 && H > 0 && W > 0, "conv_mat_fused: bad dims B=%d H=%d W=%d", B, H, W);
@@ -741,12 +786,13 @@ extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_
   S2P_CHECK_ARG(up == 1 || (up == 2 && H % 2 == 0 && W % 2 == 0), "conv_mat_fused: up=%d H=%d W=%d", up, H, W);
   S2P_CHECK_ARG(h_pitch >= Cin && h_pitch % 8 == 0, "conv_mat_fused: h_pitch=%d", h_pitch);
   S2P_CHECK_ARG(x_pitch >= C && x_pitch % 8 == 0 && y_pitch >= C && y_pitch % 8 == 0, "conv_mat_fused: pitch");
-  S2P_CHECK_ARG(aligned16(h) && aligned16(x) && aligned16(y) && aligned16(w_packed_gb) && aligned16(mod_table),
-                "conv_mat_fused: pointers must be 16-byte aligned");
+  S2P_CHECK_ARG(aligned16(h) && aligned16(x) && aligned16(x_lo) && aligned16(y) && aligned16(w_packed_gb) &&
+                    aligned16(mod_table), "conv_mat_fused: pointers must be 16-byte aligned");
   ConvParams p{};
   p.out_pitch = y_pitch; p.act = act;
   p.out = static_cast<__nv_bfloat16*>(y);
   p.mat_x = static_cast<const __nv_bfloat16*>(x);
+  p.mat_x_lo = static_cast<const __nv_bfloat16*>(x_lo);
   p.mat_tab = reinterpret_cast<const float4*>(mod_table);
   p.mat_x_pitch = x_pitch; p.mat_up = up; p.mat_C = C;
   const int block_n = 2 * s2p_mat_fused_ct(C);

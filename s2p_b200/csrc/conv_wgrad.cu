@@ -312,11 +312,12 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
 
 template <int BN, int TAPS>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradPlan& pl, cudaStream_t st) {
-  static int configured = 0;
-  if (pl.smem_bytes > configured) {
+  static int configured[kMaxDevices] = {};   // per device
+  const int dev = current_device();
+  if (pl.smem_bytes > configured[dev]) {
     S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BN, TAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         pl.smem_bytes));
-    configured = pl.smem_bytes;
+    configured[dev] = pl.smem_bytes;
   }
   conv_wgrad_kernel<BN, TAPS><<<pl.grid, 192, pl.smem_bytes, st>>>(tdy, tx, pl.p);
   count_launch();

@@ -84,6 +84,9 @@ mat_prepare_kernel(const float2* __restrict__ partial, int rows, const float* __
 
 struct NormParams {
   const __nv_bfloat16* x;
+  const __nv_bfloat16* x_lo;   // low halves of a wide (bf16 hi + lo pair) input, same pitch; or null
+  __nv_bfloat16* y_lo;         // low halves of a wide output (same pitch as y) or null
+  __nv_bfloat16* y_dup;        // second copy of the high halves (operand layout [hi | lo | hi]) or null
   const float2* mean_rstd;   // [B][C]
   const float* gs;           // [B][gsbs_pitch] or null
   const float* bs;
@@ -112,7 +115,7 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 }
 
 // blockDim = (C/8 channel groups, PY pixel slots).  grid = (chunks per image, B).
-template <bool HAS_GB, bool UP2>
+template <bool HAS_GB, bool UP2, bool WIDE>
 __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
   const int cg = threadIdx.x;              // channel group (8 channels)
   const int c0 = cg * 8;
@@ -138,7 +141,7 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
 
   constexpr int UNROLL = 4;
   for (int base = pix_begin + threadIdx.y; base < pix_end; base += blockDim.y * UNROLL) {
-    uint4 xv[UNROLL], gv[UNROLL], bv[UNROLL];
+    uint4 xv[UNROLL], xlv[UNROLL], gv[UNROLL], bv[UNROLL];
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
       const int pix = base + u * blockDim.y;
@@ -148,9 +151,11 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
           const int h = pix / p.W, w = pix - h * p.W;
           xpix = img_pix_x + static_cast<size_t>(h >> 1) * Wx + (w >> 1);
           xv[u] = __ldg(reinterpret_cast<const uint4*>(p.x + xpix * p.x_pitch + c0));
+          if (WIDE) xlv[u] = __ldg(reinterpret_cast<const uint4*>(p.x_lo + xpix * p.x_pitch + c0));
         } else {
           xpix = img_pix + pix;
           xv[u] = ld_stream(p.x + xpix * p.x_pitch + c0);
+          if (WIDE) xlv[u] = ld_stream(p.x_lo + xpix * p.x_pitch + c0);
         }
         if (HAS_GB) {
           const __nv_bfloat16* g = p.gb + (img_pix + pix) * p.gb_pitch + c0;
@@ -165,6 +170,12 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
       if (pix < pix_end) {
         float xf[8], gf[8], bf[8], o[8];
         unpack8(xv[u], xf);
+        if (WIDE) {
+          float xl[8];
+          unpack8(xlv[u], xl);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) xf[j] += xl[j];
+        }
         if (HAS_GB) { unpack8(gv[u], gf); unpack8(bv[u], bf); }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -179,6 +190,14 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
         uint4 ov = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
                               pack_bf16x2(o[6], o[7]));
         st_stream(p.y + (img_pix + pix) * p.y_pitch + c0, ov);
+        if (p.y_lo != nullptr) {
+          const uint4 lv = make_uint4(pack_bf16x2(o[0] - bf16_lo(ov.x), o[1] - bf16_hi(ov.x)),
+                                      pack_bf16x2(o[2] - bf16_lo(ov.y), o[3] - bf16_hi(ov.y)),
+                                      pack_bf16x2(o[4] - bf16_lo(ov.z), o[5] - bf16_hi(ov.z)),
+                                      pack_bf16x2(o[6] - bf16_lo(ov.w), o[7] - bf16_hi(ov.w)));
+          st_stream(p.y_lo + (img_pix + pix) * p.y_pitch + c0, lv);
+        }
+        if (p.y_dup != nullptr) st_stream(p.y_dup + (img_pix + pix) * p.y_pitch + c0, ov);
       }
     }
   }
@@ -217,9 +236,10 @@ extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float
   return check_launch("mat_prepare_kernel");
 }
 
-extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float* mean_rstd, const float* gs,
-                                const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y,
-                                int y_pitch, int B, int H, int W, int C, int act, void* stream) {
+extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd,
+                                const float* gs, const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch,
+                                void* y, void* y_lo, void* y_dup, int y_pitch, int B, int H, int W, int C, int act,
+                                void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && mean_rstd && y, "mat_norm: null pointer");
   S2P_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && C <= 2048, "mat_norm: bad dims C=%d", C);
@@ -228,10 +248,14 @@ extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float*
   S2P_CHECK_ARG(!gb_spatial || (gb_pitch >= 2 * C && gb_pitch % 8 == 0), "mat_norm: gb_pitch=%d", gb_pitch);
   S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_norm: gs and bs must both be given or both null");
   S2P_CHECK_ARG(act >= 0 && act <= 2, "mat_norm: act=%d", act);
-  S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+  S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(x_lo) |
+                  reinterpret_cast<uintptr_t>(y_lo) | reinterpret_cast<uintptr_t>(y_dup) |
                   reinterpret_cast<uintptr_t>(gb_spatial)) & 15) == 0, "mat_norm: 16-byte alignment");
   NormParams p{};
   p.x = static_cast<const __nv_bfloat16*>(x);
+  p.x_lo = static_cast<const __nv_bfloat16*>(x_lo);
+  p.y_lo = static_cast<__nv_bfloat16*>(y_lo);
+  p.y_dup = static_cast<__nv_bfloat16*>(y_dup);
   p.mean_rstd = reinterpret_cast<const float2*>(mean_rstd);
   p.gs = gs; p.bs = bs;
   p.gb = static_cast<const __nv_bfloat16*>(gb_spatial);
@@ -257,13 +281,19 @@ extern "C" int s2p_mat_norm_fwd(const void* x, int x_pitch, int up, const float*
   S2P_CHECK_ARG(B <= 65535, "mat_norm: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 block(groups, py), grid(chunks, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define S2P_NORM_LAUNCH(GB, UP)                                                      \
+  do {                                                                               \
+    if (x_lo) mat_norm_kernel<GB, UP, true><<<grid, block, 0, st>>>(p);              \
+    else mat_norm_kernel<GB, UP, false><<<grid, block, 0, st>>>(p);                  \
+  } while (0)
   if (gb_spatial) {
-    if (up == 2) mat_norm_kernel<true, true><<<grid, block, 0, st>>>(p);
-    else mat_norm_kernel<true, false><<<grid, block, 0, st>>>(p);
+    if (up == 2) S2P_NORM_LAUNCH(true, true);
+    else S2P_NORM_LAUNCH(true, false);
   } else {
-    if (up == 2) mat_norm_kernel<false, true><<<grid, block, 0, st>>>(p);
-    else mat_norm_kernel<false, false><<<grid, block, 0, st>>>(p);
+    if (up == 2) S2P_NORM_LAUNCH(false, true);
+    else S2P_NORM_LAUNCH(false, false);
   }
+#undef S2P_NORM_LAUNCH
   count_launch();
   return check_launch("mat_norm_kernel");
 }

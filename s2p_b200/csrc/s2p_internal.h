@@ -31,7 +31,11 @@ inline int check_launch(const char* what) {
   return S2P_OK;
 }
 
-int num_sms();
+// Per-device caches (SM count, cudaFuncSetAttribute done-flags) are indexed by the CURRENT device's ordinal:
+// a process that drives a second GPU must not inherit the first one's state.
+constexpr int kMaxDevices = 64;
+int current_device();   // ordinal of the calling thread's current device, clamped to [0, kMaxDevices)
+int num_sms();          // SM count of the current device
 void count_launch();
 
 }  // namespace s2p

@@ -234,10 +234,11 @@ extern "C" int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_t
   p.rows_per_cta = 256 / p.Wo;
   const size_t smem = (sw::kC1Taps * sw::kC1Out + static_cast<size_t>(2 * p.rows_per_cta + 3) * (W + 4) * 3) * 4;
   if (smem > 200 * 1024) return set_error(S2P_ERR_UNSUPPORTED, "slac_conv1: %zu B of shared memory needed", smem);
-  static size_t configured = 48 * 1024;
-  if (smem > configured) {
+  static size_t configured[kMaxDevices] = {};   // per device (0 = the 48 KB default)
+  const int dev = current_device();
+  if (smem > 48 * 1024 && smem > configured[dev]) {
     S2P_CHECK_CUDA(cudaFuncSetAttribute(sw::slac_conv1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+    configured[dev] = smem;
   }
   const dim3 grid((p.Ho + p.rows_per_cta - 1) / p.rows_per_cta, static_cast<unsigned>(n_frames));
   sw::slac_conv1_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(p);

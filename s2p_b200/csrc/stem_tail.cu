@@ -20,8 +20,8 @@ constexpr int kStemMaxW = 256;
 template <bool U8>
 __global__ void __launch_bounds__(256, 2)
 stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oihw,
-                 const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int y_pitch,
-                 float2* __restrict__ stats, int H, int W, int Cout, int rows) {
+                 const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ y_lo,
+                 int y_pitch, float2* __restrict__ stats, int H, int W, int Cout, int rows) {
   extern __shared__ __align__(16) float sm[];
   const int PW = (W + 2 + 8 + 3) & ~3;              // patch row pitch: halo + the last 8-pixel group's overhang, 16-B rows
   float* ws = sm;                                   // [27][Cout], tap = ci*9 + r*3 + s
@@ -125,6 +125,19 @@ stem_conv_kernel(const void* __restrict__ image, const float* __restrict__ w_oih
                             pack_bf16x2(acc[i][4], acc[i][5]), pack_bf16x2(acc[i][6], acc[i][7]));
       *reinterpret_cast<uint4*>(y + (pix0 + i) * y_pitch + c0) = ov;
       const uint32_t pk[4] = {ov.x, ov.y, ov.z, ov.w};
+      if (y_lo != nullptr) {
+        // wide store (bf16 hi + lo pair): the statistics are those of the fp32 values
+        uint32_t lo[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float a = acc[i][2 * j], b = acc[i][2 * j + 1];
+          lo[j] = pack_bf16x2(a - bf16_lo(pk[j]), b - bf16_hi(pk[j]));
+          s1[2 * j] += a; s1[2 * j + 1] += b;
+          s2[2 * j] += a * a; s2[2 * j + 1] += b * b;
+        }
+        *reinterpret_cast<uint4*>(y_lo + (pix0 + i) * y_pitch + c0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        continue;
+      }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float a = bf16_lo(pk[j]), b = bf16_hi(pk[j]);
@@ -225,7 +238,7 @@ torgb_tanh_kernel(const __nv_bfloat16* __restrict__ x, int x_pitch, const float*
 extern "C" int s2p_stem_stats_rows(int H, int W) { (void)W; return (H + s2p::kStemRows - 1) / s2p::kStemRows; }
 
 extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* w_oihw, const float* bias,
-                                 void* y, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
+                                 void* y, void* y_lo, int y_pitch, float* stats_partial, int B, int H, int W, int Cout,
                                  void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(image && w_oihw && y, "stem: null pointer");
@@ -247,18 +260,21 @@ extern "C" int s2p_stem_conv_fwd(const void* image, int image_fmt, const float* 
   S2P_CHECK_ARG(B <= 65535, "stem: B=%d exceeds the grid's y extent (65535 images per call)", B);
   dim3 grid(rows, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  static size_t smem_configured = 48 * 1024;
-  if (smem > smem_configured) {
+  static size_t smem_configured_dev[kMaxDevices] = {};   // per device (0 = the 48 KB default)
+  size_t& smem_configured = smem_configured_dev[current_device()];
+  if (smem > 48 * 1024 && smem > smem_configured) {
     S2P_CHECK_ARG(smem <= 200 * 1024, "stem: W=%d Cout=%d needs %zu bytes of shared memory", W, Cout, smem);
     S2P_CHECK_CUDA(cudaFuncSetAttribute(stem_conv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     S2P_CHECK_CUDA(cudaFuncSetAttribute(stem_conv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_configured = smem;
   }
   if (image_fmt == S2P_IMG_U8_NHWC)
-    stem_conv_kernel<true><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
+    stem_conv_kernel<true><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y),
+                                                    static_cast<__nv_bfloat16*>(y_lo), y_pitch,
                                                     reinterpret_cast<float2*>(stats_partial), H, W, Cout, rows);
   else
-    stem_conv_kernel<false><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y), y_pitch,
+    stem_conv_kernel<false><<<grid, threads, smem, st>>>(image, w_oihw, bias, static_cast<__nv_bfloat16*>(y),
+                                                     static_cast<__nv_bfloat16*>(y_lo), y_pitch,
                                                      reinterpret_cast<float2*>(stats_partial), H, W, Cout, rows);
   count_launch();
   return check_launch("stem_conv_kernel");

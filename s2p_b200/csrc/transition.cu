@@ -362,11 +362,12 @@ extern "C" int s2p_ensemble_transition_fwd(const float* obs, int obs_pitch, cons
   const size_t smem = smem_bytes(n_members, obs_dim + 1);
   if (smem > 227 * 1024)
     return set_error(S2P_ERR_UNSUPPORTED, "ensemble_transition: %zu B of shared memory needed", smem);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[kMaxDevices] = {};   // per device
+  const int dev = current_device();
+  if (!attr_set[dev]) {
     S2P_CHECK_CUDA(cudaFuncSetAttribute(ensemble_transition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         227 * 1024));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   Params p;
   p.obs = obs; p.obs_pitch = obs_pitch; p.action = action; p.act_pitch = act_pitch;

@@ -13,6 +13,15 @@ vectors fp32; conv weights packed [Cout][R][S][Cin] bf16 once per load.  The MAT
 blend factors sigmoid(blend_*) are folded into the packed gamma/beta conv weights
 and into the batched state-head linear at pack time, and the 3x3 ``mlp_shared``
 convs of all MATs that read the same encoder feature are merged into one wide conv.
+
+Precision (``opt.precision``, default "high"; tools/precision_attribution.py is the error budget behind it):
+every tensor-core operand is bf16, but the tensors that only an instance norm or a residual add reads -- the
+encoder's pre-norm maps e1..e3, the residual stream x and the block-internal dx -- are stored as bf16 hi + lo
+PAIRS (~16 mantissa bits), and the three convs of the image encoder's main line (conv2, conv3, head: 2 % of the
+flops, upstream of every modulation) run split-precision: operand [hi | lo | hi] against weights
+[W_hi | W_hi | W_lo], i.e. the three significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core
+pass.  That is what holds PSNR >= 50 dB against the fp32 oracle on O(1)-activation weights (BASELINE.json
+north_star); "standard" is the plain single-bf16 schedule of round 1 (48.6 dB), kept for A/B timing.
 """
 from __future__ import annotations
 
@@ -81,12 +90,25 @@ def _init_weights(net, init_type, gain):
                 nn.init.xavier_normal_(m.weight, gain=gain)
                 if m.bias is not None:
                     nn.init.zeros_(m.bias)
-            elif init_type == "scaled":
+            elif init_type in ("scaled", "trained_like"):
                 nn.init.normal_(m.weight, 0.0, (1.0 / m.weight[0].numel()) ** 0.5)
                 if m.bias is not None:
                     nn.init.normal_(m.bias, 0.0, 0.1)
             else:
                 raise ValueError(f"unknown init_type {init_type}")
+    if init_type in ("scaled", "trained_like"):
+        for m in net.modules():
+            if isinstance(m, _MATParams):
+                if init_type == "scaled":
+                    nn.init.normal_(m.blend_gamma, 0.0, 1.0)
+                    nn.init.normal_(m.blend_beta, 0.0, 1.0)
+                else:          # blend scalars away from sigmoid = 0.5 (a state- or an image-dominated mix)
+                    for p in (m.blend_gamma, m.blend_beta):
+                        with torch.no_grad():
+                            p.fill_(float((1.0 + 1.5 * torch.rand(())) * (1.0 if torch.rand(()) < 0.5 else -1.0)))
+        if init_type == "trained_like" and hasattr(net, "conv_img"):
+            with torch.no_grad():
+                net.conv_img.weight.mul_(0.3)    # non-saturating tanh head
 
 
 class S2PGeneratorB200(nn.Module):
@@ -119,6 +141,9 @@ class S2PGeneratorB200(nn.Module):
         # fuse_mat: the gamma/beta conv applies the MAT norm in its own epilogue (default).
         # False keeps the two-kernel form (conv -> bf16 maps -> mat_norm kernel).
         self.fuse_mat = bool(getattr(opt, "fuse_mat", True))
+        self.precision = str(getattr(opt, "precision", "high"))
+        if self.precision not in ("high", "standard"):
+            raise ValueError(f"precision must be 'high' or 'standard', got {self.precision}")
         self._packed = None
         self._ws = {}
 
@@ -155,9 +180,11 @@ class S2PGeneratorB200(nn.Module):
         P["se"] = [(f32(l.weight), f32(l.bias)) for l in self.state_encoder.layers]
         enc = self.image_encoder
         P["stem_w"], P["stem_b"] = f32(enc.conv1.weight), f32(enc.conv1.bias)
-        P["e2_w"], P["e2_b"] = ops.pack_conv_weight(enc.conv2.weight), f32(enc.conv2.bias)
-        P["e3_w"], P["e3_b"] = ops.pack_conv_weight(enc.conv3.weight), f32(enc.conv3.bias)
-        P["head_w"], P["head_b"] = ops.pack_conv_weight(self.head.weight), f32(self.head.bias)
+        # the encoder's main line runs split-precision in "high" mode: weights [W_hi | W_hi | W_lo] along Cin
+        pack_main = ops.pack_conv_weight_split if self.precision == "high" else ops.pack_conv_weight
+        P["e2_w"], P["e2_b"] = pack_main(enc.conv2.weight), f32(enc.conv2.bias)
+        P["e3_w"], P["e3_b"] = pack_main(enc.conv3.weight), f32(enc.conv3.bias)
+        P["head_w"], P["head_b"] = pack_main(self.head.weight), f32(self.head.bias)
         P["img_w"], P["img_b"] = ops.pack_torgb_weight(f32(self.conv_img.weight)), f32(self.conv_img.bias)
         # group the MATs by the encoder feature they are conditioned on
         groups = {4: [], 2: [], 1: []}
@@ -215,25 +242,48 @@ class S2PGeneratorB200(nn.Module):
             self._ws[key] = t
         return t[:shape[0]]
 
+    def _act(self, name, shape, wide):
+        """activation buffer -> (hi, lo): the two channel halves of one [.., 2C] tensor when `wide` (bf16 pair), else
+        (tensor, None)"""
+        c = shape[3]
+        if wide:
+            t = self._buf(name, tuple(shape[:3]) + (2 * c,), torch.bfloat16)
+            return t[..., :c], t[..., c:]
+        return self._buf(name, shape, torch.bfloat16), None
+
     def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False,
-              finalize=True, x2=None):
-        """returns (y, stats) where stats is the finalized (mean, rstd) table when `finalize`,
-        else the raw (partials, HW) pair consumed by ops.mat_prepare."""
+              finalize=True, x2=None, wide=False):
+        """returns ((y, y_lo), stats) where stats is the finalized (mean, rstd) table when `finalize`,
+        else the raw (partials, HW) pair consumed by ops.mat_prepare.  `residual` is a (hi, lo) pair."""
         B, hin, win, _ = x.shape
         ho = (hin + 2 * (k // 2) - k) // stride + 1
         wo = (win + 2 * (k // 2) - k) // stride + 1
-        y = self._buf(name, (B, ho, wo, cout), torch.bfloat16)
+        y, y_lo = self._act(name, (B, ho, wo, cout), wide)
         mr = None
         st = None
         if want_stats:
             st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
-        ops.conv_igemm(x, w, b, cout, k, stride, act, residual, y, st, x2=x2)
+        res, res_lo = residual if residual is not None else (None, None)
+        ops.conv_igemm(x, w, b, cout, k, stride, act, res, y, st, x2=x2, out_lo=y_lo, residual_lo=res_lo)
         if want_stats:
             if not finalize:
-                return y, (st, ho * wo)
+                return (y, y_lo), (st, ho * wo)
             mr = self._buf(name + ".mr", (B, cout, 2), torch.float32)
             ops.in_stats_finalize(st, ho * wo, 1e-5, mr)
-        return y, mr
+        return (y, y_lo), mr
+
+    def _enc_norm(self, name, e, mr, split):
+        """LReLU(IN(e)) of the image encoder -> (feature [.., C] bf16, operand of the next main-line conv): the
+        operand is the [hi | lo | hi] layout of the split-precision conv when `split`, else the feature itself"""
+        eh, el = e
+        B, h, w, c = eh.shape
+        if split:
+            t = self._buf(name, (B, h, w, 3 * c), torch.bfloat16)
+            ops.mat_norm(eh, mr, act=ACT_LRELU, out=t[..., :c], x_lo=el, out_lo=t[..., c:2 * c], out_dup=t[..., 2 * c:])
+            return t[..., :c], t
+        t = self._buf(name, (B, h, w, c), torch.bfloat16)
+        ops.mat_norm(eh, mr, act=ACT_LRELU, out=t, x_lo=el)
+        return t, t
 
     # ------------------------------------------------------------------ forward
     @torch.no_grad()
@@ -259,25 +309,27 @@ class S2PGeneratorB200(nn.Module):
         if H % 4 or W % 4:
             raise RuntimeError("image height/width must be multiples of 4")
         bf = torch.bfloat16
-        # ---- image encoder
-        e1 = self._buf("e1", (B, H, W, ngf), bf)
+        hp = self.precision == "high"
+        # ---- image encoder (pre-norm maps wide, main-line operands split, in "high" precision)
+        e1 = self._act("e1", (B, H, W, ngf), hp)
         st = self._buf("e1.st", (B, ops.stem_stats_rows(H, W), ngf, 2), torch.float32)
-        ops.stem_conv(image, P["stem_w"], P["stem_b"], ngf, e1, st)
+        ops.stem_conv(image, P["stem_w"], P["stem_b"], ngf, e1[0], st, out_lo=e1[1])
         mr = ops.in_stats_finalize(st, H * W, 1e-5, self._buf("e1.mr", (B, ngf, 2), torch.float32))
-        f = {1: ops.mat_norm(e1, mr, act=ACT_LRELU, out=self._buf("f1", (B, H, W, ngf), bf))}
-        e2, mr = self._conv("e2", f[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True)
-        f[2] = ops.mat_norm(e2, mr, act=ACT_LRELU, out=self._buf("f2", tuple(e2.shape), bf))
-        e3, mr = self._conv("e3", f[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True)
-        f[4] = ops.mat_norm(e3, mr, act=ACT_LRELU, out=self._buf("f4", tuple(e3.shape), bf))
+        f, fx = {}, {}
+        f[1], fx[1] = self._enc_norm("f1", e1, mr, hp)
+        e2, mr = self._conv("e2", fx[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True, wide=hp)
+        f[2], fx[2] = self._enc_norm("f2", e2, mr, hp)
+        e3, mr = self._conv("e3", fx[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True, wide=hp)
+        f[4], fx[4] = self._enc_norm("f4", e3, mr, hp)
         # ---- merged mlp_shared convs: one wide conv per conditioning feature
         hs = {}
         for ds in (4, 2, 1):
             sw, sb, n = P["shared"][ds]
-            hs[ds], _ = self._conv(f"hs{ds}", f[ds], sw, sb, n, 3, 1, ACT_RELU)
+            hs[ds] = self._conv(f"hs{ds}", f[ds], sw, sb, n, 3, 1, ACT_RELU)[0][0]
         # ---- trunk
         fuse = self.fuse_mat
-        x, mr_x = self._conv("head", f[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True,
-                             finalize=not fuse)
+        x, mr_x = self._conv("head", fx[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True,
+                             finalize=not fuse, wide=hp)
         cur = 4
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
             up = cur // ds
@@ -296,11 +348,12 @@ class S2PGeneratorB200(nn.Module):
                     st_in, hw_in = mr_in
                     tab = ops.mat_prepare(st_in, hw_in, gs, bs, m["gb_b"], 1e-5,
                                           self._buf(f"tab.{C}.{tag}", (B, C, 4), torch.float32))
-                    return ops.conv_mat_fused(hsl, m["gb_w"], xin, tab, up_, act, 3,
-                                              self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
+                    return ops.conv_mat_fused(hsl, m["gb_w"], xin[0], tab, up_, act, 3,
+                                              self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf), x_lo=xin[1])
                 gbuf = self._buf(f"gb{ds}.{2 * C}", (B, hh, ww, 2 * C), bf)
                 ops.conv_igemm(hsl, m["gb_w"], m["gb_b"], 2 * C, 3, 1, ACT_NONE, None, gbuf, None)
-                return ops.mat_norm(xin, mr_in, gs, bs, gbuf, up_, act, self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf))
+                return ops.mat_norm(xin[0], mr_in, gs, bs, gbuf, up_, act, self._buf(f"t{ds}.{C}.{tag}", (B, hh, ww, C), bf),
+                                    x_lo=xin[1])
 
             ts = None
             if blk.learned_shortcut:
@@ -313,13 +366,13 @@ class S2PGeneratorB200(nn.Module):
                 xs = x
             t = mat("norm_0", x, mr_x, up, ACT_LRELU, "a")
             dx, mr_dx = self._conv(f"dx{bi}", t, pb["c0_w"], pb["c0_b"], blk.fmid, 3, 1, want_stats=True,
-                                   finalize=not fuse)
+                                   finalize=not fuse, wide=hp)
             t = mat("norm_1", dx, mr_dx, 1, ACT_LRELU, "b")
             # the last block's output is only ever read through LeakyReLU (ToRGB): apply it here
             x, mr_x = self._conv(f"x{bi}", t, pb["c1s_w"] if ts is not None else pb["c1_w"], pb["c1_b"], blk.fout, 3, 1,
                                  act=ACT_LRELU if last else ACT_NONE, residual=xs,
-                                 want_stats=not last, finalize=not fuse, x2=ts)
-        ops.torgb_igemm(x, P["img_w"], P["img_b"], out_f32, out_u8)
+                                 want_stats=not last, finalize=not fuse, x2=ts, wide=hp and not last)
+        ops.torgb_igemm(x[0], P["img_w"], P["img_b"], out_f32, out_u8)
 
     def _run(self, image, state, want_f32=True, want_u8=False):
         if not image.is_cuda or not state.is_cuda:

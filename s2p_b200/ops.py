@@ -59,13 +59,38 @@ def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scal
     return out
 
 
+def _lo_of(t, lo, what):
+    """pointer of the low halves of a wide (bf16 hi + lo pair) tensor: same shape and pixel pitch as the high halves"""
+    if lo is None:
+        return 0
+    if tuple(lo.shape) != tuple(t.shape) or _nhwc_pitch(lo, what) != _nhwc_pitch(t, what):
+        raise RuntimeError(f"{what}: the low halves must have the shape and pitch of the high halves")
+    return lo.data_ptr()
+
+
+def wide(t):
+    """(hi, lo) channel slices of a wide activation tensor [B, H, W, 2C] = [hi | lo]"""
+    c = t.shape[3] // 2
+    return t[..., :c], t[..., c:]
+
+
+def pack_conv_weight_split(w_oihw: torch.Tensor) -> torch.Tensor:
+    """packed weight of the split-precision conv: [Cout, R*S*3*Cin] bf16 with [W_hi | W_hi | W_lo] along Cin
+    (W_hi = bf16(W), W_lo = bf16(W - W_hi)), for an operand laid out [x_hi | x_lo | x_hi]: one tensor-core pass
+    computes W_hi x_hi + W_hi x_lo + W_lo x_hi, i.e. (W x) to ~2^-16 instead of 2^-8."""
+    w = w_oihw.detach().float()
+    hi = w.to(torch.bfloat16).float()
+    return pack_conv_weight(torch.cat([hi, hi, w - hi], dim=1))
+
+
 def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None, pad=None,
-               x2=None):
+               x2=None, out_lo=None, residual_lo=None):
     """y = act(conv(x) + bias + residual); returns y.  ``stats`` (fp32
     [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given.  ``x2`` (NHWC bf16 of the output's
     spatial size): a second operand whose 1x1 convolution is accumulated into the same tile; ``w_packed`` is then
-    [Cout, k*k*Cin + Cin2] (the two packed weights concatenated along the row)."""
-    _require_cuda(x, w_packed, bias, residual, out, stats, x2)
+    [Cout, k*k*Cin + Cin2] (the two packed weights concatenated along the row).  ``out_lo`` / ``residual_lo``: low
+    halves of a wide output / residual (bf16 hi + lo pair, see include/s2p_b200.h)."""
+    _require_cuda(x, w_packed, bias, residual, out, stats, x2, out_lo, residual_lo)
     b, hin, win, cin = x.shape
     pad = ksize // 2 if pad is None else pad
     hout = (hin + 2 * pad - ksize) // stride + 1
@@ -95,9 +120,9 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
     _lib.check(
         _lib.load().s2p_conv_igemm_fwd2(
             x.data_ptr(), _nhwc_pitch(x, "x"), _ptr(x2), _nhwc_pitch(x2, "x2") if x2 is not None else 0, cin2,
-            w_packed.data_ptr(), _ptr(bias), _ptr(residual), res_pitch,
-            out.data_ptr(), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout, ksize, stride, pad, act,
-            _stream()),
+            w_packed.data_ptr(), _ptr(bias), _ptr(residual), _lo_of(residual, residual_lo, "residual_lo"), res_pitch,
+            out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout,
+            ksize, stride, pad, act, _stream()),
         "s2p_conv_igemm_fwd2")
     return out
 
@@ -152,11 +177,13 @@ def in_stats_finalize(stats: torch.Tensor, hw: int, eps: float = 1e-5, out=None)
     return out
 
 
-def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, out=None):
+def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, out=None, x_lo=None, out_lo=None,
+             out_dup=None):
     """y = act(((x_up - mean) * rstd) * (1 + gs + gI) + bs + bI); gs/bs are [B, C]
     fp32 views (row pitch taken from stride(0)); gb_spatial is NHWC bf16 with 2C
-    channels (gI | bI) at the OUTPUT resolution."""
-    _require_cuda(x, mean_rstd, gs, bs, gb_spatial, out)
+    channels (gI | bI) at the OUTPUT resolution.  ``x_lo``: low halves of a wide x; ``out_lo`` / ``out_dup``: low
+    halves and a second copy of the high halves of the output (the [hi | lo | hi] split-precision conv operand)."""
+    _require_cuda(x, mean_rstd, gs, bs, gb_spatial, out, x_lo, out_lo, out_dup)
     b, hx, wx, c = x.shape
     h, w = hx * up, wx * up
     if out is None:
@@ -177,8 +204,9 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
         gbp = _nhwc_pitch(gb_spatial, "gb_spatial")
     _lib.check(
         _lib.load().s2p_mat_norm_fwd(
-            x.data_ptr(), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs), _ptr(bs), gpitch,
-            _ptr(gb_spatial), gbp, out.data_ptr(), _nhwc_pitch(out, "out"), b, h, w, c, act, _stream()),
+            x.data_ptr(), _lo_of(x, x_lo, "x_lo"), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs), _ptr(bs), gpitch,
+            _ptr(gb_spatial), gbp, out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _lo_of(out, out_dup, "out_dup"),
+            _nhwc_pitch(out, "out"), b, h, w, c, act, _stream()),
         "s2p_mat_norm_fwd")
     return out
 
@@ -245,10 +273,10 @@ def mat_prepare(stats, hw, gs, bs, bias_gb, eps: float = 1e-5, out=None):
     return out
 
 
-def conv_mat_fused(h, w_packed_gb, x, mod_table, up=1, act=ACT_LRELU, ksize=3, out=None):
+def conv_mat_fused(h, w_packed_gb, x, mod_table, up=1, act=ACT_LRELU, ksize=3, out=None, x_lo=None):
     """y = act(IN(x_up) * (1 + gs + conv_gamma(h)) + bs + conv_beta(h)) in one kernel: the
-    gamma/beta conv's accumulators are consumed by its own epilogue."""
-    _require_cuda(h, w_packed_gb, x, mod_table, out)
+    gamma/beta conv's accumulators are consumed by its own epilogue.  ``x_lo``: low halves of a wide x."""
+    _require_cuda(h, w_packed_gb, x, mod_table, out, x_lo)
     b, hh, ww, cin = h.shape
     bx, hx, wx, c = x.shape
     if bx != b or hx * up != hh or wx * up != ww:
@@ -263,15 +291,17 @@ def conv_mat_fused(h, w_packed_gb, x, mod_table, up=1, act=ACT_LRELU, ksize=3, o
         raise RuntimeError("conv_mat_fused: mod_table must be contiguous fp32 [B, C, 4]")
     _lib.check(
         _lib.load().s2p_conv_mat_fused_fwd(
-            h.data_ptr(), _nhwc_pitch(h, "h"), w_packed_gb.data_ptr(), x.data_ptr(), _nhwc_pitch(x, "x"), up,
+            h.data_ptr(), _nhwc_pitch(h, "h"), w_packed_gb.data_ptr(), x.data_ptr(), _lo_of(x, x_lo, "x_lo"),
+            _nhwc_pitch(x, "x"), up,
             mod_table.data_ptr(), out.data_ptr(), _nhwc_pitch(out, "out"), b, hh, ww, cin, c, ksize, act, _stream()),
         "s2p_conv_mat_fused_fwd")
     return out
 
 
-def stem_conv(image, w_oihw, bias, cout, out=None, stats=None):
-    """Cin=3 3x3 conv from the boundary image: fp32 NCHW [B,3,H,W] or uint8 NHWC [B,H,W,3]."""
-    _require_cuda(image, w_oihw, bias, out, stats)
+def stem_conv(image, w_oihw, bias, cout, out=None, stats=None, out_lo=None):
+    """Cin=3 3x3 conv from the boundary image: fp32 NCHW [B,3,H,W] or uint8 NHWC [B,H,W,3].  ``out_lo``: low halves
+    of a wide output."""
+    _require_cuda(image, w_oihw, bias, out, stats, out_lo)
     if image.dtype == torch.uint8:
         b, h, w, _ = image.shape
         fmt = IMG_U8_NHWC
@@ -286,7 +316,8 @@ def stem_conv(image, w_oihw, bias, cout, out=None, stats=None):
         out = torch.empty(b, h, w, cout, dtype=torch.bfloat16, device=image.device)
     _lib.check(
         _lib.load().s2p_stem_conv_fwd(image.data_ptr(), fmt, w_oihw.data_ptr(), _ptr(bias), out.data_ptr(),
-                                      _nhwc_pitch(out, "out"), _ptr(stats), b, h, w, cout, _stream()),
+                                      _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), _ptr(stats), b, h, w, cout,
+                                      _stream()),
         "s2p_stem_conv_fwd")
     return out
 

@@ -26,6 +26,9 @@ def make_options(argv=None, **overrides):
     p.add_argument("--init_type", type=str, default="xavier")
     p.add_argument("--init_variance", type=float, default=0.02)
     p.add_argument("--max_microbatch", type=int, default=128)
+    # "high": wide (bf16 hi + lo) residual stream / pre-norm maps and split-precision encoder convs, PSNR >= 50 dB
+    # vs the fp32 oracle; "standard": single-bf16 storage everywhere (round-1 schedule, ~48.6 dB), for A/B timing
+    p.add_argument("--precision", type=str, default="high", choices=["high", "standard"])
     opt, _ = p.parse_known_args(argv if argv is not None else [])
     for k, v in overrides.items():
         setattr(opt, k, v)

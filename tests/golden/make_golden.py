@@ -30,6 +30,8 @@ CASES = [
     ("cheetah_scaled_b2", "cheetah", "scaled", 2, 1),
     ("walker_scaled_b2", "walker", "scaled", 2, 1),
     ("cheetah_scaled_roll5_b1", "cheetah", "scaled", 1, 5),
+    ("cheetah_trained_like_b2", "cheetah", "trained_like", 2, 1),
+    ("walker_trained_like_roll5_b1", "walker", "trained_like", 1, 5),
 ]
 
 
@@ -84,7 +86,9 @@ def main():
                             u8_last=O.to_uint8_hwc(last).numpy())
         manifest["cases"][name] = dict(env=env, init_type=init, batch=batch, steps=steps,
                                        weight_abs_sum=weight_checksum(net),
-                                       out_mean=float(last.mean()), out_std=float(last.std()))
+                                       out_mean=float(last.mean()), out_std=float(last.std()),
+                                       out_range=float(last.max() - last.min()),
+                                       saturated_frac=float((last.abs() > 0.98).float().mean()))
         print(name, manifest["cases"][name])
     with open(os.path.join(HERE, "manifest.json"), "w") as f:
         json.dump(manifest, f, indent=1)

@@ -10,12 +10,13 @@ import s2p_oracle as O
 
 pytestmark = pytest.mark.gpu
 
-MAX_ABS = 0.08     # on the [-1,1] output, 'scaled' (O(1) activations) init
-PSNR_MIN = 50.0    # BASELINE.json north_star, on the spec's own random init (SPADE xavier, gain 0.02)
-# 'scaled' is this repo's stress init: O(1) activations everywhere and a saturating tanh, so
-# every bf16 rounding of the ~30 stored activations shows up in the output.  Measured 48.4 dB
-# (round 1, bf16 gamma/beta maps); the floor below guards against regressions.
-PSNR_MIN_STRESS = 47.0
+MAX_ABS = 0.08     # on the [-1,1] output, O(1)-activation inits
+# BASELINE.json north_star: PSNR >= 50 dB vs the fp32 reference, images mapped to [0,1], peak = 1.  It is asserted
+# on EVERY init: 'scaled' (O(1) activations everywhere, tanh partly saturated), 'trained_like' (non-saturating
+# head, blend scalars away from 0.5) and the spec's own xavier-0.02 init -- whose outputs span only ~5e-3, so that
+# case is additionally held to 50 dB relative to the GOLDEN'S OWN RANGE (peak = max - min), which an all-zero
+# image would fail by 40 dB.
+PSNR_MIN = 50.0
 
 
 @pytest.fixture(scope="module")
@@ -35,7 +36,15 @@ def _pair(pkg, env, init):
     return ora, net.eval()
 
 
-@pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2"])
+def _psnr_range(a, gold):
+    """PSNR with peak = the golden's own dynamic range (non-vacuous for near-constant outputs)"""
+    import math
+    rng = (gold.max() - gold.min()).item()
+    mse = (a.double() - gold.double()).pow(2).mean().item()
+    return float("inf") if mse == 0 else 10.0 * math.log10(rng * rng / mse)
+
+
+@pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2", "cheetah_trained_like_b2"])
 def test_one_step_vs_golden_and_oracle(pkg, name):
     case = common.manifest()["cases"][name]
     ora, net = _pair(pkg, case["env"], case["init_type"])
@@ -48,17 +57,35 @@ def test_one_step_vs_golden_and_oracle(pkg, name):
     assert out.shape == gold.shape and torch.isfinite(out).all()
     p = common.psnr01(out, gold)
     e = (out - gold).abs().max().item()
-    print(f"{name}: psnr={p:.1f} dB max_abs={e:.3e}")
-    assert p >= (PSNR_MIN_STRESS if case["init_type"] == "scaled" else PSNR_MIN)
-    assert e <= (MAX_ABS if case["init_type"] == "scaled" else 1e-4)
+    pr = _psnr_range(out, gold)
+    print(f"{name}: psnr={p:.2f} dB (peak 1), {pr:.2f} dB (peak = golden range {case['out_range']:.3g}), max_abs={e:.3e}")
+    assert p >= PSNR_MIN
+    assert pr >= PSNR_MIN
+    assert e <= (1e-4 if case["init_type"] == "xavier" else MAX_ABS)
 
 
-def test_rollout_5_steps(pkg):
+def test_standard_precision_is_the_round1_schedule(pkg):
+    """opt.precision='standard' (single-bf16 storage everywhere; kept for A/B timing) still runs, and the default
+    'high' schedule (wide residual stream / pre-norm maps, split-precision encoder convs) is what buys the 50 dB"""
+    case = common.manifest()["cases"]["walker_scaled_b2"]
+    ora = common.build_oracle(case["env"], case["init_type"])
+    image, states = common.make_inputs(case["env"], case["batch"], 1)
+    gold = torch.from_numpy(common.load_golden("walker_scaled_b2")["first"])
+    ps = {}
+    for prec in ("standard", "high"):
+        net = pkg.define_G(pkg.make_options(env_type=case["env"], gpu_ids="0", precision=prec))
+        net.load_state_dict(ora.state_dict())
+        ps[prec] = common.psnr01(net.eval()(image.cuda(), states[:, 0].cuda()).cpu(), gold)
+    print(f"walker_scaled_b2: standard {ps['standard']:.2f} dB, high {ps['high']:.2f} dB")
+    assert ps["standard"] >= 46.0 and ps["high"] >= PSNR_MIN and ps["high"] >= ps["standard"] + 2.0
+
+
+@pytest.mark.parametrize("name", ["cheetah_scaled_roll5_b1", "walker_trained_like_roll5_b1"])
+def test_rollout_5_steps(pkg, name):
     """N-step autoregressive synthesis (README.md:30-33).  Per-step parity is checked
     teacher-forced (oracle and B200 step from the SAME previous frame), because a
     random-weight generator amplifies any input perturbation from step to step; the
     free-running distance to the golden rollout is reported and loosely bounded."""
-    name = "cheetah_scaled_roll5_b1"
     case = common.manifest()["cases"][name]
     ora, net = _pair(pkg, case["env"], case["init_type"])
     ora = ora.cuda()
@@ -70,8 +97,8 @@ def test_rollout_5_steps(pkg):
         with torch.no_grad():
             ref = ora(prev, states[:, k].cuda())
         p = common.psnr01(out[:, k].cpu(), ref.cpu())
-        print(f"rollout step {k + 1}: teacher-forced psnr={p:.1f} dB")
-        assert p >= PSNR_MIN_STRESS
+        print(f"rollout step {k + 1}: teacher-forced psnr={p:.2f} dB")
+        assert p >= PSNR_MIN
         prev = out[:, k]
     gold = common.load_golden(name)
     g1 = torch.from_numpy(gold["first"])
@@ -89,7 +116,7 @@ def test_rollout_5_steps(pkg):
     p5_oracle = common.psnr01(frame.cpu(), g5)
     print(f"rollout free-running vs golden: step1 psnr={p1:.1f} step5 psnr={p5:.1f} "
           f"(fp32 oracle under an equal-power step-1 perturbation: {p5_oracle:.1f})")
-    assert p1 >= PSNR_MIN_STRESS
+    assert p1 >= PSNR_MIN
     assert p5 >= p5_oracle - 6.0, "free-running drift exceeds the oracle's own sensitivity"
 
 
@@ -139,8 +166,8 @@ def test_fused_and_unfused_mat_agree(pkg):
     with torch.no_grad():
         ref = ora(image, states[:, 0])
     pa, pb, pab = common.psnr01(a, ref), common.psnr01(b, ref), common.psnr01(a, b)
-    print(f"fused psnr={pa:.1f} dB, unfused psnr={pb:.1f} dB, fused vs unfused {pab:.1f} dB")
-    assert pa >= PSNR_MIN_STRESS and pb >= PSNR_MIN_STRESS and pab >= PSNR_MIN_STRESS - 3
+    print(f"fused psnr={pa:.2f} dB, unfused psnr={pb:.2f} dB, fused vs unfused {pab:.2f} dB")
+    assert pa >= PSNR_MIN and pb >= PSNR_MIN and pab >= PSNR_MIN
 
 
 def test_state_changes_output(pkg):

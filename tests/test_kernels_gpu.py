@@ -290,3 +290,154 @@ def test_state_encoder_kernels(ops):
     b = torch.randn(130, generator=g).cuda()
     y = ops.linear(x, w, b, 2)
     assert (y - F.leaky_relu(F.linear(x, w, b), 0.2)).abs().max().item() <= 1e-4
+
+
+# --------------------------------------------------------------------------------------------------------------
+# wide (bf16 hi + lo pair) activations and the split-precision convolution ("high" precision schedule)
+def _split(t):
+    hi = t.to(torch.bfloat16)
+    return hi, (t - hi.float()).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("b,h,cin,cout,stride,residual", [(2, 25, 256, 512, 1, False), (2, 25, 128, 512, 1, True),
+                                                        (3, 100, 64, 128, 2, False), (2, 50, 64, 64, 1, True)])
+def test_conv_wide_output_and_residual(ops, b, h, cin, cout, stride, residual):
+    """y stored as a bf16 pair: hi + lo reproduces the fp32 result to ~2^-16 (not 2^-8), hi alone is the plain
+    kernel's output bit for bit, the statistics are those of the fp32 values, and a wide residual is added whole."""
+    g = torch.Generator().manual_seed(cin + cout + h)
+    xb = torch.randn(b, h, h, cin, generator=g).cuda().to(torch.bfloat16)
+    wt = (torch.randn(cout, cin, 3, 3, generator=g) / (9 * cin) ** 0.5).cuda()
+    bs = torch.randn(cout, generator=g).cuda()
+    wp = ops.pack_conv_weight(wt)
+    ho = (h + 2 - 3) // stride + 1
+    res_hi = res_lo = None
+    res32 = None
+    if residual:
+        res32 = torch.randn(b, ho, ho, cout, generator=g).cuda() * 3
+        pair = torch.empty(b, ho, ho, 2 * cout, dtype=torch.bfloat16, device="cuda")
+        pair[..., :cout], pair[..., cout:] = _split(res32)
+        res_hi, res_lo = ops.wide(pair)
+    out = torch.full((b, ho, ho, 2 * cout), float("nan"), dtype=torch.bfloat16, device="cuda")
+    y_hi, y_lo = ops.wide(out)
+    st = torch.full((b, ops.conv_stats_rows(ho, ho), cout, 2), float("nan"), device="cuda")
+    ops.conv_igemm(xb, wp, bs, cout, 3, stride, 0, res_hi, y_hi, st, out_lo=y_lo, residual_lo=res_lo)
+    ref = nhwc(F.conv2d(xb.float().permute(0, 3, 1, 2), wt.to(torch.bfloat16).float(), bs, stride, 1))
+    if residual:
+        ref = ref + (res_hi.float() + res_lo.float())
+    y = y_hi.float() + y_lo.float()
+    scale = ref.abs().max().item()
+    assert torch.isfinite(y).all()
+    assert (y - ref).abs().max().item() <= 2.0 ** -15 * scale + 2e-5 * scale      # fp32 accumulation order + 2^-17 pair rounding
+    assert torch.equal(y_hi, ref.to(torch.bfloat16)) or (y_hi.float() - ref).abs().max().item() <= 2.0 ** -8 * scale
+    mr = ops.in_stats_finalize(st, ho * ho)
+    assert torch.allclose(mr[..., 0], ref.mean(dim=(1, 2)), atol=2e-5 * scale)
+    assert torch.allclose(mr[..., 1], 1.0 / torch.sqrt(ref.var(dim=(1, 2), unbiased=False) + 1e-5), rtol=1e-4)
+    # the plain (narrow) call on the same operands stores exactly the high halves
+    if not residual:
+        y_narrow = ops.conv_igemm(xb, wp, bs, cout, 3, stride, 0)
+        assert torch.equal(y_narrow, y_hi)
+
+
+@pytest.mark.parametrize("b,h,cin,cout,stride", [(2, 100, 64, 128, 2), (2, 50, 128, 256, 2), (2, 25, 256, 512, 1)])
+def test_conv_split_precision(ops, b, h, cin, cout, stride):
+    """operand [hi | lo | hi] x weights [W_hi | W_hi | W_lo]: the fp32 convolution of UN-rounded inputs to ~2^-15
+    (the image encoder's main-line convs in the "high" precision schedule)"""
+    g = torch.Generator().manual_seed(cin * 3 + cout)
+    x = torch.randn(b, h, h, cin, generator=g).cuda()
+    wt = (torch.randn(cout, cin, 3, 3, generator=g) / (9 * cin) ** 0.5).cuda()
+    hi, lo = _split(x)
+    op3 = torch.cat([hi, lo, hi], dim=3).contiguous()
+    wp = ops.pack_conv_weight_split(wt)
+    assert tuple(wp.shape) == (cout, 9 * 3 * cin)
+    ho = (h + 2 - 3) // stride + 1
+    out = torch.empty(b, ho, ho, 2 * cout, dtype=torch.bfloat16, device="cuda")
+    y_hi, y_lo = ops.wide(out)
+    ops.conv_igemm(op3, wp, None, cout, 3, stride, 0, None, y_hi, None, out_lo=y_lo)
+    ref = nhwc(F.conv2d(x.permute(0, 3, 1, 2), wt, None, stride, 1))
+    plain = nhwc(F.conv2d(hi.float().permute(0, 3, 1, 2), wt.to(torch.bfloat16).float(), None, stride, 1))
+    err = (y_hi.float() + y_lo.float() - ref).pow(2).mean().sqrt().item()
+    err_plain = (plain - ref).pow(2).mean().sqrt().item()
+    print(f"split conv rms error {err:.3e} vs single-bf16 operands {err_plain:.3e}")
+    assert err <= err_plain / 50 and err <= 3e-5 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("c,up,hx,gb", [(64, 1, 100, False), (128, 1, 50, False), (256, 2, 25, True), (512, 1, 25, True)])
+def test_mat_norm_wide_in_and_split_out(ops, c, up, hx, gb):
+    """mat_norm reading a wide x and writing the [hi | lo | hi] operand layout"""
+    g = torch.Generator().manual_seed(c + up + 11)
+    b = 2
+    x32 = (torch.randn(b, hx, hx, c, generator=g) * 2 + 0.5).cuda()
+    pair = torch.empty(b, hx, hx, 2 * c, dtype=torch.bfloat16, device="cuda")
+    pair[..., :c], pair[..., c:] = _split(x32)
+    x_hi, x_lo = ops.wide(pair)
+    xw = x_hi.float() + x_lo.float()
+    mean = xw.mean(dim=(1, 2))
+    rstd = 1.0 / torch.sqrt(xw.var(dim=(1, 2), unbiased=False) + 1e-5)
+    mr = torch.stack([mean, rstd], dim=2).contiguous()
+    h = hx * up
+    gs = bs_ = gbm = None
+    if gb:
+        gs, bs_ = torch.randn(b, c, generator=g).cuda() * 0.3, torch.randn(b, c, generator=g).cuda() * 0.3
+        gbm = (torch.randn(b, h, h, 2 * c, generator=g) * 0.3).cuda().to(torch.bfloat16)
+    out3 = torch.full((b, h, h, 3 * c), float("nan"), dtype=torch.bfloat16, device="cuda")
+    ops.mat_norm(x_hi, mr, gs, bs_, gbm, up, 2, out3[..., :c], x_lo=x_lo, out_lo=out3[..., c:2 * c], out_dup=out3[..., 2 * c:])
+    xu = xw.repeat_interleave(up, 1).repeat_interleave(up, 2)
+    xh = (xu - mean[:, None, None]) * rstd[:, None, None]
+    if gb:
+        ref = xh * (1 + gs[:, None, None] + gbm[..., :c].float()) + bs_[:, None, None] + gbm[..., c:].float()
+    else:
+        ref = xh
+    ref = F.leaky_relu(ref, 0.2)
+    y = out3[..., :c].float() + out3[..., c:2 * c].float()
+    assert torch.equal(out3[..., :c], out3[..., 2 * c:])
+    assert (y - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 2e-5
+    # a narrow input with the same high halves differs at the bf16 level: the low halves are really read
+    y_narrow = ops.mat_norm(x_hi, mr, gs, bs_, gbm, up, 2)
+    assert (y_narrow.float() - ref).abs().max().item() > 10 * (y - ref).abs().max().item()
+
+
+@pytest.mark.parametrize("c,up,h", [(64, 1, 100), (128, 2, 100), (512, 1, 25), (256, 2, 50)])
+def test_conv_mat_fused_wide_x(ops, c, up, h):
+    """the fused gamma/beta conv + MAT norm epilogue with a wide pre-norm activation == mat_norm on the same pair"""
+    g = torch.Generator().manual_seed(c + up + h)
+    b, nh = 2, 128
+    hx = h // up
+    hs = F.relu(torch.randn(b, h, h, nh, generator=g)).cuda().to(torch.bfloat16)
+    wg = (torch.randn(c, nh, 3, 3, generator=g) / (9 * nh) ** 0.5).cuda()
+    wb = (torch.randn(c, nh, 3, 3, generator=g) / (9 * nh) ** 0.5).cuda()
+    x32 = (torch.randn(b, hx, hx, c, generator=g) * 2 + 0.5).cuda()
+    pair = torch.empty(b, hx, hx, 2 * c, dtype=torch.bfloat16, device="cuda")
+    pair[..., :c], pair[..., c:] = _split(x32)
+    x_hi, x_lo = ops.wide(pair)
+    xw = x_hi.float() + x_lo.float()
+    mean = xw.mean(dim=(1, 2))
+    rstd = 1.0 / torch.sqrt(xw.var(dim=(1, 2), unbiased=False) + 1e-5)
+    gs, bs_ = torch.randn(b, c, generator=g).cuda() * 0.3, torch.randn(b, c, generator=g).cuda() * 0.3
+    tab = torch.stack([rstd, -mean * rstd, 1 + gs, bs_], dim=2).contiguous()
+    y = ops.conv_mat_fused(hs, ops.pack_conv_weight(ops.interleave_gamma_beta(wg, wb)), x_hi, tab, up, 2, 3, x_lo=x_lo)
+    gi = nhwc(F.conv2d(hs.float().permute(0, 3, 1, 2), wg.to(torch.bfloat16).float(), None, 1, 1))
+    bi = nhwc(F.conv2d(hs.float().permute(0, 3, 1, 2), wb.to(torch.bfloat16).float(), None, 1, 1))
+    xu = xw.repeat_interleave(up, 1).repeat_interleave(up, 2)
+    xh = xu * rstd[:, None, None] - (mean * rstd)[:, None, None]
+    ref = F.leaky_relu(xh * (1 + gs[:, None, None] + gi) + bs_[:, None, None] + bi, 0.2)
+    assert (y.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 1e-3
+    # rms error is the output's own bf16 rounding only (~2^-9 / sqrt(3) relative), not two roundings
+    rel = ((y.float() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()).item()
+    assert rel <= 1.6e-3
+
+
+def test_stem_wide_output(ops):
+    g = torch.Generator().manual_seed(8)
+    img = (torch.rand(2, 3, 100, 100, generator=g) * 2 - 1).cuda()
+    wt = (torch.randn(64, 3, 3, 3, generator=g) / 27 ** 0.5).cuda()
+    bs = torch.randn(64, generator=g).cuda() * 0.1
+    out = torch.empty(2, 100, 100, 128, dtype=torch.bfloat16, device="cuda")
+    y_hi, y_lo = ops.wide(out)
+    st = torch.empty(2, ops.stem_stats_rows(100, 100), 64, 2, device="cuda")
+    ops.stem_conv(img, wt, bs, 64, y_hi, st, out_lo=y_lo)
+    ref = nhwc(F.conv2d(img, wt, bs, 1, 1))
+    assert (y_hi.float() + y_lo.float() - ref).abs().max().item() <= 3e-5 * ref.abs().max().item()
+    mr = ops.in_stats_finalize(st, 100 * 100)
+    assert torch.allclose(mr[..., 0], ref.mean(dim=(1, 2)), atol=1e-5)
+    narrow = ops.stem_conv(img, wt, bs, 64)
+    assert torch.equal(narrow, y_hi)

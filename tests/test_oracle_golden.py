@@ -8,7 +8,7 @@ import common
 import s2p_oracle as O
 
 
-@pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2"])
+@pytest.mark.parametrize("name", ["cheetah_xavier_b2", "cheetah_scaled_b2", "walker_scaled_b2", "cheetah_trained_like_b2"])
 def test_oracle_matches_golden_one_step(name):
     case = common.manifest()["cases"][name]
     net = common.build_oracle(case["env"], case["init_type"])
@@ -26,8 +26,17 @@ def test_oracle_matches_golden_one_step(name):
     assert (u8.int() - gold_u8).abs().max().item() <= 1
 
 
-def test_oracle_rollout_golden():
-    name = "cheetah_scaled_roll5_b1"
+def test_trained_like_init_is_non_degenerate():
+    """ORACLE_SPEC v1.3 init: tanh unsaturated, output O(0.3), every blend factor away from 0.5"""
+    case = common.manifest()["cases"]["cheetah_trained_like_b2"]
+    assert case["saturated_frac"] == 0.0 and 0.2 <= case["out_std"] <= 0.5 and case["out_range"] >= 1.0
+    net = common.build_oracle("cheetah", "trained_like")
+    blends = [torch.sigmoid(p).item() for n, p in net.named_parameters() if "blend_" in n]
+    assert len(blends) == 26 and all(abs(b - 0.5) >= 0.2 for b in blends)
+
+
+@pytest.mark.parametrize("name", ["cheetah_scaled_roll5_b1", "walker_trained_like_roll5_b1"])
+def test_oracle_rollout_golden(name):
     case = common.manifest()["cases"][name]
     net = common.build_oracle(case["env"], case["init_type"])
     image, states = common.make_inputs(case["env"], case["batch"], case["steps"])
