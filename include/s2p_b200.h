@@ -67,11 +67,16 @@ int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const f
  * weights concatenated along the row.  Replaces `conv_1(h) + conv_s(x_s)` of the oracle's res-block (SPADEResnetBlock
  * lineage: learned shortcut) in one launch, without the bf16 round trip of the shortcut through HBM.  x2 == NULL: the
  * plain call.  residual_lo / y_lo: low halves of a wide residual / output (see Conventions); with y_lo the statistics
- * partials are those of the fp32 values. */
+ * partials are those of the fp32 values.
+ * cin_wrap > 0: SPLIT-PRECISION convolution.  x holds cin_wrap = 2*C channels [x_hi | x_lo] (a wide activation as one
+ * tensor) and is walked as Cin = 3*C logical channels [x_hi | x_lo | x_hi] (channels >= cin_wrap re-read the tensor
+ * from channel 0) against weights packed [W_hi | W_hi | W_lo] along Cin: one tensor-core pass computes the three
+ * significant products of (W_hi + W_lo)(x_hi + x_lo), i.e. the convolution to ~2^-16 instead of 2^-8.  Used for the
+ * image encoder's main-line convs (2 % of the generator's flops, upstream of every modulation). */
 int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2, const void* w_packed,
                         const float* bias, const void* residual, const void* residual_lo, int res_pitch, void* y,
                         void* y_lo, int y_pitch, float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
-                        int ksize, int stride, int pad, int act, void* stream);
+                        int ksize, int stride, int pad, int act, int cin_wrap, void* stream);
 
 /* ---- (a8) weight gradient of the convolution (training) -----------------------------
  * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]
@@ -97,15 +102,13 @@ int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int 
  *   y[n,h,w,c] = act( (x[n,h/up,w/up,c]-mean)*rstd * (1 + gs[n,c] + gI[n,h,w,c]) + bs[n,c] + bI[n,h,w,c] )
  * gb_spatial holds gI in channels [0,C) and bI in [C,2C) of each pixel; gs/bs/gb_spatial
  * may be NULL (plain IN + act, oracle ImageEncoder).  C % 8 == 0.
- * x_lo: low halves of a wide x.  y_lo: the output is stored wide; y_dup: a second copy of the output's high
- * halves -- with y, y_lo, y_dup = three channel slices of one tensor the result is the operand layout
- * [hi | lo | hi] of the split-precision convolution (weights [W_hi | W_hi | W_lo] along Cin: the three
- * significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core pass, used for the encoder's convs). */
+ * x_lo: low halves of a wide x.  y_lo: the output is stored wide (with y and y_lo the two channel halves of one
+ * tensor it is the [hi | lo] operand of the split-precision convolution, s2p_conv_igemm_fwd2 cin_wrap). */
 int s2p_in_stats_finalize(const float* stats_partial, int rows, float* mean_rstd, int B, int C,
                           int HW, float eps, void* stream);
 int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd, const float* gs,
                      const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y, void* y_lo,
-                     void* y_dup, int y_pitch, int B, int H, int W, int C, int act, void* stream);
+                     int y_pitch, int B, int H, int W, int C, int act, void* stream);
 
 /* ---- (a3 fused into a4) gamma/beta conv with the MAT norm applied in its epilogue ----
  * replaces, in ONE kernel, oracle MAT.mlp_gamma + MAT.mlp_beta (nn.Conv2d 3x3) and the
@@ -119,8 +122,10 @@ int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const
  * [2*ct*j, 2*ct*j+ct) are gamma channels [ct*j, ct*(j+1)) and the next ct rows the beta
  * channels of the same range (so one accumulator tile holds both for its channels).
  * bias_gb in s2p_mat_prepare is in plain [gamma(C) | beta(C)] order.
- * x_lo: low halves of a wide x (NULL = plain bf16).
- * Requires Cin % 64 == 0, C in {32, 64} or C % 128 == 0. */
+ * x reaches the epilogue through TMA (the tile's pixels as 64-channel boxes in slots of the operand ring), not
+ * through per-thread global loads.  x_lo: low halves of a wide x (NULL = plain bf16); a wide x must be ONE tensor
+ * [hi | lo], i.e. x_lo == x + C channels, x_pitch >= 2*C.
+ * Requires Cin % 64 == 0, C == 64 or C % 128 == 0. */
 int s2p_mat_fused_ct(int C);
 int s2p_mat_prepare(const float* stats_partial, int rows, const float* gs, const float* bs, int gsbs_pitch,
                     const float* bias_gb, float* mod_table, int B, int C, int HW, float eps, void* stream);
@@ -177,6 +182,22 @@ long long s2p_linear_workspace_floats(int B, int K, int N);
 int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const float* bias, float* y,
                    int y_pitch, int B, int K, int N, int act, float* workspace, long long workspace_floats,
                    void* stream);
+
+/* The WHOLE state path in one launch: gsbs = heads(MLP(pos_encode(state))), i.e. oracle StateEncoder.forward
+ * (positional_encoding + (Linear + LeakyReLU(0.2)) x n_layers, width `width`) followed by every MAT's
+ * fc_gamma / fc_beta batched into one Linear [heads_n, width] (no activation).  A persistent cooperative kernel
+ * (grid <= SM count) whose phases (= layers) meet at a global-memory barrier; for small batches (the batch-16
+ * latency case of BASELINE configs[0]/[1]) it replaces 1 + 2*(n_layers+1) launches.  Results are BIT-IDENTICAL to
+ * s2p_pos_encode_fwd + s2p_linear_fwd chained (same split-K slices, same summation order), so which of the two a
+ * batch size selects is invisible in the output.  layer_w / layer_b: HOST arrays of n_layers device pointers
+ * (weights [width, K_l] row-major fp32, K_0 = S*(1+2*n_freqs) <= 512, width <= 512; bias may be NULL);
+ * workspace: s2p_state_encoder_workspace_bytes(B, width) bytes, 256-B aligned, ZERO-INITIALISED once by the caller
+ * (the kernel leaves its barrier counters zeroed) and not shared between concurrent launches. */
+long long s2p_state_encoder_workspace_bytes(int B, int width);
+int s2p_state_encoder_fwd(const float* state, int B, int S, int n_freqs, const float* const* layer_w,
+                          const float* const* layer_b, int n_layers, int width, const float* heads_w,
+                          const float* heads_b, int heads_n, float* gsbs, int gsbs_pitch, void* workspace,
+                          long long workspace_bytes, void* stream);
 
 /* packed weight of the data-gradient convolution: dst[ci][R-1-r][S-1-s][co] = w[co][ci][r][s]
  * (bf16 rows of R*S*Cout), so dX = s2p_conv_igemm_fwd(dY (zero-inserted when stride 2), dst,

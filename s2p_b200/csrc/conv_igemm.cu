@@ -22,7 +22,7 @@
 //
 // Wide activations: a tensor the following instance norm / residual add reads (the residual stream x,
 // the block-internal dx, the encoder's pre-norm e) can be stored as a bf16 PAIR hi + lo (lo = bf16(v - hi),
-// ~16 mantissa bits) instead of one bf16: `out_lo`, `residual_lo`, `mat_x_lo`.  Conv operands stay bf16.
+// ~16 mantissa bits) instead of one bf16: `out_lo`, `residual_lo`, `x_wide`.  Conv operands stay bf16.
 #include <stdlib.h>
 
 #include "ptx.cuh"
@@ -46,10 +46,15 @@ struct ConvParams {
   float* stats_partial;   // [B][tiles_per_img*4][Cout][2] (sum, sumsq) or null
   // fused MAT epilogue (conv_mat_fused): the accumulators are the spatial gamma|beta maps,
   // the stored value is act((x*A + Bc) * (G1 + gamma) + (B0 + beta)) with (A,Bc,G1,B0) = mat_tab[n][c]
-  const __nv_bfloat16* mat_x;   // pre-norm activation [B][H/up][W/up][mat_x_pitch]
-  const __nv_bfloat16* mat_x_lo; // its low halves when it is stored wide (same pitch) or null
+  // the pre-norm activation x [B][H/up][W/up][..] arrives through tmap_x: per tile the producer warp TMA-loads the
+  // tile's x pixels (64-channel boxes, 128B-swizzled; low halves of a wide x = the boxes at channel + mat_C) into
+  // slots of the operand ring, and the epilogue reads them from shared memory
   const float4* mat_tab;        // [B][mat_C]
-  int mat_x_pitch, mat_up, mat_C;
+  int mat_up, mat_C;
+  int x_wide;                   // x is a bf16 pair [hi | lo] (2 * mat_C channels)
+  int x_bw;                     // pixels per row of an x box
+  uint32_t x_box_bytes;         // bytes of one x box (x_bw * rows * 128)
+  int cin_wrap;                 // A-operand channels >= cin_wrap re-read the tensor from channel 0 ([hi | lo] as [hi | lo | hi])
   // ToRGB epilogue (BLOCK_N = 16, 3 live columns): tanh(acc + bias) -> fp32 NCHW and/or uint8 NHWC
   float* rgb_f32;
   uint8_t* rgb_u8;
@@ -144,7 +149,8 @@ __device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* pa
 template <int BLOCK_N, int EPI, int CL>
 __global__ void __launch_bounds__(320, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const __grid_constant__ CUtensorMap tmap_a2, const ConvParams p) {
+                  const __grid_constant__ CUtensorMap tmap_a2, const __grid_constant__ CUtensorMap tmap_x,
+                  const ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -163,6 +169,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     if (p.kb2 > 0) tma_prefetch_desc(&tmap_a2);
+    if constexpr (EPI == kEpiMat) tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_b);
     for (int i = 0; i < Cfg::kStages; ++i) {
       mbar_init(&full_bar[i], 1);
@@ -200,6 +207,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int num_kb = num_kb_main + p.kb2;      // the second operand's k-blocks follow the filter taps
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
+  // fused MAT epilogue: after a tile's k-blocks the ring carries the tile's x boxes (not MMA operands: the MMA warp
+  // skips those slots, the epilogue warps read and release them).  A slot holds kXBoxPerSlot boxes of <= 16 KB.
+  constexpr int kXBoxPerSlot = (Cfg::kBBytes >= Cfg::kABytes) ? 2 : 1;
+  const int x_boxes = (EPI == kEpiMat) ? (BLOCK_N / 128) * (p.x_wide ? 2 : 1) : 0;
+  const int x_slots = (x_boxes + kXBoxPerSlot - 1) / kXBoxPerSlot;
 
   // The producer and MMA loops run with the whole warp converged (uniform control flow, uniform
   // operands) and elect one lane only around the asynchronous issue itself: a loop written under
@@ -220,16 +232,21 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (elect_one()) {
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
+          int ach = cc * Cfg::kBlockK;
+          if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
           if constexpr (CL > 1) {
             constexpr int kPart = BLOCK_N / CL;
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+            // (the peer's own full barrier is only ever waited on for x slots: a plain arrival keeps its
+            // phase in step with the ring -- one completed phase per pass over the slot)
+            else if constexpr (EPI == kEpiMat) mbar_arrive(&full_bar[stage]);
             const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
-            if (kb < num_kb_main) tma_load_4d_pair(sa, &tmap_a, lead_bar, cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            if (kb < num_kb_main) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, win0 + sx, hin0 + r, img);
             else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
             tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-            if (kb < num_kb_main) tma_load_4d(sa, &tmap_a, &full_bar[stage], cc * Cfg::kBlockK, win0 + sx, hin0 + r, img);
+            if (kb < num_kb_main) tma_load_4d(sa, &tmap_a, &full_bar[stage], ach, win0 + sx, hin0 + r, img);
             else tma_load_4d(sa, &tmap_a2, &full_bar[stage], (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
             tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
           }
@@ -237,6 +254,28 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         __syncwarp();
         if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+      if constexpr (EPI == kEpiMat) {
+        // this tile's x pixels (at half resolution when the block upsamples), CTA-local: each CTA of a pair loads
+        // the rows of its own m-tile and is signalled on its own barrier
+        constexpr int CT = BLOCK_N / 2;
+        const int xw0 = p.mat_up == 2 ? (w0 >> 1) : w0, xh0 = p.mat_up == 2 ? (h0 >> 1) : h0;
+        for (int b0 = 0; b0 < x_boxes; b0 += kXBoxPerSlot) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (elect_one()) {
+            const int nb = (x_boxes - b0) < kXBoxPerSlot ? (x_boxes - b0) : kXBoxPerSlot;
+            uint8_t* sa = smem + stage * Cfg::kStageBytes;
+            mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * p.x_box_bytes);
+            for (int j = 0; j < nb; ++j) {
+              const int bidx = b0 + j;
+              const int jbox = p.x_wide ? (bidx >> 1) : bidx, lo = p.x_wide ? (bidx & 1) : 0;
+              tma_load_4d(sa + j * Cfg::kABytes, &tmap_x, &full_bar[stage], lo * p.mat_C + n_tile * CT + jbox * 64, xw0, xh0,
+                          img);
+            }
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else if (warp == 1) {
@@ -277,6 +316,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
+        for (int xs = 0; xs < x_slots; ++xs)      // the tile's x slots are not MMA operands
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp >= 2) {
@@ -327,23 +368,32 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         constexpr int CT = BLOCK_N / 2;        // channels per n-tile: columns [0,CT) = gamma, [CT,2CT) = beta
         constexpr int kSteps = CT / 32;        // 16-channel steps per warp (each warp owns CT/2 channels)
         const int cw = half * (CT / 2);        // first channel (inside the tile) of this warp
-        size_t xpix;
-        if (p.mat_up == 2) {
-          xpix = (static_cast<size_t>(img) * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
-        } else {
-          xpix = pix;
-        }
         const int ch0 = n_tile * CT;
         const StoreRows<2> rows2 = store_rows_prepare<2>(static_cast<uint32_t>(pix), valid, lane);
         float4* tab_s = tab_smem + acc * 128;
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
-        const uint4* x4 = reinterpret_cast<const uint4*>(p.mat_x + xpix * p.mat_x_pitch + ch0 + cw);
-        const bool wide_x = p.mat_x_lo != nullptr;
-        const uint4* xl4 = reinterpret_cast<const uint4*>(p.mat_x_lo + xpix * p.mat_x_pitch + ch0 + cw);
-        uint4 xn[2], xln[2];
-        if (valid) { xn[0] = __ldg(x4); xn[1] = __ldg(x4 + 1); }
-        if (valid && wide_x) { xln[0] = __ldg(xl4); xln[1] = __ldg(xl4 + 1); }
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps
+        // x: row of this thread's pixel inside the tile's x boxes (128-byte rows of 64 channels, 128B-swizzled by TMA)
+        const bool wide_x = p.x_wide != 0;
+        const int tw0 = (t % p.tiles_x) * p.tile_w, th0 = (t / p.tiles_x) * p.tile_h;
+        const int rx = p.mat_up == 2 ? (((th0 + my) >> 1) - (th0 >> 1)) * p.x_bw + (((tw0 + mx) >> 1) - (tw0 >> 1)) : m;
+        const uint32_t g0 = static_cast<uint32_t>(it) * static_cast<uint32_t>(num_kb + x_slots) + num_kb;   // ring position of the first x slot
+        const int jbox = cw / 64;                          // 64-channel box of this warp's channels
+        const int bidx = wide_x ? 2 * jbox : jbox;         // its (high-half) box; the low halves are the next box
+        const uint32_t gx = g0 + bidx / kXBoxPerSlot, gxl = g0 + (bidx + 1) / kXBoxPerSlot;
+        const uint32_t xs_hi = smem_u32(smem) + (gx % Cfg::kStages) * Cfg::kStageBytes + (bidx % kXBoxPerSlot) * Cfg::kABytes +
+                               static_cast<uint32_t>(rx) * 128u;
+        const uint32_t xs_lo = smem_u32(smem) + (gxl % Cfg::kStages) * Cfg::kStageBytes +
+                               ((bidx + 1) % kXBoxPerSlot) * Cfg::kABytes + static_cast<uint32_t>(rx) * 128u;
+        const uint32_t xkey = static_cast<uint32_t>(rx) & 7u;
+        const uint32_t xc0 = static_cast<uint32_t>(cw % 64) / 8u;   // first 16-byte chunk of this warp's channels in the box
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps; previous tile fully read
+        if (it > 0 && et == 0) {
+          // every epilogue warp is past the previous tile: hand its x slots back to the producer
+          const uint32_t gp = g0 - static_cast<uint32_t>(num_kb + x_slots);
+          for (int xs = 0; xs < x_slots; ++xs) mbar_arrive(&empty_bar[(gp + xs) % Cfg::kStages]);
+        }
+        mbar_wait(&full_bar[gx % Cfg::kStages], (gx / Cfg::kStages) & 1);
+        if (wide_x) mbar_wait(&full_bar[gxl % Cfg::kStages], (gxl / Cfg::kStages) & 1);
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
         uint32_t rg[16], rb[16];
@@ -355,13 +405,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           float g[16], bt[16];
 #pragma unroll
           for (int k = 0; k < 16; ++k) { g[k] = __uint_as_float(rg[k]); bt[k] = __uint_as_float(rb[k]); }
-          const uint4 xr0 = xn[0], xr1 = xn[1];
-          const uint4 xq0 = xln[0], xq1 = xln[1];
+          uint4 xr0 = make_uint4(0u, 0u, 0u, 0u), xr1 = xr0, xq0 = xr0, xq1 = xr0;
+          if (valid) {
+            const uint32_t c0 = ((xc0 + 2u * sidx) ^ xkey) << 4, c1 = ((xc0 + 2u * sidx + 1u) ^ xkey) << 4;
+            xr0 = lds128(xs_hi + c0);
+            xr1 = lds128(xs_hi + c1);
+            if (wide_x) { xq0 = lds128(xs_lo + c0); xq1 = lds128(xs_lo + c1); }
+          }
           if (sidx + 1 < kSteps) {
             tmem_ld16(t_row + cw + (sidx + 1) * 16, rg);
             tmem_ld16(t_row + CT + cw + (sidx + 1) * 16, rb);
-            if (valid) { xn[0] = __ldg(x4 + (sidx + 1) * 2); xn[1] = __ldg(x4 + (sidx + 1) * 2 + 1); }
-            if (valid && wide_x) { xln[0] = __ldg(xl4 + (sidx + 1) * 2); xln[1] = __ldg(xl4 + (sidx + 1) * 2 + 1); }
           } else {
             release_acc();
           }
@@ -588,8 +641,8 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
 }
 
 template <int BLOCK_N, int EPI, int CL>
-static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const ConvParams& p,
-                          cudaStream_t st) {
+static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const CUtensorMap& tx,
+                          const ConvParams& p, cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N, CL>;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   const int dev = current_device();
@@ -613,7 +666,7 @@ static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, ta2, p));
+  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, ta2, tx, p));
   count_launch();
   return check_launch("conv_igemm_kernel");
 }
@@ -629,10 +682,10 @@ int conv_cluster_size() {
 }
 
 template <int BLOCK_N, int EPI>
-static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const ConvParams& p,
-                       cudaStream_t st) {
-  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, ta2, p, st);
-  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, ta2, p, st);
+static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const CUtensorMap& tx,
+                       const ConvParams& p, cudaStream_t st) {
+  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, ta2, tx, p, st);
+  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, ta2, tx, p, st);
 }
 
 }  // namespace s2p
@@ -649,7 +702,8 @@ namespace s2p {
 // two tensor maps and launches.  `p` arrives with the epilogue fields already filled.
 static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B, int Hin, int Win, int Cin,
                          int Cout, int ksize, int stride, int pad, int block_n, int epi, ConvParams p, void* stream,
-                         const void* x2 = nullptr, int x2_pitch = 0, int Cin2 = 0) {
+                         const void* x2 = nullptr, int x2_pitch = 0, int Cin2 = 0, const void* mat_x = nullptr,
+                         int mat_x_pitch = 0) {
   EncodeTiledFn encode = get_encode_fn();
   if (!encode) return set_error(S2P_ERR_CUDA, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   p.B = B;
@@ -667,7 +721,8 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
   p.kb2 = x2 != nullptr ? Cin2 / 64 : 0;
   CUtensorMap ta, tb, ta2;
   {
-    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)B};
+    // (with cin_wrap the logical Cin walks [hi | lo | hi] over a tensor that holds [hi | lo])
+    cuuint64_t dims[4] = {(cuuint64_t)(p.cin_wrap > 0 ? p.cin_wrap : Cin), (cuuint64_t)Win, (cuuint64_t)Hin, (cuuint64_t)B};
     cuuint64_t strides[3] = {(cuuint64_t)x_pitch * 2, (cuuint64_t)x_pitch * 2 * Win,
                              (cuuint64_t)x_pitch * 2 * Win * Hin};
     cuuint32_t box[4] = {64, (cuuint32_t)(p.tile_w * stride), (cuuint32_t)(p.tile_h * stride), 1};
@@ -700,20 +755,39 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: second operand tensor map encode failed (CUresult %d)", (int)r);
   }
+  CUtensorMap tx = ta;
+  if (epi == kEpiMat) {
+    // the pre-norm activation of the fused MAT epilogue: [B][H/up][W/up][C or 2C] NHWC bf16, 64-channel boxes covering
+    // one output tile's pixels (at half resolution: tile/2 + 1 per axis reaches every parent pixel of the tile)
+    const int up = p.mat_up;
+    const int Hx = p.H / up, Wx = p.W / up;
+    const int bw = up == 2 ? p.tile_w / 2 + 1 : p.tile_w, bh = up == 2 ? p.tile_h / 2 + 1 : p.tile_h;
+    if (bw * bh > 128 || bw > 256 || bh > 256) return set_error(S2P_ERR_UNSUPPORTED, "conv_mat_fused: x box %dx%d", bw, bh);
+    p.x_bw = bw;
+    p.x_box_bytes = static_cast<uint32_t>(bw) * bh * 128u;
+    cuuint64_t dims[4] = {(cuuint64_t)(p.x_wide ? 2 * p.mat_C : p.mat_C), (cuuint64_t)Wx, (cuuint64_t)Hx, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)mat_x_pitch * 2, (cuuint64_t)mat_x_pitch * 2 * Wx,
+                             (cuuint64_t)mat_x_pitch * 2 * Wx * Hx};
+    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(mat_x), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv_mat_fused: x tensor map encode failed (CUresult %d)", (int)r);
+  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, ta2, p, st);
+  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, ta2, tx, p, st);
   if (epi == kEpiMat) {
     switch (block_n) {
-      case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, p, st);
-      case 128: return launch_conv<128, kEpiMat>(ta, tb, ta2, p, st);
-      default: return launch_conv<64, kEpiMat>(ta, tb, ta2, p, st);
+      case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, tx, p, st);
+      default: return launch_conv<128, kEpiMat>(ta, tb, ta2, tx, p, st);
     }
   }
   switch (block_n) {
-    case 256: return launch_conv<256, kEpiPlain>(ta, tb, ta2, p, st);
-    case 192: return launch_conv<192, kEpiPlain>(ta, tb, ta2, p, st);
-    case 128: return launch_conv<128, kEpiPlain>(ta, tb, ta2, p, st);
-    default: return launch_conv<64, kEpiPlain>(ta, tb, ta2, p, st);
+    case 256: return launch_conv<256, kEpiPlain>(ta, tb, ta2, tx, p, st);
+    case 192: return launch_conv<192, kEpiPlain>(ta, tb, ta2, tx, p, st);
+    case 128: return launch_conv<128, kEpiPlain>(ta, tb, ta2, tx, p, st);
+    default: return launch_conv<64, kEpiPlain>(ta, tb, ta2, tx, p, st);
   }
 }
 
@@ -726,16 +800,18 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
                                   int ksize, int stride, int pad, int act, void* stream) {
   return s2p_conv_igemm_fwd2(x, x_pitch, nullptr, 0, 0, w_packed, bias, residual, nullptr, res_pitch, y, nullptr, y_pitch,
-                             stats_partial, B, Hin, Win, Cin, Cout, ksize, stride, pad, act, stream);
+                             stats_partial, B, Hin, Win, Cin, Cout, ksize, stride, pad, act, 0, stream);
 }
 
 extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2,
                                    const void* w_packed, const float* bias, const void* residual,
                                    const void* residual_lo, int res_pitch, void* y, void* y_lo, int y_pitch,
                                    float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
-                                   int stride, int pad, int act, void* stream) {
+                                   int stride, int pad, int act, int cin_wrap, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
+  S2P_CHECK_ARG(cin_wrap == 0 || (cin_wrap > 0 && cin_wrap % 64 == 0 && cin_wrap < Cin && Cin <= 2 * cin_wrap),
+                "conv: cin_wrap=%d (Cin=%d)", cin_wrap, Cin);
   S2P_CHECK_ARG(!residual_lo || residual, "conv: residual_lo without residual");
   S2P_CHECK_ARG(aligned16(residual_lo) && aligned16(y_lo), "conv: pointers must be 16-byte aligned");
   if (x2 != nullptr) {
@@ -751,7 +827,7 @@ extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, i
   S2P_CHECK_ARG(pad >= 0 && pad < ksize && Hin + 2 * pad >= ksize && Win + 2 * pad >= ksize, "conv: pad=%d", pad);
   S2P_CHECK_ARG(stride == 1 || stride == 2, "conv: stride=%d unsupported", stride);
   S2P_CHECK_ARG(act >= 0 && act <= 2, "conv: act=%d unsupported", act);
-  S2P_CHECK_ARG(x_pitch >= Cin && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
+  S2P_CHECK_ARG(x_pitch >= (cin_wrap > 0 ? cin_wrap : Cin) && x_pitch % 8 == 0, "conv: x_pitch=%d", x_pitch);
   S2P_CHECK_ARG(y_pitch >= Cout && y_pitch % 8 == 0, "conv: y_pitch=%d", y_pitch);
   S2P_CHECK_ARG(!residual || (res_pitch >= Cout && res_pitch % 8 == 0), "conv: res_pitch=%d", res_pitch);
   S2P_CHECK_ARG(aligned16(x) && aligned16(y) && aligned16(w_packed) && aligned16(residual) && aligned16(bias),
@@ -764,6 +840,7 @@ extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, i
   p.out = static_cast<__nv_bfloat16*>(y);
   p.out_lo = static_cast<__nv_bfloat16*>(y_lo);
   p.stats_partial = stats_partial;
+  p.cin_wrap = cin_wrap;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
   return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream,
                        x2, x2_pitch, Cin2);
@@ -779,24 +856,25 @@ extern "C" int s2p_conv_mat_fused_fwd(const void* h, int h_pitch, const void* w_
   S2P_CHECK_ARG(h && w_packed_gb && x && mod_table && y, "conv_mat_fused: null pointer");
   S2P_CHECK_ARG(B > 0 && H > 0 && W > 0, "conv_mat_fused: bad dims B=%d H=%d W=%d", B, H, W);
   S2P_CHECK_ARG(Cin > 0 && Cin % 64 == 0, "conv_mat_fused: Cin=%d must be a multiple of 64", Cin);
-  S2P_CHECK_ARG(C >= 32 && C % 32 == 0 && (C < 128 || C % 128 == 0),
-                "conv_mat_fused: C=%d must be 32, 64 or a multiple of 128", C);
+  S2P_CHECK_ARG(C == 64 || (C >= 128 && C % 128 == 0), "conv_mat_fused: C=%d must be 64 or a multiple of 128", C);
+  S2P_CHECK_ARG(!x_lo || x_lo == static_cast<const __nv_bfloat16*>(x) + C,
+                "conv_mat_fused: a wide x must be one [hi | lo] tensor (x_lo == x + C channels)");
   S2P_CHECK_ARG(ksize == 1 || ksize == 3, "conv_mat_fused: ksize=%d unsupported", ksize);
   S2P_CHECK_ARG(act >= 0 && act <= 2, "conv_mat_fused: act=%d unsupported", act);
   S2P_CHECK_ARG(up == 1 || (up == 2 && H % 2 == 0 && W % 2 == 0), "conv_mat_fused: up=%d H=%d W=%d", up, H, W);
   S2P_CHECK_ARG(h_pitch >= Cin && h_pitch % 8 == 0, "conv_mat_fused: h_pitch=%d", h_pitch);
-  S2P_CHECK_ARG(x_pitch >= C && x_pitch % 8 == 0 && y_pitch >= C && y_pitch % 8 == 0, "conv_mat_fused: pitch");
+  S2P_CHECK_ARG(x_pitch >= (x_lo ? 2 * C : C) && x_pitch % 8 == 0 && y_pitch >= C && y_pitch % 8 == 0, "conv_mat_fused: pitch");
   S2P_CHECK_ARG(aligned16(h) && aligned16(x) && aligned16(x_lo) && aligned16(y) && aligned16(w_packed_gb) &&
                     aligned16(mod_table), "conv_mat_fused: pointers must be 16-byte aligned");
   ConvParams p{};
   p.out_pitch = y_pitch; p.act = act;
   p.out = static_cast<__nv_bfloat16*>(y);
-  p.mat_x = static_cast<const __nv_bfloat16*>(x);
-  p.mat_x_lo = static_cast<const __nv_bfloat16*>(x_lo);
   p.mat_tab = reinterpret_cast<const float4*>(mod_table);
-  p.mat_x_pitch = x_pitch; p.mat_up = up; p.mat_C = C;
+  p.mat_up = up; p.mat_C = C;
+  p.x_wide = x_lo != nullptr;
   const int block_n = 2 * s2p_mat_fused_ct(C);
-  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, ksize / 2, block_n, kEpiMat, p, stream);
+  return conv_dispatch(h, h_pitch, w_packed_gb, B, H, W, Cin, 2 * C, ksize, 1, ksize / 2, block_n, kEpiMat, p, stream,
+                       nullptr, 0, 0, x, x_pitch);
 }
 
 extern "C" int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, const float* bias,

@@ -86,7 +86,6 @@ struct NormParams {
   const __nv_bfloat16* x;
   const __nv_bfloat16* x_lo;   // low halves of a wide (bf16 hi + lo pair) input, same pitch; or null
   __nv_bfloat16* y_lo;         // low halves of a wide output (same pitch as y) or null
-  __nv_bfloat16* y_dup;        // second copy of the high halves (operand layout [hi | lo | hi]) or null
   const float2* mean_rstd;   // [B][C]
   const float* gs;           // [B][gsbs_pitch] or null
   const float* bs;
@@ -197,7 +196,6 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
                                       pack_bf16x2(o[6] - bf16_lo(ov.w), o[7] - bf16_hi(ov.w)));
           st_stream(p.y_lo + (img_pix + pix) * p.y_pitch + c0, lv);
         }
-        if (p.y_dup != nullptr) st_stream(p.y_dup + (img_pix + pix) * p.y_pitch + c0, ov);
       }
     }
   }
@@ -238,8 +236,7 @@ extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float
 
 extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd,
                                 const float* gs, const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch,
-                                void* y, void* y_lo, void* y_dup, int y_pitch, int B, int H, int W, int C, int act,
-                                void* stream) {
+                                void* y, void* y_lo, int y_pitch, int B, int H, int W, int C, int act, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && mean_rstd && y, "mat_norm: null pointer");
   S2P_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && C <= 2048, "mat_norm: bad dims C=%d", C);
@@ -249,13 +246,12 @@ extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, in
   S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_norm: gs and bs must both be given or both null");
   S2P_CHECK_ARG(act >= 0 && act <= 2, "mat_norm: act=%d", act);
   S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(x_lo) |
-                  reinterpret_cast<uintptr_t>(y_lo) | reinterpret_cast<uintptr_t>(y_dup) |
+                  reinterpret_cast<uintptr_t>(y_lo) |
                   reinterpret_cast<uintptr_t>(gb_spatial)) & 15) == 0, "mat_norm: 16-byte alignment");
   NormParams p{};
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.x_lo = static_cast<const __nv_bfloat16*>(x_lo);
   p.y_lo = static_cast<__nv_bfloat16*>(y_lo);
-  p.y_dup = static_cast<__nv_bfloat16*>(y_dup);
   p.mean_rstd = reinterpret_cast<const float2*>(mean_rstd);
   p.gs = gs; p.bs = bs;
   p.gb = static_cast<const __nv_bfloat16*>(gb_spatial);

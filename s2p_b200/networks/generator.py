@@ -18,8 +18,8 @@ Precision (``opt.precision``, default "high"; tools/precision_attribution.py is 
 every tensor-core operand is bf16, but the tensors that only an instance norm or a residual add reads -- the
 encoder's pre-norm maps e1..e3, the residual stream x and the block-internal dx -- are stored as bf16 hi + lo
 PAIRS (~16 mantissa bits), and the three convs of the image encoder's main line (conv2, conv3, head: 2 % of the
-flops, upstream of every modulation) run split-precision: operand [hi | lo | hi] against weights
-[W_hi | W_hi | W_lo], i.e. the three significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core
+flops, upstream of every modulation) run split-precision: the wide operand [hi | lo] walked as [hi | lo | hi]
+against weights [W_hi | W_hi | W_lo], i.e. the three significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core
 pass.  That is what holds PSNR >= 50 dB against the fp32 oracle on O(1)-activation weights (BASELINE.json
 north_star); "standard" is the plain single-bf16 schedule of round 1 (48.6 dB), kept for A/B timing.
 """
@@ -120,6 +120,7 @@ class S2PGeneratorB200(nn.Module):
     """
 
     RES_OF_BLOCK = (4, 4, 2, 1, 1)  # downscale factor of each block's resolution
+    FUSED_STATE_MAX_BATCH = 64      # up to here the state path is the one-launch fused kernel (same bits either way)
 
     def __init__(self, opt):
         super().__init__()
@@ -252,7 +253,7 @@ class S2PGeneratorB200(nn.Module):
         return self._buf(name, shape, torch.bfloat16), None
 
     def _conv(self, name, x, w, b, cout, k, stride=1, act=ACT_NONE, residual=None, want_stats=False,
-              finalize=True, x2=None, wide=False):
+              finalize=True, x2=None, wide=False, split=False):
         """returns ((y, y_lo), stats) where stats is the finalized (mean, rstd) table when `finalize`,
         else the raw (partials, HW) pair consumed by ops.mat_prepare.  `residual` is a (hi, lo) pair."""
         B, hin, win, _ = x.shape
@@ -264,7 +265,7 @@ class S2PGeneratorB200(nn.Module):
         if want_stats:
             st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
         res, res_lo = residual if residual is not None else (None, None)
-        ops.conv_igemm(x, w, b, cout, k, stride, act, res, y, st, x2=x2, out_lo=y_lo, residual_lo=res_lo)
+        ops.conv_igemm(x, w, b, cout, k, stride, act, res, y, st, x2=x2, out_lo=y_lo, residual_lo=res_lo, split=split)
         if want_stats:
             if not finalize:
                 return (y, y_lo), (st, ho * wo)
@@ -274,12 +275,12 @@ class S2PGeneratorB200(nn.Module):
 
     def _enc_norm(self, name, e, mr, split):
         """LReLU(IN(e)) of the image encoder -> (feature [.., C] bf16, operand of the next main-line conv): the
-        operand is the [hi | lo | hi] layout of the split-precision conv when `split`, else the feature itself"""
+        operand is the wide [hi | lo] tensor of the split-precision conv when `split`, else the feature itself"""
         eh, el = e
         B, h, w, c = eh.shape
         if split:
-            t = self._buf(name, (B, h, w, 3 * c), torch.bfloat16)
-            ops.mat_norm(eh, mr, act=ACT_LRELU, out=t[..., :c], x_lo=el, out_lo=t[..., c:2 * c], out_dup=t[..., 2 * c:])
+            t = self._buf(name, (B, h, w, 2 * c), torch.bfloat16)
+            ops.mat_norm(eh, mr, act=ACT_LRELU, out=t[..., :c], x_lo=el, out_lo=t[..., c:])
             return t[..., :c], t
         t = self._buf(name, (B, h, w, c), torch.bfloat16)
         ops.mat_norm(eh, mr, act=ACT_LRELU, out=t, x_lo=el)
@@ -292,6 +293,10 @@ class S2PGeneratorB200(nn.Module):
         (fp32): [B, S] -> [B, 2*sum(C)] rows of (gs | bs) per MAT."""
         P, opt = self._packed, self.opt
         B = state.shape[0]
+        if B <= self.FUSED_STATE_MAX_BATCH:
+            # one persistent launch instead of 1 + 2 x 9 (batch-16 latency case); bit-identical to the chain below
+            return ops.state_encoder_fused(state, P["se"], P["heads_w"], P["heads_b"], opt.pe_freqs,
+                                           self._buf("gsbs", (B, P["heads_n"]), torch.float32))
         h = ops.pos_encode(state, opt.pe_freqs, self._buf("pe", (B, state.shape[1] * (1 + 2 * opt.pe_freqs)), torch.float32))
         for i, (w, b) in enumerate(P["se"]):
             h = ops.linear(h, w, b, ACT_LRELU, self._buf(f"se{i % 2}", (B, w.shape[0]), torch.float32))
@@ -317,9 +322,9 @@ class S2PGeneratorB200(nn.Module):
         mr = ops.in_stats_finalize(st, H * W, 1e-5, self._buf("e1.mr", (B, ngf, 2), torch.float32))
         f, fx = {}, {}
         f[1], fx[1] = self._enc_norm("f1", e1, mr, hp)
-        e2, mr = self._conv("e2", fx[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True, wide=hp)
+        e2, mr = self._conv("e2", fx[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True, wide=hp, split=hp)
         f[2], fx[2] = self._enc_norm("f2", e2, mr, hp)
-        e3, mr = self._conv("e3", fx[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True, wide=hp)
+        e3, mr = self._conv("e3", fx[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True, wide=hp, split=hp)
         f[4], fx[4] = self._enc_norm("f4", e3, mr, hp)
         # ---- merged mlp_shared convs: one wide conv per conditioning feature
         hs = {}
@@ -329,7 +334,7 @@ class S2PGeneratorB200(nn.Module):
         # ---- trunk
         fuse = self.fuse_mat
         x, mr_x = self._conv("head", fx[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True,
-                             finalize=not fuse, wide=hp)
+                             finalize=not fuse, wide=hp, split=hp)
         cur = 4
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
             up = cur // ds

@@ -76,22 +76,29 @@ def wide(t):
 
 def pack_conv_weight_split(w_oihw: torch.Tensor) -> torch.Tensor:
     """packed weight of the split-precision conv: [Cout, R*S*3*Cin] bf16 with [W_hi | W_hi | W_lo] along Cin
-    (W_hi = bf16(W), W_lo = bf16(W - W_hi)), for an operand laid out [x_hi | x_lo | x_hi]: one tensor-core pass
-    computes W_hi x_hi + W_hi x_lo + W_lo x_hi, i.e. (W x) to ~2^-16 instead of 2^-8."""
+    (W_hi = bf16(W), W_lo = bf16(W - W_hi)), for a wide operand [x_hi | x_lo] walked as [x_hi | x_lo | x_hi]
+    (conv_igemm split=True): one tensor-core pass computes W_hi x_hi + W_hi x_lo + W_lo x_hi, i.e. (W x) to
+    ~2^-16 instead of 2^-8."""
     w = w_oihw.detach().float()
     hi = w.to(torch.bfloat16).float()
     return pack_conv_weight(torch.cat([hi, hi, w - hi], dim=1))
 
 
 def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=None, out=None, stats=None, pad=None,
-               x2=None, out_lo=None, residual_lo=None):
+               x2=None, out_lo=None, residual_lo=None, split=False):
     """y = act(conv(x) + bias + residual); returns y.  ``stats`` (fp32
     [B, conv_stats_rows, Cout, 2]) receives (sum, sumsq) partials when given.  ``x2`` (NHWC bf16 of the output's
     spatial size): a second operand whose 1x1 convolution is accumulated into the same tile; ``w_packed`` is then
     [Cout, k*k*Cin + Cin2] (the two packed weights concatenated along the row).  ``out_lo`` / ``residual_lo``: low
-    halves of a wide output / residual (bf16 hi + lo pair, see include/s2p_b200.h)."""
+    halves of a wide output / residual (bf16 hi + lo pair, see include/s2p_b200.h).  ``split``: x is a wide tensor
+    [x_hi | x_lo] (2C channels) and ``w_packed`` comes from pack_conv_weight_split (split-precision convolution)."""
     _require_cuda(x, w_packed, bias, residual, out, stats, x2, out_lo, residual_lo)
     b, hin, win, cin = x.shape
+    cin_wrap = 0
+    if split:
+        if cin % 128:
+            raise RuntimeError("conv_igemm: a split operand is [hi | lo] with C % 64 == 0 channels each")
+        cin_wrap, cin = cin, cin // 2 * 3
     pad = ksize // 2 if pad is None else pad
     hout = (hin + 2 * pad - ksize) // stride + 1
     wout = (win + 2 * pad - ksize) // stride + 1
@@ -122,7 +129,7 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
             x.data_ptr(), _nhwc_pitch(x, "x"), _ptr(x2), _nhwc_pitch(x2, "x2") if x2 is not None else 0, cin2,
             w_packed.data_ptr(), _ptr(bias), _ptr(residual), _lo_of(residual, residual_lo, "residual_lo"), res_pitch,
             out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout,
-            ksize, stride, pad, act, _stream()),
+            ksize, stride, pad, act, cin_wrap, _stream()),
         "s2p_conv_igemm_fwd2")
     return out
 
@@ -177,13 +184,12 @@ def in_stats_finalize(stats: torch.Tensor, hw: int, eps: float = 1e-5, out=None)
     return out
 
 
-def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, out=None, x_lo=None, out_lo=None,
-             out_dup=None):
+def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LRELU, out=None, x_lo=None, out_lo=None):
     """y = act(((x_up - mean) * rstd) * (1 + gs + gI) + bs + bI); gs/bs are [B, C]
     fp32 views (row pitch taken from stride(0)); gb_spatial is NHWC bf16 with 2C
-    channels (gI | bI) at the OUTPUT resolution.  ``x_lo``: low halves of a wide x; ``out_lo`` / ``out_dup``: low
-    halves and a second copy of the high halves of the output (the [hi | lo | hi] split-precision conv operand)."""
-    _require_cuda(x, mean_rstd, gs, bs, gb_spatial, out, x_lo, out_lo, out_dup)
+    channels (gI | bI) at the OUTPUT resolution.  ``x_lo``: low halves of a wide x; ``out_lo``: low halves of a
+    wide output (with ``out`` the two halves of one tensor: the [hi | lo] split-precision conv operand)."""
+    _require_cuda(x, mean_rstd, gs, bs, gb_spatial, out, x_lo, out_lo)
     b, hx, wx, c = x.shape
     h, w = hx * up, wx * up
     if out is None:
@@ -205,8 +211,8 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
     _lib.check(
         _lib.load().s2p_mat_norm_fwd(
             x.data_ptr(), _lo_of(x, x_lo, "x_lo"), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs), _ptr(bs), gpitch,
-            _ptr(gb_spatial), gbp, out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _lo_of(out, out_dup, "out_dup"),
-            _nhwc_pitch(out, "out"), b, h, w, c, act, _stream()),
+            _ptr(gb_spatial), gbp, out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), b, h, w, c, act,
+            _stream()),
         "s2p_mat_norm_fwd")
     return out
 
@@ -387,6 +393,41 @@ def linear(x, w, bias, act=ACT_NONE, out=None):
 
 
 _linear_ws = {}
+_state_ws = {}
+
+
+def state_encoder_fused(state, layers, heads_w, heads_b, n_freqs, out=None):
+    """gsbs = heads(MLP(pos_encode(state))) in ONE launch (s2p_state_encoder_fwd); bit-identical to pos_encode +
+    linear chained.  layers: [(w [width, K] fp32, b [width] fp32)], heads_w [N, width], heads_b [N]."""
+    import ctypes
+    _require_cuda(state, heads_w, heads_b, out, *[t for wb in layers for t in wb])
+    b, s = state.shape
+    width, n = layers[0][0].shape[0], heads_w.shape[0]
+    if state.dtype != torch.float32 or not state.is_contiguous():
+        raise RuntimeError("state_encoder_fused: contiguous fp32 state required")
+    for w, bias in layers:
+        if w.dtype != torch.float32 or not w.is_contiguous() or w.shape[0] != width or not bias.is_contiguous():
+            raise RuntimeError("state_encoder_fused: contiguous fp32 [width, K] layer weights required")
+    if not heads_w.is_contiguous() or heads_w.shape[1] != width or heads_w.dtype != torch.float32:
+        raise RuntimeError("state_encoder_fused: heads_w must be contiguous fp32 [N, width]")
+    if out is None:
+        out = torch.empty(b, n, dtype=torch.float32, device=state.device)
+    lib = _lib.load()
+    need = int(lib.s2p_state_encoder_workspace_bytes(b, width))
+    key = (state.device, torch.cuda.current_stream().cuda_stream)    # one workspace per stream: launches on a stream are ordered
+    ws = _state_ws.get(key)
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _retired_ws.append(ws)        # a captured CUDA graph may still hold its pointer
+        ws = torch.zeros(max(need, 2 * (ws.numel() if ws is not None else 0)), dtype=torch.uint8, device=state.device)
+        _state_ws[key] = ws
+    k = len(layers)
+    wp = (ctypes.c_void_p * k)(*[w.data_ptr() for w, _ in layers])
+    bp = (ctypes.c_void_p * k)(*[bias.data_ptr() for _, bias in layers])
+    _lib.check(lib.s2p_state_encoder_fwd(state.data_ptr(), b, s, n_freqs, wp, bp, k, width, heads_w.data_ptr(), _ptr(heads_b), n,
+                                         out.data_ptr(), out.stride(0), ws.data_ptr(), ws.numel(), _stream()),
+               "s2p_state_encoder_fwd")
+    return out
 
 
 # Kernels of this library update parameters through raw pointers (fused Adam, a replayed CUDA graph of the whole

@@ -21,10 +21,11 @@ ap.add_argument("--batch", type=int, default=128)
 ap.add_argument("--warm", type=int, default=2)
 ap.add_argument("--env", type=str, default="cheetah")
 ap.add_argument("--fuse", type=int, default=1)
+ap.add_argument("--precision", type=str, default="high")
 a = ap.parse_args()
 
 torch.manual_seed(1234)
-net = s2p_b200.define_G(s2p_b200.make_options(env_type=a.env, gpu_ids="0", init_type="scaled", fuse_mat=bool(a.fuse))).eval()
+net = s2p_b200.define_G(s2p_b200.make_options(env_type=a.env, gpu_ids="0", init_type="scaled", fuse_mat=bool(a.fuse), precision=a.precision)).eval()
 net.pack()
 g = torch.Generator().manual_seed(0)
 frames = torch.randint(0, 256, (a.batch, 100, 100, 3), dtype=torch.uint8, generator=g).cuda()
