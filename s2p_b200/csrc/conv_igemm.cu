@@ -66,7 +66,7 @@ struct ConvParams {
 
 enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
 
-template <int BLOCK_N, int CL>
+template <int BLOCK_N, int CL, int EPI>
 struct ConvCfg {
   static constexpr int kBlockM = 128;
   static constexpr int kBlockK = 64;
@@ -74,12 +74,22 @@ struct ConvCfg {
   static constexpr int kBBytes = BLOCK_N / CL * kBlockK * 2;   // a CTA of a pair holds half of the weight tile
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStoreBytes = 8 * 2048;   // per-epilogue-warp 32 x 64 B transpose rows
-  static constexpr int kMaxStages = (204 * 1024) / kStageBytes;
-  static constexpr int kStages = kMaxStages > 8 ? 8 : kMaxStages;
+  static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
+  // fused MAT epilogue: the tile's pre-norm activation x, TMA-loaded as 64-channel boxes of <= 16 KB
+  // (BLOCK_N / 128 boxes of high halves + as many of low halves when x is stored wide)
+  static constexpr int kXBoxes = EPI == kEpiMat ? 2 * (BLOCK_N / 128) : 0;
+  static constexpr int kXBytes = kXBoxes * kABytes;
+  static constexpr int kFixedBytes = 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes + kXBytes;
+  static constexpr int kMaxStages = (227 * 1024 - kFixedBytes) / kStageBytes;
+  // Ring depth.  Measured (profiles/r02_stage_sweep.txt): the wide tiles do not gain from more than 4-5 stages --
+  // their operands come from L2 and 4 x 256 clk of look-ahead covers it -- while every KB of shared memory NOT
+  // claimed is L1 for the epilogue's scattered accesses (BLOCK_N = 256: 6 -> 5 stages is +7 % on the store-bound
+  // mlp_shared conv and neutral elsewhere).  The narrow tiles are operand-ingest bound and keep the deepest ring.
+  static constexpr int kWant = BLOCK_N >= 256 ? (EPI == kEpiMat ? 4 : 5) : 8;
+  static constexpr int kStages = kMaxStages > kWant ? kWant : kMaxStages;
   static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
   static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 32 / 128 / 256 / 512
-  static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kFixedBytes;
 };
 
 // transposed butterfly: on exit lane L holds sum over the warp's 32 rows of column L
@@ -151,17 +161,20 @@ __global__ void __launch_bounds__(320, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_a2, const __grid_constant__ CUtensorMap tmap_x,
                   const ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N, CL>;
+  using Cfg = ConvCfg<BLOCK_N, CL, EPI>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  // [operand ring | x boxes (1024-aligned: the ring is a multiple of 8 KB) | barriers | modulation table | store staging]
+  uint8_t* x_smem = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(x_smem + Cfg::kXBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + Cfg::kStages;
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float4* tab_smem = reinterpret_cast<float4*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
-  uint8_t* store_smem = smem + Cfg::kStages * Cfg::kStageBytes + 256 + Cfg::kTabBytes;
+  uint64_t* x_full = tmem_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_full + 1);
+  float4* tab_smem = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(bars) + 256);
+  uint8_t* store_smem = reinterpret_cast<uint8_t*>(bars) + 256 + Cfg::kTabBytes;
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -179,6 +192,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 8 * CL);   // the leader's MMA thread waits for both CTAs' 8 epilogue warps
     }
+    mbar_init(x_full, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -207,11 +221,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int num_kb = num_kb_main + p.kb2;      // the second operand's k-blocks follow the filter taps
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
-  // fused MAT epilogue: after a tile's k-blocks the ring carries the tile's x boxes (not MMA operands: the MMA warp
-  // skips those slots, the epilogue warps read and release them).  A slot holds kXBoxPerSlot boxes of <= 16 KB.
-  constexpr int kXBoxPerSlot = (Cfg::kBBytes >= Cfg::kABytes) ? 2 : 1;
-  const int x_boxes = (EPI == kEpiMat) ? (BLOCK_N / 128) * (p.x_wide ? 2 : 1) : 0;
-  const int x_slots = (x_boxes + kXBoxPerSlot - 1) / kXBoxPerSlot;
 
   // The producer and MMA loops run with the whole warp converged (uniform control flow, uniform
   // operands) and elect one lane only around the asynchronous issue itself: a loop written under
@@ -237,9 +246,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if constexpr (CL > 1) {
             constexpr int kPart = BLOCK_N / CL;
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-            // (the peer's own full barrier is only ever waited on for x slots: a plain arrival keeps its
-            // phase in step with the ring -- one completed phase per pass over the slot)
-            else if constexpr (EPI == kEpiMat) mbar_arrive(&full_bar[stage]);
             const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
             if (kb < num_kb_main) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, win0 + sx, hin0 + r, img);
             else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
@@ -254,28 +260,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         __syncwarp();
         if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-      }
-      if constexpr (EPI == kEpiMat) {
-        // this tile's x pixels (at half resolution when the block upsamples), CTA-local: each CTA of a pair loads
-        // the rows of its own m-tile and is signalled on its own barrier
-        constexpr int CT = BLOCK_N / 2;
-        const int xw0 = p.mat_up == 2 ? (w0 >> 1) : w0, xh0 = p.mat_up == 2 ? (h0 >> 1) : h0;
-        for (int b0 = 0; b0 < x_boxes; b0 += kXBoxPerSlot) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (elect_one()) {
-            const int nb = (x_boxes - b0) < kXBoxPerSlot ? (x_boxes - b0) : kXBoxPerSlot;
-            uint8_t* sa = smem + stage * Cfg::kStageBytes;
-            mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * p.x_box_bytes);
-            for (int j = 0; j < nb; ++j) {
-              const int bidx = b0 + j;
-              const int jbox = p.x_wide ? (bidx >> 1) : bidx, lo = p.x_wide ? (bidx & 1) : 0;
-              tma_load_4d(sa + j * Cfg::kABytes, &tmap_x, &full_bar[stage], lo * p.mat_C + n_tile * CT + jbox * 64, xw0, xh0,
-                          img);
-            }
-          }
-          __syncwarp();
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-        }
       }
     }
   } else if (warp == 1) {
@@ -316,8 +300,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        for (int xs = 0; xs < x_slots; ++xs)      // the tile's x slots are not MMA operands
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp >= 2) {
@@ -372,28 +354,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const StoreRows<2> rows2 = store_rows_prepare<2>(static_cast<uint32_t>(pix), valid, lane);
         float4* tab_s = tab_smem + acc * 128;
         if (et < CT && live) tab_s[et] = __ldg(p.mat_tab + static_cast<size_t>(img) * p.mat_C + ch0 + et);
-        // x: row of this thread's pixel inside the tile's x boxes (128-byte rows of 64 channels, 128B-swizzled by TMA)
+        // x: the tile's pixels arrive as 64-channel boxes (128-byte rows, 128B-swizzled) TMA-loaded by this group
+        // itself: once all eight warps are past the previous tile (the bar.sync below) its buffer is free, and the
+        // load of THIS tile's boxes flies while the tile's MMAs finish.  Per-thread global loads of x (one 128-byte
+        // line per pixel row, 32 lines per warp instruction) kept the SM's single L1 wavefront queue busy for ~90 %
+        // of a tile's MMA time (profiles/r02_history.md).
         const bool wide_x = p.x_wide != 0;
         const int tw0 = (t % p.tiles_x) * p.tile_w, th0 = (t / p.tiles_x) * p.tile_h;
         const int rx = p.mat_up == 2 ? (((th0 + my) >> 1) - (th0 >> 1)) * p.x_bw + (((tw0 + mx) >> 1) - (tw0 >> 1)) : m;
-        const uint32_t g0 = static_cast<uint32_t>(it) * static_cast<uint32_t>(num_kb + x_slots) + num_kb;   // ring position of the first x slot
         const int jbox = cw / 64;                          // 64-channel box of this warp's channels
         const int bidx = wide_x ? 2 * jbox : jbox;         // its (high-half) box; the low halves are the next box
-        const uint32_t gx = g0 + bidx / kXBoxPerSlot, gxl = g0 + (bidx + 1) / kXBoxPerSlot;
-        const uint32_t xs_hi = smem_u32(smem) + (gx % Cfg::kStages) * Cfg::kStageBytes + (bidx % kXBoxPerSlot) * Cfg::kABytes +
-                               static_cast<uint32_t>(rx) * 128u;
-        const uint32_t xs_lo = smem_u32(smem) + (gxl % Cfg::kStages) * Cfg::kStageBytes +
-                               ((bidx + 1) % kXBoxPerSlot) * Cfg::kABytes + static_cast<uint32_t>(rx) * 128u;
+        const uint32_t xs_hi = smem_u32(x_smem) + bidx * Cfg::kABytes + static_cast<uint32_t>(rx) * 128u;
+        const uint32_t xs_lo = xs_hi + Cfg::kABytes;
         const uint32_t xkey = static_cast<uint32_t>(rx) & 7u;
         const uint32_t xc0 = static_cast<uint32_t>(cw % 64) / 8u;   // first 16-byte chunk of this warp's channels in the box
         asm volatile("bar.sync 1, 256;" ::: "memory");   // table rows visible to the 8 epilogue warps; previous tile fully read
-        if (it > 0 && et == 0) {
-          // every epilogue warp is past the previous tile: hand its x slots back to the producer
-          const uint32_t gp = g0 - static_cast<uint32_t>(num_kb + x_slots);
-          for (int xs = 0; xs < x_slots; ++xs) mbar_arrive(&empty_bar[(gp + xs) % Cfg::kStages]);
+        if (et == 0) {
+          const int nbox = (BLOCK_N / 128) * (wide_x ? 2 : 1);
+          const int xw0 = p.mat_up == 2 ? (tw0 >> 1) : tw0, xh0 = p.mat_up == 2 ? (th0 >> 1) : th0;
+          mbar_arrive_expect_tx(x_full, static_cast<uint32_t>(nbox) * p.x_box_bytes);
+          for (int j = 0; j < nbox; ++j) {
+            const int jb = wide_x ? (j >> 1) : j, lo = wide_x ? (j & 1) : 0;
+            tma_load_4d(x_smem + j * Cfg::kABytes, &tmap_x, x_full, lo * p.mat_C + ch0 + jb * 64, xw0, xh0, img);
+          }
         }
-        mbar_wait(&full_bar[gx % Cfg::kStages], (gx / Cfg::kStages) & 1);
-        if (wide_x) mbar_wait(&full_bar[gxl % Cfg::kStages], (gxl / Cfg::kStages) & 1);
+        mbar_wait(x_full, static_cast<uint32_t>(it) & 1u);
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
         uint32_t rg[16], rb[16];
@@ -643,7 +628,7 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
 template <int BLOCK_N, int EPI, int CL>
 static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const CUtensorMap& tx,
                           const ConvParams& p, cudaStream_t st) {
-  using Cfg = ConvCfg<BLOCK_N, CL>;
+  using Cfg = ConvCfg<BLOCK_N, CL, EPI>;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   const int dev = current_device();
   if (!configured[dev]) {

@@ -145,8 +145,15 @@ class S2PGeneratorB200(nn.Module):
         self.precision = str(getattr(opt, "precision", "high"))
         if self.precision not in ("high", "standard"):
             raise ValueError(f"precision must be 'high' or 'standard', got {self.precision}")
+        # CUDA-graphed inference for small batches (the batch-16 latency case of BASELINE configs[0]/[1]: ~55 launches
+        # of host overhead per call otherwise): one captured graph per (input shape, dtype, outputs), replayed on
+        # static buffers.  Bulk batches (> graph_max_batch rows) keep the eager launch sequence: they are GPU-bound.
+        self.cuda_graph = bool(getattr(opt, "cuda_graph", True))
+        self.graph_max_batch = int(getattr(opt, "graph_max_batch", 32))
         self._packed = None
         self._ws = {}
+        self._graphs = {}
+        self._graph_stream = None
 
     # ------------------------------------------------------------------ packing
     def blocks(self):
@@ -161,6 +168,7 @@ class S2PGeneratorB200(nn.Module):
         self._packed = None
         self._plist = None
         self._ws = {}
+        self._graphs = {}
         return super()._apply(fn, *a, **k)
 
     def _pack_key(self):
@@ -229,6 +237,7 @@ class S2PGeneratorB200(nn.Module):
             P["blk"].append(d)
         self._packed = P
         self._packed_key = self._pack_key()
+        self._graphs = {}          # captured graphs hold pointers into the previous packed weights
         return self
 
     # ------------------------------------------------------------------ workspace
@@ -239,6 +248,8 @@ class S2PGeneratorB200(nn.Module):
         key = (name, tuple(shape[1:]), dtype)
         t = self._ws.get(key)
         if t is None or t.shape[0] < shape[0]:
+            if t is not None:
+                self._graphs = {}  # captured graphs hold the outgrown buffer's address: recapture on the new one
             t = torch.empty(shape, dtype=dtype, device=self.head.weight.device)
             self._ws[key] = t
         return t[:shape[0]]
@@ -399,13 +410,61 @@ class S2PGeneratorB200(nn.Module):
         out_u8 = torch.empty(B, H, W, 3, dtype=torch.uint8, device=image.device) if want_u8 else None
         if B == 0:                       # empty batch: nothing to launch (nn.Module semantics of the oracle)
             return out_f32, out_u8
+        if self.cuda_graph and B <= self.graph_max_batch and not torch.cuda.is_current_stream_capturing():
+            return self._run_graphed(image, state, out_f32, out_u8)
+        self._launch_all(image, state, out_f32, out_u8)
+        return out_f32, out_u8
+
+    def _launch_all(self, image, state, out_f32, out_u8):
+        """the eager launch sequence of one call: state path once, then the micro-batches"""
+        B = state.shape[0]
         mb = self.max_microbatch
         gsbs = self._state_path(state)
         for s in range(0, B, mb):
             e = min(B, s + mb)
             self._forward_mb(image[s:e], gsbs[s:e], None if out_f32 is None else out_f32[s:e],
                              None if out_u8 is None else out_u8[s:e])
+
+    def _run_graphed(self, image, state, out_f32, out_u8):
+        """replay the captured launch sequence of this (shape, dtype, outputs) on static buffers; same kernels, same
+        bytes as the eager path (tests/test_generator_gpu.py::test_cuda_graph_forward_is_bit_identical)"""
+        key = (tuple(image.shape), image.dtype, out_f32 is not None, out_u8 is not None, self.max_microbatch, self.fuse_mat)
+        ent = self._graphs.get(key)
+        if ent is None:
+            ent = self._capture(key, image, state, out_f32, out_u8)
+        ent["image"].copy_(image)
+        ent["state"].copy_(state)
+        ent["graph"].replay()
+        if out_f32 is not None:
+            out_f32.copy_(ent["out_f32"])
+        if out_u8 is not None:
+            out_u8.copy_(ent["out_u8"])
         return out_f32, out_u8
+
+    def _capture(self, key, image, state, out_f32, out_u8):
+        cur = torch.cuda.current_stream(image.device)
+        if self._graph_stream is None:
+            self._graph_stream = torch.cuda.Stream(image.device)
+        s = self._graph_stream
+        ent = dict(image=torch.empty_like(image), state=torch.empty_like(state),
+                   out_f32=None if out_f32 is None else torch.empty_like(out_f32),
+                   out_u8=None if out_u8 is None else torch.empty_like(out_u8))
+        ent["image"].copy_(image)
+        ent["state"].copy_(state)
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):
+            # eager warm-up ON the capture stream: workspace allocation (which may invalidate older graphs),
+            # per-device kernel attributes and per-stream scratch all happen here, not inside the capture
+            for _ in range(2):
+                self._launch_all(ent["image"], ent["state"], ent["out_f32"], ent["out_u8"])
+        s.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            self._launch_all(ent["image"], ent["state"], ent["out_f32"], ent["out_u8"])
+        cur.wait_stream(s)
+        ent["graph"] = graph
+        self._graphs[key] = ent
+        return ent
 
     def forward(self, image, state):
         # train.py semantics: a module in train() mode under grad mode returns a differentiable

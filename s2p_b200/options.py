@@ -29,6 +29,9 @@ def make_options(argv=None, **overrides):
     # "high": wide (bf16 hi + lo) residual stream / pre-norm maps and split-precision encoder convs, PSNR >= 50 dB
     # vs the fp32 oracle; "standard": single-bf16 storage everywhere (round-1 schedule, ~48.6 dB), for A/B timing
     p.add_argument("--precision", type=str, default="high", choices=["high", "standard"])
+    # inference calls of up to graph_max_batch rows replay a captured CUDA graph (0 = never)
+    p.add_argument("--cuda_graph", type=int, default=1)
+    p.add_argument("--graph_max_batch", type=int, default=32)
     opt, _ = p.parse_known_args(argv if argv is not None else [])
     for k, v in overrides.items():
         setattr(opt, k, v)

@@ -229,6 +229,7 @@ def test_workspace_does_not_grow_with_distinct_batch_sizes(pkg):
     """variable-size serving: after the largest batch has been seen, smaller batches reuse its workspace (leading
     slices) and give the same bytes as when run first on a fresh module"""
     ora, net = _pair(pkg, "cheetah", "scaled")
+    net.cuda_graph = False      # this test is about the eager path's workspace (a captured graph adds static I/O buffers per size)
     image, states = common.make_inputs("cheetah", 5, 1)
     image, st = image.cuda(), states[:, 0].cuda()
     full = net(image, st)
@@ -241,4 +242,49 @@ def test_workspace_does_not_grow_with_distinct_batch_sizes(pkg):
     assert torch.cuda.memory_allocated() <= mem + 8 * 3 * 100 * 100 * 4 + (1 << 20)
     assert torch.equal(outs[0], full[:3])
     _, fresh = _pair(pkg, "cheetah", "scaled")
-    assert torch.equal(fresh(image[:3], st[:3]), outs[0])
+    assert torch.equal(fresh(image[:3], st[:3]), outs[0])      # (fresh replays a captured graph: same bytes)
+
+
+def test_cuda_graph_forward_is_bit_identical(pkg):
+    """small batches replay a captured CUDA graph of the launch sequence (state path = ONE fused launch): same bytes
+    as the eager launches, across changing inputs, both entry points, a buffer-growing bulk call in between and a
+    weight reload (which must invalidate the captured graphs)"""
+    from s2p_b200 import _lib
+    ora, net = _pair(pkg, "cheetah", "scaled")
+    eager = pkg.define_G(pkg.make_options(env_type="cheetah", gpu_ids="0", cuda_graph=0))
+    eager.load_state_dict(ora.state_dict())
+    eager.eval()
+    assert net.cuda_graph and not eager.cuda_graph
+    for b in (2, 16):
+        for seed in (5, 6):
+            image, states = common.make_inputs("cheetah", b, 1, seed_img=seed, seed_state=seed + 10)
+            image, st = image.cuda(), states[:, 0].cuda()
+            assert torch.equal(net(image, st), eager(image, st))
+        g = torch.Generator().manual_seed(b)
+        frames = torch.randint(0, 256, (b, 100, 100, 3), dtype=torch.uint8, generator=g).cuda()
+        assert torch.equal(net.forward_u8(frames, st), eager.forward_u8(frames, st))
+    # (growing the workspace from batch 2 to batch 16 dropped the batch-2 graphs: they pointed into the old buffers)
+    assert len(net._graphs) == 2 and len(eager._graphs) == 0
+    l0 = _lib.launch_count()
+    out = net(image, st)                       # a replay launches nothing through the library's host path
+    assert _lib.launch_count() == l0
+    l0 = _lib.launch_count()
+    ref = eager(image, st)
+    n_eager = _lib.launch_count() - l0
+    print(f"eager launches per batch-16 forward: {n_eager} (state path: 1)")
+    assert n_eager <= 56
+    assert torch.equal(out, ref)
+    # a bulk call grows the workspace: the captured graphs are dropped and recaptured on the new buffers
+    big = torch.randint(0, 256, (40, 100, 100, 3), dtype=torch.uint8).cuda()
+    net.forward_u8(big, torch.randn(40, 17).cuda())
+    assert len(net._graphs) == 0
+    assert torch.equal(net(image, st), ref)
+    # new weights -> re-pack -> graphs invalidated
+    ora2 = common.build_oracle("cheetah", "scaled", seed=99)
+    net.load_state_dict(ora2.state_dict())
+    eager.load_state_dict(ora2.state_dict())
+    out2 = net(image, st)
+    assert torch.equal(out2, eager(image, st)) and not torch.equal(out2, ref)
+    # rollout goes through the same graph every step
+    _, states5 = common.make_inputs("cheetah", 2, 5)
+    assert torch.equal(net.rollout(image[:2], states5.cuda()), eager.rollout(image[:2], states5.cuda()))
