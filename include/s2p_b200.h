@@ -72,11 +72,15 @@ int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const f
  * tensor) and is walked as Cin = 3*C logical channels [x_hi | x_lo | x_hi] (channels >= cin_wrap re-read the tensor
  * from channel 0) against weights packed [W_hi | W_hi | W_lo] along Cin: one tensor-core pass computes the three
  * significant products of (W_hi + W_lo)(x_hi + x_lo), i.e. the convolution to ~2^-16 instead of 2^-8.  Used for the
- * image encoder's main-line convs (2 % of the generator's flops, upstream of every modulation). */
+ * image encoder's main-line convs when their weights do not fit fp16 (see operands_f16).
+ * operands_f16 != 0: x (and x2) and w_packed hold fp16, not bf16 (s2p_pack_conv_weight f16 = 1): the same tcgen05
+ * kind::f16 rate with an 11-bit significand.  For operands whose range is bounded by construction -- the
+ * instance-normalised feature maps of the image encoder (|v| <= sqrt(H*W)), which feed conv2 / conv3 / head and
+ * every MAT's mlp_shared: 13 % of the flops, upstream of every modulation. */
 int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2, const void* w_packed,
                         const float* bias, const void* residual, const void* residual_lo, int res_pitch, void* y,
                         void* y_lo, int y_pitch, float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
-                        int ksize, int stride, int pad, int act, int cin_wrap, void* stream);
+                        int ksize, int stride, int pad, int act, int cin_wrap, int operands_f16, void* stream);
 
 /* ---- (a8) weight gradient of the convolution (training) -----------------------------
  * dW[co,ci,r,s] (+)= sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho*stride-pad+r, wo*stride-pad+s, ci]
@@ -91,10 +95,10 @@ int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, flo
                    long long workspace_bytes, int B, int Hin, int Win, int Cin, int Cout, int ksize,
                    int stride, int pad, int accumulate, void* stream);
 
-/* OIHW fp32 -> [Cout][R][S][Cin] bf16 rows, each weight multiplied by `scale`
+/* OIHW fp32 -> [Cout][R][S][Cin] bf16 (f16 = 0) or fp16 (f16 = 1) rows, each weight multiplied by `scale`
  * (used to fold the MAT blend factors at load time). */
 int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S,
-                         float scale, void* stream);
+                         float scale, int f16, void* stream);
 
 /* ---- (a3) param-free instance norm + MAT modulation + LeakyReLU, one fused pass ---
  * replaces F.instance_norm + the gamma/beta arithmetic of oracle MAT.forward + the
@@ -103,12 +107,13 @@ int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int 
  * gb_spatial holds gI in channels [0,C) and bI in [C,2C) of each pixel; gs/bs/gb_spatial
  * may be NULL (plain IN + act, oracle ImageEncoder).  C % 8 == 0.
  * x_lo: low halves of a wide x.  y_lo: the output is stored wide (with y and y_lo the two channel halves of one
- * tensor it is the [hi | lo] operand of the split-precision convolution, s2p_conv_igemm_fwd2 cin_wrap). */
+ * tensor it is the [hi | lo] operand of the split-precision convolution, s2p_conv_igemm_fwd2 cin_wrap).
+ * y_f16 != 0: y is stored as fp16 (the operand of an operands_f16 convolution; no y_lo then). */
 int s2p_in_stats_finalize(const float* stats_partial, int rows, float* mean_rstd, int B, int C,
                           int HW, float eps, void* stream);
 int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd, const float* gs,
                      const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch, void* y, void* y_lo,
-                     int y_pitch, int B, int H, int W, int C, int act, void* stream);
+                     int y_pitch, int B, int H, int W, int C, int act, int y_f16, void* stream);
 
 /* ---- (a3 fused into a4) gamma/beta conv with the MAT norm applied in its epilogue ----
  * replaces, in ONE kernel, oracle MAT.mlp_gamma + MAT.mlp_beta (nn.Conv2d 3x3) and the

@@ -24,12 +24,12 @@ SIGNATURES = {
     "s2p_launch_count": (C.c_longlong, []),
     "s2p_conv_stats_rows": (_i, [_i, _i]),
     "s2p_conv_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
-    "s2p_conv_igemm_fwd2": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2p_conv_igemm_fwd2": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_conv_wgrad_workspace_bytes": (C.c_longlong, [_i, _i, _i, _i, _i, _i, _i, _i]),
     "s2p_conv_wgrad": (_i, [_vp, _i, _vp, _i, _vp, _vp, C.c_longlong, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
-    "s2p_pack_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp]),
+    "s2p_pack_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _i, _vp]),
     "s2p_in_stats_finalize": (_i, [_vp, _i, _vp, _i, _i, _i, _f, _vp]),
-    "s2p_mat_norm_fwd": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2p_mat_norm_fwd": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_mat_fused_ct": (_i, [_i]),
     "s2p_mat_prepare": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _f, _vp]),
     "s2p_conv_mat_fused_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

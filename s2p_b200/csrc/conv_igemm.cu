@@ -55,6 +55,7 @@ struct ConvParams {
   int x_bw;                     // pixels per row of an x box
   uint32_t x_box_bytes;         // bytes of one x box (x_bw * rows * 128)
   int cin_wrap;                 // A-operand channels >= cin_wrap re-read the tensor from channel 0 ([hi | lo] as [hi | lo | hi])
+  int op_f16;                   // the activation and weight operands are fp16 (not bf16)
   // ToRGB epilogue (BLOCK_N = 16, 3 live columns): tanh(acc + bias) -> fp32 NCHW and/or uint8 NHWC
   float* rgb_f32;
   uint8_t* rgb_u8;
@@ -265,7 +266,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (pair leader only)
     if (cta_rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128 * CL, BLOCK_N);
+      const uint32_t idesc = p.op_f16 ? umma_idesc_f16(128 * CL, BLOCK_N) : umma_idesc_bf16(128 * CL, BLOCK_N);
       const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
       int stage = 0;
       uint32_t phase = 0;
@@ -314,12 +315,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int m = q * 32 + lane;      // accumulator row = pixel inside the tile
     const int my = m / p.tile_w, mx = m - my * p.tile_w;
     const float* bias_s = p.bias;
+    bool bias_staged = false;
     if constexpr (EPI == kEpiPlain) {
       // bias vector staged in shared memory once per CTA (broadcast LDS instead of global loads)
       if (p.bias != nullptr && p.Cout <= 1024) {
         float* bs = reinterpret_cast<float*>(tab_smem);
         for (int i = et; i < p.Cout; i += 256) bs[i] = __ldg(p.bias + i);
         bias_s = bs;
+        bias_staged = true;
         asm volatile("bar.sync 1, 256;" ::: "memory");
       }
     }
@@ -378,9 +381,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             tma_load_4d(x_smem + j * Cfg::kABytes, &tmap_x, x_full, lo * p.mat_C + ch0 + jb * 64, xw0, xh0, img);
           }
         }
-        mbar_wait(x_full, static_cast<uint32_t>(it) & 1u);
-        mbar_wait(&tmem_full[acc], acc_phase);
+        mbar_wait_relaxed(x_full, static_cast<uint32_t>(it) & 1u);
+        mbar_wait_relaxed(&tmem_full[acc], acc_phase);
         tc_fence_after();
+        const uint32_t tab_a = smem_u32(tab_s + cw);   // explicit ld.shared: a generic load of the table costs two wavefronts
         uint32_t rg[16], rb[16];
         tmem_ld16(t_row + cw, rg);
         tmem_ld16(t_row + CT + cw, rb);
@@ -414,7 +418,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
               for (int hlf = 0; hlf < 2; ++hlf) {
                 const int k = 2 * e + hlf;
-                const float4 tb = tab_s[cw + sidx * 16 + k];
+                const float4 tb = lds128f(tab_a + static_cast<uint32_t>(sidx * 16 + k) * 16u);
                 float xv = hlf ? bf16_hi(xw[e]) : bf16_lo(xw[e]);
                 if (wide_x) xv += hlf ? bf16_hi(xlw[e]) : bf16_lo(xlw[e]);
                 const float xh = fmaf(xv, tb.x, tb.y);
@@ -431,7 +435,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           warp_store_rows<2>(stg_s, ow_out, p.out + ch0 + cw + sidx * 16, p.out_pitch, rows2, lane);
         }
       } else if constexpr (EPI == kEpiToRGB) {
-        mbar_wait(&tmem_full[acc], acc_phase);
+        mbar_wait_relaxed(&tmem_full[acc], acc_phase);
         tc_fence_after();
         if (half == 0) {
           uint32_t r16[16];
@@ -471,7 +475,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + j);
         }
-        mbar_wait(&tmem_full[acc], acc_phase);
+        mbar_wait_relaxed(&tmem_full[acc], acc_phase);
         tc_fence_after();
         uint32_t raw[32];
         tmem_ld32(t_row + cbeg * 32, raw);
@@ -480,10 +484,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const int c = cbeg + i;
           // the chunk's bias values leave shared memory before the accumulator wait, not after it
           float4 bb[8];
-          if (bias_s != nullptr) {
+          if (bias_staged) {       // explicit ld.shared (a generic load of a shared address costs two wavefronts)
+            const uint32_t b_a = smem_u32(bias_s + n0 + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bb[j] = lds128f(b_a + 16u * j);
+          } else if (bias_s != nullptr) {
             const float4* b4 = reinterpret_cast<const float4*>(bias_s + n0 + c * 32);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) bb[j] = b4[j];
+            for (int j = 0; j < 8; ++j) bb[j] = __ldg(b4 + j);
           }
           tmem_ld_wait();
           float v[32];
@@ -785,14 +793,14 @@ extern "C" int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_pack
                                   float* stats_partial, int B, int Hin, int Win, int Cin, int Cout,
                                   int ksize, int stride, int pad, int act, void* stream) {
   return s2p_conv_igemm_fwd2(x, x_pitch, nullptr, 0, 0, w_packed, bias, residual, nullptr, res_pitch, y, nullptr, y_pitch,
-                             stats_partial, B, Hin, Win, Cin, Cout, ksize, stride, pad, act, 0, stream);
+                             stats_partial, B, Hin, Win, Cin, Cout, ksize, stride, pad, act, 0, 0, stream);
 }
 
 extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, int x2_pitch, int Cin2,
                                    const void* w_packed, const float* bias, const void* residual,
                                    const void* residual_lo, int res_pitch, void* y, void* y_lo, int y_pitch,
                                    float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,
-                                   int stride, int pad, int act, int cin_wrap, void* stream) {
+                                   int stride, int pad, int act, int cin_wrap, int operands_f16, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && w_packed && y, "conv: null pointer");
   S2P_CHECK_ARG(cin_wrap == 0 || (cin_wrap > 0 && cin_wrap % 64 == 0 && cin_wrap < Cin && Cin <= 2 * cin_wrap),
@@ -826,6 +834,7 @@ extern "C" int s2p_conv_igemm_fwd2(const void* x, int x_pitch, const void* x2, i
   p.out_lo = static_cast<__nv_bfloat16*>(y_lo);
   p.stats_partial = stats_partial;
   p.cin_wrap = cin_wrap;
+  p.op_f16 = operands_f16 != 0;
   const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
   return conv_dispatch(x, x_pitch, w_packed, B, Hin, Win, Cin, Cout, ksize, stride, pad, block_n, kEpiPlain, p, stream,
                        x2, x2_pitch, Cin2);

@@ -86,6 +86,7 @@ struct NormParams {
   const __nv_bfloat16* x;
   const __nv_bfloat16* x_lo;   // low halves of a wide (bf16 hi + lo pair) input, same pitch; or null
   __nv_bfloat16* y_lo;         // low halves of a wide output (same pitch as y) or null
+  int y_f16;                   // y is stored as fp16 (an instance-normalised operand of an fp16 tensor-core conv)
   const float2* mean_rstd;   // [B][C]
   const float* gs;           // [B][gsbs_pitch] or null
   const float* bs;
@@ -186,8 +187,10 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
           else if (p.act == 1) v = fmaxf(v, 0.f);
           o[j] = v;
         }
-        uint4 ov = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
-                              pack_bf16x2(o[6], o[7]));
+        uint4 ov = p.y_f16 ? make_uint4(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3]), pack_f16x2(o[4], o[5]),
+                                        pack_f16x2(o[6], o[7]))
+                           : make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                                        pack_bf16x2(o[6], o[7]));
         st_stream(p.y + (img_pix + pix) * p.y_pitch + c0, ov);
         if (p.y_lo != nullptr) {
           const uint4 lv = make_uint4(pack_bf16x2(o[0] - bf16_lo(ov.x), o[1] - bf16_hi(ov.x)),
@@ -236,7 +239,8 @@ extern "C" int s2p_mat_prepare(const float* stats_partial, int rows, const float
 
 extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, int up, const float* mean_rstd,
                                 const float* gs, const float* bs, int gsbs_pitch, const void* gb_spatial, int gb_pitch,
-                                void* y, void* y_lo, int y_pitch, int B, int H, int W, int C, int act, void* stream) {
+                                void* y, void* y_lo, int y_pitch, int B, int H, int W, int C, int act, int y_f16,
+                                void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(x && mean_rstd && y, "mat_norm: null pointer");
   S2P_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && C <= 2048, "mat_norm: bad dims C=%d", C);
@@ -245,6 +249,7 @@ extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, in
   S2P_CHECK_ARG(!gb_spatial || (gb_pitch >= 2 * C && gb_pitch % 8 == 0), "mat_norm: gb_pitch=%d", gb_pitch);
   S2P_CHECK_ARG((gs == nullptr) == (bs == nullptr), "mat_norm: gs and bs must both be given or both null");
   S2P_CHECK_ARG(act >= 0 && act <= 2, "mat_norm: act=%d", act);
+  S2P_CHECK_ARG(!(y_f16 && y_lo), "mat_norm: an fp16 output has no low halves");
   S2P_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(x_lo) |
                   reinterpret_cast<uintptr_t>(y_lo) |
                   reinterpret_cast<uintptr_t>(gb_spatial)) & 15) == 0, "mat_norm: 16-byte alignment");
@@ -252,6 +257,7 @@ extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, in
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.x_lo = static_cast<const __nv_bfloat16*>(x_lo);
   p.y_lo = static_cast<__nv_bfloat16*>(y_lo);
+  p.y_f16 = y_f16 != 0;
   p.mean_rstd = reinterpret_cast<const float2*>(mean_rstd);
   p.gs = gs; p.bs = bs;
   p.gb = static_cast<const __nv_bfloat16*>(gb_spatial);

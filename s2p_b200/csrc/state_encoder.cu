@@ -4,6 +4,8 @@
 // host module).  Tiny next to the convs (0.006 GMAC of 56.4 per frame), so plain
 // fp32 CUDA-core SGEMM keeps the state path exact; latency at small batch is hidden
 // by capturing the whole forward in a CUDA graph.
+#include <cuda_fp16.h>
+
 #include "ptx.cuh"
 #include "s2p_internal.h"
 
@@ -294,7 +296,7 @@ constexpr size_t kSmemBytes = (2 * 16 * kPitch + 4 * 16 * 16) * sizeof(float);
 
 // OIHW fp32 -> [Cout][R][S][Cin] bf16
 __global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int Cout,
-                                        int Cin, int R, int S, float scale) {
+                                        int Cin, int R, int S, float scale, int f16) {
   const long long total = static_cast<long long>(Cout) * Cin * R * S;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -303,7 +305,9 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, __nv_bfloat
     const int s = static_cast<int>(t % S); t /= S;
     const int r = static_cast<int>(t % R);
     const int co = static_cast<int>(t / R);
-    dst[i] = __float2bfloat16_rn(w[((static_cast<long long>(co) * Cin + ci) * R + r) * S + s] * scale);
+    const float v = w[((static_cast<long long>(co) * Cin + ci) * R + r) * S + s] * scale;
+    if (f16) reinterpret_cast<__half*>(dst)[i] = __float2half_rn(v);
+    else dst[i] = __float2bfloat16_rn(v);
   }
 }
 
@@ -386,13 +390,13 @@ extern "C" int s2p_linear_fwd(const float* x, int x_pitch, const float* w, const
 }
 
 extern "C" int s2p_pack_conv_weight(const float* w_oihw, void* dst, int Cout, int Cin, int R, int S, float scale,
-                                    void* stream) {
+                                    int f16, void* stream) {
   using namespace s2p;
   S2P_CHECK_ARG(w_oihw && dst && Cout > 0 && Cin > 0 && R > 0 && S > 0, "pack_conv_weight: bad args");
   const long long total = static_cast<long long>(Cout) * Cin * R * S;
   const int blocks = static_cast<int>((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
   pack_conv_weight_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      w_oihw, static_cast<__nv_bfloat16*>(dst), Cout, Cin, R, S, scale);
+      w_oihw, static_cast<__nv_bfloat16*>(dst), Cout, Cin, R, S, scale, f16);
   count_launch();
   return check_launch("pack_conv_weight_kernel");
 }

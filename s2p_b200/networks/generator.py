@@ -14,14 +14,19 @@ blend factors sigmoid(blend_*) are folded into the packed gamma/beta conv weight
 and into the batched state-head linear at pack time, and the 3x3 ``mlp_shared``
 convs of all MATs that read the same encoder feature are merged into one wide conv.
 
-Precision (``opt.precision``, default "high"; tools/precision_attribution.py is the error budget behind it):
-every tensor-core operand is bf16, but the tensors that only an instance norm or a residual add reads -- the
-encoder's pre-norm maps e1..e3, the residual stream x and the block-internal dx -- are stored as bf16 hi + lo
-PAIRS (~16 mantissa bits), and the three convs of the image encoder's main line (conv2, conv3, head: 2 % of the
-flops, upstream of every modulation) run split-precision: the wide operand [hi | lo] walked as [hi | lo | hi]
-against weights [W_hi | W_hi | W_lo], i.e. the three significant products of (W_hi + W_lo)(x_hi + x_lo) in one tensor-core
-pass.  That is what holds PSNR >= 50 dB against the fp32 oracle on O(1)-activation weights (BASELINE.json
-north_star); "standard" is the plain single-bf16 schedule of round 1 (48.6 dB), kept for A/B timing.
+Precision (``opt.precision``, default "high"; tools/precision_attribution.py is the error budget behind it).  More
+than half of the round-1 error came from the image encoder's main line (2 % of the flops, upstream of every
+modulation) and a fifth from single-bf16 storage of tensors that are never tensor-core operands.  So:
+  * the tensors that only an instance norm or a residual add reads -- the encoder's pre-norm maps e1..e3, the
+    residual stream x and the block-internal dx -- are stored as bf16 hi + lo PAIRS (~16 mantissa bits);
+  * the encoder's instance-normalised feature maps f100 / f50 / f25 (|v| <= sqrt(H*W) by construction) are stored
+    as fp16 and every conv that reads them (conv2, conv3, head, all mlp_shared: 13 % of the flops) runs with
+    fp16 operands: the same tcgen05 kind::f16 rate, 11-bit significand instead of 8.  Weights that do not fit fp16
+    fall back to the bf16 split-precision conv ([hi | lo] x [W_hi | W_hi | W_lo], three products in one pass);
+  * everything else (the trunk's operands t / ts / hs and their weights, unbounded in range) stays bf16.
+That holds PSNR >= 50 dB against the fp32 oracle on O(1)-activation weights (BASELINE.json north_star: measured
+53.7 / 52.2 / 60 dB on the cheetah / walker 'scaled' and the 'trained_like' golden cases) for +2 % of step time;
+"standard" is the plain single-bf16 schedule of round 1 (48.6 dB), kept for A/B timing.
 """
 from __future__ import annotations
 
@@ -189,8 +194,18 @@ class S2PGeneratorB200(nn.Module):
         P["se"] = [(f32(l.weight), f32(l.bias)) for l in self.state_encoder.layers]
         enc = self.image_encoder
         P["stem_w"], P["stem_b"] = f32(enc.conv1.weight), f32(enc.conv1.bias)
-        # the encoder's main line runs split-precision in "high" mode: weights [W_hi | W_hi | W_lo] along Cin
-        pack_main = ops.pack_conv_weight_split if self.precision == "high" else ops.pack_conv_weight
+        # "high" precision: the convs that read the encoder's instance-normalised features run with fp16 operands
+        # (feature maps stored fp16, weights packed fp16); weights outside fp16's range -> bf16 split-precision conv
+        hp = self.precision == "high"
+        feat_w = [enc.conv2.weight, enc.conv3.weight, self.head.weight] + [m.mlp_shared.weight for b in self.blocks() for _, m in b.mats()]
+        want = str(getattr(self.opt, "feat_operands", "auto"))       # "split" forces the bf16 fallback (tests)
+        self._feat_mode = "bf16" if not hp else ("f16" if want != "split" and all(ops.fits_f16(w) for w in feat_w) else "split")
+        if self._feat_mode == "f16":
+            pack_main = pack_feat = lambda w: ops.pack_conv_weight(w, dtype=torch.float16)  # noqa: E731
+        elif self._feat_mode == "split":
+            pack_main, pack_feat = ops.pack_conv_weight_split, ops.pack_conv_weight
+        else:
+            pack_main = pack_feat = ops.pack_conv_weight
         P["e2_w"], P["e2_b"] = pack_main(enc.conv2.weight), f32(enc.conv2.bias)
         P["e3_w"], P["e3_b"] = pack_main(enc.conv3.weight), f32(enc.conv3.bias)
         P["head_w"], P["head_b"] = pack_main(self.head.weight), f32(self.head.bias)
@@ -208,7 +223,7 @@ class S2PGeneratorB200(nn.Module):
         for ds, mats in groups.items():
             sw = torch.cat([m.mlp_shared.weight.detach().float() for _, _, m in mats], dim=0)
             sb = torch.cat([m.mlp_shared.bias.detach().float() for _, _, m in mats], dim=0).contiguous()
-            P["shared"][ds] = (ops.pack_conv_weight(sw), sb, sw.shape[0])
+            P["shared"][ds] = (pack_feat(sw), sb, sw.shape[0])
             for j, (bi, name, m) in enumerate(mats):
                 a = torch.sigmoid(m.blend_gamma.detach().float())
                 c = torch.sigmoid(m.blend_beta.detach().float())
@@ -284,16 +299,17 @@ class S2PGeneratorB200(nn.Module):
             ops.in_stats_finalize(st, ho * wo, 1e-5, mr)
         return (y, y_lo), mr
 
-    def _enc_norm(self, name, e, mr, split):
-        """LReLU(IN(e)) of the image encoder -> (feature [.., C] bf16, operand of the next main-line conv): the
-        operand is the wide [hi | lo] tensor of the split-precision conv when `split`, else the feature itself"""
+    def _enc_norm(self, name, e, mr):
+        """LReLU(IN(e)) of the image encoder -> (feature [.., C] for the mlp_shared convs, operand of the next
+        main-line conv).  'f16': one fp16 tensor serves both; 'split': the wide [hi | lo] bf16 tensor of the
+        split-precision conv, whose high halves are the bf16 feature; 'bf16': one bf16 tensor."""
         eh, el = e
         B, h, w, c = eh.shape
-        if split:
+        if self._feat_mode == "split":
             t = self._buf(name, (B, h, w, 2 * c), torch.bfloat16)
             ops.mat_norm(eh, mr, act=ACT_LRELU, out=t[..., :c], x_lo=el, out_lo=t[..., c:])
             return t[..., :c], t
-        t = self._buf(name, (B, h, w, c), torch.bfloat16)
+        t = self._buf(name, (B, h, w, c), torch.float16 if self._feat_mode == "f16" else torch.bfloat16)
         ops.mat_norm(eh, mr, act=ACT_LRELU, out=t, x_lo=el)
         return t, t
 
@@ -326,17 +342,18 @@ class S2PGeneratorB200(nn.Module):
             raise RuntimeError("image height/width must be multiples of 4")
         bf = torch.bfloat16
         hp = self.precision == "high"
-        # ---- image encoder (pre-norm maps wide, main-line operands split, in "high" precision)
+        split = self._feat_mode == "split"
+        # ---- image encoder (pre-norm maps wide, feature maps fp16, in "high" precision)
         e1 = self._act("e1", (B, H, W, ngf), hp)
         st = self._buf("e1.st", (B, ops.stem_stats_rows(H, W), ngf, 2), torch.float32)
         ops.stem_conv(image, P["stem_w"], P["stem_b"], ngf, e1[0], st, out_lo=e1[1])
         mr = ops.in_stats_finalize(st, H * W, 1e-5, self._buf("e1.mr", (B, ngf, 2), torch.float32))
         f, fx = {}, {}
-        f[1], fx[1] = self._enc_norm("f1", e1, mr, hp)
-        e2, mr = self._conv("e2", fx[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True, wide=hp, split=hp)
-        f[2], fx[2] = self._enc_norm("f2", e2, mr, hp)
-        e3, mr = self._conv("e3", fx[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True, wide=hp, split=hp)
-        f[4], fx[4] = self._enc_norm("f4", e3, mr, hp)
+        f[1], fx[1] = self._enc_norm("f1", e1, mr)
+        e2, mr = self._conv("e2", fx[1], P["e2_w"], P["e2_b"], ngf * 2, 3, 2, want_stats=True, wide=hp, split=split)
+        f[2], fx[2] = self._enc_norm("f2", e2, mr)
+        e3, mr = self._conv("e3", fx[2], P["e3_w"], P["e3_b"], ngf * 4, 3, 2, want_stats=True, wide=hp, split=split)
+        f[4], fx[4] = self._enc_norm("f4", e3, mr)
         # ---- merged mlp_shared convs: one wide conv per conditioning feature
         hs = {}
         for ds in (4, 2, 1):
@@ -345,7 +362,7 @@ class S2PGeneratorB200(nn.Module):
         # ---- trunk
         fuse = self.fuse_mat
         x, mr_x = self._conv("head", fx[4], P["head_w"], P["head_b"], ngf * 8, 3, 1, want_stats=True,
-                             finalize=not fuse, wide=hp, split=hp)
+                             finalize=not fuse, wide=hp, split=split)
         cur = 4
         for bi, (blk, ds) in enumerate(zip(self.blocks(), self.RES_OF_BLOCK)):
             up = cur // ds

@@ -27,9 +27,9 @@ def _require_cuda(*ts):
             raise RuntimeError("s2p_b200 ops need CUDA tensors: there is no CPU path (use oracle/ for a CPU run)")
 
 
-def _nhwc_pitch(t: torch.Tensor, what: str) -> int:
-    """pixel pitch of an NHWC (possibly channel-sliced) bf16 tensor"""
-    if t.dtype != torch.bfloat16 or t.dim() != 4:
+def _nhwc_pitch(t: torch.Tensor, what: str, f16_ok: bool = False) -> int:
+    """pixel pitch of an NHWC (possibly channel-sliced) bf16 tensor (fp16 where the callee takes an fp16 operand)"""
+    if (t.dtype != torch.bfloat16 and not (f16_ok and t.dtype == torch.float16)) or t.dim() != 4:
         raise RuntimeError(f"{what}: expected a 4-D bf16 NHWC tensor, got {tuple(t.shape)} {t.dtype}")
     b, h, w, c = t.shape
     pitch = t.stride(2)
@@ -46,17 +46,24 @@ def stem_stats_rows(h: int, w: int) -> int:
     return int(_lib.load().s2p_stem_stats_rows(h, w))
 
 
-def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scale: float = 1.0) -> torch.Tensor:
-    """OIHW fp32 -> [Cout, R*S*Cin] bf16 (tap-major, channel-minor)."""
+def pack_conv_weight(w_oihw: torch.Tensor, out: torch.Tensor | None = None, scale: float = 1.0,
+                     dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """OIHW fp32 -> [Cout, R*S*Cin] bf16 (tap-major, channel-minor); dtype=torch.float16 for the fp16-operand convs."""
     _require_cuda(w_oihw)
     w = w_oihw.detach().contiguous().float()
     co, ci, r, s = w.shape
     if out is None:
-        out = torch.empty(co, r * s * ci, dtype=torch.bfloat16, device=w.device)
-    assert out.is_contiguous() and out.numel() == w.numel() and out.dtype == torch.bfloat16
-    _lib.check(_lib.load().s2p_pack_conv_weight(w.data_ptr(), out.data_ptr(), co, ci, r, s, float(scale), _stream()),
+        out = torch.empty(co, r * s * ci, dtype=dtype, device=w.device)
+    assert out.is_contiguous() and out.numel() == w.numel() and out.dtype in (torch.bfloat16, torch.float16)
+    _lib.check(_lib.load().s2p_pack_conv_weight(w.data_ptr(), out.data_ptr(), co, ci, r, s, float(scale),
+                                                1 if out.dtype == torch.float16 else 0, _stream()),
                "s2p_pack_conv_weight")
     return out
+
+
+def fits_f16(w: torch.Tensor) -> bool:
+    """can these fp32 values be fp16 tensor-core operands (finite after rounding)?  One host sync, at pack time."""
+    return bool(torch.isfinite(w.detach().float().to(torch.float16)).all())
 
 
 def _lo_of(t, lo, what):
@@ -111,8 +118,11 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
         cin2 = x2.shape[3]
         if tuple(x2.shape[:3]) != (b, hout, wout):
             raise RuntimeError(f"conv_igemm: x2 must have the output's spatial size, got {tuple(x2.shape)}")
-    if w_packed.dtype != torch.bfloat16 or w_packed.numel() != cout * (ksize * ksize * cin + cin2) or not w_packed.is_contiguous():
-        raise RuntimeError("conv_igemm: packed weight has the wrong size/dtype")
+    op_f16 = x.dtype == torch.float16        # fp16 operands: activation(s) and packed weight all fp16
+    if w_packed.dtype != x.dtype or (x2 is not None and x2.dtype != x.dtype):
+        raise RuntimeError(f"conv_igemm: operands disagree on dtype (x {x.dtype}, w {w_packed.dtype})")
+    if w_packed.numel() != cout * (ksize * ksize * cin + cin2) or not w_packed.is_contiguous():
+        raise RuntimeError("conv_igemm: packed weight has the wrong size")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout or not bias.is_contiguous()):
         raise RuntimeError("conv_igemm: bias must be contiguous fp32 [Cout]")
     if stats is not None:
@@ -126,10 +136,10 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
         res_pitch = _nhwc_pitch(residual, "residual")
     _lib.check(
         _lib.load().s2p_conv_igemm_fwd2(
-            x.data_ptr(), _nhwc_pitch(x, "x"), _ptr(x2), _nhwc_pitch(x2, "x2") if x2 is not None else 0, cin2,
+            x.data_ptr(), _nhwc_pitch(x, "x", True), _ptr(x2), _nhwc_pitch(x2, "x2", True) if x2 is not None else 0, cin2,
             w_packed.data_ptr(), _ptr(bias), _ptr(residual), _lo_of(residual, residual_lo, "residual_lo"), res_pitch,
             out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), _ptr(stats), b, hin, win, cin, cout,
-            ksize, stride, pad, act, cin_wrap, _stream()),
+            ksize, stride, pad, act, cin_wrap, 1 if op_f16 else 0, _stream()),
         "s2p_conv_igemm_fwd2")
     return out
 
@@ -196,6 +206,7 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
         out = torch.empty(b, h, w, c, dtype=torch.bfloat16, device=x.device)
     if tuple(out.shape) != (b, h, w, c):
         raise RuntimeError("mat_norm: out shape mismatch")
+    y_f16 = out.dtype == torch.float16       # an fp16 output: the operand of an fp16-operand conv
     if tuple(mean_rstd.shape) != (b, c, 2) or mean_rstd.dtype != torch.float32 or not mean_rstd.is_contiguous():
         raise RuntimeError("mat_norm: mean_rstd must be contiguous fp32 [B, C, 2]")
     gpitch = 0
@@ -211,8 +222,8 @@ def mat_norm(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=ACT_LREL
     _lib.check(
         _lib.load().s2p_mat_norm_fwd(
             x.data_ptr(), _lo_of(x, x_lo, "x_lo"), _nhwc_pitch(x, "x"), up, mean_rstd.data_ptr(), _ptr(gs), _ptr(bs), gpitch,
-            _ptr(gb_spatial), gbp, out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out"), b, h, w, c, act,
-            _stream()),
+            _ptr(gb_spatial), gbp, out.data_ptr(), _lo_of(out, out_lo, "out_lo"), _nhwc_pitch(out, "out", True), b, h, w, c, act,
+            1 if y_f16 else 0, _stream()),
         "s2p_mat_norm_fwd")
     return out
 

@@ -48,7 +48,7 @@ def test_bad_arguments_are_reported_not_launched():
     lib = _lib.load()
     rc = lib.s2p_conv_igemm_fwd(16, 64, 16, None, None, 0, 16, 64, None, 1, 25, 25, 48, 64, 3, 1, 1, 0, None)
     assert rc == -1 and b"Cin" in lib.s2p_last_error_string()
-    rc = lib.s2p_mat_norm_fwd(None, None, 64, 1, None, None, None, 0, None, 0, None, None, 64, 1, 25, 25, 64, 2, None)
+    rc = lib.s2p_mat_norm_fwd(None, None, 64, 1, None, None, None, 0, None, 0, None, None, 64, 1, 25, 25, 64, 2, 0, None)
     assert rc == -1
     assert lib.s2p_launch_count() == 0
 

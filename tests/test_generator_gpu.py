@@ -288,3 +288,22 @@ def test_cuda_graph_forward_is_bit_identical(pkg):
     # rollout goes through the same graph every step
     _, states5 = common.make_inputs("cheetah", 2, 5)
     assert torch.equal(net.rollout(image[:2], states5.cuda()), eager.rollout(image[:2], states5.cuda()))
+
+
+def test_split_precision_fallback_matches_the_fp16_feature_path(pkg):
+    """weights that do not fit fp16 make the encoder-feature convs fall back to the bf16 split-precision conv
+    ([hi | lo] x [W_hi | W_hi | W_lo]); forced here through opt.feat_operands: same 50 dB bar, and the two
+    schedules are within the same distance of each other"""
+    ora, net = _pair(pkg, "walker", "scaled")
+    assert net(*[t.cuda() for t in (common.make_inputs("walker", 1, 1)[0], common.make_inputs("walker", 1, 1)[1][:, 0])]) is not None
+    assert net._feat_mode == "f16"
+    fb = pkg.define_G(pkg.make_options(env_type="walker", gpu_ids="0", feat_operands="split"))
+    fb.load_state_dict(ora.state_dict())
+    fb.eval()
+    image, states = common.make_inputs("walker", 2, 1)
+    gold = torch.from_numpy(common.load_golden("walker_scaled_b2")["first"])
+    a, b = net(image.cuda(), states[:, 0].cuda()).cpu(), fb(image.cuda(), states[:, 0].cuda()).cpu()
+    assert fb._feat_mode == "split"
+    pa, pb, pab = common.psnr01(a, gold), common.psnr01(b, gold), common.psnr01(a, b)
+    print(f"walker_scaled_b2: fp16 features {pa:.2f} dB, split fallback {pb:.2f} dB, one vs the other {pab:.2f} dB")
+    assert pa >= PSNR_MIN and pb >= PSNR_MIN and pab >= PSNR_MIN

@@ -480,3 +480,48 @@ def test_state_encoder_fused_is_bit_identical_to_the_chain(ops, b, s_dim):
     assert (fused - ref32).abs().max().item() <= 2e-4 * ref32.abs().max().item()
     # the barrier counters are left zeroed: a second launch on the same workspace gives the same bytes
     assert torch.equal(ops.state_encoder_fused(state, layers, hw, hb, 10), chain)
+
+
+@pytest.mark.parametrize("b,h,cin,cout,stride,k", [(2, 100, 64, 128, 2, 3), (2, 25, 256, 512, 1, 3), (3, 50, 128, 384, 1, 3), (2, 25, 256, 64, 1, 1)])
+def test_conv_fp16_operands(ops, b, h, cin, cout, stride, k):
+    """fp16 activation x fp16 weights (tcgen05 kind::f16, format F16): exact products of the fp16-rounded operands,
+    and ~8x closer to the un-rounded fp32 convolution than bf16 operands"""
+    g = torch.Generator().manual_seed(cin + cout + k)
+    x = torch.randn(b, h, h, cin, generator=g).cuda()
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (k * k * cin) ** 0.5).cuda()
+    bs = torch.randn(cout, generator=g).cuda()
+    xh = x.to(torch.float16)
+    wp = ops.pack_conv_weight(wt, dtype=torch.float16)
+    assert wp.dtype == torch.float16 and torch.equal(wp.view(cout, k, k, cin).permute(0, 3, 1, 2), wt.to(torch.float16))
+    ho = (h + 2 * (k // 2) - k) // stride + 1
+    out = torch.empty(b, ho, ho, 2 * cout, dtype=torch.bfloat16, device="cuda")
+    y_hi, y_lo = ops.wide(out)
+    ops.conv_igemm(xh, wp, bs, cout, k, stride, 0, None, y_hi, None, out_lo=y_lo)
+    y = y_hi.float() + y_lo.float()
+    ref16 = nhwc(F.conv2d(xh.float().permute(0, 3, 1, 2), wt.to(torch.float16).float(), bs, stride, k // 2))
+    ref32 = nhwc(F.conv2d(x.permute(0, 3, 1, 2), wt, bs, stride, k // 2))
+    refbf = nhwc(F.conv2d(x.to(torch.bfloat16).float().permute(0, 3, 1, 2), wt.to(torch.bfloat16).float(), bs, stride, k // 2))
+    scale = ref32.abs().max().item()
+    assert (y - ref16).abs().max().item() <= 3e-5 * scale
+    e16 = (y - ref32).pow(2).mean().sqrt().item()
+    ebf = (refbf - ref32).pow(2).mean().sqrt().item()
+    print(f"fp16 operands rms error {e16:.3e} vs bf16 operands {ebf:.3e}")
+    assert e16 <= ebf / 6
+    with pytest.raises(RuntimeError):          # operands must agree on the dtype
+        ops.conv_igemm(xh, ops.pack_conv_weight(wt), bs, cout, k, stride)
+
+
+def test_mat_norm_fp16_output(ops):
+    g = torch.Generator().manual_seed(41)
+    b, h, c = 2, 50, 128
+    x32 = (torch.randn(b, h, h, c, generator=g) * 2 + 0.5).cuda()
+    pair = torch.empty(b, h, h, 2 * c, dtype=torch.bfloat16, device="cuda")
+    pair[..., :c], pair[..., c:] = _split(x32)
+    x_hi, x_lo = ops.wide(pair)
+    xw = x_hi.float() + x_lo.float()
+    mean, var = xw.mean(dim=(1, 2)), xw.var(dim=(1, 2), unbiased=False)
+    mr = torch.stack([mean, 1.0 / torch.sqrt(var + 1e-5)], dim=2).contiguous()
+    out = torch.empty(b, h, h, c, dtype=torch.float16, device="cuda")
+    ops.mat_norm(x_hi, mr, act=2, out=out, x_lo=x_lo)
+    ref = F.leaky_relu((xw - mean[:, None, None]) * mr[:, None, None, :, 1], 0.2)
+    assert torch.equal(out, ref.to(torch.float16)) or (out.float() - ref).abs().max().item() <= 2.0 ** -11 * ref.abs().max().item() + 1e-6
