@@ -30,9 +30,21 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# rank 0 prints exactly ONE JSON line on stdout: keep NCCL's own banner ("NCCL version ...") out of it
-os.environ["NCCL_DEBUG"] = os.environ.get("S2P_NCCL_DEBUG", "WARN")
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL prints its version banner at WARN level too: to stderr
+# rank 0 prints exactly ONE JSON line on stdout: NCCL's own lines (banner at WARN, rank/ring lines at INFO) go to
+# stderr.  NCCL_DEBUG itself is only DEFAULTED: a driver that asks for INFO keeps its rank evidence.
+os.environ.setdefault("NCCL_DEBUG", "WARN")
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
+# diagnostic switches of the library / tools change what a step does or how fast it runs: a bench line measured with
+# one of them set is not the product's number
+_DIAGNOSTIC_ENV = ("S2P_CONV_CLUSTER", "S2P_CONV_DEBUG", "S2P_NORM_PIX_PER_THREAD", "S2P_WGRAD_ROWS", "S2P_WGRAD_TAP_SPLIT",
+                   "S2P_WGRAD_PAD16")
+
+
+def refuse_diagnostic_env():
+    bad = [k for k in _DIAGNOSTIC_ENV if os.environ.get(k) not in (None, "")]
+    if bad:
+        raise SystemExit(f"bench.py refuses to run with diagnostic switches set: {bad} (unset them)")
 
 METRIC = "generated_frames_per_sec"
 UNIT = "frames/s"
@@ -179,6 +191,7 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    refuse_diagnostic_env()
     opt = s2p_b200.make_options(env_type=ENV, gpu_ids=str(local), init_type="scaled", precision=args.precision)
     torch.manual_seed(1234)
     net = s2p_b200.define_G(opt).eval()
@@ -214,8 +227,12 @@ def run_b200(args):
         for _ in range(args.steps):
             res = net.forward_u8(frames_d, states_d)
         e1.record()
-        barrier()
         launches = _lib.launch_count() - l0
+        # ---- instrumented steps, back to back with the timed ones (no barrier, no pause: same clocks, same power
+        # state): CUDA events around every conv / norm launch give each kernel class's SHARE of a step; the roofline
+        # is then algorithmic flops / (share x the timed ms_per_step)
+        inst = instrumented_steps(net, frames_d, states_d, ops, torch, n_steps=3) if rank == 0 else None
+        barrier()
         ms_dev = max_over_ranks(e0.elapsed_time(e1))
         # ---- end to end through the public bulk API with host buffers
         synth = BulkSynthesizer(net, batch=min(B, 256))
@@ -232,11 +249,18 @@ def run_b200(args):
     assert torch.equal(out_h.to(dev), res), "e2e result differs from the device-resident result"
     clocks = clk.summary()
 
-    # ---- instrumented step: CUDA events around every conv / norm launch (rank 0)
     roof, roof_norm, shares = None, None, None
     if rank == 0:
-        roof, roof_norm, shares = instrumented_step(net, frames_d, states_d, ops, torch)
+        roof, roof_norm, shares = rooflines(inst, ms_dev / args.steps)
 
+    # ---- N > 1: BASELINE configs[4] beside the headline -- data-parallel GAN training, 256 frames per GPU, gradient
+    # all-reduce over NVLink overlapped with backward (every rank takes part; rank 0 reports)
+    train_dp = None
+    if world > 1 and not args.no_train:
+        try:
+            train_dp = train_dp_side_measurement(torch, dist, s2p_b200, dev, world, rank)
+        except Exception as e:  # noqa: BLE001
+            train_dp = {"error": repr(e)[:200]}
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -254,6 +278,23 @@ def run_b200(args):
                     "d2h_bytes_per_step": synth.d2h_bytes // args.steps, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_norm": roof_norm,
             "kernel_time_share": shares}
+    # ---- parity of THIS run's output: 64 of the rows just synthesised against the fp32 oracle (the checker; on the
+    # GPU, TF32 off), as PSNR on [0,1]-mapped frames.  north_star: >= 50 dB.
+    try:
+        line["parity_check"] = parity_spot_check(torch, net, frames_d, states_d, res, dev)
+    except Exception as e:  # noqa: BLE001
+        line["parity_check"] = {"error": repr(e)[:200]}
+    if train_dp is not None:
+        line["training_step"] = train_dp
+    if world == 1 and not args.no_train:
+        try:
+            line["latency_b16"] = latency_b16_side_measurement(torch, s2p_b200, dev)
+        except Exception as e:  # noqa: BLE001
+            line["latency_b16"] = {"error": repr(e)[:200]}
+        try:
+            line["eager_gpu_baseline"] = eager_gpu_baseline(torch, dev)
+        except Exception as e:  # noqa: BLE001
+            line["eager_gpu_baseline"] = {"error": repr(e)[:200]}
     if world == 1 and not args.no_train:
         try:
             line["training_step"] = train_side_measurement(torch, s2p_b200, dev)
@@ -278,6 +319,140 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _oracle_on(torch, dev, env=ENV):
+    """the fp32 oracle (test infrastructure, used here only as the checker / the eager baseline) with the weights of
+    the benchmarked generator: same seeded 'scaled' init"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import s2p_oracle as O
+    torch.manual_seed(1234)
+    return O, O.define_G(O.make_options(env_type=env, init_type="scaled")).eval().to(dev)
+
+
+def parity_spot_check(torch, net, frames_d, states_d, res, dev, rows=64):
+    O, ora = _oracle_on(torch, dev)
+    # bench.py builds the generator from its own seeded init: load the oracle's weights' twin check instead of
+    # trusting two inits to agree -- compare the oracle run ON THE GENERATOR'S OWN WEIGHTS
+    ora.load_state_dict(net.state_dict())
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            ref = ora(O.from_uint8_hwc(frames_d[:rows]), states_d[:rows])
+        got = net(O.from_uint8_hwc(frames_d[:rows]), states_d[:rows])
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+    mse = ((got - ref).double() * 0.5).pow(2).mean().item()
+    import math
+    psnr = 10.0 * math.log10(1.0 / max(mse, 1e-30))
+    u8_ref = O.to_uint8_hwc(ref)
+    d = (res[:rows].int() - u8_ref.int()).abs()
+    return {"rows": rows, "psnr_db": psnr, "max_abs": float((got - ref).abs().max()), "tolerance_db": 50.0,
+            "ok": bool(psnr >= 50.0), "u8_max_lsb": int(d.max()), "u8_mean_lsb": float(d.float().mean()),
+            "against": "fp32 oracle on the same weights and rows (cuDNN, TF32 off), fp32 [-1,1] outputs; the u8 line "
+                       "compares the benchmarked uint8 result rows with the oracle's quantised output"}
+
+
+def latency_b16_side_measurement(torch, s2p_b200, dev, batch=16, reps=20):
+    """BASELINE configs[0]/[1] size: one-step forward at batch 16 (README.md:59's batch size), cheetah, fp32 NCHW in /
+    out through netG(image, state).  ms_graph = the default path (CUDA-graph replay of the launch sequence, state path
+    = one fused launch); ms_eager = the same kernels launched one by one from Python."""
+    from s2p_b200 import _lib
+    torch.manual_seed(1234)
+    nets = {}
+    for name, graph in (("graph", 1), ("eager", 0)):
+        n = s2p_b200.define_G(s2p_b200.make_options(env_type=ENV, gpu_ids=str(dev.index), init_type="scaled", cuda_graph=graph)).eval()
+        if nets:
+            n.load_state_dict(nets["graph"].state_dict())
+        nets[name] = n
+    g = torch.Generator().manual_seed(16)
+    image = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    state = torch.randn(batch, 17, generator=g).to(dev)
+    out = {"config": f"one-step forward, cheetah, batch {batch}, fp32 NCHW in/out, 1 GPU (BASELINE configs[0] on the GPU)"}
+    results = {}
+    for name, n in nets.items():
+        for _ in range(3):
+            results[name] = n(image, state)
+        torch.cuda.synchronize()
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_host = time.perf_counter()
+        e0.record()
+        for _ in range(reps):
+            n(image, state)
+        e1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t_host) / reps * 1e3
+        out[f"ms_{name}"] = e0.elapsed_time(e1) / reps
+        out[f"ms_{name}_wall"] = wall
+        out[f"launches_{name}"] = (_lib.launch_count() - l0) // reps
+    out["bit_identical"] = bool(torch.equal(results["graph"], results["eager"]))
+    out["frames_per_sec_graph"] = batch / out["ms_graph"] * 1e3
+    return out
+
+
+def eager_gpu_baseline(torch, dev, batch=128, reps=3):
+    """the practical bar of BASELINE.md section 3: the oracle module (plain torch.nn -> cuDNN) on the same GPU under
+    bf16 autocast, 128-frame batches"""
+    O, ora = _oracle_on(torch, dev)
+    g = torch.Generator().manual_seed(5)
+    image = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    state = torch.randn(batch, 17, generator=g).to(dev)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        for _ in range(2):
+            ora(image, state)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            ora(image, state)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"what": "oracle torch.nn module on cuda under bf16 autocast (cuDNN / cuBLAS library kernels)", "batch": batch,
+            "reps": reps, "ms_per_batch": ms, "frames_per_sec": batch / ms * 1e3}
+
+
+def train_dp_side_measurement(torch, dist, s2p_b200, dev, world, rank, batch=256, steps=3, warmup=2):
+    """BASELINE configs[4]: data-parallel G + D training step, walker, 256 frames per GPU, NCCL gradient all-reduce
+    (GradBuckets: issued from the backward hooks on a side stream).  Max over ranks, CUDA events."""
+    from s2p_b200.training import S2PTrainer
+    torch.manual_seed(1234)                      # same initial weights on every rank
+    opt = s2p_b200.make_options(env_type="walker", gpu_ids=str(dev.index), init_type="scaled")
+    tr = S2PTrainer(s2p_b200.define_G(opt), s2p_b200.define_D(opt), world_size=world, vgg=s2p_b200.VGG19FeaturesB200().to(dev))
+    g = torch.Generator().manual_seed(300 + rank)
+    prev = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    real = (torch.rand(batch, 3, 100, 100, generator=g) * 2 - 1).to(dev)
+    state = torch.randn(batch, opt.state_dim, generator=g).to(dev)
+    for _ in range(warmup):
+        tr.train_step(prev, state, real)
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        gl, dl = tr.train_step(prev, state, real)
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # same weights on every rank after the steps <=> the all-reduce really averaged the gradients
+    w = torch.cat([p.detach().flatten()[:64].double() for p in tr.netG.parameters()]).sum().reshape(1)
+    lo, hi = w.clone(), w.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    flops_frame = 3 * 112.9e9 * 1.03 + 3 * 7.006e9
+    del tr
+    torch.cuda.empty_cache()
+    return {"config": f"BASELINE configs[4]: data-parallel generator + multiscale-discriminator training step, walker, batch {batch} per GPU, "
+                      f"{world} GPUs, NCCL gradient all-reduce overlapped with backward",
+            "n_gpus": world, "batch_per_gpu": batch, "ms_per_step": ms, "frames_per_sec": batch * world / ms * 1e3, "steps": steps,
+            "warmup": warmup, "tflops_per_gpu": flops_frame * batch / (ms / 1e3) / 1e12, "weights_in_sync": bool((hi - lo).abs().item() == 0.0),
+            "losses": {k: float(v) for k, v in gl.items()} | {"D": float(dl)}}
 
 
 def adjacent_side_measurements(torch, dev):
@@ -407,20 +582,12 @@ def train_side_measurement(torch, s2p_b200, dev, batch=16, steps=5, warmup=3):
             "losses": {k: float(v) for k, v in gl.items()} | {"D": float(dl)}}
 
 
-def instrumented_step(net, frames_d, states_d, ops, torch):
-    """One extra step with a CUDA-event pair around every conv / norm launch."""
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
-    tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+def instrumented_steps(net, frames_d, states_d, ops, torch, n_steps=3):
+    """n_steps extra steps with a CUDA-event pair around every conv / norm launch, enqueued right behind the timed
+    steps.  Returns the raw records; rooflines() turns them into the JSON objects once the events have completed."""
     rec = {"conv": [], "norm": [], "other": []}
     orig = {n: getattr(ops, n) for n in ("conv_igemm", "conv_mat_fused", "mat_norm", "stem_conv", "torgb_tanh", "torgb_igemm",
-                                         "linear", "pos_encode", "in_stats_finalize", "mat_prepare")}
+                                         "linear", "pos_encode", "in_stats_finalize", "mat_prepare", "state_encoder_fused")}
 
     def wrap(name, kind, work_fn):
         fn = orig[name]
@@ -435,19 +602,22 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
         return inner
 
     def conv_flops(x, w_packed, bias, cout, ksize, stride=1, *a, **k):
+        # ALGORITHMIC flops: the convolution the oracle defines.  A split-precision launch walks 3x the channels of
+        # the conv it computes (three products of one weight x activation pair): counted once.
         b, h, w, cin = x.shape
+        if k.get("split"):
+            cin //= 2
         ho = (h + 2 * (ksize // 2) - ksize) // stride + 1
         wo = (w + 2 * (ksize // 2) - ksize) // stride + 1
         cin2 = k["x2"].shape[3] if k.get("x2") is not None else 0     # the 1x1 shortcut riding along as a second operand
         return 2.0 * b * ho * wo * cout * (cin * ksize * ksize + cin2)
 
-    def norm_bytes(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=2, out=None, x_lo=None, out_lo=None,
-                   out_dup=None):
-        # bytes the launch has to move: a wide (hi + lo) input is 4 B per element, the [hi | lo | hi] operand 6 B
+    def norm_bytes(x, mean_rstd, gs=None, bs=None, gb_spatial=None, up=1, act=2, out=None, x_lo=None, out_lo=None):
+        # bytes the launch has to move: a wide (hi + lo) tensor is 4 B per element
         b, hx, wx, c = x.shape
         px = b * hx * up * wx * up
         rd = (4.0 if x_lo is not None else 2.0) * c * (b * hx * wx)
-        wr = (2.0 + (2.0 if out_lo is not None else 0.0) + (2.0 if out_dup is not None else 0.0)) * c * px
+        wr = (4.0 if out_lo is not None else 2.0) * c * px
         return rd + wr + (4.0 * c * px if gb_spatial is not None else 0.0)
 
     def fused_flops(h, w_packed_gb, x, mod_table, up=1, act=2, ksize=3, out=None, x_lo=None):
@@ -457,25 +627,48 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
     ops.conv_igemm = wrap("conv_igemm", "conv", conv_flops)
     ops.conv_mat_fused = wrap("conv_mat_fused", "conv", fused_flops)
     ops.mat_norm = wrap("mat_norm", "norm", norm_bytes)
-    for n in ("stem_conv", "torgb_tanh", "torgb_igemm", "linear", "pos_encode", "in_stats_finalize", "mat_prepare"):
+    for n in ("stem_conv", "torgb_tanh", "torgb_igemm", "linear", "pos_encode", "in_stats_finalize", "mat_prepare",
+              "state_encoder_fused"):
         setattr(ops, n, wrap(n, "other", None))
     try:
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
-        net.forward_u8(frames_d, states_d)
+        for _ in range(n_steps):
+            net.forward_u8(frames_d, states_d)
         t1.record()
-        torch.cuda.synchronize()
     finally:
         for n, fn in orig.items():
             setattr(ops, n, fn)
-    total = t0.elapsed_time(t1)
+    return {"rec": rec, "t0": t0, "t1": t1, "n_steps": n_steps}
+
+
+def rooflines(inst, ms_per_step_timed):
+    """roofline objects from the instrumented steps: share of each kernel class inside a step (events), applied to the
+    TIMED ms_per_step.  achieved = algorithmic work per step / (share x ms_per_step)."""
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+    rec, n_steps = inst["rec"], inst["n_steps"]
+    total = inst["t0"].elapsed_time(inst["t1"])                       # all instrumented steps
     tms = {k: sum(s.elapsed_time(e) for s, e, _ in v) for k, v in rec.items()}
-    work = {k: sum(w for _, _, w in v) for k, v in rec.items()}
-    nconv, nnorm = len(rec["conv"]), len(rec["norm"])
+    work = {k: sum(w for _, _, w in v) / n_steps for k, v in rec.items()}     # per step
+    nconv, nnorm = len(rec["conv"]) // n_steps, len(rec["norm"]) // n_steps
+    shares = {k: tms[k] / total for k in tms}
     traffic_conv = traffic_norm = None
+    traffic_file = None
+    for cand in ("r02_kernel_metrics.csv", "r01_kernel_metrics.csv"):
+        if os.path.exists(os.path.join(ROOT, "profiles", cand)):
+            traffic_file = cand
+            break
     try:   # DRAM bytes per launch from the committed ncu pass of the same forward (128-frame micro-batch)
         import csv
-        with open(os.path.join(ROOT, "profiles", "r01_kernel_metrics.csv")) as f:
+        with open(os.path.join(ROOT, "profiles", traffic_file)) as f:
             rows = list(csv.DictReader(l for l in f if not l.startswith("==")))
         by = {}
         for r in rows:
@@ -489,20 +682,24 @@ def instrumented_step(net, frames_d, states_d, ops, torch):
         traffic_norm = sum(n) / len(n) if n else None
     except Exception:
         pass
-    ach_tf = work["conv"] / (tms["conv"] / 1e3) / 1e12
-    ach_gb = work["norm"] / (tms["norm"] / 1e3) / 1e9
+    conv_ms = shares["conv"] * ms_per_step_timed
+    norm_ms = shares["norm"] * ms_per_step_timed
+    ach_tf = work["conv"] / (conv_ms / 1e3) / 1e12
+    ach_gb = work["norm"] / (norm_ms / 1e3) / 1e9
     roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM, plain and MAT-fused epilogues; all launches of one step)",
-            "bound": "tensor",
-            "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak, "traffic": traffic_conv,
-            "traffic_note": "avg dram__bytes_read+write per conv launch, profiles/r01_kernel_metrics.csv (ncu, 128-frame micro-batch)",
-            "peak_source": src, "launches": nconv, "avg_launch_ms": tms["conv"] / nconv,
-            "flops_per_launch_avg": work["conv"] / nconv}
-    roof_norm = {"kernel": "mat_norm_kernel (fused IN + MAT modulation + LeakyReLU; all launches of one step)",
+            "bound": "tensor", "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak,
+            "traffic": traffic_conv,
+            "traffic_note": f"avg dram__bytes_read+write per conv launch, profiles/{traffic_file} (ncu, 128-frame micro-batch)",
+            "peak_source": src, "launches": nconv, "avg_launch_ms": conv_ms / nconv,
+            "flops_per_launch_avg": work["conv"] / nconv, "flops_per_step": work["conv"],
+            "how": f"algorithmic flops of a step / (conv share {shares['conv']:.4f} x timed ms_per_step {ms_per_step_timed:.3f}); "
+                   f"share = CUDA-event time of the conv launches / total, over {n_steps} instrumented steps enqueued "
+                   "directly behind the timed steps"}
+    roof_norm = {"kernel": "mat_norm_kernel (fused IN + LeakyReLU of the image encoder; all launches of one step)",
                  "bound": "hbm", "achieved": ach_gb, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gb / hbm_peak,
-                 "traffic": traffic_norm, "peak_source": src, "launches": nnorm, "avg_launch_ms": tms["norm"] / nnorm,
+                 "traffic": traffic_norm, "peak_source": src, "launches": nnorm, "avg_launch_ms": norm_ms / nnorm,
                  "bytes_per_launch_avg": work["norm"] / nnorm}
-    shares = {k: tms[k] / total for k in tms}
-    shares["step_ms_instrumented"] = total
+    shares["step_ms_instrumented"] = total / n_steps
     return roof, roof_norm, shares
 
 

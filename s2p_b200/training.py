@@ -2,9 +2,11 @@
 feature matching + VGG19 perceptual when a `vgg` extractor is given; rebuttal.md:71,131-135) then one discriminator step, SPADE Pix2PixTrainer order.
 Mirrors oracle/s2p_oracle.py `training_step` (ORACLE_SPEC v1.1) term by term.
 
-Multi-GPU (BASELINE configs[4]): one process per GPU, data parallel; after each backward the
-gradients are all-reduced (NCCL, flat buckets) and averaged.  Parameters are updated by the
-repo's fused Adam kernel (fp32 master weights, torch.optim.Adam arithmetic)."""
+Multi-GPU (BASELINE configs[4]): one process per GPU, data parallel.  Gradients live in flat fp32 buckets
+(`GradBuckets`: every p.grad is a view into its bucket); a bucket's NCCL all-reduce is issued on a side stream the
+moment the backward pass has produced its last gradient, so communication overlaps the rest of the backward and
+nothing is staged through torch.cat copies.  Parameters are updated by the repo's fused Adam kernel (fp32 master
+weights, torch.optim.Adam arithmetic)."""
 from __future__ import annotations
 
 import torch
@@ -34,6 +36,9 @@ class FusedAdam:
         return int(self.step_dev.item())
 
     def zero_grad(self, set_to_none=True):
+        if getattr(self, "buckets", None) is not None:
+            self.buckets.zero()           # gradients are views into flat buckets: clear those, keep the views
+            return
         for p in self.params:
             p.grad = None
 
@@ -59,7 +64,9 @@ class FusedAdam:
 
 
 def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
-    """average .grad over ranks: flat fp32 buckets, one NCCL all-reduce each."""
+    """average .grad over ranks after the fact (flat fp32 buckets through staging copies, one all-reduce each).
+    The trainer uses GradBuckets (overlapped, in place); this is the simple form for callers with ordinary .grad
+    tensors."""
     import torch.distributed as dist
     grads = [p.grad for p in params if p.grad is not None]
     i = 0
@@ -76,6 +83,80 @@ def allreduce_gradients(params, world_size, bucket_elems=32 * 1024 * 1024):
             g.copy_(flat[off:off + g.numel()].view_as(g))
             off += g.numel()
         i = j
+
+
+class GradBuckets:
+    """Data-parallel gradient exchange overlapped with backward (SURVEY.md section 8 e, training).
+
+    The parameters' gradients are views into a few flat fp32 buckets, filled in reverse parameter order (roughly the
+    order backward produces them).  A post-accumulate hook counts a bucket's gradients as they arrive; the last one
+    issues that bucket's all-reduce on a communication stream (which first waits for the producing stream), so the
+    reduce runs under the remaining backward kernels and reads / writes the gradient memory in place.  `finish()`
+    joins the streams and scales by 1 / world_size before the optimiser step.  On CPU tensors (gloo tests) the same
+    logic runs with async work handles instead of streams."""
+
+    def __init__(self, params, world_size, bucket_elems=16 * 1024 * 1024):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = world_size
+        self.params = [p for p in params if p.requires_grad]
+        self.cuda = self.params[0].is_cuda
+        dev = self.params[0].device
+        order = list(reversed(self.params))
+        self.buckets, self.where = [], {}
+        i = 0
+        while i < len(order):
+            j, n = i, 0
+            while j < len(order) and (n == 0 or n + order[j].numel() <= bucket_elems):
+                n += order[j].numel()
+                j += 1
+            flat = torch.zeros(n, dtype=torch.float32, device=dev)
+            off = 0
+            for p in order[i:j]:
+                p.grad = flat[off:off + p.numel()].view_as(p)
+                self.where[p] = len(self.buckets)
+                off += p.numel()
+            self.buckets.append(dict(flat=flat, size=j - i, ready=0, work=None))
+            i = j
+        self.comm = torch.cuda.Stream(dev) if self.cuda else None
+        self.handles = [p.register_post_accumulate_grad_hook(self._hook) for p in self.params]
+        self.launched = 0
+
+    def zero(self):
+        for b in self.buckets:
+            b["flat"].zero_()
+            b["ready"], b["work"] = 0, None
+        self.launched = 0
+
+    def _launch(self, b):
+        if self.cuda:
+            self.comm.wait_stream(torch.cuda.current_stream())      # the bucket's gradients are complete on the compute stream
+            with torch.cuda.stream(self.comm):
+                self.dist.all_reduce(b["flat"])
+                b["flat"].mul_(1.0 / self.world)
+        else:
+            b["work"] = self.dist.all_reduce(b["flat"], async_op=True)
+        self.launched += 1
+
+    def _hook(self, p):
+        b = self.buckets[self.where[p]]
+        b["ready"] += 1
+        if b["ready"] == b["size"]:
+            self._launch(b)
+
+    def finish(self):
+        """every bucket reduced and averaged before the optimiser reads the gradients.  A bucket whose parameters did
+        not all receive a gradient this step (none do in this model) is reduced here, so ranks never disagree on the
+        set of collectives."""
+        for b in self.buckets:
+            if b["ready"] != b["size"]:
+                self._launch(b)
+        if self.cuda:
+            torch.cuda.current_stream().wait_stream(self.comm)
+        else:
+            for b in self.buckets:
+                b["work"].wait()
+                b["flat"].mul_(1.0 / self.world)
 
 
 def _split(pred):
@@ -114,6 +195,9 @@ class S2PTrainer:
         self.optD = FusedAdam(netD.parameters(), lr, betas)
         self.world_size = world_size
         self.fake = None
+        if world_size > 1:      # gradients of G and of D live in flat buckets whose all-reduce overlaps backward
+            self.optG.buckets = GradBuckets(self.optG.params, world_size)
+            self.optD.buckets = GradBuckets(self.optD.params, world_size)
 
     def _d(self, prev, fake, real):
         return _split(self.netD(torch.cat([torch.cat([prev, fake], 1), torch.cat([prev, real], 1)], 0)))
@@ -130,7 +214,7 @@ class S2PTrainer:
         self.optG.zero_grad()
         sum(losses.values()).backward()
         if self.world_size > 1:
-            allreduce_gradients(self.optG.params, self.world_size)
+            self.optG.buckets.finish()
         self.optG.step()
         self.fake = fake.detach()
         return losses
@@ -145,7 +229,7 @@ class S2PTrainer:
         self.optD.zero_grad()
         loss.backward()
         if self.world_size > 1:
-            allreduce_gradients(self.optD.params, self.world_size)
+            self.optD.buckets.finish()
         self.optD.step()
         self.fake = None
         return loss

@@ -106,6 +106,72 @@ def test_gradient_allreduce_two_ranks_gloo():
     assert got == [1.5, None, 4.5, 6.0]       # mean over ranks of (rank+1)*(i+1)
 
 
+def _bucket_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from s2p_b200.training import GradBuckets
+    torch.manual_seed(0)                                     # same weights on both ranks
+    net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 4), torch.nn.Tanh(), torch.nn.Linear(4, 1))
+    gb = GradBuckets(net.parameters(), world, bucket_elems=30)   # several buckets
+    views_ok = all(p.grad.data_ptr() >= gb.buckets[gb.where[p]]["flat"].data_ptr() for p in net.parameters())
+    outs = []
+    for step in range(2):                                    # two steps: zero() must re-arm the buckets
+        gb.zero()
+        x = torch.full((3, 6), float(rank + 1 + step))
+        net(x).sum().backward()
+        launched_by_hooks = gb.launched
+        gb.finish()
+        outs.append([p.grad.clone() for p in net.parameters()])
+    # reference: mean over ranks of the local gradients
+    refs = []
+    for step in range(2):
+        acc = None
+        for r in range(world):
+            ref = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 4), torch.nn.Tanh(), torch.nn.Linear(4, 1))
+            ref.load_state_dict(net.state_dict())
+            ref(torch.full((3, 6), float(r + 1 + step))).sum().backward()
+            g = [p.grad for p in ref.parameters()]
+            acc = g if acc is None else [a + b for a, b in zip(acc, g)]
+        refs.append([a / world for a in acc])
+    err = max((a - b).abs().max().item() for o, r in zip(outs, refs) for a, b in zip(o, r))
+    if rank == 0:
+        q.put((len(gb.buckets), launched_by_hooks, views_ok, err))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_grad_buckets_overlapped_allreduce_two_ranks_gloo():
+    """GradBuckets: p.grad are views into flat buckets, every bucket's all-reduce is launched from the backward
+    hooks (not after backward), the result is the mean over ranks, and a second step works after zero()."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bucket_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    nb, launched, views_ok, err = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert nb >= 3 and launched == nb and views_ok
+    assert err <= 1e-6
+
+
+def test_every_rank_runs_the_same_number_of_training_steps():
+    """train.py: steps per epoch = (n // world) // B on EVERY rank; the per-rank row counts of shard_range can differ
+    by one, which used to give ranks different step counts (a hung all-reduce)."""
+    from s2p_b200.synthesis import shard_range
+    for n, world, B in ((1001, 2, 167), (1000, 8, 16), (1023, 4, 51), (50, 3, 16)):
+        steps = (n // world) // B
+        old = {(shard_range(n, r, world)[1] - shard_range(n, r, world)[0]) // B for r in range(world)}
+        assert all(shard_range(n, r, world)[1] - shard_range(n, r, world)[0] >= steps * B for r in range(world))
+        if (n, world, B) == (1001, 2, 167):
+            assert old == {2, 3} and steps == 2
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "train.py")).read()
+    assert "steps_per_epoch = (n // world) // B" in src and "range(0, steps_per_epoch * B, B)" in src
+
+
 def test_flat_dataset_dir_roundtrip(tmp_path):
     """the .npy-per-key twin of the HDF5 schema: exact round trip, row limit, memory-mapped frames"""
     import numpy as np

@@ -77,9 +77,12 @@ def main(argv=None):
     to_f = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev).permute(0, 3, 1, 2).float().div_(127.5).sub_(1.0)
     graphed = False
     t0 = time.time()
+    # every rank runs the SAME number of steps per epoch (each step is a collective when world > 1): shard_range gives
+    # the first n % world ranks one extra row, which can cross a batch boundary (n=1001, world=2, B=167: 3 vs 2 steps)
+    steps_per_epoch = (n // world) // B
     for epoch in range(start_epoch, ex.niter + 1):
         perm = lo + rs.permutation(hi - lo)
-        for b0 in range(0, len(perm) - B + 1, B):  # drop the ragged tail (fixed batch: the step is a CUDA graph)
+        for b0 in range(0, steps_per_epoch * B, B):  # drop the ragged tail (fixed batch: the step is a CUDA graph)
             idx = np.sort(perm[b0:b0 + B])
             prev, real = to_f(data["image_observations"][idx]), to_f(data["image_observations_tp1"][idx])
             state = torch.from_numpy(np.ascontiguousarray(data["next_observations"][idx], dtype=np.float32)).to(dev)
