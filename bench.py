@@ -497,6 +497,33 @@ def adjacent_side_measurements(torch, dev):
         "kernel": "ensemble_transition_kernel (7 x MLP 23-256-256-256-36 + selection + uncertainties, fp32 CUDA cores)",
         "rows": T, "ms": ms, "rows_per_sec": T / ms * 1e3, "fp32_tflops": flops / ms / 1e9, "launches_per_call": 1}
     del obs, act, idx
+    # multi-step generated dataset (random_state_5step_random_action): 5 chained ensemble steps + 5-step generator
+    # rollout + row assembly, host arrays in / out (the whole producer call)
+    try:
+        import s2p_b200
+        from s2p_b200.synthesis import synthesize_multistep_dataset
+        netg = s2p_b200.define_G(s2p_b200.make_options(env_type=ENV, gpu_ids=str(dev.index), init_type="scaled")).eval()
+        rs = np.random.RandomState(3)
+        n_real, J = 4000, 1024
+        real = {"observations": rs.randn(n_real, 17).astype(np.float32), "actions": rs.uniform(-1, 1, (n_real, 6)).astype(np.float32),
+                "rewards": rs.randn(n_real).astype(np.float32), "timeouts": np.zeros(n_real, np.float32),
+                "image_observations": rs.randint(0, 256, (n_real, 100, 100, 3)).astype(np.uint8)}
+        real["timeouts"][249::250] = 1
+        lo_a, hi_a = -np.ones(6, np.float32), np.ones(6, np.float32)
+        synthesize_multistep_dataset(netg, tm, real, norm, lo_a, hi_a, n_starts=64, rng=np.random.RandomState(0))   # warm-up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ms_d = synthesize_multistep_dataset(netg, tm, real, norm, lo_a, hi_a, n_starts=J, rng=np.random.RandomState(1))
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out["multistep_dataset_producer"] = {
+            "what": "synthesize_multistep_dataset: random_state_5step_random_action (5 chained ensemble steps + 5-step generator "
+                    "rollout + row assembly), host arrays in and out, wall clock",
+            "starts": J, "steps": 5, "rows_out": int(ms_d["actions"].shape[0]), "generated_frames": J * 5, "seconds": dt,
+            "generated_frames_per_sec": J * 5 / dt, "rows_per_sec": int(ms_d["actions"].shape[0]) / dt}
+        del netg, real, ms_d
+    except Exception as e:  # noqa: BLE001
+        out["multistep_dataset_producer"] = {"error": repr(e)[:200]}
     N, Bw = 40_000, 1024
     buf = SlacReplayBufferB200(N, 8, (3, 100, 100), (6,), dev)
     buf.frames = torch.randint(0, 256, (N, 100, 100, 3), dtype=torch.uint8, device=dev)

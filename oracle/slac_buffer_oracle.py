@@ -173,3 +173,37 @@ def fill_plain(buffer, dataset, reset_buff=False):
             if i == n - 1:
                 break
             buffer.reset_episode(dataset["image_observations"][i + 1])  # :400-403
+
+
+def multistep_rows(dataset, starts, history, gen):
+    """Row layout of the multi-step generated datasets (random_state_5step_*), written as the per-trajectory loop a
+    producer script would run; s2p_b200.synthesis.assemble_multistep_rows is the vectorised product form.  The
+    reference's own producer for these modes is absent; what IS the reference's is how the
+    result is consumed: the plain-trajectory branch of load_data_in_buffer (algo.py:355-405, fill_plain above with
+    reset_buff=True) -- a generated trajectory must therefore hold num_sequences rows to yield a window."""
+    keys = ("observations", "actions", "rewards", "next_observations", "image_observations", "image_observations_tp1",
+            "disagreement_uncertainty", "aleatoric_uncertainty", "timeouts")
+    rows = {k: [] for k in keys}
+    steps = gen["actions"].shape[1]
+    for j, i in enumerate(starts):
+        for r in range(i - history, i):          # the real prefix
+            rows["observations"].append(dataset["observations"][r])
+            rows["actions"].append(dataset["actions"][r])
+            rows["rewards"].append(np.float32(np.asarray(dataset["rewards"]).reshape(-1)[r]))
+            rows["next_observations"].append(dataset["next_observations"][r] if "next_observations" in dataset else dataset["observations"][r + 1])
+            rows["image_observations"].append(dataset["image_observations"][r])
+            rows["image_observations_tp1"].append(dataset["image_observations_tp1"][r] if "image_observations_tp1" in dataset
+                                                  else dataset["image_observations"][r + 1])
+            rows["disagreement_uncertainty"].append(np.zeros(1, np.float32))
+            rows["aleatoric_uncertainty"].append(np.zeros(1, np.float32))
+            rows["timeouts"].append(np.float32(0))
+        for k in range(steps):                   # the generated steps
+            for key in keys[:-1]:
+                rows[key].append(gen[key][j, k])
+            rows["timeouts"].append(np.float32(1 if k == steps - 1 else 0))
+    # sentinel: the consumer never appends a LAST row that is a timeout (algo.py:374-378); a trailing copy with
+    # timeout 0 keeps the last generated trajectory's window and cannot complete one itself
+    for key in keys[:-1]:
+        rows[key].append(rows[key][-1])
+    rows["timeouts"].append(np.float32(0))
+    return {k: np.stack(v) for k, v in rows.items()}

@@ -157,6 +157,19 @@ class SlacReplayBufferB200:
         if real:
             self._real_n = self._n                                 # :410-412
 
+    def load_data(self, dataset, generated_for_slac=False, data_mix_type=None, uncertainty_type=None,
+                  uncertainty_penalty_lambda=None):
+        """branch selection of SlacAlgorithm.load_data_in_buffer (rlkit/torch/slac/algo.py:267, :355-371) on a dataset
+        dict: the 1-step generated mode -> load_generated; the multi-step generated modes (random_state_*) and real
+        data -> the plain-trajectory loop (the reference resets its sequence buffer first for generated data, :370:
+        windows never span two load calls here, which is the same thing)."""
+        if generated_for_slac and data_mix_type == "all_state_1step_random_action":
+            return self.load_generated(dataset, uncertainty_type, uncertainty_penalty_lambda)
+        if generated_for_slac and data_mix_type not in ("random_state_5step_random_action", "random_state_1step_random_action",
+                                                        "random_state_5step_offRL_action"):
+            raise NotImplementedError(f"data_mix_type {data_mix_type} (algo.py:183-236 reads no such generated dataset)")
+        return self.load_plain(dataset, real=not generated_for_slac)
+
     # ------------------------------------------------------------------ sampling
     def gather_states(self, idxes) -> torch.Tensor:
         """float windows [B, num_seq+1, C, H, W] in [0,1] (buffer.py:132-135)"""

@@ -56,8 +56,17 @@ def main():
         SO.fill_plain(buf, loaded(d2))
         for k, v in dump(buf).items():
             out[f"{tag}_{k}"] = v
+    # ---- multi-step generated mode (random_state_5step_*): a real dataset, then a generated one through the same
+    # plain branch with generated_for_slac=True (algo.py:355-405: buff.reset() first), in ONE reference buffer
+    from slac_dataset import make_multistep  # noqa: E402
+    real, ms = make_multistep(23, lengths, 11, n_starts=9, steps=5)
+    buf = ref.ReplayBuffer(1000, 8, (C, H, W), (A,), torch.device("cpu"))
+    SO.fill_plain(buf, loaded(real))
+    SO.fill_plain(buf, loaded(ms), reset_buff=True)
+    for k, v in dump(buf).items():
+        out[f"multistep_{k}"] = v
     path = os.path.join(HERE, "slac_buffer.npz")
-    np.savez_compressed(path, seed_gen=21, seed_plain=22, lengths=np.array(lengths), tail_plain=11, sample_seed=77, **out)
+    np.savez_compressed(path, seed_gen=21, seed_plain=22, seed_multistep=23, multistep_starts=9, lengths=np.array(lengths), tail_plain=11, sample_seed=77, **out)
     print("wrote", path, os.path.getsize(path), {k: (v.shape if hasattr(v, "shape") else v) for k, v in out.items() if k.endswith("_n") or k.endswith("states")})
 
 

@@ -97,3 +97,20 @@ def test_rejects_cpu_and_bad_layout():
     d["image_observations"] = SO.to_chw(d["image_observations"]).copy()   # CHW instead of the disk layout
     with pytest.raises(RuntimeError):
         buf.load_plain(d)
+
+
+def test_multistep_generated_mode_vs_reference_buffer():
+    """random_state_5step_random_action through load_data (the consumer's branch selection, algo.py:355-371): real
+    data first, the generated trajectories appended: bit-exact against what the reference's ReplayBuffer held"""
+    from slac_dataset import make_multistep
+    g = load_golden("slac_buffer")
+    real, ms = make_multistep(int(g["seed_multistep"]), list(g["lengths"]), int(g["tail_plain"]), int(g["multistep_starts"]), 5)
+    buf = _buf()
+    buf.load_data({k: v for k, v in real.items()}, generated_for_slac=False)
+    n_real = buf._n
+    buf.load_data({k: v for k, v in ms.items() if not k.startswith("_")}, generated_for_slac=True,
+                  data_mix_type="random_state_5step_random_action")
+    assert buf._real_n == n_real and buf._n - n_real == int(g["multistep_starts"])
+    _check_against(buf, g, "multistep")
+    with pytest.raises(NotImplementedError):
+        buf.load_data(ms, generated_for_slac=True, data_mix_type="no_such_mode")
