@@ -359,6 +359,16 @@ int s2p_rad_augment(const void* in, void* out, int elem_bytes, long long N, int 
  * gray = trunc(u8_r*0.2989f + u8_g*0.587f + u8_b*0.114f); out = (mask[n] ? gray : u8) / 255.
  * in/out: float32 [N][frames*3][H][W]; mask: int32 DEVICE [N]. */
 int s2p_rad_grayscale(const float* in, float* out, long long N, int frames, int H, int W, const int* mask, void* stream);
+/* grayscale (data_augs.py:26-38), the public helper random_grayscale is built on: values taken as they are (uint8,
+ * elem_bytes 1, or float32, 4), per frame gray = float(uint8(r*0.2989f + g*0.587f + b*0.114f)) (separately rounded fp32
+ * products and sums, truncation), tiled over a new channel axis: out float32 [N][frames][3][H][W]. */
+int s2p_rad_grayscale_plain(const void* in, int elem_bytes, float* out, long long N, int frames, int H, int W, void* stream);
+/* random_convolution (data_augs.py:193-223): image n gets its own 3x3 convolution 3 -> 3 channels (padding 1, no bias;
+ * weights [N][3][3][3][3] float32 = nn.Conv2d.weight per image, drawn by the host mirror with torch's RNG in the
+ * reference's order), applied to each of its `frames` frames: in / out float32 [N][frames*3][H][W].  Replaces N
+ * nn.Conv2d launches and N torch.cat copies of the growing result by one launch.  out must not alias in. */
+int s2p_rad_random_convolution(const float* in, float* out, const float* weights, long long N, int frames, int H, int W,
+                               void* stream);
 
 #ifdef __cplusplus
 }

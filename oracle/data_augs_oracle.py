@@ -132,3 +132,28 @@ def random_translate(imgs, size, return_random_idxs=False, h1s=None, w1s=None):
 
 def no_aug(x):
     return x
+
+
+def grayscale(imgs):
+    """data_augs.py:26-38 on a numpy array [B, frames*3, H, W] (uint8 or float32, values as they are): float32 luma
+    with separately rounded fp32 products and sums, truncated to uint8, tiled over a new 3-channel axis."""
+    b, c, h, w = imgs.shape
+    x = imgs.reshape(b, c // 3, 3, h, w).astype(np.float32)
+    g = (x[:, :, 0] * np.float32(0.2989) + x[:, :, 1] * np.float32(0.587)) + x[:, :, 2] * np.float32(0.114)
+    g = g.astype(np.uint8).astype(np.float32)
+    return np.repeat(g[:, :, None], 3, axis=2)
+
+
+def random_convolution_at(imgs, weights):
+    """data_augs.py:193-223 with the per-image filters given ([B,3,3,3,3] = nn.Conv2d.weight of each transformation):
+    every frame (3 channels) of image b is convolved 3x3, padding 1, no bias, with weights[b]; float32 accumulation in
+    float64 here (the checker), compared with a tolerance."""
+    b, c, h, w = imgs.shape
+    x = imgs.reshape(b, c // 3, 3, h, w).astype(np.float64)
+    xp = np.pad(x, ((0, 0), (0, 0), (0, 0), (1, 1), (1, 1)))
+    out = np.zeros((b, c // 3, 3, h, w), dtype=np.float64)
+    for r in range(3):
+        for s in range(3):
+            patch = xp[:, :, :, r:r + h, s:s + w]                      # [b, f, ci, h, w]
+            out += np.einsum("bfchw,boc->bfohw", patch, weights[:, :, :, r, s].astype(np.float64))
+    return out.reshape(b, c, h, w).astype(np.float32)

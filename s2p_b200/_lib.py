@@ -73,6 +73,8 @@ SIGNATURES = {
     "s2p_slac_indices": (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_longlong, _vp]),
     "s2p_rad_augment": (_i, [_vp, _vp, _i, C.c_longlong, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "s2p_rad_grayscale": (_i, [_vp, _vp, C.c_longlong, _i, _i, _i, _vp, _vp]),
+    "s2p_rad_grayscale_plain": (_i, [_vp, _i, _vp, C.c_longlong, _i, _i, _i, _vp]),
+    "s2p_rad_random_convolution": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
 }
 
 _lib = None

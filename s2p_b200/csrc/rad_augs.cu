@@ -149,6 +149,77 @@ grayscale_kernel(const float* __restrict__ in, float* __restrict__ out, int fram
   }
 }
 
+// grayscale (data_augs.py:26-38), the public helper: values as they are (uint8 or float), per frame
+// gray = float(uint8(r * 0.2989f + g * 0.587f + b * 0.114f)) tiled over the three channels of a NEW axis:
+// out [N][frames][3][H][W] float32.  One thread = one pixel of one frame (three loads, three stores).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+grayscale_plain_kernel(const T* __restrict__ in, float* __restrict__ out, int frames, int HW) {
+  const unsigned t = blockIdx.x * kThreads + threadIdx.x;
+  if (t >= static_cast<unsigned>(frames) * HW) return;
+  const unsigned f = t / HW, p = t - f * HW;
+  const long long base = ((static_cast<long long>(blockIdx.y) * frames + f) * 3) * HW + p;
+  const float r = static_cast<float>(in[base]), g = static_cast<float>(in[base + HW]), b = static_cast<float>(in[base + 2ll * HW]);
+  const float s = __fadd_rn(__fadd_rn(__fmul_rn(r, 0.2989f), __fmul_rn(g, 0.587f)), __fmul_rn(b, 0.114f));
+  const float v = static_cast<float>(static_cast<uint8_t>(s));
+  __stcs(out + base, v); __stcs(out + base + HW, v); __stcs(out + base + 2ll * HW, v);
+}
+
+// random_convolution (data_augs.py:193-223, "network randomization"): every image of the batch gets its OWN
+// 3 -> 3 channel 3x3 convolution (padding 1, no bias), applied to each of its frames (3 channels per frame).  The
+// reference runs B separate nn.Conv2d calls and concatenates their outputs one by one; here the B weight sets
+// (drawn on the host side exactly as the reference draws them, s2p_b200/data_augs.py) arrive as one table and the
+// whole batch is one launch.  One thread = 4 consecutive pixels of a row x 3 output channels of one frame.
+__global__ void __launch_bounds__(kThreads)
+random_conv_kernel(const float* __restrict__ in, float* __restrict__ out, const float* __restrict__ weights,
+                   int frames, int H, int W) {
+  __shared__ float ws[81];
+  const long long n = blockIdx.y;
+  if (threadIdx.x < 81) ws[threadIdx.x] = __ldg(weights + n * 81 + threadIdx.x);   // [co][ci][r][s]
+  __syncthreads();
+  const unsigned quads = static_cast<unsigned>(W + 3) / 4;
+  const unsigned t = blockIdx.x * kThreads + threadIdx.x;
+  if (t >= static_cast<unsigned>(frames) * H * quads) return;
+  const int xq = static_cast<int>(t % quads);
+  const unsigned fy = t / quads;
+  const int y = static_cast<int>(fy % H), f = static_cast<int>(fy / H);
+  const int x0 = xq * 4;
+  const long long HW = static_cast<long long>(H) * W;
+  const float* src = in + (n * frames + f) * 3 * HW;
+  float acc[3][4];
+#pragma unroll
+  for (int co = 0; co < 3; ++co)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[co][i] = 0.f;
+#pragma unroll
+  for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int yy = y + r - 1;
+      float v[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int xx = x0 + j - 1;
+        v[j] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(src + ci * HW + static_cast<long long>(yy) * W + xx) : 0.f;
+      }
+#pragma unroll
+      for (int s = 0; s < 3; ++s)
+#pragma unroll
+        for (int co = 0; co < 3; ++co) {
+          const float wv = ws[((co * 3 + ci) * 3 + r) * 3 + s];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) acc[co][i] = fmaf(v[i + s], wv, acc[co][i]);
+        }
+    }
+  }
+  float* dst = out + (n * frames + f) * 3 * HW + static_cast<long long>(y) * W + x0;
+#pragma unroll
+  for (int co = 0; co < 3; ++co)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (x0 + i < W) dst[co * HW + i] = acc[co][i];
+}
+
 // uint8 fast path (rows of whole 32-bit words, 4-B aligned buffers): one thread = 16 consecutive output bytes of a
 // row.  The source run of a crop / translate / cutout / flip / half turn is contiguous in memory at an arbitrary byte
 // offset: five ALIGNED 32-bit loads cover it and funnel shifts realign it (a byte-reversing permute for the mirrored
@@ -377,6 +448,53 @@ extern "C" int s2p_rad_grayscale(const float* in, float* out, long long N, int f
     else rad::grayscale_kernel<1><<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per * 3, out + n0 * per * 3, frames, HW, mask + n0);
     count_launch();
     const int rc = check_launch("rad grayscale_kernel");
+    if (rc != S2P_OK) return rc;
+  }
+  return S2P_OK;
+}
+
+extern "C" int s2p_rad_grayscale_plain(const void* in, int elem_bytes, float* out, long long N, int frames, int H, int W,
+                                       void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(in && out, "rad_grayscale_plain: null pointer");
+  S2P_CHECK_ARG(elem_bytes == 1 || elem_bytes == 4, "rad_grayscale_plain: elem_bytes=%d (uint8 or float32)", elem_bytes);
+  S2P_CHECK_ARG(N > 0 && frames > 0 && H > 0 && W > 0, "rad_grayscale_plain: bad dims");
+  const int HW = H * W;
+  const long long per = static_cast<long long>(frames) * HW;
+  S2P_CHECK_ARG(per < (1ll << 31), "rad_grayscale_plain: image too large");
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned gx = static_cast<unsigned>((per + rad::kThreads - 1) / rad::kThreads);
+  for (long long n0 = 0; n0 < N; n0 += 65535) {
+    const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
+    if (elem_bytes == 1)
+      rad::grayscale_plain_kernel<uint8_t><<<dim3(gx, ny), rad::kThreads, 0, st>>>(static_cast<const uint8_t*>(in) + n0 * per * 3,
+                                                                                  out + n0 * per * 3, frames, HW);
+    else
+      rad::grayscale_plain_kernel<float><<<dim3(gx, ny), rad::kThreads, 0, st>>>(static_cast<const float*>(in) + n0 * per * 3,
+                                                                                out + n0 * per * 3, frames, HW);
+    count_launch();
+    const int rc = check_launch("rad grayscale_plain_kernel");
+    if (rc != S2P_OK) return rc;
+  }
+  return S2P_OK;
+}
+
+extern "C" int s2p_rad_random_convolution(const float* in, float* out, const float* weights, long long N, int frames, int H,
+                                          int W, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(in && out && weights, "rad_random_convolution: null pointer");
+  S2P_CHECK_ARG(N > 0 && frames > 0 && H > 0 && W > 0, "rad_random_convolution: bad dims");
+  S2P_CHECK_ARG(in != out, "rad_random_convolution: out must not alias in");
+  const long long slots = static_cast<long long>(frames) * H * ((W + 3) / 4);
+  S2P_CHECK_ARG(slots < (1ll << 31), "rad_random_convolution: image too large");
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned gx = static_cast<unsigned>((slots + rad::kThreads - 1) / rad::kThreads);
+  const long long per = static_cast<long long>(frames) * 3 * H * W;
+  for (long long n0 = 0; n0 < N; n0 += 65535) {
+    const unsigned ny = static_cast<unsigned>(N - n0 < 65535 ? N - n0 : 65535);
+    rad::random_conv_kernel<<<dim3(gx, ny), rad::kThreads, 0, st>>>(in + n0 * per, out + n0 * per, weights + n0 * 81, frames, H, W);
+    count_launch();
+    const int rc = check_launch("rad random_conv_kernel");
     if (rc != S2P_OK) return rc;
   }
   return S2P_OK;

@@ -11,7 +11,7 @@ translate).  The per-image draws are made on the host and uploaded as int32 (a f
 
 No CPU path: without a CUDA device or libs2p_sm100.so every function raises.
 Not provided: random_color_jitter (its ColorJitterLayer import is commented out in the reference, data_augs.py:5,
-so it cannot run there either) and random_convolution (weights drawn from torch's RNG inside the call).
+so it raises NameError there too).
 """
 from __future__ import annotations
 
@@ -130,6 +130,54 @@ def random_grayscale(images, p=.3, device=None):
             _lib.check(_lib.load().s2p_rad_grayscale(x.data_ptr(), out.data_ptr(), n, c // 3, h, w, m.data_ptr(), _stream()),
                        "s2p_rad_grayscale")
     return _leave(out, was_np)
+
+
+def grayscale(imgs):
+    """data_augs.py:26-38: [B, frames*3, H, W] (uint8 or float32, values as they are) -> float32 [B, frames, 3, H, W],
+    every frame replaced by its truncated luma, tiled over the 3 channels."""
+    x, _ = _enter(imgs, None)
+    n, c, h, w = x.shape
+    if c % 3:
+        raise RuntimeError("grayscale: 3 channels per frame")
+    out = torch.empty(n, c // 3, 3, h, w, dtype=torch.float32, device=x.device)
+    if n:
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.load().s2p_rad_grayscale_plain(x.data_ptr(), _ELEM[x.dtype], out.data_ptr(), n, c // 3, h, w, _stream()),
+                       "s2p_rad_grayscale_plain")
+    return out
+
+
+def random_convolution(imgs, weights=None, return_weights=False):
+    """data_augs.py:193-223 ("network randomization"): every image gets its own random 3x3 conv 3 -> 3 channels
+    (xavier-normal weights, padding 1, no bias) applied to each of its frames.  imgs: float32 CUDA [B, frames*3, H, W].
+
+    The weights come from torch's RNG exactly as in the reference: it constructs ``nn.Conv2d(3, 3, 3, bias=False,
+    padding=1)`` (whose default init consumes the CPU generator), moves it to the images' device and calls
+    ``xavier_normal_`` on its weight once per image (the DEVICE generator) -- the same calls are made here, so a
+    caller that seeds torch gets the reference's filters.  What changes is the arithmetic's shape: one launch over
+    the batch instead of B conv launches and B torch.cat copies of a growing result.  ``weights`` ([B,3,3,3,3]
+    float32) overrides the draw (tests, replay)."""
+    x, _ = _enter(imgs, None)
+    if x.dtype != torch.float32 or x.shape[1] % 3:
+        raise RuntimeError("random_convolution: float32 images with 3 channels per frame")
+    n, c, h, w = x.shape
+    if weights is None:
+        rand_conv = torch.nn.Conv2d(3, 3, kernel_size=3, bias=False, padding=1).to(x.device)      # same RNG consumption as :208
+        rand_conv.weight.requires_grad = False
+        weights = torch.empty(n, 3, 3, 3, 3, dtype=torch.float32, device=x.device)
+        for i in range(n):                                                                       # :211-212, one draw per image
+            torch.nn.init.xavier_normal_(rand_conv.weight.data)
+            weights[i].copy_(rand_conv.weight.data)
+    else:
+        weights = torch.as_tensor(weights, dtype=torch.float32).to(x.device).contiguous()
+        if tuple(weights.shape) != (n, 3, 3, 3, 3):
+            raise RuntimeError(f"random_convolution: weights must be [{n}, 3, 3, 3, 3]")
+    out = torch.empty_like(x)
+    if n:
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.load().s2p_rad_random_convolution(x.data_ptr(), out.data_ptr(), weights.data_ptr(), n, c // 3, h, w,
+                                                              _stream()), "s2p_rad_random_convolution")
+    return (out, weights) if return_weights else out
 
 
 def random_translate(imgs, size, return_random_idxs=False, h1s=None, w1s=None, device=None):

@@ -167,3 +167,45 @@ def test_errors_and_empty():
     assert b"rad_augment" in lib.s2p_last_error_string()
     e = R.random_cutout(torch.zeros(0, 3, 8, 8, dtype=torch.uint8, device="cuda"))
     assert e.shape == (0, 3, 8, 8)
+
+
+@pytest.mark.parametrize("tag", ["u8", "f32"])
+def test_grayscale_helper_vs_reference_output(tag):
+    g = load_golden("data_augs")
+    u8, f32 = golden_inputs(g)
+    x = torch.from_numpy(u8).cuda() if tag == "u8" else (torch.from_numpy(f32) * 255.).cuda()
+    out = rad().grayscale(x)
+    assert out.dtype == torch.float32 and np.array_equal(out.cpu().numpy(), g[f"gray_plain_{tag}"])
+    big = torch.randint(0, 256, (64, 9, 100, 100), dtype=torch.uint8, device="cuda")
+    assert np.array_equal(rad().grayscale(big).cpu().numpy(), DO.grayscale(big.cpu().numpy()))
+
+
+def test_random_convolution_vs_reference_output_and_draw_order():
+    """(1) the reference's own output for the filters it drew (fixture), <= 2e-6 relative (fp32 summation order);
+    (2) at the repo's frame shape against the float64 oracle; (3) the filters are drawn with the reference's calls in
+    the reference's order: nn.Conv2d construction (CPU generator), then one xavier_normal_ per image on the device."""
+    R = rad()
+    g = load_golden("data_augs")
+    _, f32 = golden_inputs(g)
+    out = R.random_convolution(torch.from_numpy(f32).cuda(), weights=g["randconv_weights"])
+    ref = g["randconv_f32"]
+    assert np.abs(out.cpu().numpy() - ref).max() <= 2e-6 * np.abs(ref).max()
+    x = torch.rand(16, 9, 100, 100, device="cuda")
+    torch.manual_seed(5)
+    torch.cuda.manual_seed(6)
+    y, w = R.random_convolution(x, return_weights=True)
+    want = DO.random_convolution_at(x.cpu().numpy(), w.cpu().numpy())
+    assert np.abs(y.cpu().numpy() - want).max() <= 2e-6 * np.abs(want).max()
+    torch.manual_seed(5)
+    torch.cuda.manual_seed(6)
+    conv = torch.nn.Conv2d(3, 3, kernel_size=3, bias=False, padding=1).cuda()       # data_augs.py:208
+    ws = []
+    for _ in range(16):
+        torch.nn.init.xavier_normal_(conv.weight.data)                              # :212
+        ws.append(conv.weight.data.clone())
+    assert torch.equal(w, torch.stack(ws))
+    # ragged width (not a multiple of 4) and a single frame
+    xs = torch.rand(3, 3, 7, 9, device="cuda")
+    ys, wsmall = R.random_convolution(xs, return_weights=True)
+    want = DO.random_convolution_at(xs.cpu().numpy(), wsmall.cpu().numpy())
+    assert np.abs(ys.cpu().numpy() - want).max() <= 2e-6 * np.abs(want).max() + 1e-7

@@ -50,3 +50,22 @@ def test_translate_returns_and_reuses_draws():
     again = DO.random_translate(u8, 9, **idx)
     assert np.array_equal(out, again)
     assert np.array_equal(DO.crop_at(out, idx["h1s"], idx["w1s"], 5), u8)   # crop undoes translate
+
+
+def test_grayscale_helper_matches_reference():
+    g = load_golden("data_augs")
+    u8, f32 = golden_inputs(g)
+    assert np.array_equal(DO.grayscale(u8), g["gray_plain_u8"])
+    assert np.array_equal(DO.grayscale((f32 * np.float32(255.0))), g["gray_plain_f32"])
+    assert g["gray_plain_u8"].shape == (u8.shape[0], u8.shape[1] // 3, 3, u8.shape[2], u8.shape[3])
+
+
+def test_random_convolution_matches_reference():
+    """the reference's own output for the filters IT drew (torch.manual_seed, kept in the fixture)"""
+    g = load_golden("data_augs")
+    _, f32 = golden_inputs(g)
+    w = g["randconv_weights"]
+    assert w.shape == (f32.shape[0], 3, 3, 3, 3)
+    out = DO.random_convolution_at(f32, w)
+    ref = g["randconv_f32"]
+    assert out.shape == ref.shape and np.abs(out - ref).max() <= 2e-6 * np.abs(ref).max()
