@@ -131,7 +131,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
       if (++stage == kWgStages) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    constexpr uint32_t idesc = umma_idesc_bf16_mn(128, BN);
+    // The taps of a stage are ONE wide MMA where they fit (N = G * BN <= 256): their X tiles sit in consecutive
+    // 64-channel blocks of the stage (LBO apart, exactly like the blocks of a wider ci tile) and their accumulators in
+    // consecutive TMEM columns, so a group of G taps is an MN-major B operand of G * BN columns.  The dY slice (A,
+    // 128 x 16) is then read from shared memory once per group instead of once per tap: 3 taps x 64 ci go from
+    // 3 x (4 + 2) KB to 4 + 6 KB of operand reads per 96 MMA clocks (192 -> 107 B/clk against the 128 B/clk port).
+    constexpr int G = (256 / BN) < TAPS ? (256 / BN) : TAPS;          // taps per MMA
+    constexpr uint32_t idesc_full = umma_idesc_bf16_mn(128, G * BN);
+    constexpr int kRest = TAPS % G;                                    // taps of a last, narrower MMA
+    constexpr uint32_t idesc_rest = umma_idesc_bf16_mn(128, (kRest ? kRest : G) * BN);
     const uint32_t lbo = static_cast<uint32_t>(atom_stride), sbo = 1024u;
     int stage = 0;
     uint32_t phase = 0;
@@ -142,8 +150,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
       if (elect_one()) {
         const uint32_t s0 = smem_u32(smem + stage * stage_bytes);
         const uint64_t da = umma_desc_mn_sw128(s0, lbo, sbo);
-        for (int s = 0; s < TAPS; ++s) {
+        for (int s = 0; s < TAPS; s += G) {
           const uint64_t db = umma_desc_mn_sw128(s0 + (kAtomsA + s * kAtomsB) * atom_stride, lbo, sbo);
+          const uint32_t idesc = (s + G <= TAPS) ? idesc_full : idesc_rest;
           for (int k = 0; k < ksteps; ++k) {
             // K = 16 pixel rows = two 8-row groups = 2048 B further into every 64-channel block
             umma_bf16(tmem_base + s * BN, da + static_cast<uint64_t>(k * (2048 >> 4)),
