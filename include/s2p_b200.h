@@ -53,10 +53,11 @@ long long s2p_launch_count(void);
  * MAT.mlp_shared/mlp_gamma/mlp_beta, ImageEncoder.conv2/conv3, S2PGenerator.head).
  * y = act(conv(x, w) + bias + residual); optionally emits per-image per-channel
  * (sum, sumsq) partials of the STORED bf16 values for the following instance norm:
- * stats_partial is [B][s2p_conv_stats_rows(Hout,Wout)][Cout][2] fp32.
+ * stats_partial is [B][s2p_conv_stats_rows(Hout,Wout,Cout,ksize,stride)][Cout][2] fp32 (the row count follows the
+ * tile geometry the convolution will use: 3x3 stride-1 convs with Cout <= 64 run in a horizontal-halo layout).
  * Requires Cin % 64 == 0, Cout % 64 == 0, ksize in 1..5 (3x3/1x1: generator; 4x4: discriminator; 5x5: SLAC),
  * stride in {1,2}, explicit symmetric zero padding `pad` (nn.Conv2d padding). */
-int s2p_conv_stats_rows(int Hout, int Wout);
+int s2p_conv_stats_rows(int Hout, int Wout, int Cout, int ksize, int stride);
 int s2p_conv_igemm_fwd(const void* x, int x_pitch, const void* w_packed, const float* bias,
                        const void* residual, int res_pitch, void* y, int y_pitch,
                        float* stats_partial, int B, int Hin, int Win, int Cin, int Cout, int ksize,

@@ -22,7 +22,7 @@ SIGNATURES = {
     "s2p_version": (_i, []),
     "s2p_last_error_string": (C.c_char_p, []),
     "s2p_launch_count": (C.c_longlong, []),
-    "s2p_conv_stats_rows": (_i, [_i, _i]),
+    "s2p_conv_stats_rows": (_i, [_i, _i, _i, _i, _i]),
     "s2p_conv_igemm_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_conv_igemm_fwd2": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_conv_wgrad_workspace_bytes": (C.c_longlong, [_i, _i, _i, _i, _i, _i, _i, _i]),

@@ -247,7 +247,8 @@ def tanh_out(rgb, c=3):
     return TanhOutFn.apply(rgb, c)
 
 
-def conv_stats(y_shape, device):
-    """scratch for the conv epilogue's statistics partials of an output of shape [B,H,W,C]"""
+def conv_stats(y_shape, device, ksize=3, stride=1):
+    """scratch for the conv epilogue's statistics partials of an output of shape [B,H,W,C] (the row count follows the
+    tile geometry of the conv that writes them: ops.conv_stats_rows)"""
     b, h, w, c = y_shape
-    return torch.empty(b, ops.conv_stats_rows(h, w), c, 2, dtype=torch.float32, device=device)
+    return torch.empty(b, ops.conv_stats_rows(h, w, c, ksize, stride), c, 2, dtype=torch.float32, device=device)

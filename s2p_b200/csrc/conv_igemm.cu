@@ -35,6 +35,7 @@ struct ConvParams {
   int Cin, Cout;
   int R, S, pad, stride;
   int tile_w, tile_h, tiles_x, tiles_y;
+  int mpitch;             // M rows per tile row: tile_w, or tile_w + 2 in the horizontal-halo mode
   int num_m_tiles, num_n_tiles;
   int out_pitch, res_pitch;
   int act;                // 0 none, 1 relu, 2 lrelu(0.2)
@@ -43,7 +44,7 @@ struct ConvParams {
   const __nv_bfloat16* residual_lo;   // low halves of a wide residual (same pitch) or null
   __nv_bfloat16* out;
   __nv_bfloat16* out_lo;              // low halves of a wide output (same pitch) or null
-  float* stats_partial;   // [B][tiles_per_img*4][Cout][2] (sum, sumsq) or null
+  float* stats_partial;   // [B][tiles_per_img][Cout][2] (sum, sumsq) or null
   // fused MAT epilogue (conv_mat_fused): the accumulators are the spatial gamma|beta maps,
   // the stored value is act((x*A + Bc) * (G1 + gamma) + (B0 + beta)) with (A,Bc,G1,B0) = mat_tab[n][c]
   // the pre-norm activation x [B][H/up][W/up][..] arrives through tmap_x: per tile the producer warp TMA-loads the
@@ -67,20 +68,26 @@ struct ConvParams {
 
 enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
 
-template <int BLOCK_N, int CL, int EPI>
+template <int BLOCK_N, int CL, int EPI, bool HH = false>
 struct ConvCfg {
   static constexpr int kBlockM = 128;
   static constexpr int kBlockK = 64;
   static constexpr int kABytes = kBlockM * kBlockK * 2;        // 16 KB
-  static constexpr int kBBytes = BLOCK_N / CL * kBlockK * 2;   // a CTA of a pair holds half of the weight tile
-  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBTapBytes = BLOCK_N / CL * kBlockK * 2;   // one tap's weight tile; a CTA of a pair holds half of it
+  // HH (horizontal halo, thin tiles): a stage carries ONE activation box with a 1-pixel halo left and right and the
+  // weight tiles of the three taps of a filter row that read it
+  static constexpr int kBBytes = (HH ? 3 : 1) * kBTapBytes;
+  static constexpr int kStageBytes = kABytes + ((kBBytes + 1023) / 1024) * 1024;
   static constexpr int kStoreBytes = 8 * 2048;   // per-epilogue-warp 32 x 64 B transpose rows
   static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
   // fused MAT epilogue: the tile's pre-norm activation x, TMA-loaded as 64-channel boxes of <= 16 KB
   // (BLOCK_N / 128 boxes of high halves + as many of low halves when x is stored wide)
   static constexpr int kXBoxes = EPI == kEpiMat ? 2 * (BLOCK_N / 128) : 0;
   static constexpr int kXBytes = kXBoxes * kABytes;
-  static constexpr int kFixedBytes = 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes + kXBytes;
+  // statistics: the four lane-quarter warps of a tile combine their (sum, sumsq) columns here before ONE partial row
+  // per tile goes to global memory (double buffered by tile parity)
+  static constexpr int kStatBytes = EPI == kEpiPlain ? 2 * 4 * BLOCK_N * 8 : 0;
+  static constexpr int kFixedBytes = 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes + kXBytes + kStatBytes;
   static constexpr int kMaxStages = (227 * 1024 - kFixedBytes) / kStageBytes;
   // Ring depth.  Measured (profiles/r02_stage_sweep.txt): the wide tiles do not gain from more than 4-5 stages --
   // their operands come from L2 and 4 x 256 clk of look-ahead covers it -- while every KB of shared memory NOT
@@ -157,12 +164,12 @@ __device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* pa
   __syncwarp();
 }
 
-template <int BLOCK_N, int EPI, int CL>
+template <int BLOCK_N, int EPI, int CL, bool HH>
 __global__ void __launch_bounds__(320, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_a2, const __grid_constant__ CUtensorMap tmap_x,
                   const ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N, CL, EPI>;
+  using Cfg = ConvCfg<BLOCK_N, CL, EPI, HH>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   // [operand ring | x boxes (1024-aligned: the ring is a multiple of 8 KB) | barriers | modulation table | store staging]
@@ -176,6 +183,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_full + 1);
   float4* tab_smem = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(bars) + 256);
   uint8_t* store_smem = reinterpret_cast<uint8_t*>(bars) + 256 + Cfg::kTabBytes;
+  float2* stat_smem = reinterpret_cast<float2*>(store_smem + Cfg::kStoreBytes);   // [2][4 quarters][BLOCK_N]
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -220,8 +228,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int cchunks = p.Cin / Cfg::kBlockK;
   const int num_kb_main = p.R * p.S * cchunks;
   const int num_kb = num_kb_main + p.kb2;      // the second operand's k-blocks follow the filter taps
-  const uint32_t a_bytes = static_cast<uint32_t>(p.tile_w * p.tile_h) * 128u;
+  // HH: the M rows of a tile are laid out with pitch tile_w + 2 (the halo columns are rows whose results are
+  // discarded), so that tap s of a filter row is the SAME activation box read s rows further down: a K-major
+  // SWIZZLE_128B descriptor may start at any 128-byte row of a tile TMA wrote (profiles/r01_umma_rowshift_probe.txt).
+  // One box per (filter row, channel chunk) feeds three taps: 2.8x fewer activation bytes enter the SM, which is what
+  // bounds the thin (Cout <= 64) tiles; the price is 100 live rows of 128 instead of 125.
+  const uint32_t a_bytes = static_cast<uint32_t>(p.mpitch * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
+  const int num_kb_hh = HH ? p.R * cchunks + p.kb2 : 0;      // HH: a k-block = (filter row, chunk): three taps
 
   // The producer and MMA loops run with the whole warp converged (uniform control flow, uniform
   // operands) and elect one lane only around the asynchronous issue itself: a loop written under
@@ -237,6 +251,42 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int h0 = (t / p.tiles_x) * p.tile_h, w0 = (t % p.tiles_x) * p.tile_w;
       const int hin0 = h0 * p.stride - p.pad, win0 = w0 * p.stride - p.pad;
       int r = 0, sx = 0, cc = 0;
+      if constexpr (HH) {
+        for (int kb = 0; kb < num_kb_hh; ++kb) {
+          const bool main_kb = kb < p.R * cchunks;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (elect_one()) {
+            uint8_t* sa = smem + stage * Cfg::kStageBytes;
+            uint8_t* sb = sa + Cfg::kABytes;
+            const int rr = kb / cchunks, ck = kb - rr * cchunks;
+            int ach = ck * Cfg::kBlockK;
+            if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
+            const int ntap = main_kb ? 3 : 1;
+            const uint32_t tx = (a_bytes + static_cast<uint32_t>(ntap) * Cfg::kBTapBytes) * CL;
+            if constexpr (CL > 1) {
+              constexpr int kPart = BLOCK_N / CL;
+              if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx);
+              const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+              if (main_kb) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, w0 - 1, h0 - 1 + rr, img);
+              else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - p.R * cchunks) * Cfg::kBlockK, w0 - 1, h0, img);
+              for (int s = 0; s < ntap; ++s)
+                tma_load_2d_pair(sb + s * Cfg::kBTapBytes, &tmap_b, lead_bar,
+                                 main_kb ? ((rr * 3 + s) * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK,
+                                 n_tile * BLOCK_N + cta_rank * kPart);
+            } else {
+              mbar_arrive_expect_tx(&full_bar[stage], tx);
+              if (main_kb) tma_load_4d(sa, &tmap_a, &full_bar[stage], ach, w0 - 1, h0 - 1 + rr, img);
+              else tma_load_4d(sa, &tmap_a2, &full_bar[stage], (kb - p.R * cchunks) * Cfg::kBlockK, w0 - 1, h0, img);
+              for (int s = 0; s < ntap; ++s)
+                tma_load_2d(sb + s * Cfg::kBTapBytes, &tmap_b, &full_bar[stage],
+                            main_kb ? ((rr * 3 + s) * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK,
+                            n_tile * BLOCK_N);
+            }
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      } else {
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
@@ -262,6 +312,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
+      }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (pair leader only)
@@ -277,6 +328,38 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+        if constexpr (HH) {
+          for (int kb = 0; kb < num_kb_hh; ++kb) {
+            const bool main_kb = kb < p.R * cchunks;
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t da = desc0 + static_cast<uint64_t>(stage * (Cfg::kStageBytes >> 4));
+              const uint64_t db = da + (Cfg::kABytes >> 4);
+              // tap s reads the box s rows (s * 128 B = 8 descriptor units) further down; the second operand (a 1x1
+              // convolution) reads its box at the centre column: one row down
+              const int s_lo = main_kb ? 0 : 1, s_hi = main_kb ? 3 : 2;
+              for (int s = s_lo; s < s_hi; ++s) {
+                const uint64_t das = da + 8u * s, dbs = db + (main_kb ? s : 0) * (Cfg::kBTapBytes >> 4);
+#pragma unroll
+                for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
+                  const uint32_t accum = (kb != 0 || s != s_lo || k != 0) ? 1u : 0u;
+                  if constexpr (CL > 1) umma_bf16_pair(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
+                  else umma_bf16(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
+                }
+              }
+              if constexpr (CL > 1) {
+                umma_commit_pair(&empty_bar[stage], 3);
+                if (kb == num_kb_hh - 1) umma_commit_pair(&tmem_full[acc], 3);
+              } else {
+                umma_commit(&empty_bar[stage]);
+                if (kb == num_kb_hh - 1) umma_commit(&tmem_full[acc]);
+              }
+            }
+            __syncwarp();
+            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          }
+        } else {
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -301,6 +384,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
+        }
       }
     }
   } else if (warp >= 2) {
@@ -313,7 +397,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int half = (warp - 2) >> 2;
     const int et = threadIdx.x - 64;  // 0..255 inside the epilogue group
     const int m = q * 32 + lane;      // accumulator row = pixel inside the tile
-    const int my = m / p.tile_w, mx = m - my * p.tile_w;
+    const int my = m / p.mpitch, mx = m - my * p.mpitch;   // (HH: mpitch = tile_w + 2, columns >= tile_w are halo rows)
     const float* bias_s = p.bias;
     bool bias_staged = false;
     if constexpr (EPI == kEpiPlain) {
@@ -334,7 +418,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const bool live = m_tile < p.num_m_tiles;     // false only for a pair's dummy tile
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
       const int h = (t / p.tiles_x) * p.tile_h + my, w = (t % p.tiles_x) * p.tile_w + mx;
-      const bool valid = live && (my < p.tile_h) && (h < p.H) && (w < p.W);
+      const bool valid = live && (mx < p.tile_w) && (my < p.tile_h) && (h < p.H) && (w < p.W);
       const size_t pix = (static_cast<size_t>(img) * p.H + h) * p.W + w;
       const int n0 = n_tile * BLOCK_N;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::kAccStride;
@@ -577,9 +661,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
             for (int j = 0; j < 32; ++j) s1[j] = valid ? v[j] * v[j] : 0.f;
             const float cq = warp_colsum32(s1, lane);
-            const size_t prow = (static_cast<size_t>(img) * tiles_per_img + t) * 4 + q;
-            float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + ch + lane;
-            *dst = make_float2(cs, cq);
+            stat_smem[((acc * 4 + q) * BLOCK_N) + c * 32 + lane] = make_float2(cs, cq);
+          }
+        }
+        if (p.stats_partial != nullptr && live) {
+          // one partial row per TILE: the quarter-0 warp of each column half adds the four quarters in a fixed order
+          // (4x fewer partial rows for the finalize kernels to read: they were 50 MB per 100x100 layer and micro-batch)
+          if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
+          else asm volatile("bar.sync 3, 128;" ::: "memory");
+          if (q == 0) {
+            const size_t prow = static_cast<size_t>(img) * tiles_per_img + t;
+            float2* dst = reinterpret_cast<float2*>(p.stats_partial) + prow * p.Cout + n0;
+#pragma unroll 1
+            for (int i = 0; i < kChunks; ++i) {
+              const int col = (cbeg + i) * 32 + lane;
+              const float2 a0 = stat_smem[(acc * 4 + 0) * BLOCK_N + col], a1 = stat_smem[(acc * 4 + 1) * BLOCK_N + col];
+              const float2 a2 = stat_smem[(acc * 4 + 2) * BLOCK_N + col], a3 = stat_smem[(acc * 4 + 3) * BLOCK_N + col];
+              dst[col] = make_float2(((a0.x + a1.x) + a2.x) + a3.x, ((a0.y + a1.y) + a2.y) + a3.y);
+            }
           }
         }
       }
@@ -633,14 +732,36 @@ void conv_pick_tile(int H, int W, int max_box_w, int* tw_out, int* th_out) {
   *th_out = bth;
 }
 
-template <int BLOCK_N, int EPI, int CL>
+// horizontal-halo geometry: tile_w x tile_h output pixels laid out as tile_h rows of tile_w + 2 M-rows (<= 128 in all)
+void conv_pick_tile_hh(int H, int W, int* tw_out, int* th_out) {
+  double best = -1.0;
+  int btw = 1, bth = 1;
+  for (int tw = 1; tw <= W && tw + 2 <= 128; ++tw) {
+    int th = 128 / (tw + 2);
+    if (th > H) th = H;
+    if (th < 1) continue;
+    const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
+    const double eff = static_cast<double>(H) * W / (tiles * 128.0);
+    if (eff > best + 1e-9 || (eff > best - 1e-9 && tw > btw)) { best = eff; btw = tw; bth = th; }
+  }
+  *tw_out = btw;
+  *th_out = bth;
+}
+
+// which convolutions run in the horizontal-halo mode: 3x3 stride-1 'same' convs whose accumulator tile is at most 64
+// columns wide (operand-ingest bound otherwise: 35 % tensor pipe at Cout = 64, 8 % for ToRGB)
+static bool conv_uses_hh(int Cout_tile, int ksize, int stride, int pad, int epi) {
+  return ksize == 3 && stride == 1 && pad == 1 && Cout_tile <= 64 && epi != kEpiMat;
+}
+
+template <int BLOCK_N, int EPI, int CL, bool HH = false>
 static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const CUtensorMap& tx,
                           const ConvParams& p, cudaStream_t st) {
-  using Cfg = ConvCfg<BLOCK_N, CL, EPI>;
+  using Cfg = ConvCfg<BLOCK_N, CL, EPI, HH>;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   const int dev = current_device();
   if (!configured[dev]) {
-    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI, CL>,
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, EPI, CL, HH>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured[dev] = true;
   }
@@ -659,7 +780,7 @@ static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL>, ta, tb, ta2, tx, p));
+  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<BLOCK_N, EPI, CL, HH>, ta, tb, ta2, tx, p));
   count_launch();
   return check_launch("conv_igemm_kernel");
 }
@@ -674,19 +795,21 @@ int conv_cluster_size() {
   return cl;
 }
 
-template <int BLOCK_N, int EPI>
+template <int BLOCK_N, int EPI, bool HH = false>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const CUtensorMap& tx,
                        const ConvParams& p, cudaStream_t st) {
-  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2>(ta, tb, ta2, tx, p, st);
-  return launch_conv_cl<BLOCK_N, EPI, 1>(ta, tb, ta2, tx, p, st);
+  if (conv_cluster_size() == 2) return launch_conv_cl<BLOCK_N, EPI, 2, HH>(ta, tb, ta2, tx, p, st);
+  return launch_conv_cl<BLOCK_N, EPI, 1, HH>(ta, tb, ta2, tx, p, st);
 }
 
 }  // namespace s2p
 
-extern "C" int s2p_conv_stats_rows(int Hout, int Wout) {
+extern "C" int s2p_conv_stats_rows(int Hout, int Wout, int Cout, int ksize, int stride) {
   int tw, th;
-  s2p::conv_pick_tile(Hout, Wout, 128, &tw, &th);
-  return ((Wout + tw - 1) / tw) * ((Hout + th - 1) / th) * 4;
+  const int block_n = (Cout % 256 == 0) ? 256 : (Cout % 192 == 0) ? 192 : (Cout % 128 == 0) ? 128 : 64;
+  if (s2p::conv_uses_hh(block_n, ksize, stride, ksize / 2, s2p::kEpiPlain)) s2p::conv_pick_tile_hh(Hout, Wout, &tw, &th);
+  else s2p::conv_pick_tile(Hout, Wout, 128, &tw, &th);
+  return ((Wout + tw - 1) / tw) * ((Hout + th - 1) / th);   // one partial row per tile
 }
 
 namespace s2p {
@@ -705,7 +828,10 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
   p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
   if (static_cast<long long>(B) * p.H * p.W >= (1LL << 32))
     return set_error(S2P_ERR_BAD_ARG, "conv: B*H*W must be below 2^32 pixels per call");
-  conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
+  const bool hh = conv_uses_hh(block_n, ksize, stride, pad, epi);
+  if (hh) conv_pick_tile_hh(p.H, p.W, &p.tile_w, &p.tile_h);
+  else conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
+  p.mpitch = hh ? p.tile_w + 2 : p.tile_w;
   p.tiles_x = (p.W + p.tile_w - 1) / p.tile_w;
   p.tiles_y = (p.H + p.tile_h - 1) / p.tile_h;
   p.num_m_tiles = B * p.tiles_x * p.tiles_y;
@@ -719,6 +845,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     cuuint64_t strides[3] = {(cuuint64_t)x_pitch * 2, (cuuint64_t)x_pitch * 2 * Win,
                              (cuuint64_t)x_pitch * 2 * Win * Hin};
     cuuint32_t box[4] = {64, (cuuint32_t)(p.tile_w * stride), (cuuint32_t)(p.tile_h * stride), 1};
+    if (hh) box[1] = (cuuint32_t)p.mpitch;      // one box per filter row: the tile's columns plus a halo column each side
     cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
     CUresult r = encode(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box,
                         estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -741,7 +868,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     cuuint64_t dims[4] = {(cuuint64_t)Cin2, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)B};
     cuuint64_t strides[3] = {(cuuint64_t)x2_pitch * 2, (cuuint64_t)x2_pitch * 2 * p.W,
                              (cuuint64_t)x2_pitch * 2 * p.W * p.H};
-    cuuint32_t box[4] = {64, (cuuint32_t)p.tile_w, (cuuint32_t)p.tile_h, 1};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.mpitch, (cuuint32_t)p.tile_h, 1};   // (halo mode: same row pitch as the main operand)
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(&ta2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x2), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -769,7 +896,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv_mat_fused: x tensor map encode failed (CUresult %d)", (int)r);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (epi == kEpiToRGB) return launch_conv<16, kEpiToRGB>(ta, tb, ta2, tx, p, st);
+  if (epi == kEpiToRGB) return hh ? launch_conv<16, kEpiToRGB, true>(ta, tb, ta2, tx, p, st) : launch_conv<16, kEpiToRGB>(ta, tb, ta2, tx, p, st);
   if (epi == kEpiMat) {
     switch (block_n) {
       case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, tx, p, st);
@@ -780,7 +907,7 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     case 256: return launch_conv<256, kEpiPlain>(ta, tb, ta2, tx, p, st);
     case 192: return launch_conv<192, kEpiPlain>(ta, tb, ta2, tx, p, st);
     case 128: return launch_conv<128, kEpiPlain>(ta, tb, ta2, tx, p, st);
-    default: return launch_conv<64, kEpiPlain>(ta, tb, ta2, tx, p, st);
+    default: return hh ? launch_conv<64, kEpiPlain, true>(ta, tb, ta2, tx, p, st) : launch_conv<64, kEpiPlain>(ta, tb, ta2, tx, p, st);
   }
 }
 

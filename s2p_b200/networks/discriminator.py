@@ -54,7 +54,7 @@ class _NLayerParams(nn.Module):
             B, h, wd, _ = x.shape
             ho, wo = (h + 4 - 4) // st + 1, (wd + 4 - 4) // st + 1
             if norm:
-                stt = A.conv_stats((B, ho, wo, w.shape[0]), x.device)
+                stt = A.conv_stats((B, ho, wo, w.shape[0]), x.device, 4, st)
                 y = A.conv(x, w, b, None, st, ACT_NONE, stt, 2, packed=pk)
                 x = A.mat_norm(y, ops.in_stats_finalize(stt, ho * wo))
             else:

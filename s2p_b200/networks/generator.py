@@ -289,7 +289,7 @@ class S2PGeneratorB200(nn.Module):
         mr = None
         st = None
         if want_stats:
-            st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo), cout, 2), torch.float32)
+            st = self._buf(name + ".st", (B, ops.conv_stats_rows(ho, wo, cout, k, stride), cout, 2), torch.float32)
         res, res_lo = residual if residual is not None else (None, None)
         ops.conv_igemm(x, w, b, cout, k, stride, act, res, y, st, x2=x2, out_lo=y_lo, residual_lo=res_lo, split=split)
         if want_stats:
@@ -512,7 +512,7 @@ class S2PGeneratorB200(nn.Module):
             k = w.shape[2]
             ho = (x.shape[1] + 2 * (k // 2) - k) // stride + 1
             wo = (x.shape[2] + 2 * (k // 2) - k) // stride + 1
-            st = A.conv_stats((B, ho, wo, w.shape[0]), dev) if want_stats else None
+            st = A.conv_stats((B, ho, wo, w.shape[0]), dev, k, stride) if want_stats else None
             y = A.conv(x, w, b, residual, stride, act, st, packed=packed)
             mr = ops.in_stats_finalize(st, ho * wo) if want_stats else None
             return y, mr

@@ -38,8 +38,10 @@ def _nhwc_pitch(t: torch.Tensor, what: str, f16_ok: bool = False) -> int:
     return pitch
 
 
-def conv_stats_rows(hout: int, wout: int) -> int:
-    return int(_lib.load().s2p_conv_stats_rows(hout, wout))
+def conv_stats_rows(hout: int, wout: int, cout: int = 256, ksize: int = 3, stride: int = 1) -> int:
+    """partial-statistics rows per image written by the conv with this output size / width / filter (the library
+    picks the tile geometry from them; the default arguments describe a wide conv in the standard geometry)"""
+    return int(_lib.load().s2p_conv_stats_rows(hout, wout, cout, ksize, stride))
 
 
 def stem_stats_rows(h: int, w: int) -> int:
@@ -126,7 +128,7 @@ def conv_igemm(x, w_packed, bias, cout, ksize, stride=1, act=ACT_NONE, residual=
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout or not bias.is_contiguous()):
         raise RuntimeError("conv_igemm: bias must be contiguous fp32 [Cout]")
     if stats is not None:
-        rows = conv_stats_rows(hout, wout)
+        rows = conv_stats_rows(hout, wout, cout, ksize, stride)
         if stats.dtype != torch.float32 or stats.numel() != b * rows * cout * 2 or not stats.is_contiguous():
             raise RuntimeError("conv_igemm: stats buffer has the wrong size")
     res_pitch = 0

@@ -34,10 +34,13 @@ def test_host_only_entry_points(repo_root):
     from s2p_b200 import _lib
     lib = _lib.load()
     assert lib.s2p_version() == 1
-    # 100x100 -> 25x5 tiles (125 of 128 MMA rows used): 80 tiles x 4 warp partials
-    assert lib.s2p_conv_stats_rows(100, 100) == 320
-    assert lib.s2p_conv_stats_rows(50, 50) == 80
-    assert lib.s2p_conv_stats_rows(25, 25) == 20
+    # 100x100 -> 25x5 tiles (125 of 128 MMA rows used): 80 tiles, one statistics partial row each
+    assert lib.s2p_conv_stats_rows(100, 100, 256, 3, 1) == 80
+    assert lib.s2p_conv_stats_rows(50, 50, 256, 3, 1) == 20
+    assert lib.s2p_conv_stats_rows(25, 25, 512, 3, 1) == 5
+    # Cout <= 64, 3x3 stride 1: horizontal-halo tiles (25 x 4 pixels in 27-row pitch): 100 tiles
+    assert lib.s2p_conv_stats_rows(100, 100, 64, 3, 1) == 100
+    assert lib.s2p_conv_stats_rows(100, 100, 64, 1, 1) == 80
     assert lib.s2p_stem_stats_rows(100, 100) == 13   # 8 full-width rows per CTA
     assert lib.s2p_mat_fused_ct(512) == 128 and lib.s2p_mat_fused_ct(64) == 64
     assert lib.s2p_launch_count() == 0

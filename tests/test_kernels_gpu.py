@@ -51,7 +51,7 @@ def test_conv_igemm(ops, case):
     pad = k // 2
     ho, wo = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
     res = torch.randn(b, ho, wo, cout, generator=g).cuda().to(torch.bfloat16) if residual else None
-    st = torch.full((b, ops.conv_stats_rows(ho, wo), cout, 2), float("nan"), device="cuda") if stats else None
+    st = torch.full((b, ops.conv_stats_rows(ho, wo, cout, k, stride), cout, 2), float("nan"), device="cuda") if stats else None
     y = ops.conv_igemm(xb, wp, bs, cout, k, stride, act, res, None, st)
     ref = F.conv2d(xb.float().permute(0, 3, 1, 2),
                    wp.float().view(cout, k, k, cin).permute(0, 3, 1, 2), bs, stride, pad)
@@ -96,7 +96,7 @@ def test_conv_second_operand(ops, b, h, cin, cin2, cout, act, stats):
     w1 = (torch.randn(cout, cin2, 1, 1, generator=g) / cin2 ** 0.5).cuda()
     bs = torch.randn(cout, generator=g).cuda()
     wp = torch.cat([ops.pack_conv_weight(w3), ops.pack_conv_weight(w1)], dim=1).contiguous()
-    st = torch.full((b, ops.conv_stats_rows(h, h), cout, 2), float("nan"), device="cuda") if stats else None
+    st = torch.full((b, ops.conv_stats_rows(h, h, cout, 3, 1), cout, 2), float("nan"), device="cuda") if stats else None
     y = ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, None, None, st, x2=x2)
     ref = F.conv2d(xb.float().permute(0, 3, 1, 2), w3.to(torch.bfloat16).float(), bs, 1, 1) \
         + F.conv2d(x2.float().permute(0, 3, 1, 2), w1.to(torch.bfloat16).float(), None, 1, 0)
@@ -114,7 +114,7 @@ def test_conv_bit_stable(ops):
     g = torch.Generator().manual_seed(5)
     x = torch.randn(4, 50, 50, 128, generator=g).cuda().to(torch.bfloat16)
     wp = ops.pack_conv_weight((torch.randn(256, 128, 3, 3, generator=g) / 34).cuda())
-    rows = ops.conv_stats_rows(50, 50)
+    rows = ops.conv_stats_rows(50, 50, 256, 3, 1)
     outs = []
     for _ in range(3):
         st = torch.empty(4, rows, 256, 2, device="cuda")
@@ -319,7 +319,7 @@ def test_conv_wide_output_and_residual(ops, b, h, cin, cout, stride, residual):
         res_hi, res_lo = ops.wide(pair)
     out = torch.full((b, ho, ho, 2 * cout), float("nan"), dtype=torch.bfloat16, device="cuda")
     y_hi, y_lo = ops.wide(out)
-    st = torch.full((b, ops.conv_stats_rows(ho, ho), cout, 2), float("nan"), device="cuda")
+    st = torch.full((b, ops.conv_stats_rows(ho, ho, cout, 3, stride), cout, 2), float("nan"), device="cuda")
     ops.conv_igemm(xb, wp, bs, cout, 3, stride, 0, res_hi, y_hi, st, out_lo=y_lo, residual_lo=res_lo)
     ref = nhwc(F.conv2d(xb.float().permute(0, 3, 1, 2), wt.to(torch.bfloat16).float(), bs, stride, 1))
     if residual:
@@ -525,3 +525,46 @@ def test_mat_norm_fp16_output(ops):
     ops.mat_norm(x_hi, mr, act=2, out=out, x_lo=x_lo)
     ref = F.leaky_relu((xw - mean[:, None, None]) * mr[:, None, None, :, 1], 0.2)
     assert torch.equal(out, ref.to(torch.float16)) or (out.float() - ref).abs().max().item() <= 2.0 ** -11 * ref.abs().max().item() + 1e-6
+
+
+@pytest.mark.parametrize("case", [
+    # b, h, w, cin, cout, act, bias, residual, stats, x2 channels
+    (2, 100, 100, 128, 64, 2, True, False, True, 0), (3, 100, 100, 64, 64, 0, True, False, False, 128),
+    (2, 50, 50, 64, 64, 0, True, True, True, 0), (2, 25, 25, 256, 64, 1, False, False, True, 0),
+    (1, 7, 9, 64, 64, 0, True, False, True, 64), (2, 20, 36, 64, 64, 0, True, False, True, 0),
+    (150, 25, 25, 64, 64, 0, True, False, True, 0)], ids=lambda c: "-".join(map(str, c)))
+def test_conv_horizontal_halo_mode(ops, case):
+    """Cout <= 64, 3x3 stride 1: the conv runs in the horizontal-halo layout (one activation box per filter row
+    feeds its three taps through row-shifted descriptors; M rows in pitch tile_w + 2, halo rows discarded): same
+    results as the plain geometry -- fp32 accumulation of exact bf16 products -- incl. statistics, residual, ragged
+    sizes, the second (1x1) operand and the persistent loop"""
+    b, h, w, cin, cout, act, bias, residual, stats, c2 = case
+    g = torch.Generator().manual_seed(cin + cout + h + c2)
+    xb = torch.randn(b, h, w, cin, generator=g).cuda().to(torch.bfloat16)
+    wt = (torch.randn(cout, cin, 3, 3, generator=g) / (9 * cin) ** 0.5).cuda()
+    bs = torch.randn(cout, generator=g).cuda() if bias else None
+    res = torch.randn(b, h, w, cout, generator=g).cuda().to(torch.bfloat16) if residual else None
+    wp = ops.pack_conv_weight(wt)
+    x2 = w1 = None
+    if c2:
+        x2 = torch.randn(b, h, w, c2, generator=g).cuda().to(torch.bfloat16)
+        w1 = (torch.randn(cout, c2, 1, 1, generator=g) / c2 ** 0.5).cuda()
+        wp = torch.cat([wp, ops.pack_conv_weight(w1)], dim=1).contiguous()
+    rows = ops.conv_stats_rows(h, w, cout, 3, 1)
+    st = torch.full((b, rows, cout, 2), float("nan"), device="cuda") if stats else None
+    y = ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, res, None, st, x2=x2)
+    ref = F.conv2d(xb.float().permute(0, 3, 1, 2), wt.to(torch.bfloat16).float(), bs, 1, 1)
+    if c2:
+        ref = ref + F.conv2d(x2.float().permute(0, 3, 1, 2), w1.to(torch.bfloat16).float(), None, 1, 0)
+    ref = nhwc(ref)
+    if residual:
+        ref = ref + res.float()
+    ref = F.relu(ref) if act == 1 else F.leaky_relu(ref, 0.2) if act == 2 else ref
+    assert torch.isfinite(y.float()).all()
+    assert (y.float() - ref).abs().max().item() <= 2.0 ** -8 * ref.abs().max().item() + 1e-3
+    if stats:
+        mr = ops.in_stats_finalize(st, h * w)
+        assert torch.isfinite(st).all()
+        assert torch.allclose(mr[..., 0], y.float().mean(dim=(1, 2)), atol=1e-4)
+        assert torch.allclose(mr[..., 1], 1.0 / torch.sqrt(y.float().var(dim=(1, 2), unbiased=False) + 1e-5), rtol=1e-4, atol=1e-5)
+    assert torch.equal(ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, res, None, None, x2=x2), y)      # bit-stable

@@ -28,7 +28,7 @@ for name, hw, cin, cout, k, act, res, stats in LAYERS:
     w = ops.pack_conv_weight((torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).cuda())
     bias = torch.randn(cout, generator=g).cuda()
     r = torch.randn(B, hw, hw, cout, generator=g).cuda().to(torch.bfloat16) if res else None
-    st = torch.empty(B, ops.conv_stats_rows(hw, hw), cout, 2, device="cuda") if stats else None
+    st = torch.empty(B, ops.conv_stats_rows(hw, hw, cout, k, 1), cout, 2, device="cuda") if stats else None
     y = torch.empty(B, hw, hw, cout, dtype=torch.bfloat16, device="cuda")
     ts = []
     for i in range(6):

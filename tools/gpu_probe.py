@@ -40,7 +40,7 @@ def probe_conv(b, h, w, cin, cout, k, stride, act=0, bias=True, residual=False, 
     res = torch.randn(b, ho, wo, cout, generator=g).to(dev).to(torch.bfloat16) if residual else None
     st = None
     if stats:
-        st = torch.full((b, ops.conv_stats_rows(ho, wo), cout, 2), float("nan"), device=dev)
+        st = torch.full((b, ops.conv_stats_rows(ho, wo, cout, k, stride), cout, 2), float("nan"), device=dev)
     y = ops.conv_igemm(xb, wp, bs, cout, k, stride, act, res, None, st)
     torch.cuda.synchronize()
     ref = F.conv2d(xb.float().permute(0, 3, 1, 2), wp.float().view(cout, k, k, cin).permute(0, 3, 1, 2), bs, stride, pad)
