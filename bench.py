@@ -38,7 +38,7 @@ os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 # diagnostic switches of the library / tools change what a step does or how fast it runs: a bench line measured with
 # one of them set is not the product's number
 _DIAGNOSTIC_ENV = ("S2P_CONV_CLUSTER", "S2P_CONV_DEBUG", "S2P_NORM_PIX_PER_THREAD", "S2P_WGRAD_ROWS", "S2P_WGRAD_TAP_SPLIT",
-                   "S2P_WGRAD_PAD16")
+                   "S2P_WGRAD_PAD16", "S2P_WGRAD_PAIRS")
 
 
 def refuse_diagnostic_env():

@@ -201,6 +201,167 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// CTA-pair form (cta_group::2): one 256-wide co tile x one 128-wide ci tile x TAPS taps of a filter row.
+// Each CTA of the pair loads ITS 128 co of the dY tile and HALF (64 ci) of every tap's X tile; the leader issues
+// M = 256 MMAs whose B operand takes N/2 columns from each CTA.  Per CTA and 16-pixel K step that is 4 KB (A) + 2 KB
+// per tap (B) of operand reads and (32 + 16 * TAPS) KB of TMA fill per pixel tile instead of 4 + 4 KB and
+// (32 + 32 * TAPS) KB: the single-CTA kernel's 128 x 128 MMAs need 250 B/clk of the 128 B/clk shared-memory port
+// (54-58 % tensor pipe, profiles/r02_train_kernel_table.txt); the pair with three taps needs ~125 B/clk.
+// Pixel tiles are <= 64 rows here (8 KB per 64-channel block) so that a stage of 2 + TAPS blocks leaves a 5-deep ring.
+// Accumulator columns of a group of G taps (N = G * 128): [g * 64, g * 64 + 64) = tap g, ci 0..63 (CTA 0's X tiles),
+// [G * 64 + g * 64, ...) = tap g, ci 64..127 (CTA 1's).
+template <int TAPS>
+__global__ void __launch_bounds__(192, 1)
+conv_wgrad_pair_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
+                       const WgradParams p) {
+  constexpr int kAtomsA = 2;              // this CTA's 128 co = two 64-wide MN blocks
+  constexpr int BNT = 128;                // ci tile of the pair; 64 per CTA
+  constexpr uint32_t kTmemCols = (TAPS * BNT <= 128) ? 128 : (TAPS * BNT <= 256) ? 256 : 512;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int atom_bytes = p.kb_rows * 128;
+  const int atom_stride = ((p.kb_rows + 15) / 16) * 16 * 128;
+  const int stage_bytes = (kAtomsA + TAPS) * atom_stride;
+  const int kWgStages = p.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kWgMaxStages;
+  uint64_t* done_bar = bars + 2 * kWgMaxStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  if (p.kb_rows % 16) {
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = kWgStages * stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_pair<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // the peer's barriers and zero-filled ring exist before anything lands in them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int co0 = static_cast<int>(blockIdx.x >> 1) * 256 + static_cast<int>(rank) * 128;
+  const int ci_tiles = p.Cin / BNT;
+  const int ci_pair0 = (blockIdx.y % ci_tiles) * BNT;
+  const int ci0 = ci_pair0 + static_cast<int>(rank) * 64;     // the 64 ci this CTA feeds
+  const int s_groups = p.S / TAPS;
+  const int rs = blockIdx.y / ci_tiles;
+  const int r = rs / s_groups;
+  const int s_base = (rs % s_groups) * TAPS;
+  const int split = blockIdx.z, splits = gridDim.z;
+  const int t_begin = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * split / splits);
+  const int t_end = static_cast<int>(static_cast<long long>(p.num_pix_tiles) * (split + 1) / splits);
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const uint32_t stage_tx = 2u * static_cast<uint32_t>((kAtomsA + TAPS) * atom_bytes);   // both CTAs' boxes
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t_begin; t < t_end; ++t) {
+      const int img = t / tiles_per_img, tt = t % tiles_per_img;
+      const int h0 = (tt / p.tiles_x) * p.tile_h, w0 = (tt % p.tiles_x) * p.tile_w;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        uint8_t* s0 = smem + stage * stage_bytes;
+        if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+        const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+#pragma unroll
+        for (int a = 0; a < kAtomsA; ++a)
+          tma_load_4d_pair(s0 + a * atom_stride, &tmap_dy, lead_bar, co0 + 64 * a, w0, h0, img);
+#pragma unroll
+        for (int s = 0; s < TAPS; ++s)
+          tma_load_4d_pair(s0 + (kAtomsA + s) * atom_stride, &tmap_x, lead_bar, ci0,
+                           w0 * p.stride - p.pad + s_base + s, h0 * p.stride - p.pad + r, img);
+      }
+      __syncwarp();
+      if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      constexpr int G = (256 / BNT) < TAPS ? (256 / BNT) : TAPS;         // taps per MMA (N = G * 128 <= 256)
+      constexpr uint32_t idesc_full = umma_idesc_bf16_mn(256, G * BNT);
+      constexpr int kRest = TAPS % G;
+      constexpr uint32_t idesc_rest = umma_idesc_bf16_mn(256, (kRest ? kRest : G) * BNT);
+      const uint32_t lbo = static_cast<uint32_t>(atom_stride), sbo = 1024u;
+      int stage = 0;
+      uint32_t phase = 0;
+      const int ksteps = (p.kb_rows + 15) / 16;
+      for (int t = t_begin; t < t_end; ++t) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t s0 = smem_u32(smem + stage * stage_bytes);
+          const uint64_t da = umma_desc_mn_sw128(s0, lbo, sbo);
+          for (int s = 0; s < TAPS; s += G) {
+            const uint64_t db = umma_desc_mn_sw128(s0 + (kAtomsA + s) * atom_stride, lbo, sbo);
+            const uint32_t idesc = (s + G <= TAPS) ? idesc_full : idesc_rest;
+            for (int k = 0; k < ksteps; ++k)
+              umma_bf16_pair(tmem_base + s * BNT, da + static_cast<uint64_t>(k * (2048 >> 4)),
+                             db + static_cast<uint64_t>(k * (2048 >> 4)), idesc, (t != t_begin || k != 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[stage], 3);
+          if (t == t_end - 1) umma_commit_pair(done_bar, 3);
+        }
+        __syncwarp();
+        if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue: this CTA's 128 co rows -> fp32 partials
+    constexpr int G = (256 / BNT) < TAPS ? (256 / BNT) : TAPS;
+    const int q = warp & 3;
+    const int co = co0 + q * 32 + lane;
+    if (t_end > t_begin) {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+    }
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    for (int s = 0; s < TAPS; s += G) {
+      const int g_taps = (s + G <= TAPS) ? G : (TAPS - s);      // taps in this group; its N is g_taps * 128
+#pragma unroll 1
+      for (int c = 0; c < g_taps * BNT / 32; ++c) {
+        uint32_t raw[32];
+        if (t_end > t_begin) {
+          tmem_ld32(t_row + s * BNT + c * 32, raw);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) raw[j] = 0u;
+        }
+        // column c * 32 of the group: half = which CTA's X tiles, then tap, then ci inside the 64-wide block
+        const int col = c * 32;
+        const int half = col / (g_taps * 64), in_half = col - half * (g_taps * 64);
+        const int tap = s + in_half / 64, ci = ci_pair0 + half * 64 + (in_half % 64);
+        if (co < p.Cout) {
+          float4* dst = reinterpret_cast<float4*>(
+              p.partial + (((static_cast<size_t>(split) * p.Cout + co) * p.R + r) * p.S + s_base + tap) * p.Cin + ci);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            dst[j] = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]),
+                                 __uint_as_float(raw[4 * j + 2]), __uint_as_float(raw[4 * j + 3]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_pair<kTmemCols>(tmem_base);
+}
+
 // dW_oihw[co][ci][r][s] (+)= sum_split partial[split][co][r][s][ci]   (fixed order)
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw_oihw, int splits,
                                     int Cout, int Cin, int R, int S, int accumulate) {
@@ -241,8 +402,8 @@ static int wgrad_pad16() {
 // Pixel tile (the GEMM K block): tile_w * tile_h <= 128 rows.  The MMA consumes K in steps of 16, so a tile costs
 // ceil16(rows) rows of tensor time; rows need not be a multiple of 16 (the kernel zero-fills the slack), which is what
 // lets 25 x 5 = 125 -> 128 tile 100^2, 50^2 and 25^2 maps at 97.7 % instead of 80-row tiles at 78-100 %.
-static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out) {
-  const int max_rows = wgrad_max_rows();
+static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out, int cap_rows = 128) {
+  const int max_rows = wgrad_max_rows() < cap_rows ? wgrad_max_rows() : cap_rows;
   const bool pad_ok = wgrad_pad16() != 0;
   double best = -1.0;
   int btw = 16, bth = 1;
@@ -252,8 +413,10 @@ static void wgrad_pick_tile(int H, int W, int* tw_out, int* th_out) {
       const int cost = (tw * th + 15) / 16 * 16;
       const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
       const double eff = static_cast<double>(H) * W / (tiles * static_cast<double>(cost));
-      // prefer efficiency, then bigger tiles (fewer pipeline turns)
-      const double score = eff + 1e-4 * cost;
+      // prefer efficiency, then bigger tiles (fewer pipeline turns).  Under a row cap (the pair kernel's 64) small
+      // exact tiles would win on efficiency alone (4 x 4 = 16 rows at 100^2: one K step per ring slot); a slot's fixed
+      // cost is worth about 8 rows of tensor time
+      const double score = cap_rows < 128 ? eff * cost / (cost + 8.0) : eff + 1e-4 * cost;
       if (score > best) { best = score; btw = tw; bth = th; }
     }
   }
@@ -279,8 +442,15 @@ static EncodeTiledFn wg_encode_fn() {
 struct WgradPlan {
   WgradParams p;
   int bn, taps, splits, smem_bytes;
+  int pair;      // CTA-pair kernel (256 co x 128 ci per pair)
   dim3 grid;
 };
+
+static int wgrad_pairs() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("S2P_WGRAD_PAIRS"); v = e ? atoi(e) : 1; }
+  return v;
+}
 
 static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int stride, int pad, WgradPlan* pl) {
   WgradParams& p = pl->p;
@@ -289,6 +459,33 @@ static int wgrad_plan(int B, int Hin, int Win, int Cin, int Cout, int ksize, int
   p.Ho = (Hin + 2 * pad - ksize) / stride + 1;
   p.Wo = (Win + 2 * pad - ksize) / stride + 1;
   p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
+  pl->pair = 0;
+  if (wgrad_pairs() && Cout % 256 == 0 && Cin % 128 == 0 && (ksize == 3 || ksize == 1)) {
+    // CTA pairs: 256 co x 128 ci x all taps of a filter row; pixel tiles of <= 64 rows keep a stage of 2 + taps
+    // 64-channel blocks small enough for a deep ring
+    pl->pair = 1;
+    wgrad_pick_tile(p.Ho, p.Wo, &p.tile_w, &p.tile_h, ksize == 3 ? 64 : 128);
+    p.tiles_x = (p.Wo + p.tile_w - 1) / p.tile_w;
+    p.tiles_y = (p.Ho + p.tile_h - 1) / p.tile_h;
+    p.kb_rows = p.tile_w * p.tile_h;
+    p.num_pix_tiles = B * p.tiles_x * p.tiles_y;
+    pl->taps = ksize;
+    pl->bn = 128;
+    const int ctas = 2 * (Cout / 256) * (Cin / 128) * ksize;
+    int splits = num_sms() / ctas;
+    if (splits > p.num_pix_tiles) splits = p.num_pix_tiles;
+    if (splits < 1) splits = 1;
+    pl->splits = splits;
+    pl->grid = dim3(2 * (Cout / 256), (Cin / 128) * ksize, splits);
+    const int atom_stride = ((p.kb_rows + 15) / 16) * 16 * 128;
+    const int stage_bytes = (2 + ksize) * atom_stride;
+    int stages = (200 * 1024) / stage_bytes;
+    if (stages > kWgMaxStages) stages = kWgMaxStages;
+    if (stages < 2) stages = 2;
+    p.stages = stages;
+    pl->smem_bytes = stages * stage_bytes + 1024 + 256;
+    return S2P_OK;
+  }
   wgrad_pick_tile(p.Ho, p.Wo, &p.tile_w, &p.tile_h);
   p.tiles_x = (p.Wo + p.tile_w - 1) / p.tile_w;
   p.tiles_y = (p.Ho + p.tile_h - 1) / p.tile_h;
@@ -331,6 +528,32 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Wgr
   conv_wgrad_kernel<BN, TAPS><<<pl.grid, 192, pl.smem_bytes, st>>>(tdy, tx, pl.p);
   count_launch();
   return check_launch("conv_wgrad_kernel");
+}
+
+template <int TAPS>
+static int launch_wgrad_pair(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradPlan& pl, cudaStream_t st) {
+  static int configured[kMaxDevices] = {};   // per device
+  const int dev = current_device();
+  if (pl.smem_bytes > configured[dev]) {
+    S2P_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_pair_kernel<TAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        pl.smem_bytes));
+    configured[dev] = pl.smem_bytes;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = pl.grid;
+  cfg.blockDim = dim3(192, 1, 1);
+  cfg.dynamicSmemBytes = pl.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  S2P_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_wgrad_pair_kernel<TAPS>, tdy, tx, pl.p));
+  count_launch();
+  return check_launch("conv_wgrad_pair_kernel");
 }
 
 }  // namespace s2p
@@ -391,7 +614,9 @@ extern "C" int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc;
-  if (pl.bn == 128) {
+  if (pl.pair) {
+    rc = pl.taps == 3 ? launch_wgrad_pair<3>(tdy, tx, pl, st) : launch_wgrad_pair<1>(tdy, tx, pl, st);
+  } else if (pl.bn == 128) {
     switch (pl.taps) {
       case 1: rc = launch_wgrad<128, 1>(tdy, tx, pl, st); break;
       case 3: rc = launch_wgrad<128, 3>(tdy, tx, pl, st); break;

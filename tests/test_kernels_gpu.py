@@ -205,13 +205,17 @@ WGRAD_CASES = [  # b, h, w, cin, cout, k, stride
     (1, 16, 16, 64, 128, 1, 1), (1, 16, 16, 64, 128, 3, 1), (2, 25, 25, 128, 128, 3, 1), (2, 100, 100, 64, 64, 3, 1),
     (2, 50, 50, 128, 256, 3, 1), (3, 100, 100, 64, 128, 3, 2), (2, 25, 25, 512, 512, 3, 1), (2, 50, 50, 256, 128, 1, 1),
     (1, 7, 9, 64, 64, 3, 1), (2, 20, 36, 64, 72, 3, 1),
+    # CTA-pair kernel (Cout % 256 == 0, Cin % 128 == 0, 3x3 / 1x1): 256 co x 128 ci per pair, pixel tiles <= 64 rows
+    (2, 100, 100, 128, 512, 3, 1), (3, 50, 50, 256, 256, 1, 1), (1, 7, 9, 128, 256, 3, 1), (2, 100, 100, 128, 256, 3, 2),
+    (2, 25, 25, 256, 1024, 3, 1), (130, 25, 25, 128, 256, 3, 1),
 ]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES, ids=lambda c: "-".join(map(str, c)))
 def test_conv_wgrad(ops, case):
-    """dW of the conv against torch autograd on the same bf16-rounded x and dy (fp32 accumulate:
-    only the summation order differs)."""
+    """dW of the conv against torch autograd IN FLOAT64 on the same bf16-rounded x and dy (fp32 accumulation of exact
+    bf16 products here: measured 1e-7 .. 4e-6 of the largest gradient; torch's own fp32 backward is 10x further from
+    float64 at the large-K shapes, so it cannot be the yardstick)."""
     b, h, w, cin, cout, k, st = case
     g = torch.Generator().manual_seed(cin + cout + k)
     pad = k // 2
@@ -219,11 +223,11 @@ def test_conv_wgrad(ops, case):
     ho, wo = (h + 2 * pad - k) // st + 1, (w + 2 * pad - k) // st + 1
     dy = torch.randn(b, ho, wo, cout, generator=g).cuda().to(torch.bfloat16)
     dw = ops.conv_wgrad(x, dy, k, st)
-    wt = torch.zeros(cout, cin, k, k, device="cuda", requires_grad=True)
-    F.conv2d(x.float().permute(0, 3, 1, 2), wt, None, st, pad).backward(dy.float().permute(0, 3, 1, 2))
+    wt = torch.zeros(cout, cin, k, k, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv2d(x.double().permute(0, 3, 1, 2), wt, None, st, pad).backward(dy.double().permute(0, 3, 1, 2))
     ref = wt.grad
     assert torch.isfinite(dw).all()
-    assert (dw - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() + 1e-3
+    assert (dw.double() - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() + 1e-4
     dw2 = ops.conv_wgrad(x, dy, k, st, out=dw.clone(), accumulate=True)
     assert torch.allclose(dw2, 2 * dw, rtol=1e-6, atol=1e-6)
     assert torch.equal(ops.conv_wgrad(x, dy, k, st), dw)      # bit-stable split-K
