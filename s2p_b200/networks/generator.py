@@ -508,7 +508,7 @@ class S2PGeneratorB200(nn.Module):
 
         def conv_in(x, conv, stride=1, act=ACT_NONE, residual=None, want_stats=True, weight=None, bias=None, packed=None):
             w = conv.weight if weight is None else weight
-            b = conv.bias if bias is None else bias
+            b = (conv.bias if conv is not None else None) if bias is None else bias
             k = w.shape[2]
             ho = (x.shape[1] + 2 * (k // 2) - k) // stride + 1
             wo = (x.shape[2] + 2 * (k // 2) - k) // stride + 1
@@ -603,8 +603,13 @@ class S2PGeneratorB200(nn.Module):
         def mat(bi, name, m, xin, mr_in, up, act):
             gs, bs = gsbs[(bi, name)]
             gbw, gbb = gbwb[(bi, name)]
-            gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=gbb, packed=pk[("gb", bi, name)])
-            return A.mat_norm(xin, mr_in, gs, bs, gb, up, act)
+            # the gamma/beta conv runs WITHOUT its bias: the bias is a per-channel constant, so it joins the state
+            # branch's per-(n, c) terms (as the inference schedule folds it into the modulation table).  Its gradient
+            # is then the batch sum of d gs / d bs, which the norm's backward produces anyway -- instead of a
+            # column-sum pass over the gradient of the 2C-channel full-resolution map (the largest tensors of the step)
+            C = m.norm_nc
+            gb, _ = conv_in(hs[(bi, name)], None, want_stats=False, weight=gbw, bias=None, packed=pk[("gb", bi, name)])
+            return A.mat_norm(xin, mr_in, gs + gbb[:C], bs + gbb[C:], gb, up, act)
 
         x, mr_x = conv_in(f[4], self.head, packed=pk["head"])
         cur = 4
