@@ -34,6 +34,17 @@ sys.path.insert(0, ROOT)
 # stderr.  NCCL_DEBUG itself is only DEFAULTED: a driver that asks for INFO keeps its rank evidence.
 os.environ.setdefault("NCCL_DEBUG", "WARN")
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# ... and because a library can still write to file descriptor 1 behind Python's back (NCCL's version banner does when
+# the launcher exported its own NCCL_DEBUG settings), the real stdout is kept aside for the JSON line and descriptor 1
+# is pointed at stderr for everything else
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line: dict):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
 
 # diagnostic switches of the library / tools change what a step does or how fast it runs: a bench line measured with
 # one of them set is not the product's number
@@ -120,7 +131,7 @@ def run_reference(args):
                              "sample": f"{sample} frames per step (the oracle: reference generator source is absent)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------- clocks
@@ -316,7 +327,7 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": best, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{cpu_n} frames x 2 forwards of the fp32 oracle (best of 2), "
                                           "same uint8->uint8 row workload"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -830,7 +841,7 @@ def run_train(args):
                 "clocks": clocks,
                 "roofline": {"kernel": "whole training step (conv fwd/dgrad/wgrad dominate)", "bound": "tensor",
                              "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "traffic": None}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
