@@ -126,8 +126,11 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 }
 
 // blockDim = (C/8 channel groups, PY pixel slots).  grid = (chunks per image, B).
-template <bool HAS_GB, bool UP2, bool WIDE>
-__global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
+// (launch bounds: the plain-IN variants -- the image encoder's three norms -- are held to 3 CTAs per SM; at 96 registers
+// the wide-input variant ran 2 per SM and its load / compute phases did not overlap enough to hold the HBM rate at the
+// power-capped clock)
+template <bool HAS_GB, bool UP2, bool WIDE, bool HAS_GS>
+__global__ void __launch_bounds__(256, (HAS_GB || HAS_GS) ? 2 : 3) mat_norm_kernel(const NormParams p) {
   const int cg = threadIdx.x;              // channel group (8 channels)
   const int c0 = cg * 8;
   const int n = blockIdx.y;
@@ -139,8 +142,9 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
     const float2 mr = __ldg(p.mean_rstd + static_cast<size_t>(n) * p.C + c0 + j);
     sc[j] = mr.y;
     sh[j] = -mr.x * mr.y;
-    g1[j] = 1.f + (p.gs ? __ldg(p.gs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 0.f);
-    b0[j] = p.bs ? __ldg(p.bs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 0.f;
+    // (HAS_GS == false: plain instance norm -- no per-channel modulation registers at all)
+    g1[j] = HAS_GS ? 1.f + __ldg(p.gs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 1.f;
+    b0[j] = HAS_GS ? __ldg(p.bs + static_cast<size_t>(n) * p.gsbs_pitch + c0 + j) : 0.f;
   }
   const int HW = p.H * p.W;
   const int Wx = UP2 ? (p.W >> 1) : p.W;
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(256) mat_norm_kernel(const NormParams p) {
           const float xh = fmaf(xf[j], sc[j], sh[j]);
           const float g = HAS_GB ? g1[j] + gf[j] : g1[j];
           const float b = HAS_GB ? b0[j] + bf[j] : b0[j];
-          float v = fmaf(xh, g, b);
+          float v = (HAS_GB || HAS_GS) ? fmaf(xh, g, b) : xh;
           if (p.act == 2) v = v > 0.f ? v : 0.2f * v;
           else if (p.act == 1) v = fmaxf(v, 0.f);
           o[j] = v;
@@ -296,8 +300,13 @@ extern "C" int s2p_mat_norm_fwd(const void* x, const void* x_lo, int x_pitch, in
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define S2P_NORM_LAUNCH(GB, UP)                                                      \
   do {                                                                               \
-    if (x_lo) mat_norm_kernel<GB, UP, true><<<grid, block, 0, st>>>(p);              \
-    else mat_norm_kernel<GB, UP, false><<<grid, block, 0, st>>>(p);                  \
+    if (x_lo) {                                                                      \
+      if (gs) mat_norm_kernel<GB, UP, true, true><<<grid, block, 0, st>>>(p);        \
+      else mat_norm_kernel<GB, UP, true, false><<<grid, block, 0, st>>>(p);          \
+    } else {                                                                         \
+      if (gs) mat_norm_kernel<GB, UP, false, true><<<grid, block, 0, st>>>(p);       \
+      else mat_norm_kernel<GB, UP, false, false><<<grid, block, 0, st>>>(p);         \
+    }                                                                                \
   } while (0)
   if (gb_spatial) {
     if (up == 2) S2P_NORM_LAUNCH(true, true);
