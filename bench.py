@@ -564,7 +564,7 @@ def adjacent_side_measurements(torch, dev):
     ms_gray = timed(lambda: rad.random_grayscale(stacks_f, p=.3), reps=10)
     b_crop, b_gray = Bw * 9 * (84 * 84 * 2), Bw * 9 * 10000 * 8
     out["rad_augmentations"] = {
-        "kernel": "augment_u8_words_kernel<crop> (uint8) / grayscale_kernel<4> (float32); whole call incl. host draws + upload",
+        "kernel": "augment_u8_staged_kernel<crop> (uint8, rows bulk-copied to shared memory) / grayscale_kernel<4> (float32); whole call incl. host draws + upload",
         "stacks": Bw, "shape": "9x100x100", "bound": "hbm", "peak": hbm_peak, "unit": "GB/s",
         "random_crop_u8": {"ms": ms_crop, "achieved": b_crop / ms_crop / 1e6, "frac": b_crop / ms_crop / 1e6 / hbm_peak},
         "random_grayscale_f32": {"ms": ms_gray, "achieved": b_gray / ms_gray / 1e6, "frac": b_gray / ms_gray / 1e6 / hbm_peak}}

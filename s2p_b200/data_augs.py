@@ -46,8 +46,12 @@ def _leave(t, was_np):
 
 def _draws(dev, *arrays):
     """One host->device copy for all per-image draws of a call: int32 [len(arrays), n], row k = arrays[k]."""
-    host = np.ascontiguousarray(np.stack([np.asarray(a).astype(np.int32) for a in arrays]))
-    return torch.from_numpy(host).to(dev)
+    host = np.empty((len(arrays), len(arrays[0])), dtype=np.int32)
+    for k, a in enumerate(arrays):
+        host[k] = a
+    # pageable source: cudaMemcpyAsync returns once the bytes are staged, so `host` may be dropped at once, and the call
+    # does not wait for the stream to drain as the blocking copy did
+    return torch.from_numpy(host).to(dev, non_blocking=True)
 
 
 def _augment(x, op, ho, wo, p0, p1=None, fill=None):
@@ -55,11 +59,17 @@ def _augment(x, op, ho, wo, p0, p1=None, fill=None):
     out = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device)
     if n == 0:
         return out
-    with torch.cuda.device(x.device):
+    def launch():
         d = _draws(x.device, p0) if p1 is None else _draws(x.device, p0, p1)
+        base = d.data_ptr()
         _lib.check(_lib.load().s2p_rad_augment(x.data_ptr(), out.data_ptr(), _ELEM[x.dtype], n, c, h, w, ho, wo, op,
-                                               d[0].data_ptr(), 0 if p1 is None else d[1].data_ptr(),
+                                               base, 0 if p1 is None else base + 4 * n,
                                                0 if fill is None else fill.data_ptr(), _stream()), "s2p_rad_augment")
+    if torch.cuda.current_device() == x.device.index:     # the usual case: skip the device-guard context manager
+        launch()
+    else:
+        with torch.cuda.device(x.device):
+            launch()
     return out
 
 

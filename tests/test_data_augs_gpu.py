@@ -56,8 +56,10 @@ def _imgs(shape, dtype, seed):
 
 @pytest.mark.parametrize("dtype", [np.uint8, np.float32], ids=["u8", "f32"])
 @pytest.mark.parametrize("shape,out,size", [((16, 9, 100, 100), 84, 108), ((5, 3, 37, 37), 30, 41), ((3, 1, 7, 7), 7, 7),
-                                             ((4, 3, 37, 37), 32, 40), ((6, 2, 52, 52), 36, 64)],
-                         ids=["frames100", "ragged37", "tiny7", "unaligned_rows37", "words52"])
+                                             ((4, 3, 37, 37), 32, 40), ((6, 2, 52, 52), 36, 64), ((3, 5, 100, 100), 84, 108),
+                                             ((2, 2, 35, 36), 28, 44)],
+                         ids=["frames100", "ragged37", "tiny7", "unaligned_rows37", "words52", "ragged_plane_groups",
+                              "staged_skew_nonsquare"])
 def test_every_op_vs_oracle(dtype, shape, out, size):
     R = rad()
     x = _imgs(shape, dtype, 5)
@@ -66,6 +68,8 @@ def test_every_op_vs_oracle(dtype, shape, out, size):
     calls = [("random_crop", dict(out=out)), ("random_cutout", dict(min_cut=lo, max_cut=hi)),
              ("random_cutout_color", dict(min_cut=lo, max_cut=hi)), ("random_translate", dict(size=size)),
              ("random_flip", dict(p=.5)), ("random_rotation", dict(p=.8))]
+    if shape[2] != shape[3]:
+        calls = calls[:-1]           # quarter turns need square frames (data_augs.py:164-186 asserts nothing, numpy would raise)
     for k, (name, kw) in enumerate(calls):
         np.random.seed(100 + k)
         got = getattr(R, name)(xc, **kw)
