@@ -238,17 +238,20 @@ __global__ void __launch_bounds__(kThreads, 1) state_encoder_fused_kernel(const 
     const int cgs = (p.N[phase] + NC - 1) / NC;
     const int ntasks = rbs * cgs;
     bool first = true;
+    if (phase > 0) {
+      // weights of this phase's first task were fetched before the barrier (see below); now wait for every CTA
+      // to have finished the previous phase, then read its activations.  EVERY CTA waits here, also one without a
+      // task in this phase (B <= 16: 128 tasks per MLP layer on 148 CTAs): the counter is monotonic, so a CTA that
+      // ran ahead and arrived for later phases would release this barrier before the previous phase is complete
+      // (seen as a rare mismatch on the first, cold-cache launch of a process).
+      if (t == 0) {
+        const unsigned target = static_cast<unsigned>(phase) * G;
+        while (ld_acquire_u32(p.sync) < target) { }
+      }
+      __syncthreads();
+    }
     for (int task = blockIdx.x; task < ntasks; task += G) {
       const int rb = task / cgs, cg = task - rb * cgs;
-      if (first && phase > 0) {
-        // weights of this phase's first task were fetched before the barrier (see below); now wait for every CTA
-        // to have finished the previous phase, then read its activations
-        if (t == 0) {
-          const unsigned target = static_cast<unsigned>(phase) * G;
-          while (ld_acquire_u32(p.sync) < target) { }
-        }
-        __syncthreads();
-      }
       if (head) run_task<4>(p, phase, rb, cg, a_s, w_s, part, first && w_loaded);
       else run_task<1>(p, phase, rb, cg, a_s, w_s, part, first && w_loaded);
       first = false;
