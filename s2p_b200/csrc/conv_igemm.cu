@@ -11,8 +11,8 @@
 // Replaces the cuDNN convs behind nn.Conv2d in the (absent) reference generator
 // (oracle/s2p_oracle.py MATResBlk / MAT / ImageEncoder / head).
 //
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer and owner of the TMEM
-// allocation (both loops run warp-converged and elect one lane around the asynchronous issue),
+// Warp roles (384 threads): warps 0, 10, 11 = TMA producers (each fills every third ring stage), warp 1 = MMA issuer
+// and owner of the TMEM allocation (both loops run warp-converged and elect one lane around the asynchronous issue),
 // warps 2..9 = epilogue (TMEM lane quarter = warp % 4, two warps per quarter split the columns).
 // CTA pairs (cta_group::2): two CTAs of a cluster walk two adjacent m-tiles of one n-tile as one
 // M=256 UMMA, each loading its own activation rows and half of the weight tile.
@@ -164,8 +164,20 @@ __device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* pa
   __syncwarp();
 }
 
+constexpr int kConvThreads = 384;   // 12 warps: TMA producer, MMA issuer, 8 epilogue warps, two more TMA producers
+
+// Timeline probe (tools/conv_trace_build.sh builds a private copy of the library with -DS2P_CONV_TRACE; the product
+// build has none of this): CTA 0 records clock64() at the pipeline hand-offs of its first kTraceN stages / tiles.
+#ifdef S2P_CONV_TRACE
+constexpr int kTraceN = 1024;
+__device__ long long g_conv_trace[12][kTraceN];
+#define S2P_TRACE(row, idx) do { if (blockIdx.x == 0 && (idx) < kTraceN) g_conv_trace[row][idx] = clock64(); } while (0)
+#else
+#define S2P_TRACE(row, idx) do { } while (0)
+#endif
+
 template <int BLOCK_N, int EPI, int CL, bool HH>
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(kConvThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_a2, const __grid_constant__ CUtensorMap tmap_x,
                   const ConvParams p) {
@@ -241,77 +253,108 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   // operands) and elect one lane only around the asynchronous issue itself: a loop written under
   // `lane == 0` forces the compiler to serialise every uniform-datapath operand through
   // elect/R2UR waterfall loops (~700 clk per k-block, which used to bound every layer).
-  if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
+  if (warp == 0 || warp >= 10) {
+    // ------------------------------------------------------------ TMA producers (three warps)
+    // The three warps walk the same (tile, k-block, ring stage) sequence and each fills every third stage.  One
+    // thread issuing every stage took 330 clk per stage (barrier poll ~70, the uniform-datapath address arithmetic
+    // and two UTMALDG ~170, loop ~90), 800 clk with the four loads of a halo stage: more than the 256 clk of MMA
+    // work a BLOCK_N = 128 stage holds and 2-4x what a thin halo stage holds (tools/conv_trace.py,
+    // profiles/r02_conv_trace.txt).  The stages still complete in ring order for the MMA thread: each has its own
+    // full barrier, and a producer waits on its own stage's empty barrier only.
+    const int my_turn = warp == 0 ? 0 : warp - 9;      // 0, 1, 2
+    int turn = 0;
     int stage = 0;
     uint32_t phase = 0;
+#ifdef S2P_CONV_TRACE
+    int tr_p = 0;
+#endif
     for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
       const int m_tile = (tile / p.num_n_tiles) * CL + cta_rank, n_tile = tile % p.num_n_tiles;
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;   // img == B for a dummy tile
       const int h0 = (t / p.tiles_x) * p.tile_h, w0 = (t % p.tiles_x) * p.tile_w;
       const int hin0 = h0 * p.stride - p.pad, win0 = w0 * p.stride - p.pad;
+      const int b_row = n_tile * BLOCK_N + (CL > 1 ? static_cast<int>(cta_rank) * (BLOCK_N / CL) : 0);   // first weight row of this CTA
       int r = 0, sx = 0, cc = 0;
       if constexpr (HH) {
+        int rr = 0, ck = 0;          // (filter row, channel chunk) of the k-block; second-operand blocks follow
         for (int kb = 0; kb < num_kb_hh; ++kb) {
-          const bool main_kb = kb < p.R * cchunks;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (elect_one()) {
+          if (turn == my_turn) {
+            const bool main_kb = kb < p.R * cchunks;
+            // everything the loads need is computed before the barrier poll
             uint8_t* sa = smem + stage * Cfg::kStageBytes;
             uint8_t* sb = sa + Cfg::kABytes;
-            const int rr = kb / cchunks, ck = kb - rr * cchunks;
+            const int ntap = main_kb ? 3 : 1;
             int ach = ck * Cfg::kBlockK;
             if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
-            const int ntap = main_kb ? 3 : 1;
             const uint32_t tx = (a_bytes + static_cast<uint32_t>(ntap) * Cfg::kBTapBytes) * CL;
-            if constexpr (CL > 1) {
-              constexpr int kPart = BLOCK_N / CL;
-              if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx);
-              const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
-              if (main_kb) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, w0 - 1, h0 - 1 + rr, img);
-              else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - p.R * cchunks) * Cfg::kBlockK, w0 - 1, h0, img);
-              for (int s = 0; s < ntap; ++s)
-                tma_load_2d_pair(sb + s * Cfg::kBTapBytes, &tmap_b, lead_bar,
-                                 main_kb ? ((rr * 3 + s) * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK,
-                                 n_tile * BLOCK_N + cta_rank * kPart);
-            } else {
-              mbar_arrive_expect_tx(&full_bar[stage], tx);
-              if (main_kb) tma_load_4d(sa, &tmap_a, &full_bar[stage], ach, w0 - 1, h0 - 1 + rr, img);
-              else tma_load_4d(sa, &tmap_a2, &full_bar[stage], (kb - p.R * cchunks) * Cfg::kBlockK, w0 - 1, h0, img);
-              for (int s = 0; s < ntap; ++s)
-                tma_load_2d(sb + s * Cfg::kBTapBytes, &tmap_b, &full_bar[stage],
-                            main_kb ? ((rr * 3 + s) * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK,
-                            n_tile * BLOCK_N);
+            const int kcol = main_kb ? (rr * 3 * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK;
+            const int a2ch = (kb - p.R * cchunks) * Cfg::kBlockK;
+            if (my_turn == 0) S2P_TRACE(0, tr_p);
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (my_turn == 0) S2P_TRACE(1, tr_p);
+            if (elect_one()) {
+              if constexpr (CL > 1) {
+                if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx);
+                const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+                if (main_kb) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, w0 - 1, h0 - 1 + rr, img);
+                else tma_load_4d_pair(sa, &tmap_a2, lead_bar, a2ch, w0 - 1, h0, img);
+                for (int s = 0; s < ntap; ++s)
+                  tma_load_2d_pair(sb + s * Cfg::kBTapBytes, &tmap_b, lead_bar, kcol + s * cchunks * Cfg::kBlockK, b_row);
+              } else {
+                mbar_arrive_expect_tx(&full_bar[stage], tx);
+                if (main_kb) tma_load_4d(sa, &tmap_a, &full_bar[stage], ach, w0 - 1, h0 - 1 + rr, img);
+                else tma_load_4d(sa, &tmap_a2, &full_bar[stage], a2ch, w0 - 1, h0, img);
+                for (int s = 0; s < ntap; ++s)
+                  tma_load_2d(sb + s * Cfg::kBTapBytes, &tmap_b, &full_bar[stage], kcol + s * cchunks * Cfg::kBlockK, b_row);
+              }
             }
+            __syncwarp();
+            if (my_turn == 0) S2P_TRACE(2, tr_p);
+#ifdef S2P_CONV_TRACE
+            ++tr_p;
+#endif
           }
-          __syncwarp();
+          if (++turn == 3) turn = 0;
+          if (++ck == cchunks) { ck = 0; ++rr; }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       } else {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        if (elect_one()) {
-          uint8_t* sa = smem + stage * Cfg::kStageBytes;
-          uint8_t* sb = sa + Cfg::kABytes;
-          int ach = cc * Cfg::kBlockK;
-          if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
-          if constexpr (CL > 1) {
-            constexpr int kPart = BLOCK_N / CL;
-            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-            const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
-            if (kb < num_kb_main) tma_load_4d_pair(sa, &tmap_a, lead_bar, ach, win0 + sx, hin0 + r, img);
-            else tma_load_4d_pair(sa, &tmap_a2, lead_bar, (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
-            tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, n_tile * BLOCK_N + cta_rank * kPart);
-          } else {
-            mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
-            if (kb < num_kb_main) tma_load_4d(sa, &tmap_a, &full_bar[stage], ach, win0 + sx, hin0 + r, img);
-            else tma_load_4d(sa, &tmap_a2, &full_bar[stage], (kb - num_kb_main) * Cfg::kBlockK, w0, h0, img);
-            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, n_tile * BLOCK_N);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          if (turn == my_turn) {
+            uint8_t* sa = smem + stage * Cfg::kStageBytes;
+            uint8_t* sb = sa + Cfg::kABytes;
+            const bool main_kb = kb < num_kb_main;
+            int ach = cc * Cfg::kBlockK;
+            if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
+            const int ca = main_kb ? ach : (kb - num_kb_main) * Cfg::kBlockK;
+            const int cw = main_kb ? win0 + sx : w0, chh = main_kb ? hin0 + r : h0;
+            if (my_turn == 0) S2P_TRACE(0, tr_p);
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (my_turn == 0) S2P_TRACE(1, tr_p);
+            if (elect_one()) {
+              if constexpr (CL > 1) {
+                if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+                const uint32_t lead_bar = map_to_cta(&full_bar[stage], 0);
+                if (main_kb) tma_load_4d_pair(sa, &tmap_a, lead_bar, ca, cw, chh, img);
+                else tma_load_4d_pair(sa, &tmap_a2, lead_bar, ca, cw, chh, img);
+                tma_load_2d_pair(sb, &tmap_b, lead_bar, kb * Cfg::kBlockK, b_row);
+              } else {
+                mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
+                if (main_kb) tma_load_4d(sa, &tmap_a, &full_bar[stage], ca, cw, chh, img);
+                else tma_load_4d(sa, &tmap_a2, &full_bar[stage], ca, cw, chh, img);
+                tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * Cfg::kBlockK, b_row);
+              }
+            }
+            __syncwarp();
+            if (my_turn == 0) S2P_TRACE(2, tr_p);
+#ifdef S2P_CONV_TRACE
+            ++tr_p;
+#endif
           }
+          if (++turn == 3) turn = 0;
+          if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++cc == cchunks) { cc = 0; if (++sx == p.S) { sx = 0; ++r; } }
-        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-      }
       }
     }
   } else if (warp == 1) {
@@ -322,16 +365,23 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+#ifdef S2P_CONV_TRACE
+      int tr_m = 0;
+#endif
       for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
+        S2P_TRACE(6, it);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        S2P_TRACE(7, it);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
         if constexpr (HH) {
           for (int kb = 0; kb < num_kb_hh; ++kb) {
             const bool main_kb = kb < p.R * cchunks;
+            S2P_TRACE(3, tr_m);
             mbar_wait(&full_bar[stage], phase);
+            S2P_TRACE(4, tr_m);
             tc_fence_after();
             if (elect_one()) {
               const uint64_t da = desc0 + static_cast<uint64_t>(stage * (Cfg::kStageBytes >> 4));
@@ -357,11 +407,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               }
             }
             __syncwarp();
+            S2P_TRACE(5, tr_m);
+#ifdef S2P_CONV_TRACE
+            ++tr_m;
+#endif
             if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
           }
         } else {
         for (int kb = 0; kb < num_kb; ++kb) {
+          S2P_TRACE(3, tr_m);
           mbar_wait(&full_bar[stage], phase);
+          S2P_TRACE(4, tr_m);
           tc_fence_after();
           if (elect_one()) {
             // descriptor start-address field is in 16-byte units: stage and operand offsets add directly
@@ -382,12 +438,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
           }
           __syncwarp();
+          S2P_TRACE(5, tr_m);
+#ifdef S2P_CONV_TRACE
+          ++tr_m;
+#endif
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
         }
       }
     }
-  } else if (warp >= 2) {
+  } else if (warp < 10) {
     // ------------------------------------------------------------ epilogue (8 warps)
     // warp -> TMEM lane quarter q (hardware rule: warp%4) and one half of the tile's columns.
     // TMEM loads are software pipelined (the load of step i+1 is in flight while step i is
@@ -414,6 +474,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     for (int tile = tile_first; tile < num_tiles; tile += tile_step, ++it) {
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
+      if (et == 0) S2P_TRACE(8, it);
       const int m_tile = (tile / p.num_n_tiles) * CL + cta_rank, n_tile = tile % p.num_n_tiles;
       const bool live = m_tile < p.num_m_tiles;     // false only for a pair's dummy tile
       const int img = m_tile / tiles_per_img, t = m_tile % tiles_per_img;
@@ -520,6 +581,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
       } else if constexpr (EPI == kEpiToRGB) {
         mbar_wait_relaxed(&tmem_full[acc], acc_phase);
+        if (et == 0) S2P_TRACE(9, it);
         tc_fence_after();
         if (half == 0) {
           uint32_t r16[16];
@@ -560,6 +622,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int j = 0; j < 4; ++j) rn[j] = __ldg(r4 + j);
         }
         mbar_wait_relaxed(&tmem_full[acc], acc_phase);
+        if (et == 0) S2P_TRACE(9, it);
         tc_fence_after();
         uint32_t raw[32];
         tmem_ld32(t_row + cbeg * 32, raw);
@@ -696,6 +759,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
 }  // namespace s2p
 
+#ifdef S2P_CONV_TRACE
+extern "C" int s2p_conv_trace_read(long long* host) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host, s2p::g_conv_trace, sizeof(long long) * 12 * s2p::kTraceN));
+}
+#endif
+
 // =============================================================== host side
 namespace s2p {
 
@@ -770,7 +839,7 @@ static int launch_conv_cl(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   const int grid = (super_tiles < max_clusters ? super_tiles : max_clusters) * CL;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);
-  cfg.blockDim = dim3(320, 1, 1);
+  cfg.blockDim = dim3(kConvThreads, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
