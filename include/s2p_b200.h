@@ -205,6 +205,21 @@ int s2p_state_encoder_fwd(const float* state, int B, int S, int n_freqs, const f
                           const float* heads_b, int heads_n, float* gsbs, int gsbs_pitch, void* workspace,
                           long long workspace_bytes, void* stream);
 
+/* s2p_state_encoder_fwd for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same kernel,
+ * same arguments minus the workspace, BIT-IDENTICAL results; the workspace is a file-scope device array of
+ * S2P_STATE_ENCODER_STATIC_BYTES that every GPU loading the library holds until exit.  Limit: B * width <=
+ * s2p_state_encoder_static_max_floats() = 32768 (B <= 64 at the generator's width 512); larger sizes return
+ * S2P_ERR_UNSUPPORTED and launch nothing.  The call allocates nothing (no cudaMalloc / cudaFree, no library
+ * allocation): one cudaMemsetAsync of the 256 B of barrier counters and one cooperative launch on `stream`.  ALL calls
+ * on a device share the one array: calls that overlap on the GPU (two streams, two host threads) race -- serialise
+ * them on one stream or use s2p_state_encoder_fwd with separate workspaces. */
+#define S2P_STATE_ENCODER_STATIC_BYTES (256 + 2 * 32768 * 4)
+long long s2p_state_encoder_static_max_floats(void);
+int s2p_state_encoder_fwd_static(const float* state, int B, int S, int n_freqs, const float* const* layer_w,
+                                 const float* const* layer_b, int n_layers, int width, const float* heads_w,
+                                 const float* heads_b, int heads_n, float* gsbs, int gsbs_pitch, void* stream);
+
 /* packed weight of the data-gradient convolution: dst[ci][R-1-r][S-1-s][co] = w[co][ci][r][s]
  * (bf16 rows of R*S*Cout), so dX = s2p_conv_igemm_fwd(dY (zero-inserted when stride 2), dst,
  * pad = k-1-pad) -- replaces autograd's conv backward w.r.t. the input. */

@@ -50,6 +50,8 @@ SIGNATURES = {
     "s2p_linear_workspace_floats": (C.c_longlong, [_i, _i, _i]),
     "s2p_linear_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.c_longlong, _vp]),
     "s2p_state_encoder_workspace_bytes": (C.c_longlong, [_i, _i]),
+    "s2p_state_encoder_static_max_floats": (C.c_longlong, []),
+    "s2p_state_encoder_fwd_static": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _i, _vp, _i, _vp]),
     "s2p_state_encoder_fwd": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _i, _vp, _i, _vp, C.c_longlong, _vp]),
     "s2p_adam_step_multi": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _vp]),
     "s2p_transition_member_floats": (C.c_longlong, [_i, _i, _i]),

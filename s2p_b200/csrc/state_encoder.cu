@@ -468,3 +468,48 @@ extern "C" int s2p_state_encoder_fwd(const float* state, int B, int S, int n_fre
   count_launch();
   return check_launch("state_encoder_fused_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// The same launch for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc): the workspace of s2p_state_encoder_fwd lives in a file-scope device array instead of a
+// caller-provided buffer.  Every GPU that loads the library holds S2P_STATE_ENCODER_STATIC_BYTES (256 B of barrier
+// counters + ping/pong activations for up to 32768 floats of B * width, e.g. B = 64 at width 512) until exit.
+// No counterpart in the reference.
+namespace s2p {
+namespace se {
+constexpr long long kStaticFloats = 32768;                                  // max B * width
+constexpr long long kStaticBytes = 256 + 2 * kStaticFloats * 4;             // 262 400 B
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+}  // namespace se
+}  // namespace s2p
+
+extern "C" long long s2p_state_encoder_static_max_floats(void) { return s2p::se::kStaticFloats; }
+
+extern "C" int s2p_state_encoder_fwd_static(const float* state, int B, int S, int n_freqs, const float* const* layer_w,
+                                            const float* const* layer_b, int n_layers, int width, const float* heads_w,
+                                            const float* heads_b, int heads_n, float* gsbs, int gsbs_pitch, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(B > 0 && width > 0, "state_encoder_static: bad dims B=%d width=%d", B, width);
+  if (static_cast<long long>(B) * width > se::kStaticFloats)
+    return set_error(S2P_ERR_UNSUPPORTED,
+                     "state_encoder_static: B * width = %lld floats exceeds the built-in scratch of %lld floats "
+                     "(use s2p_state_encoder_fwd with a caller-provided workspace)",
+                     static_cast<long long>(B) * width, se::kStaticFloats);
+  // In host code the array's name is a host-side stand-in, not a device address: ask the runtime for this device's
+  // copy once per device, with that device current.
+  static void* scratch[kMaxDevices] = {};
+  const int dev = current_device();
+  if (dev < 0 || dev >= kMaxDevices) return set_error(S2P_ERR_CUDA, "state_encoder_static: bad device %d", dev);
+  if (scratch[dev] == nullptr) {
+    void* ptr = nullptr;
+    S2P_CHECK_CUDA(cudaGetSymbolAddress(&ptr, se::g_static_scratch));
+    if (ptr == nullptr) return set_error(S2P_ERR_CUDA, "state_encoder_static: cudaGetSymbolAddress returned a null address");
+    scratch[dev] = ptr;
+  }
+  // The array is shared by every call and keeps the last call's contents.  Only the barrier counters must start at
+  // zero (the activations are fully written before they are read); a finished launch leaves them zeroed, an aborted
+  // one may not, so they are cleared on the stream before every launch (no allocation: a memset node / async fill).
+  S2P_CHECK_CUDA(cudaMemsetAsync(scratch[dev], 0, 256, static_cast<cudaStream_t>(stream)));
+  return s2p_state_encoder_fwd(state, B, S, n_freqs, layer_w, layer_b, n_layers, width, heads_w, heads_b, heads_n, gsbs,
+                               gsbs_pitch, scratch[dev], se::kStaticBytes, stream);
+}
