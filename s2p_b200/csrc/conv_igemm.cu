@@ -376,74 +376,69 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         S2P_TRACE(7, it);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
-        if constexpr (HH) {
-          for (int kb = 0; kb < num_kb_hh; ++kb) {
+        // one ring stage's MMAs + the commit that frees the stage (run by the elected lane)
+        auto issue_stage = [&](int stg, int kb, int nkb) {
+          // descriptor start-address field is in 16-byte units: stage and operand offsets add directly
+          const uint64_t da = desc0 + static_cast<uint64_t>(stg * (Cfg::kStageBytes >> 4));
+          const uint64_t db = da + (Cfg::kABytes >> 4);
+          if constexpr (HH) {
             const bool main_kb = kb < p.R * cchunks;
-            S2P_TRACE(3, tr_m);
-            mbar_wait(&full_bar[stage], phase);
-            S2P_TRACE(4, tr_m);
-            tc_fence_after();
-            if (elect_one()) {
-              const uint64_t da = desc0 + static_cast<uint64_t>(stage * (Cfg::kStageBytes >> 4));
-              const uint64_t db = da + (Cfg::kABytes >> 4);
-              // tap s reads the box s rows (s * 128 B = 8 descriptor units) further down; the second operand (a 1x1
-              // convolution) reads its box at the centre column: one row down
-              const int s_lo = main_kb ? 0 : 1, s_hi = main_kb ? 3 : 2;
-              for (int s = s_lo; s < s_hi; ++s) {
-                const uint64_t das = da + 8u * s, dbs = db + (main_kb ? s : 0) * (Cfg::kBTapBytes >> 4);
+            // tap s reads the box s rows (s * 128 B = 8 descriptor units) further down; the second operand (a 1x1
+            // convolution) reads its box at the centre column: one row down
+            const int s_lo = main_kb ? 0 : 1, s_hi = main_kb ? 3 : 2;
+            for (int s = s_lo; s < s_hi; ++s) {
+              const uint64_t das = da + 8u * s, dbs = db + (main_kb ? s : 0) * (Cfg::kBTapBytes >> 4);
 #pragma unroll
-                for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
-                  const uint32_t accum = (kb != 0 || s != s_lo || k != 0) ? 1u : 0u;
-                  if constexpr (CL > 1) umma_bf16_pair(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
-                  else umma_bf16(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
-                }
-              }
-              if constexpr (CL > 1) {
-                umma_commit_pair(&empty_bar[stage], 3);
-                if (kb == num_kb_hh - 1) umma_commit_pair(&tmem_full[acc], 3);
-              } else {
-                umma_commit(&empty_bar[stage]);
-                if (kb == num_kb_hh - 1) umma_commit(&tmem_full[acc]);
+              for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
+                const uint32_t accum = (kb != 0 || s != s_lo || k != 0) ? 1u : 0u;
+                if constexpr (CL > 1) umma_bf16_pair(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
+                else umma_bf16(d_tmem, das + 2 * k, dbs + 2 * k, idesc, accum);
               }
             }
-            __syncwarp();
-            S2P_TRACE(5, tr_m);
-#ifdef S2P_CONV_TRACE
-            ++tr_m;
-#endif
-            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-          }
-        } else {
-        for (int kb = 0; kb < num_kb; ++kb) {
-          S2P_TRACE(3, tr_m);
-          mbar_wait(&full_bar[stage], phase);
-          S2P_TRACE(4, tr_m);
-          tc_fence_after();
-          if (elect_one()) {
-            // descriptor start-address field is in 16-byte units: stage and operand offsets add directly
-            const uint64_t da = desc0 + static_cast<uint64_t>(stage * (Cfg::kStageBytes >> 4));
-            const uint64_t db = da + (Cfg::kABytes >> 4);
+          } else {
 #pragma unroll
             for (int k = 0; k < Cfg::kBlockK / 16; ++k) {
               // +32 B per K=16 step inside the 128 B swizzle row
               if constexpr (CL > 1) umma_bf16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
               else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
             }
-            if constexpr (CL > 1) {
-              umma_commit_pair(&empty_bar[stage], 3);
-              if (kb == num_kb - 1) umma_commit_pair(&tmem_full[acc], 3);
-            } else {
-              umma_commit(&empty_bar[stage]);
-              if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
-            }
+          }
+          if constexpr (CL > 1) {
+            umma_commit_pair(&empty_bar[stg], 3);
+            if (kb == nkb - 1) umma_commit_pair(&tmem_full[acc], 3);
+          } else {
+            umma_commit(&empty_bar[stg]);
+            if (kb == nkb - 1) umma_commit(&tmem_full[acc]);
+          }
+        };
+        // Narrow tiles take the ring two stages at a time: a BLOCK_N = 128 stage holds 256 clk of tensor work, a halo
+        // stage of a 64-wide tile 384, but this thread's serial path per stage was ~80 clk of barrier probe + the UMMA
+        // issue + ~100 clk of elect / branch / loop (320 and 700 clk per stage: profiles/r02_conv_trace.txt).  One wait on
+        // both barriers and one elected region per pair halve the fixed part.  256-wide tiles (512 clk per stage,
+        // 4-5 ring stages) keep the one-stage loop.
+        constexpr bool kPairStages = BLOCK_N <= 128;
+        const int nkb = HH ? num_kb_hh : num_kb;
+        for (int kb = 0; kb < nkb;) {
+          const bool two = kPairStages && kb + 1 < nkb;
+          int stage_b = stage + 1;
+          uint32_t phase_b = phase;
+          if (stage_b == Cfg::kStages) { stage_b = 0; phase_b ^= 1; }
+          S2P_TRACE(3, tr_m);
+          if (two) mbar_wait2(&full_bar[stage], phase, &full_bar[stage_b], phase_b);
+          else mbar_wait(&full_bar[stage], phase);
+          S2P_TRACE(4, tr_m);
+          tc_fence_after();
+          if (elect_one()) {
+            issue_stage(stage, kb, nkb);
+            if (two) issue_stage(stage_b, kb + 1, nkb);
           }
           __syncwarp();
           S2P_TRACE(5, tr_m);
 #ifdef S2P_CONV_TRACE
           ++tr_m;
 #endif
+          if (two) { stage = stage_b; phase = phase_b; kb += 2; } else { kb += 1; }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-        }
         }
       }
     }

@@ -61,6 +61,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Two barriers in one wait: both probes are in flight together, so a pair of ready barriers costs one probe latency
+// (~70-80 clk on the MMA thread's critical path, tools/conv_trace.py) instead of two.
+__device__ __forceinline__ void mbar_wait2(uint64_t* bar_a, uint32_t parity_a, uint64_t* bar_b, uint32_t parity_b) {
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P, Q;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 Q, [%3], %4;\n\t"
+        "and.pred P, P, Q;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar_a)), "r"(parity_a), "r"(smem_u32(bar_b)), "r"(parity_b)
+        : "memory");
+    if (ok) break;
+    if (++spins > (1u << 26)) __trap();
+  }
+}
+
 // The same wait for warps that are NOT on the tensor pipe's critical path (the epilogue group): every failed probe of
 // an mbarrier is a shared-memory access, and eight warps spinning on the accumulator barrier took ~15 % of the SM's
 // shared-memory wavefronts away from the UMMA operand reads (ncu, profiles/r02_history.md).  Back off between probes.

@@ -31,23 +31,32 @@ def read():
     return buf
 
 
-def report(name, stages_per_tile, skip_tiles=4, tiles=12):
+def report(name, stages_per_tile, skip_tiles=4, tiles=12, paired=True):
     t = read()
     s0, s1 = skip_tiles * stages_per_tile, (skip_tiles + tiles) * stages_per_tile
     p0, p1 = s0 // 3, s1 // 3             # producer warp 0 records its own stages only: every third
     prod_wait = (t[1] - t[0])[p0:p1]
     prod_issue = (t[2] - t[1])[p0:p1]
-    mma_wait = (t[4] - t[3])[s0:s1]
-    mma_issue = (t[5] - t[4])[s0:s1]
-    per_stage = np.diff(t[5][s0:s1 + 1])
+    # the MMA thread records one entry per loop iteration: two ring stages for tiles of at most 128 columns
+    ipt = (stages_per_tile + 1) // 2 if paired else stages_per_tile
+    m0, m1 = skip_tiles * ipt, (skip_tiles + tiles) * ipt
+    mma_wait = (t[4] - t[3])[m0:m1]
+    mma_issue = (t[5] - t[4])[m0:m1]
+    per_stage = np.diff(t[5][m0:m1 + 1]) * ipt / stages_per_tile
     tile_wait = (t[7] - t[6])[skip_tiles:skip_tiles + tiles]
     epi_wait = (t[9] - t[8])[skip_tiles:skip_tiles + tiles]
     epi_busy = (t[8][skip_tiles + 1:skip_tiles + tiles + 1] - t[9][skip_tiles:skip_tiles + tiles])
     f = lambda a: f"mean {a.mean():7.0f}  med {np.median(a):7.0f}  max {a.max():7.0f}"
     print(f"== {name}: {stages_per_tile} stages per tile; clk per stage {per_stage.mean():.0f}, per tile {per_stage.mean() * stages_per_tile:.0f}")
     print(f"   producer wait(empty) {f(prod_wait)}\n   producer issue       {f(prod_issue)}")
-    print(f"   mma wait(full)       {f(mma_wait)}\n   mma issue            {f(mma_issue)}")
+    print(f"   mma wait(full)       {f(mma_wait)}   (per loop iteration: {'two stages' if paired else 'one stage'})\n   mma issue            {f(mma_issue)}")
     print(f"   mma wait(tmem_empty) {f(tile_wait)}\n   epi wait(tmem_full)  {f(epi_wait)}\n   epi busy             {f(epi_busy)}")
+    if os.environ.get("CONV_TRACE_TIMELINE"):
+        base = t[6][skip_tiles]
+        print("   timeline of 5 tiles (clk from the first): issuer [wait acc .. got acc | per iteration: wait, got, issued] | epilogue [tile start, accumulator full]")
+        for i in range(skip_tiles, skip_tiles + 5):
+            its = " ".join(f"({t[3][j] - base},{t[4][j] - base},{t[5][j] - base})" for j in range(i * ipt, (i + 1) * ipt))
+            print(f"     tile {i}: issuer {t[6][i] - base:6d} {t[7][i] - base:6d} | {its} | epilogue {t[8][i] - base:6d} {t[9][i] - base:6d}")
 
 
 def run_plain(b, cin, cout, hw=100, cin2=0, stats=False, wide=False):
@@ -105,4 +114,4 @@ if __name__ == "__main__":
     us = run_plain(B, 256, 128, stats=True)
     report(f"<128> Cin 256 ({us:.0f} us)", 36, skip_tiles=2, tiles=6)
     us = run_plain(B, 64, 768)
-    report(f"<256> Cin 64 -> 768 (hs1-like, {us:.0f} us)", 9, skip_tiles=4, tiles=12)
+    report(f"<256> Cin 64 -> 768 (hs1-like, {us:.0f} us)", 9, skip_tiles=4, tiles=12, paired=False)
