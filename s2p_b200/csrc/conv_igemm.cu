@@ -66,7 +66,9 @@ struct ConvParams {
   int kb2;
 };
 
-enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2 };
+// kEpiSimple: the plain epilogue without residual, wide output and statistics (bias + activation + store only), as a
+// kernel of its own: compiled into the general kernel as a second path it cost that path 3-9 % (register allocation).
+enum { kEpiPlain = 0, kEpiMat = 1, kEpiToRGB = 2, kEpiSimple = 3 };
 
 template <int BLOCK_N, int CL, int EPI, bool HH = false>
 struct ConvCfg {
@@ -86,7 +88,7 @@ struct ConvCfg {
   static constexpr int kXBytes = kXBoxes * kABytes;
   // statistics: the four lane-quarter warps of a tile combine their (sum, sumsq) columns here before ONE partial row
   // per tile goes to global memory (double buffered by tile parity)
-  static constexpr int kStatBytes = EPI == kEpiPlain ? 2 * 4 * BLOCK_N * 8 : 0;
+  static constexpr int kStatBytes = EPI == kEpiPlain ? 2 * 4 * BLOCK_N * 8 : 0;   // (kEpiSimple keeps no statistics)
   static constexpr int kFixedBytes = 1024 /*align*/ + 256 /*barriers*/ + kTabBytes + kStoreBytes + kXBytes + kStatBytes;
   static constexpr int kMaxStages = (227 * 1024 - kFixedBytes) / kStageBytes;
   // Ring depth.  Measured (profiles/r02_stage_sweep.txt): the wide tiles do not gain from more than 4-5 stages --
@@ -161,6 +163,56 @@ __device__ __forceinline__ void warp_store_rows(uint32_t stg, const uint32_t* pa
     if ((rows.valid_mask >> i) & 1u)
       *reinterpret_cast<uint4*>(out_col + static_cast<size_t>(rows.pix[i]) * out_pitch + j * 8) = v;
   }
+  __syncwarp();
+}
+
+// The store of the bias / activation-only epilogue (kEpiSimple), where the store phase is a third of a chunk's
+// instructions: the destination of each of the NCH store instructions is kept as a 32-bit ELEMENT offset from the
+// tile's image (pixel inside the image x pitch + this lane's 8-channel column; the host checks H * W * pitch < 2^32),
+// so a store's address is one 64-bit add to a tile-uniform base instead of ten instructions of 64-bit index
+// arithmetic, and the validity test is a predicate on the store itself (no divergent branch per instruction).
+template <int NCH>
+struct StoreOffs {
+  uint32_t off[NCH];
+  uint32_t valid_mask;
+};
+template <int NCH>
+__device__ __forceinline__ StoreOffs<NCH> store_offs_prepare(uint32_t pix_in_image, bool valid, int lane, int out_pitch) {
+  StoreOffs<NCH> r;
+  r.valid_mask = 0u;
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int rr = i * (32 / NCH) + lane / NCH;
+    r.off[i] = __shfl_sync(0xffffffffu, pix_in_image, rr) * static_cast<uint32_t>(out_pitch) + static_cast<uint32_t>(lane % NCH) * 8u;
+    r.valid_mask |= static_cast<uint32_t>(__shfl_sync(0xffffffffu, static_cast<int>(valid), rr)) << i;
+  }
+  return r;
+}
+__device__ __forceinline__ void stg128_if(void* ptr, const uint4& v, uint32_t pred) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\t@p st.global.v4.b32 [%0], {%1, %2, %3, %4};\n\t}\n" ::"l"(ptr),
+               "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(pred));   // (no memory clobber: nothing in the kernel reads `out` back)
+}
+template <int NCH>
+__device__ __forceinline__ void warp_store_offs(uint32_t stg, const uint32_t* packed, __nv_bfloat16* out_col,
+                                                const StoreOffs<NCH>& rows, int lane) {   // out_col: image base + channel
+  constexpr int kRow = NCH * 16;
+  const int wkey = (NCH == 4) ? (lane >> 1) : (lane >> 2);
+#pragma unroll
+  for (int j = 0; j < NCH; ++j)
+    sts128(stg + lane * kRow + ((j ^ wkey) & (NCH - 1)) * 16, packed[4 * j], packed[4 * j + 1], packed[4 * j + 2],
+           packed[4 * j + 3]);
+  __syncwarp();
+  constexpr int kRowsPerInst = 32 / NCH;
+  const int j = lane % NCH;
+  uint4 vv[NCH];             // all loads first, then the stores (both are volatile asm: program order is issue order)
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const int rr = i * kRowsPerInst + lane / NCH;
+    const int rkey = (NCH == 4) ? (rr >> 1) : (rr >> 2);
+    vv[i] = lds128(stg + rr * kRow + ((j ^ rkey) & (NCH - 1)) * 16);
+  }
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) stg128_if(out_col + rows.off[i], vv[i], (rows.valid_mask >> i) & 1u);
   __syncwarp();
 }
 
@@ -455,7 +507,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int my = m / p.mpitch, mx = m - my * p.mpitch;   // (HH: mpitch = tile_w + 2, columns >= tile_w are halo rows)
     const float* bias_s = p.bias;
     bool bias_staged = false;
-    if constexpr (EPI == kEpiPlain) {
+    if constexpr (EPI == kEpiPlain || EPI == kEpiSimple) {
       // bias vector staged in shared memory once per CTA (broadcast LDS instead of global loads)
       if (p.bias != nullptr && p.Cout <= 1024) {
         float* bs = reinterpret_cast<float*>(tab_smem);
@@ -602,6 +654,64 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         } else {
           release_acc();
+        }
+      } else if constexpr (EPI == kEpiSimple) {
+        // bias + activation + store only (the merged mlp_shared convs, the discriminator / VGG convs, every
+        // data-gradient conv): the accumulators are converted in place and the next chunk is requested once they are
+        // packed -- no register copies (the general epilogue below reloads `raw` under a live copy: 32 moves per
+        // chunk), ReLU on the packed pairs (rounding to bf16 is monotonic and keeps 0: the same bits, 16 instructions
+        // instead of 32), 32-bit store offsets.  310 -> ~200 instructions per chunk; hs1 930 -> 858 us.
+        constexpr int kChunks = BLOCK_N / 64;          // 32-column chunks per warp
+        const int cbeg = half * kChunks;
+        const StoreOffs<4> offs4 = store_offs_prepare<4>(static_cast<uint32_t>(h * p.W + w), valid, lane, p.out_pitch);
+        __nv_bfloat16* out_img = p.out + static_cast<size_t>(img) * p.H * p.W * p.out_pitch + n0;   // tile-uniform
+        mbar_wait_relaxed(&tmem_full[acc], acc_phase);
+        if (et == 0) S2P_TRACE(9, it);
+        tc_fence_after();
+        uint32_t raw[32];
+        tmem_ld32(t_row + cbeg * 32, raw);
+#pragma unroll 1
+        for (int i = 0; i < kChunks; ++i) {
+          const int c = cbeg + i;
+          float4 bb[8];
+          if (bias_staged) {
+            const uint32_t b_a = smem_u32(bias_s + n0 + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bb[j] = lds128f(b_a + 16u * j);
+          } else if (bias_s != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(bias_s + n0 + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bb[j] = __ldg(b4 + j);
+          }
+          tmem_ld_wait();
+          uint32_t packed[16];
+          if (bias_s != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float a0 = __uint_as_float(raw[4 * j + 0]) + bb[j].x, a1 = __uint_as_float(raw[4 * j + 1]) + bb[j].y;
+              float a2 = __uint_as_float(raw[4 * j + 2]) + bb[j].z, a3 = __uint_as_float(raw[4 * j + 3]) + bb[j].w;
+              if (p.act == 2) {
+                a0 = a0 > 0.f ? a0 : 0.2f * a0; a1 = a1 > 0.f ? a1 : 0.2f * a1;
+                a2 = a2 > 0.f ? a2 : 0.2f * a2; a3 = a3 > 0.f ? a3 : 0.2f * a3;
+              }
+              packed[2 * j] = pack_bf16x2(a0, a1);
+              packed[2 * j + 1] = pack_bf16x2(a2, a3);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              float a0 = __uint_as_float(raw[2 * j]), a1 = __uint_as_float(raw[2 * j + 1]);
+              if (p.act == 2) { a0 = a0 > 0.f ? a0 : 0.2f * a0; a1 = a1 > 0.f ? a1 : 0.2f * a1; }
+              packed[j] = pack_bf16x2(a0, a1);
+            }
+          }
+          if (p.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) packed[j] = relu_bf16x2(packed[j]);
+          }
+          if (i + 1 < kChunks) tmem_ld32(t_row + (c + 1) * 32, raw);
+          else release_acc();
+          warp_store_offs<4>(stg_s, packed, out_img + c * 32, offs4, lane);
         }
       } else {
         constexpr int kChunks = BLOCK_N / 64;          // 32-column chunks per warp
@@ -892,6 +1002,10 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
   p.Cin = Cin; p.Cout = Cout; p.R = ksize; p.S = ksize; p.pad = pad; p.stride = stride;
   if (static_cast<long long>(B) * p.H * p.W >= (1LL << 32))
     return set_error(S2P_ERR_BAD_ARG, "conv: B*H*W must be below 2^32 pixels per call");
+  // the bias / activation-only epilogue is a kernel of its own (32-bit store offsets inside an image)
+  if (epi == kEpiPlain && p.residual == nullptr && p.out_lo == nullptr && p.stats_partial == nullptr &&
+      static_cast<long long>(p.H) * p.W * p.out_pitch < (1LL << 32))
+    epi = kEpiSimple;
   const bool hh = conv_uses_hh(block_n, ksize, stride, pad, epi);
   if (hh) conv_pick_tile_hh(p.H, p.W, &p.tile_w, &p.tile_h);
   else conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
@@ -965,6 +1079,14 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     switch (block_n) {
       case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, tx, p, st);
       default: return launch_conv<128, kEpiMat>(ta, tb, ta2, tx, p, st);
+    }
+  }
+  if (epi == kEpiSimple) {
+    switch (block_n) {
+      case 256: return launch_conv<256, kEpiSimple>(ta, tb, ta2, tx, p, st);
+      case 192: return launch_conv<192, kEpiSimple>(ta, tb, ta2, tx, p, st);
+      case 128: return launch_conv<128, kEpiSimple>(ta, tb, ta2, tx, p, st);
+      default: return hh ? launch_conv<64, kEpiSimple, true>(ta, tb, ta2, tx, p, st) : launch_conv<64, kEpiSimple>(ta, tb, ta2, tx, p, st);
     }
   }
   switch (block_n) {

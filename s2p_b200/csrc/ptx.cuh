@@ -84,10 +84,11 @@ __device__ __forceinline__ void mbar_wait2(uint64_t* bar_a, uint32_t parity_a, u
 // The same wait for warps that are NOT on the tensor pipe's critical path (the epilogue group): every failed probe of
 // an mbarrier is a shared-memory access, and eight warps spinning on the accumulator barrier took ~15 % of the SM's
 // shared-memory wavefronts away from the UMMA operand reads (ncu, profiles/r02_history.md).  Back off between probes.
+template <uint32_t kSleepNs = 128>
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    __nanosleep(128);
+    __nanosleep(kSleepNs);
     if (++spins > (1u << 24)) __trap();
   }
 }
@@ -314,6 +315,11 @@ __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint32_t relu_bf16x2(uint32_t u) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(u), "r"(0u));
+  return r;
 }
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }

@@ -1,12 +1,20 @@
 """Times individual conv layers of the generator (CUDA events, L2 flushed between runs).
-usage: python tools/conv_bench.py [batch]"""
+usage: python tools/conv_bench.py [batch] [path of another build of the library, for a same-box A/B]"""
 import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
-from s2p_b200 import ops
+from s2p_b200 import _lib
+
+if len(sys.argv) > 2:
+    import ctypes
+    _lib.LIB_PATH = os.path.abspath(sys.argv[2])
+    probe = ctypes.CDLL(_lib.LIB_PATH)
+    for name in [n for n in _lib.SIGNATURES if not hasattr(probe, n)]:
+        del _lib.SIGNATURES[name]
+from s2p_b200 import ops  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 128
 # name, H, Cin, Cout, k, act, residual, stats
