@@ -10,8 +10,15 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
     sys.path.insert(0, p)
 import torch
 
-import s2p_b200
 from s2p_b200 import _lib
+
+if os.environ.get("S2P_TOOL_LIB"):          # same-box A/B against another build of the library (tools only)
+    import ctypes
+    _lib.LIB_PATH = os.path.abspath(os.environ["S2P_TOOL_LIB"])
+    _probe = ctypes.CDLL(_lib.LIB_PATH)
+    for _n in [n for n in _lib.SIGNATURES if not hasattr(_probe, n)]:
+        del _lib.SIGNATURES[_n]
+import s2p_b200  # noqa: E402
 from s2p_b200.training import S2PTrainer
 
 ap = argparse.ArgumentParser()
