@@ -166,10 +166,13 @@ int s2p_torgb_tanh_fwd(const void* x, int x_pitch, const float* w_oihw, const fl
                        float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,
                        void* stream);
 
-/* ToRGB on the tensor cores: the same implicit-GEMM pipeline with a 16-column accumulator
- * tile (3 live columns).  x must already be activated (the producing conv applies the
- * LeakyReLU of oracle S2PGenerator.forward in its epilogue); w_packed16 is
- * [16][R*S*Cin] bf16, rows 0..2 = s2p_pack_conv_weight(conv_img.weight), rows 3..15 zero.
+/* ToRGB on the tensor cores: the same implicit-GEMM pipeline in its halo mode, with the three taps of a filter
+ * row folded into the accumulator's columns: ONE 48-column UMMA group per (filter row, 64-channel chunk) over the
+ * un-shifted activation box, and the epilogue adds the 16-column groups of rows m, m+1, m+2 (12 UMMAs per tile
+ * instead of 36; a thin UMMA costs its A-operand read whatever N is).  x must already be activated (the producing conv
+ * applies the LeakyReLU of oracle S2PGenerator.forward in its epilogue).  w_packed16 (name kept from the 16-column
+ * version) is [48][3*Cin] bf16: row 16*s + c = filter column s of output channel c (c < 3, other rows zero),
+ * column r*Cin + ci = filter row r of input channel ci.
  * out = tanh(conv3x3(x) + bias) -> fp32 NCHW and/or uint8 NHWC.  Cin % 64 == 0. */
 int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_packed16, const float* bias,
                         float* out_f32_nchw, uint8_t* out_u8_nhwc, int B, int H, int W, int Cin,

@@ -78,7 +78,8 @@ struct ConvCfg {
   static constexpr int kBTapBytes = BLOCK_N / CL * kBlockK * 2;   // one tap's weight tile; a CTA of a pair holds half of it
   // HH (horizontal halo, thin tiles): a stage carries ONE activation box with a 1-pixel halo left and right and the
   // weight tiles of the three taps of a filter row that read it
-  static constexpr int kBBytes = (HH ? 3 : 1) * kBTapBytes;
+  // (ToRGB folds the three taps of a filter row into the N dimension instead: one 48-row weight tile per stage)
+  static constexpr int kBBytes = ((HH && EPI != kEpiToRGB) ? 3 : 1) * kBTapBytes;
   static constexpr int kStageBytes = kABytes + ((kBBytes + 1023) / 1024) * 1024;
   static constexpr int kStoreBytes = 8 * 2048;   // per-epilogue-warp 32 x 64 B transpose rows
   static constexpr int kTabBytes = 2 * 128 * 16;   // fused epilogue: double-buffered (A,Bc,G1,B0) rows
@@ -97,7 +98,7 @@ struct ConvCfg {
   // mlp_shared conv and neutral elsewhere).  The narrow tiles are operand-ingest bound and keep the deepest ring.
   static constexpr int kWant = BLOCK_N >= 256 ? (EPI == kEpiMat ? 4 : 5) : 8;
   static constexpr int kStages = kMaxStages > kWant ? kWant : kMaxStages;
-  static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : BLOCK_N;
+  static constexpr int kAccStride = (BLOCK_N > 128) ? 256 : (BLOCK_N == 48 ? 64 : BLOCK_N);   // a power of two >= 32 per buffer pair
   static constexpr uint32_t kTmemCols = 2 * kAccStride;   // 32 / 128 / 256 / 512
   static constexpr int kSmemBytes = kStages * kStageBytes + kFixedBytes;
 };
@@ -297,6 +298,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   // SWIZZLE_128B descriptor may start at any 128-byte row of a tile TMA wrote (profiles/r01_umma_rowshift_probe.txt).
   // One box per (filter row, channel chunk) feeds three taps: 2.8x fewer activation bytes enter the SM, which is what
   // bounds the thin (Cout <= 64) tiles; the price is 100 live rows of 128 instead of 125.
+  // ToRGB in halo mode: the three taps of a filter row are folded into N (weight tile = 3 x 16 rows), the UMMAs read
+  // the box un-shifted and the epilogue adds the row-shifted 16-column groups: 12 UMMAs per tile instead of 36, each of
+  // which is bound by its 32-clk A-operand read whatever N is (profiles/r02_conv_trace.txt).
+  constexpr bool kFold = (EPI == kEpiToRGB) && HH;
   const uint32_t a_bytes = static_cast<uint32_t>(p.mpitch * p.tile_h) * 128u;
   const uint32_t stage_tx = (a_bytes + Cfg::kBBytes) * CL;   // both CTAs' boxes signal the leader's barrier
   const int num_kb_hh = HH ? p.R * cchunks + p.kb2 : 0;      // HH: a k-block = (filter row, chunk): three taps
@@ -335,11 +340,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             // everything the loads need is computed before the barrier poll
             uint8_t* sa = smem + stage * Cfg::kStageBytes;
             uint8_t* sb = sa + Cfg::kABytes;
-            const int ntap = main_kb ? 3 : 1;
+            const int ntap = (main_kb && !kFold) ? 3 : 1;
             int ach = ck * Cfg::kBlockK;
             if (p.cin_wrap > 0 && ach >= p.cin_wrap) ach -= p.cin_wrap;
             const uint32_t tx = (a_bytes + static_cast<uint32_t>(ntap) * Cfg::kBTapBytes) * CL;
-            const int kcol = main_kb ? (rr * 3 * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK;
+            const int kcol = kFold ? (rr * cchunks + ck) * Cfg::kBlockK
+                                   : (main_kb ? (rr * 3 * cchunks + ck) * Cfg::kBlockK : (9 * cchunks + kb - p.R * cchunks) * Cfg::kBlockK);
             const int a2ch = (kb - p.R * cchunks) * Cfg::kBlockK;
             if (my_turn == 0) S2P_TRACE(0, tr_p);
             mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -437,7 +443,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const bool main_kb = kb < p.R * cchunks;
             // tap s reads the box s rows (s * 128 B = 8 descriptor units) further down; the second operand (a 1x1
             // convolution) reads its box at the centre column: one row down
-            const int s_lo = main_kb ? 0 : 1, s_hi = main_kb ? 3 : 2;
+            // (ToRGB fold: ONE UMMA group over the un-shifted box; the taps are 16-column groups of the accumulator)
+            const int s_lo = (main_kb || kFold) ? 0 : 1, s_hi = kFold ? 1 : (main_kb ? 3 : 2);
             for (int s = s_lo; s < s_hi; ++s) {
               const uint64_t das = da + 8u * s, dbs = db + (main_kb ? s : 0) * (Cfg::kBTapBytes >> 4);
 #pragma unroll
@@ -646,15 +653,30 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_wait_relaxed(&tmem_full[acc], acc_phase);
         if (et == 0) S2P_TRACE(9, it);
         tc_fence_after();
-        if (half == 0) {
-          uint32_t r16[16];
-          tmem_ld16(t_row, r16);
+        static_assert(EPI != kEpiToRGB || (HH && BLOCK_N == 48), "ToRGB runs in the tap-folded halo mode only");
+        // The two warp groups (column halves elsewhere) take the tiles in turn: a tile's epilogue is a chain of
+        // latencies (wake-up, tcgen05.ld, exchange, tanh, stores: ~1300 clk) around very little work, and with the two
+        // accumulator buffers two of them can be in flight.  The idle group still waits for the tile's accumulator
+        // barrier before it releases, so no warp runs more than one tile ahead of the MMA thread.
+        if (half == (it & 1)) {
+          // accumulator columns [16 s, 16 s + 3) of row m hold tap s of the filter rows applied to the box row m:
+          // out(m) = D(m)[0..2] + D(m + 1)[16..18] + D(m + 2)[32..34].  Rows m + 1, m + 2 are the next two lanes: the
+          // host picks a row pitch (tile_w + 2) that divides 32, so the last two lanes of every warp are halo rows and
+          // no valid row needs another warp's accumulators.  Fixed summation order.
+          uint32_t g0[16], g1[16], g2[16];
+          tmem_ld16(t_row, g0);
+          tmem_ld16(t_row + 16, g1);
+          tmem_ld16(t_row + 32, g2);
           tmem_ld_wait();
           release_acc();
-          if (valid) {
-            float o[3];
+          float o[3];
 #pragma unroll
-            for (int k = 0; k < 3; ++k) o[k] = tanhf(__uint_as_float(r16[k]) + (p.bias ? __ldg(p.bias + k) : 0.f));
+          for (int k = 0; k < 3; ++k) {
+            const float t1 = __shfl_down_sync(0xffffffffu, __uint_as_float(g1[k]), 1);
+            const float t2 = __shfl_down_sync(0xffffffffu, __uint_as_float(g2[k]), 2);
+            o[k] = tanhf(((__uint_as_float(g0[k]) + t1) + t2) + (p.bias ? __ldg(p.bias + k) : 0.f));
+          }
+          if (valid) {
             const int HW = p.H * p.W;
             const int rem = h * p.W + w;
             if (p.rgb_f32 != nullptr) {
@@ -938,6 +960,24 @@ void conv_pick_tile_hh(int H, int W, int* tw_out, int* th_out) {
   *th_out = bth;
 }
 
+// ToRGB (tap-folded halo mode): the row pitch tile_w + 2 must divide 32, so that rows 30, 31 of every 32-row lane
+// quarter are halo rows (the epilogue takes rows m + 1, m + 2 from the next lanes of the same warp).
+void conv_pick_tile_torgb(int H, int W, int* tw_out, int* th_out) {
+  double best = -1.0;
+  int btw = 30, bth = 4;
+  const int cand[3] = {30, 14, 6};
+  for (int i = 0; i < 3; ++i) {
+    const int tw = cand[i];
+    int th = 128 / (tw + 2);
+    if (th > H) th = H;
+    const long tiles = static_cast<long>((W + tw - 1) / tw) * ((H + th - 1) / th);
+    const double eff = static_cast<double>(H) * W / (tiles * 128.0);
+    if (eff > best + 1e-9) { best = eff; btw = tw; bth = th; }
+  }
+  *tw_out = btw;
+  *th_out = bth;
+}
+
 // which convolutions run in the horizontal-halo mode: 3x3 stride-1 'same' convs whose accumulator tile is at most 64
 // columns wide (operand-ingest bound otherwise: 35 % tensor pipe at Cout = 64, 8 % for ToRGB)
 static bool conv_uses_hh(int Cout_tile, int ksize, int stride, int pad, int epi) {
@@ -1023,7 +1063,8 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
       static_cast<long long>(p.H) * p.W * p.out_pitch < (1LL << 32))
     epi = kEpiSimple;
   const bool hh = conv_uses_hh(block_n, ksize, stride, pad, epi);
-  if (hh) conv_pick_tile_hh(p.H, p.W, &p.tile_w, &p.tile_h);
+  if (epi == kEpiToRGB) conv_pick_tile_torgb(p.H, p.W, &p.tile_w, &p.tile_h);
+  else if (hh) conv_pick_tile_hh(p.H, p.W, &p.tile_w, &p.tile_h);
   else conv_pick_tile(p.H, p.W, 128, &p.tile_w, &p.tile_h);
   p.mpitch = hh ? p.tile_w + 2 : p.tile_w;
   p.tiles_x = (p.W + p.tile_w - 1) / p.tile_w;
@@ -1047,7 +1088,8 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv: activation tensor map encode failed (CUresult %d)", (int)r);
   }
   {
-    const int K = ksize * ksize * Cin + (x2 != nullptr ? Cin2 : 0);
+    // (ToRGB: [48 = 3 taps x 16][3 filter rows x Cin], see s2p_torgb_igemm_fwd)
+    const int K = epi == kEpiToRGB ? ksize * Cin : ksize * ksize * Cin + (x2 != nullptr ? Cin2 : 0);
     cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Cout};
     cuuint64_t strides[1] = {(cuuint64_t)K * 2};
     cuuint32_t box[2] = {64, (cuuint32_t)(block_n / conv_cluster_size())};   // each CTA loads its share
@@ -1090,7 +1132,10 @@ static int conv_dispatch(const void* x, int x_pitch, const void* w_packed, int B
     if (r != CUDA_SUCCESS) return set_error(S2P_ERR_CUDA, "conv_mat_fused: x tensor map encode failed (CUresult %d)", (int)r);
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (epi == kEpiToRGB) return hh ? launch_conv<16, kEpiToRGB, true>(ta, tb, ta2, tx, p, st) : launch_conv<16, kEpiToRGB>(ta, tb, ta2, tx, p, st);
+  if (epi == kEpiToRGB) {
+    if (!hh || block_n != 48) return set_error(S2P_ERR_UNSUPPORTED, "torgb: the tap-folded kernel needs a 3x3 stride-1 'same' convolution");
+    return launch_conv<48, kEpiToRGB, true>(ta, tb, ta2, tx, p, st);
+  }
   if (epi == kEpiMat) {
     switch (block_n) {
       case 256: return launch_conv<256, kEpiMat>(ta, tb, ta2, tx, p, st);
@@ -1214,5 +1259,5 @@ extern "C" int s2p_torgb_igemm_fwd(const void* x, int x_pitch, const void* w_pac
   p.bias = bias;
   p.rgb_f32 = out_f32_nchw;
   p.rgb_u8 = out_u8_nhwc;
-  return conv_dispatch(x, x_pitch, w_packed16, B, H, W, Cin, 16, 3, 1, 1, 16, kEpiToRGB, p, stream);
+  return conv_dispatch(x, x_pitch, w_packed16, B, H, W, Cin, 48, 3, 1, 1, 48, kEpiToRGB, p, stream);
 }

@@ -354,13 +354,15 @@ def torgb_tanh(x, w_oihw, bias, out_f32=None, out_u8=None):
 
 
 def pack_torgb_weight(w_oihw: torch.Tensor) -> torch.Tensor:
-    """[3, Cin, 3, 3] fp32 -> [16, 9*Cin] bf16 (rows 3..15 zero) for torgb_igemm."""
+    """[3, Cin, 3, 3] fp32 -> [48, 3*Cin] bf16 for torgb_igemm: row 16*s + c holds tap s (filter column) of output
+    channel c (rows 16*s + 3 .. 16*s + 15 zero), column r*Cin + ci filter row r of input channel ci -- the three taps
+    of a filter row are 16-column groups of ONE 48-column UMMA (see s2p_torgb_igemm_fwd)."""
     co, ci, r, s_ = w_oihw.shape
-    if co > 16:
-        raise RuntimeError("pack_torgb_weight: at most 16 output channels")
-    out = torch.zeros(16, r * s_ * ci, dtype=torch.bfloat16, device=w_oihw.device)
-    pack_conv_weight(w_oihw, out[:co])
-    return out
+    if co > 16 or r != 3 or s_ != 3:
+        raise RuntimeError("pack_torgb_weight: a 3x3 filter with at most 16 output channels")
+    out = torch.zeros(3, 16, 3, ci, dtype=torch.float32, device=w_oihw.device)
+    out[:, :co] = w_oihw.detach().float().permute(3, 0, 2, 1)        # [s, c, r, ci]
+    return out.reshape(48, 3 * ci).to(torch.bfloat16).contiguous()
 
 
 def torgb_igemm(x_activated, w_packed16, bias, out_f32=None, out_u8=None):
@@ -369,8 +371,8 @@ def torgb_igemm(x_activated, w_packed16, bias, out_f32=None, out_u8=None):
     b, h, w, cin = x_activated.shape
     if out_f32 is None and out_u8 is None:
         out_f32 = torch.empty(b, 3, h, w, dtype=torch.float32, device=x_activated.device)
-    if w_packed16.dtype != torch.bfloat16 or tuple(w_packed16.shape) != (16, 9 * cin) or not w_packed16.is_contiguous():
-        raise RuntimeError("torgb_igemm: packed weight must be contiguous bf16 [16, 9*Cin]")
+    if w_packed16.dtype != torch.bfloat16 or tuple(w_packed16.shape) != (48, 3 * cin) or not w_packed16.is_contiguous():
+        raise RuntimeError("torgb_igemm: packed weight must be contiguous bf16 [48, 3*Cin] (pack_torgb_weight)")
     _lib.check(
         _lib.load().s2p_torgb_igemm_fwd(x_activated.data_ptr(), _nhwc_pitch(x_activated, "x"), w_packed16.data_ptr(),
                                         _ptr(bias), _ptr(out_f32), _ptr(out_u8), b, h, w, cin, _stream()),

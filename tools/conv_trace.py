@@ -104,7 +104,7 @@ def run_torgb(b, cin=64, hw=100):
 if __name__ == "__main__":
     B = 128
     us = run_torgb(B)
-    report(f"ToRGB <16, HH> Cin 64 ({us:.0f} us)", 3)
+    report(f"ToRGB <48 folded, HH> Cin 64 ({us:.0f} us)", 3)
     us = run_plain(B, 64, 64)
     report(f"<64, HH> Cin 64 ({us:.0f} us)", 3)
     us = run_plain(B, 128, 64, stats=True, wide=True)
