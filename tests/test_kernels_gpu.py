@@ -281,6 +281,12 @@ def test_torgb_igemm(ops):
     o = ops.torgb_igemm(xs, ops.pack_torgb_weight(w5), None)
     ref = torch.tanh(F.conv2d(xs.float().permute(0, 3, 1, 2), w5.to(torch.bfloat16).float(), None, 1, 1))
     assert (o - ref).abs().max().item() <= 2e-5
+    # frames narrower than every candidate tile (tile_w in {30, 14, 6}: the row pitch must divide 32), odd sizes
+    for b, hh, ww in ((1, 5, 5), (2, 3, 9), (1, 33, 31), (3, 64, 64)):
+        xs = torch.randn(b, hh, ww, 64, generator=g).cuda().to(torch.bfloat16)
+        o = ops.torgb_igemm(xs, wp, b3)
+        ref = torch.tanh(F.conv2d(xs.float().permute(0, 3, 1, 2), w3.to(torch.bfloat16).float(), b3, 1, 1))
+        assert (o - ref).abs().max().item() <= 2e-5, (b, hh, ww)
 
 
 def test_state_encoder_kernels(ops):
