@@ -380,6 +380,43 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __
   }
 }
 
+// The same reduction with coalesced stores: a warp owns 32 input channels of one output channel and keeps their RS
+// taps in registers (coalesced reads along ci for every tap and split, the same fixed split order), then transposes
+// [RS][32] -> [32][RS] through shared memory: the 32 * RS floats of dW it produces are CONTIGUOUS in the OIHW layout.
+// The scalar kernel above writes 4 bytes with a stride of RS * 4: 22 us for 22 MB (44 launches per training step).
+template <int RS>
+__global__ void __launch_bounds__(256)
+wgrad_reduce_tile_kernel(const float* __restrict__ partial, float* __restrict__ dw_oihw, int splits, int Cout, int Cin,
+                         int accumulate) {
+  __shared__ float tile[8][RS * 32 + 1];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int ci_blocks = Cin / 32;
+  const long long total = static_cast<long long>(Cout) * RS * Cin;
+  const long long warps = static_cast<long long>(Cout) * ci_blocks;
+  for (long long wv = blockIdx.x * 8ll + wid; wv < warps; wv += gridDim.x * 8ll) {
+    const int co = static_cast<int>(wv / ci_blocks), cb = static_cast<int>(wv % ci_blocks);
+    float acc[RS];
+#pragma unroll
+    for (int t = 0; t < RS; ++t) acc[t] = 0.f;
+    const float* src = partial + (static_cast<long long>(co) * RS) * Cin + cb * 32 + lane;
+    for (int k = 0; k < splits; ++k) {
+#pragma unroll
+      for (int t = 0; t < RS; ++t) acc[t] += __ldg(src + k * total + static_cast<long long>(t) * Cin);
+    }
+    float* ts = tile[wid];
+#pragma unroll
+    for (int t = 0; t < RS; ++t) ts[lane * RS + t] = acc[t];      // [ci][tap]: the OIHW order of this warp's block
+    __syncwarp();
+    float* dst = dw_oihw + (static_cast<long long>(co) * Cin + cb * 32) * RS;
+#pragma unroll
+    for (int t = 0; t < RS; ++t) {
+      const int e = t * 32 + lane;
+      dst[e] = accumulate ? dst[e] + ts[e] : ts[e];
+    }
+    __syncwarp();
+  }
+}
+
 // pixel tile for the K dimension: tile_w * tile_h a multiple of 16, <= 128 rows, fewest wasted rows
 static int wgrad_max_rows() {
   static int r = 0;
@@ -634,8 +671,15 @@ extern "C" int s2p_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy
   if (rc != S2P_OK) return rc;
   const long long total = static_cast<long long>(Cout) * ksize * ksize * Cin;
   const int blocks = static_cast<int>((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(workspace), dw_oihw, pl.splits, Cout, Cin,
-                                              ksize, ksize, accumulate);
+  const long long rwarps = static_cast<long long>(Cout) * (Cin / 32);
+  const int rblocks = static_cast<int>((rwarps + 7) / 8 < 2048 ? (rwarps + 7) / 8 : 2048);
+  const float* part = static_cast<const float*>(workspace);
+  if (Cin % 32 == 0 && ksize == 3)
+    wgrad_reduce_tile_kernel<9><<<rblocks, 256, 0, st>>>(part, dw_oihw, pl.splits, Cout, Cin, accumulate);
+  else if (Cin % 32 == 0 && ksize == 4)
+    wgrad_reduce_tile_kernel<16><<<rblocks, 256, 0, st>>>(part, dw_oihw, pl.splits, Cout, Cin, accumulate);
+  else
+    wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(part, dw_oihw, pl.splits, Cout, Cin, ksize, ksize, accumulate);
   count_launch();
   return check_launch("wgrad_reduce_kernel");
 }

@@ -431,16 +431,30 @@ __global__ void __launch_bounds__(256) mat_norm_bwd_reduce_kernel(const NormBwdP
   }
 }
 
-__global__ void sum4_finalize_kernel(const float4* __restrict__ partial, int rows, float4* __restrict__ out, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// blockDim = (32 channels, 8 slices): slice k sums partial rows k, k+8, ... in fp64, the slices are combined in a fixed
+// order (bit-stable); one thread per channel walking every row was a chain of dependent L2 round trips.
+__global__ void __launch_bounds__(256)
+sum4_finalize_kernel(const float4* __restrict__ partial, int rows, float4* __restrict__ out, int C) {
+  __shared__ double red[8][32][4];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   const int n = blockIdx.y;
-  if (c >= C) return;
   double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-  for (int r = 0; r < rows; ++r) {
-    const float4 v = __ldg(partial + (static_cast<size_t>(n) * rows + r) * C + c);
-    s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+  if (c < C)
+    for (int r = threadIdx.y; r < rows; r += 8) {
+      const float4 v = __ldg(partial + (static_cast<size_t>(n) * rows + r) * C + c);
+      s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+    }
+  double* mine = red[threadIdx.y][threadIdx.x];
+  mine[0] = s0; mine[1] = s1; mine[2] = s2; mine[3] = s3;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    double t[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) t[j] += red[k][threadIdx.x][j];
+    out[static_cast<size_t>(n) * C + c] = make_float4((float)t[0], (float)t[1], (float)t[2], (float)t[3]);
   }
-  out[static_cast<size_t>(n) * C + c] = make_float4((float)s0, (float)s1, (float)s2, (float)s3);
 }
 
 // blockDim = (C/8 channel groups, PY pixel slots); grid = (chunks of INPUT pixels per image, B).  A thread keeps the
@@ -573,7 +587,7 @@ extern "C" int s2p_mat_norm_bwd(const void* dy, int dy_pitch, const void* x, int
   count_launch();
   int rc = check_launch("mat_norm_bwd_reduce_kernel");
   if (rc != S2P_OK) return rc;
-  sum4_finalize_kernel<<<dim3((C + 127) / 128, B), 128, 0, st>>>(reinterpret_cast<const float4*>(partial), p.chunks,
+  sum4_finalize_kernel<<<dim3((C + 31) / 32, B), dim3(32, 8), 0, st>>>(reinterpret_cast<const float4*>(partial), p.chunks,
                                                                reinterpret_cast<float4*>(sums), C);
   count_launch();
   rc = check_launch("sum4_finalize_kernel");

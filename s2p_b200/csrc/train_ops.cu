@@ -131,21 +131,23 @@ act_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, int dy_pitch, const 
   }
 }
 
-// blockDim = (32 channels, 8 slices): slice k sums chunks k, k+8, ... in fp64, the 8 slices are then combined in
-// a fixed order (bit-stable; 8x the memory parallelism of one serial walk over up to 592 chunks)
-__global__ void __launch_bounds__(256)
+// blockDim = (32 channels, 32 slices): slice k sums chunks k, k+32, ... in fp64, the 32 slices are then combined in
+// a fixed order (bit-stable).  The walk is a chain of dependent L2 round trips per thread: with 8 slices over up to
+// 592 chunks a launch took 19 us for 1 MB of partials (28 launches per training step).
+constexpr int kColsumSlices = 32;
+__global__ void __launch_bounds__(32 * kColsumSlices)
 colsum_finalize_kernel(const float* __restrict__ partial, int chunks, float* __restrict__ out, int C) {
-  __shared__ double red[8][32];
+  __shared__ double red[kColsumSlices][32];
   const int c = blockIdx.x * 32 + threadIdx.x;
   double s = 0.0;
   if (c < C)
-    for (int k = threadIdx.y; k < chunks; k += 8) s += static_cast<double>(partial[static_cast<size_t>(k) * C + c]);
+    for (int k = threadIdx.y; k < chunks; k += kColsumSlices) s += static_cast<double>(partial[static_cast<size_t>(k) * C + c]);
   red[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.y == 0 && c < C) {
     double t = 0.0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    for (int k = 0; k < kColsumSlices; ++k) t += red[k][threadIdx.x];
     out[c] = static_cast<float>(t);
   }
 }
@@ -281,7 +283,7 @@ extern "C" int s2p_act_bwd_bias_grad(const void* dy, int dy_pitch, const void* y
   count_launch();
   int rc = check_launch("act_bwd_colsum_kernel");
   if (rc != S2P_OK || bias_grad == nullptr) return rc;
-  colsum_finalize_kernel<<<(C + 31) / 32, dim3(32, 8), 0, st>>>(partial, static_cast<int>(chunks), bias_grad, C);
+  colsum_finalize_kernel<<<(C + 31) / 32, dim3(32, kColsumSlices), 0, st>>>(partial, static_cast<int>(chunks), bias_grad, C);
   count_launch();
   return check_launch("colsum_finalize_kernel");
 }
