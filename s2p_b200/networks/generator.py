@@ -597,7 +597,7 @@ class S2PGeneratorB200(nn.Module):
         for ds, mats in groups.items():
             sb = torch.cat([m.mlp_shared.bias for _, _, m in mats], dim=0)
             hcat, _ = conv_in(f[ds], None, act=ACT_RELU, want_stats=False, weight=w_sh[ds], bias=sb, packed=pk[("sh", ds)])
-            for (bi, name, _), hsl in zip(mats, torch.split(hcat, nh, dim=3)):
+            for (bi, name, _), hsl in zip(mats, A.split_channels(hcat, nh)):
                 hs[(bi, name)] = hsl
 
         def mat(bi, name, m, xin, mr_in, up, act):
