@@ -308,6 +308,14 @@ int s2p_slac_conv1_fwd(const uint8_t* frames, const uint8_t* frames_tp1, long lo
  * backward: dx gets dy at the first maximum of each window (nn.MaxPool2d tie rule) and zeros elsewhere,
  * including the row / column an odd H / W leaves uncovered.  C % 8 == 0. */
 int s2p_maxpool2_fwd(const void* x, int x_pitch, void* y, int y_pitch, int B, int H, int W, int C, void* stream);
+/* out[c] = sum over rows of a row-major fp32 [rows][cols] matrix with row pitch `pitch` (elements): the bias gradient
+ * of the state encoder's Linear layers (autograd's dy.sum(0) in oracle StateEncoder / the MAT state heads). */
+int s2p_colsum_rows_f32(const float* x, int pitch, int rows, int cols, float* out, void* stream);
+/* nn.AvgPool2d(3, stride=2, padding=1, count_include_pad=False) on `planes` contiguous fp32 [H][W] planes
+ * (x: [planes][H][W] -> y: [planes][(H-1)/2+1][(W-1)/2+1]) and its backward: the down-sampling between the scales of
+ * the multiscale discriminator (oracle MultiscaleDiscriminator.forward; pix2pixHD's `downsample`). */
+int s2p_avgpool3s2_fwd(const float* x, float* y, long long planes, int H, int W, void* stream);
+int s2p_avgpool3s2_bwd(const float* dy, float* dx, long long planes, int H, int W, void* stream);
 int s2p_maxpool2_bwd(const void* dy, int dy_pitch, const void* x, int x_pitch, void* dx, int dx_pitch, int B, int H,
                      int W, int C, void* stream);
 

@@ -60,6 +60,9 @@ SIGNATURES = {
     "s2p_slac_window_gather": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, C.c_longlong, _i, _i, _i, _vp]),
     "s2p_slac_conv1_fwd": (_i, [_vp, _vp, C.c_longlong, _vp, _vp, _vp, _vp, _vp, _i, C.c_longlong, _i, _i, _vp]),
     "s2p_maxpool2_fwd": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2p_colsum_rows_f32": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "s2p_avgpool3s2_fwd": (_i, [_vp, _vp, C.c_longlong, _i, _i, _vp]),
+    "s2p_avgpool3s2_bwd": (_i, [_vp, _vp, C.c_longlong, _i, _i, _vp]),
     "s2p_zero_insert2": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "s2p_tanh_nhwc_to_nchw": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp]),
     "s2p_tanh_bwd_nchw_to_nhwc64": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),

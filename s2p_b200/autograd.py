@@ -164,7 +164,7 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dw = ops.linear(dy.t().contiguous(), x.t().contiguous(), None, ACT_NONE)  # [N,B] x [B,K]
         if ctx.needs_input_grad[2]:
-            db = dy.sum(dim=0)
+            db = ops.colsum_rows(dy)
         return dx, dw, db, None
 
 
@@ -260,6 +260,23 @@ class MaxPool2Fn(torch.autograd.Function):
 
 def maxpool2(x):
     return MaxPool2Fn.apply(x)
+
+
+class AvgPool3s2Fn(torch.autograd.Function):
+    """F.avg_pool2d(x, 3, stride=2, padding=1, count_include_pad=False) on fp32 NCHW (between the discriminator scales)"""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.hw = tuple(x.shape[-2:])
+        return ops.avgpool3s2(x.contiguous())
+
+    @staticmethod
+    def backward(ctx, dy):
+        return ops.avgpool3s2_bwd(dy.contiguous(), *ctx.hw)
+
+
+def avgpool3s2(x):
+    return AvgPool3s2Fn.apply(x)
 
 
 class PadChannelsFn(torch.autograd.Function):

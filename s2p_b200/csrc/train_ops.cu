@@ -805,3 +805,112 @@ extern "C" int s2p_zero_insert2(const void* dy, int dy_pitch, void* out, int B, 
   count_launch();
   return check_launch("zero_insert2_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------
+// nn.AvgPool2d(3, stride 2, padding 1, count_include_pad=False) on fp32 planes [P][H][W] and its backward: the
+// down-sampling between the scales of the multiscale discriminator (oracle MultiscaleDiscriminator.forward).  One
+// thread per output (forward) / input (backward) element; torch's backward kernel took 323 us for the 15 MB of a
+// batch-128 step's [256, 6, 100, 100] input.
+namespace s2p {
+
+__device__ __forceinline__ int pool_count(int o, int n) {     // valid taps of the window centred at 2 * o along an axis of n
+  const int lo = max(2 * o - 1, 0), hi = min(2 * o + 1, n - 1);
+  return hi - lo + 1;
+}
+
+__global__ void __launch_bounds__(256)
+avgpool3s2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long planes, int H, int W, int Ho, int Wo) {
+  const long long total = planes * Ho * Wo;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int wo = static_cast<int>(i % Wo);
+    const long long t = i / Wo;
+    const int ho = static_cast<int>(t % Ho);
+    const float* xp = x + (t / Ho) * H * W;
+    float s = 0.f;
+    for (int dh = -1; dh <= 1; ++dh) {
+      const int h = 2 * ho + dh;
+      if (h < 0 || h >= H) continue;
+      for (int dw = -1; dw <= 1; ++dw) {
+        const int w = 2 * wo + dw;
+        if (w >= 0 && w < W) s += __ldg(xp + static_cast<long long>(h) * W + w);
+      }
+    }
+    y[i] = s / static_cast<float>(pool_count(ho, H) * pool_count(wo, W));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+avgpool3s2_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, long long planes, int H, int W, int Ho, int Wo) {
+  const long long total = planes * H * W;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int w = static_cast<int>(i % W);
+    const long long t = i / W;
+    const int h = static_cast<int>(t % H);
+    const float* dp = dy + (t / H) * Ho * Wo;
+    // outputs whose window [2o - 1, 2o + 1] contains this coordinate: o = c / 2 for even c, (c - 1) / 2 and (c + 1) / 2 for odd c
+    const int h0 = h >> 1, h1 = (h & 1) ? h0 + 1 : h0;
+    const int w0 = w >> 1, w1 = (w & 1) ? w0 + 1 : w0;
+    float s = 0.f;
+    for (int ho = h0; ho <= h1; ++ho) {
+      if (ho >= Ho) continue;
+      for (int wo = w0; wo <= w1; ++wo)
+        if (wo < Wo) s += __ldg(dp + static_cast<long long>(ho) * Wo + wo) / static_cast<float>(pool_count(ho, H) * pool_count(wo, W));
+    }
+    dx[i] = s;
+  }
+}
+
+}  // namespace s2p
+
+extern "C" int s2p_avgpool3s2_fwd(const float* x, float* y, long long planes, int H, int W, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && y && planes > 0 && H > 0 && W > 0, "avgpool3s2_fwd: bad args");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const long long total = planes * Ho * Wo;
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  avgpool3s2_fwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, planes, H, W, Ho, Wo);
+  count_launch();
+  return check_launch("avgpool3s2_fwd_kernel");
+}
+
+extern "C" int s2p_avgpool3s2_bwd(const float* dy, float* dx, long long planes, int H, int W, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(dy && dx && planes > 0 && H > 0 && W > 0, "avgpool3s2_bwd: bad args");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const long long total = planes * H * W;
+  const int blocks = static_cast<int>((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  avgpool3s2_bwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, dx, planes, H, W, Ho, Wo);
+  count_launch();
+  return check_launch("avgpool3s2_bwd_kernel");
+}
+
+// out[c] = sum_r x[r][c] for a row-major fp32 [rows][cols] matrix (bias gradient of a Linear layer: the batch sum of dy).
+// blockDim = (32 columns, 8 row slices), fp64 slices combined in a fixed order; torch's generic reduction took 24 us per
+// [128, 512] matrix (27 launches per training step).
+namespace s2p {
+__global__ void __launch_bounds__(256)
+colsum_rows_f32_kernel(const float* __restrict__ x, int pitch, int rows, int cols, float* __restrict__ out) {
+  __shared__ double red[8][32];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  double s = 0.0;
+  if (c < cols)
+    for (int r = threadIdx.y; r < rows; r += 8) s += static_cast<double>(__ldg(x + static_cast<size_t>(r) * pitch + c));
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    out[c] = static_cast<float>(t);
+  }
+}
+}  // namespace s2p
+
+extern "C" int s2p_colsum_rows_f32(const float* x, int pitch, int rows, int cols, float* out, void* stream) {
+  using namespace s2p;
+  S2P_CHECK_ARG(x && out && rows > 0 && cols > 0 && pitch >= cols, "colsum_rows_f32: bad args");
+  colsum_rows_f32_kernel<<<(cols + 31) / 32, dim3(32, 8), 0, static_cast<cudaStream_t>(stream)>>>(x, pitch, rows, cols, out);
+  count_launch();
+  return check_launch("colsum_rows_f32_kernel");
+}
+

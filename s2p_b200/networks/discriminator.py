@@ -91,7 +91,7 @@ class MultiscaleDiscriminatorB200(nn.Module):
             nl = len(params[i])
             out.append(nets[i](x0, params[i], packed[i * nl:(i + 1) * nl]))
             if i + 1 < self.num_D:
-                x = F.avg_pool2d(x, 3, 2, 1, count_include_pad=False)
+                x = A.avgpool3s2(x.float())
         return out
 
 

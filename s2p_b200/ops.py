@@ -567,6 +567,41 @@ def act_bwd_bias_grad(dy, y, act, want_bias_grad=True):
     return out, db
 
 
+def colsum_rows(x):
+    """x.sum(dim=0) of an fp32 [rows, cols] matrix (unit column stride)"""
+    _require_cuda(x)
+    if x.dtype != torch.float32 or x.dim() != 2 or x.stride(1) != 1:
+        raise RuntimeError("colsum_rows: fp32 [rows, cols] with unit column stride required")
+    out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().s2p_colsum_rows_f32(x.data_ptr(), x.stride(0), x.shape[0], x.shape[1], out.data_ptr(), _stream()),
+               "s2p_colsum_rows_f32")
+    return out
+
+
+def avgpool3s2(x):
+    """F.avg_pool2d(x, 3, 2, 1, count_include_pad=False) for contiguous fp32 [..., H, W]"""
+    _require_cuda(x)
+    if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() < 2:
+        raise RuntimeError("avgpool3s2: contiguous fp32 [..., H, W] required")
+    h, w = x.shape[-2:]
+    y = torch.empty(*x.shape[:-2], (h - 1) // 2 + 1, (w - 1) // 2 + 1, dtype=torch.float32, device=x.device)
+    if x.numel():
+        _lib.check(_lib.load().s2p_avgpool3s2_fwd(x.data_ptr(), y.data_ptr(), x.numel() // (h * w), h, w, _stream()),
+                   "s2p_avgpool3s2_fwd")
+    return y
+
+
+def avgpool3s2_bwd(dy, h, w):
+    _require_cuda(dy)
+    if dy.dtype != torch.float32 or not dy.is_contiguous():
+        raise RuntimeError("avgpool3s2_bwd: contiguous fp32 gradient required")
+    dx = torch.empty(*dy.shape[:-2], h, w, dtype=torch.float32, device=dy.device)
+    if dx.numel():
+        _lib.check(_lib.load().s2p_avgpool3s2_bwd(dy.data_ptr(), dx.data_ptr(), dx.numel() // (h * w), h, w, _stream()),
+                   "s2p_avgpool3s2_bwd")
+    return dx
+
+
 def maxpool2(x, out=None):
     """nn.MaxPool2d(2, 2) on NHWC bf16"""
     _require_cuda(x, out)

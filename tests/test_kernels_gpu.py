@@ -578,3 +578,29 @@ def test_conv_horizontal_halo_mode(ops, case):
         assert torch.allclose(mr[..., 0], y.float().mean(dim=(1, 2)), atol=1e-4)
         assert torch.allclose(mr[..., 1], 1.0 / torch.sqrt(y.float().var(dim=(1, 2), unbiased=False) + 1e-5), rtol=1e-4, atol=1e-5)
     assert torch.equal(ops.conv_igemm(xb, wp, bs, cout, 3, 1, act, res, None, None, x2=x2), y)      # bit-stable
+
+
+@pytest.mark.parametrize("shape", [(4, 6, 100, 100), (2, 3, 7, 9), (1, 1, 1, 1), (3, 2, 50, 51)])
+def test_avgpool3s2_matches_torch(ops, shape):
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(*shape, generator=g).cuda().requires_grad_(True)
+    ref = F.avg_pool2d(x, 3, 2, 1, count_include_pad=False)
+    dy = torch.randn(*ref.shape, generator=g).cuda()
+    ref.backward(dy)
+    from s2p_b200 import autograd as A
+    x2 = x.detach().clone().requires_grad_(True)
+    out = A.avgpool3s2(x2)
+    out.backward(dy)
+    assert out.shape == ref.shape and (out - ref).abs().max().item() <= 1e-6
+    assert (x2.grad - x.grad).abs().max().item() <= 1e-6
+
+
+def test_colsum_rows(ops):
+    g = torch.Generator().manual_seed(4)
+    for rows, cols in ((128, 512), (1, 17), (333, 70), (16, 8576)):
+        x = torch.randn(rows, cols, generator=g).cuda()
+        got = ops.colsum_rows(x)
+        ref = x.double().sum(0).float()
+        assert (got - ref).abs().max().item() <= 1e-5 * max(1.0, ref.abs().max().item())
+    xs = torch.randn(64, 100, generator=g).cuda()[:, :40]          # a column slice: pitch 100
+    assert (ops.colsum_rows(xs) - xs.double().sum(0).float()).abs().max().item() <= 1e-5
