@@ -477,42 +477,28 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         // of at most 128 columns.  256-wide tiles (512 clk per stage, 4-5 ring stages) keep the one-stage loop.
         // (four stages per iteration measured 5 % SLOWER at BLOCK_N = 128: half of the 8-stage ring is then released at
         // once and the producers' refill shows up as a 500-clk wait per group)
-        constexpr int kGroup = BLOCK_N > 128 ? 1 : 2;   // ring stages per loop iteration
+        constexpr bool kPairStages = BLOCK_N <= 128;   // two ring stages per loop iteration
         const int nkb = HH ? num_kb_hh : num_kb;
         for (int kb = 0; kb < nkb;) {
-          const int g = (nkb - kb) < kGroup ? (nkb - kb) : kGroup;
-          int st[4];
-          uint32_t ph[4];
-          st[0] = stage; ph[0] = phase;
-#pragma unroll
-          for (int j = 1; j < 4; ++j) {
-            st[j] = st[j - 1] + 1; ph[j] = ph[j - 1];
-            if (st[j] == Cfg::kStages) { st[j] = 0; ph[j] ^= 1; }
-          }
+          const bool two = kPairStages && kb + 1 < nkb;
+          int stage_b = stage + 1;
+          uint32_t phase_b = phase;
+          if (stage_b == Cfg::kStages) { stage_b = 0; phase_b ^= 1; }
           S2P_TRACE(3, tr_m);
-          if (kGroup == 4 && g == 4) {
-            mbar_wait4(&full_bar[st[0]], ph[0], &full_bar[st[1]], ph[1], &full_bar[st[2]], ph[2], &full_bar[st[3]], ph[3]);
-          } else if (g >= 2) {
-            mbar_wait2(&full_bar[st[0]], ph[0], &full_bar[st[1]], ph[1]);
-            if (kGroup == 4 && g == 3) mbar_wait(&full_bar[st[2]], ph[2]);
-          } else {
-            mbar_wait(&full_bar[st[0]], ph[0]);
-          }
+          if (two) mbar_wait2(&full_bar[stage], phase, &full_bar[stage_b], phase_b);
+          else mbar_wait(&full_bar[stage], phase);
           S2P_TRACE(4, tr_m);
           tc_fence_after();
           if (elect_one()) {
-#pragma unroll
-            for (int j = 0; j < kGroup; ++j)
-              if (j < g) issue_stage(st[j], kb + j, nkb);
+            issue_stage(stage, kb, nkb);
+            if (two) issue_stage(stage_b, kb + 1, nkb);
           }
           __syncwarp();
           S2P_TRACE(5, tr_m);
 #ifdef S2P_CONV_TRACE
           ++tr_m;
 #endif
-          stage = (kGroup == 4 && g == 4) ? st[3] : ((kGroup == 4 && g == 3) ? st[2] : (g == 2 ? st[1] : st[0]));
-          phase = (kGroup == 4 && g == 4) ? ph[3] : ((kGroup == 4 && g == 3) ? ph[2] : (g == 2 ? ph[1] : ph[0]));
-          kb += g;
+          if (two) { stage = stage_b; phase = phase_b; kb += 2; } else { kb += 1; }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }

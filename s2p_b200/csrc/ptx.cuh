@@ -81,29 +81,6 @@ __device__ __forceinline__ void mbar_wait2(uint64_t* bar_a, uint32_t parity_a, u
   }
 }
 
-__device__ __forceinline__ void mbar_wait4(uint64_t* b0, uint32_t p0, uint64_t* b1, uint32_t p1, uint64_t* b2, uint32_t p2,
-                                           uint64_t* b3, uint32_t p3) {
-  uint32_t spins = 0;
-  for (;;) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred P, Q, R, S;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 Q, [%3], %4;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 R, [%5], %6;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 S, [%7], %8;\n\t"
-        "and.pred P, P, Q;\n\t"
-        "and.pred R, R, S;\n\t"
-        "and.pred P, P, R;\n\t"
-        "selp.u32 %0, 1, 0, P;\n\t}\n"
-        : "=r"(ok)
-        : "r"(smem_u32(b0)), "r"(p0), "r"(smem_u32(b1)), "r"(p1), "r"(smem_u32(b2)), "r"(p2), "r"(smem_u32(b3)), "r"(p3)
-        : "memory");
-    if (ok) break;
-    if (++spins > (1u << 26)) __trap();
-  }
-}
-
 // The same wait for warps that are NOT on the tensor pipe's critical path (the epilogue group): every failed probe of
 // an mbarrier is a shared-memory access, and eight warps spinning on the accumulator barrier took ~15 % of the SM's
 // shared-memory wavefronts away from the UMMA operand reads (ncu, profiles/r02_history.md).  Back off between probes.

@@ -31,14 +31,14 @@ def read():
     return buf
 
 
-def report(name, stages_per_tile, skip_tiles=4, tiles=12, paired=True, group=2):
+def report(name, stages_per_tile, skip_tiles=4, tiles=12, paired=True):
     t = read()
     s0, s1 = skip_tiles * stages_per_tile, (skip_tiles + tiles) * stages_per_tile
     p0, p1 = s0 // 3, s1 // 3             # producer warp 0 records its own stages only: every third
     prod_wait = (t[1] - t[0])[p0:p1]
     prod_issue = (t[2] - t[1])[p0:p1]
     # the MMA thread records one entry per loop iteration: two ring stages for tiles of at most 128 columns
-    ipt = (stages_per_tile + group - 1) // group if paired else stages_per_tile
+    ipt = (stages_per_tile + 1) // 2 if paired else stages_per_tile
     m0, m1 = skip_tiles * ipt, (skip_tiles + tiles) * ipt
     mma_wait = (t[4] - t[3])[m0:m1]
     mma_issue = (t[5] - t[4])[m0:m1]
@@ -49,7 +49,7 @@ def report(name, stages_per_tile, skip_tiles=4, tiles=12, paired=True, group=2):
     f = lambda a: f"mean {a.mean():7.0f}  med {np.median(a):7.0f}  max {a.max():7.0f}"
     print(f"== {name}: {stages_per_tile} stages per tile; clk per stage {per_stage.mean():.0f}, per tile {per_stage.mean() * stages_per_tile:.0f}")
     print(f"   producer wait(empty) {f(prod_wait)}\n   producer issue       {f(prod_issue)}")
-    print(f"   mma wait(full)       {f(mma_wait)}   (per loop iteration: {group if paired else 1} stage(s))\n   mma issue            {f(mma_issue)}")
+    print(f"   mma wait(full)       {f(mma_wait)}   (per loop iteration: {2 if paired else 1} stage(s))\n   mma issue            {f(mma_issue)}")
     print(f"   mma wait(tmem_empty) {f(tile_wait)}\n   epi wait(tmem_full)  {f(epi_wait)}\n   epi busy             {f(epi_busy)}")
     if os.environ.get("CONV_TRACE_TIMELINE"):
         base = t[6][skip_tiles]
