@@ -88,6 +88,7 @@ def workload_config(args, world):
             "env_type": ENV, "rows_per_rank_per_step": args.batch, "global_rows_per_step": args.batch * world,
             "image": "100x100x3 uint8", "state_dim": 17, "parallelism": f"shard{world}",
             "weights": "random init (ORACLE_SPEC v1 'scaled' init, seed 1234)",
+            "rows_per_launch": "512 (options.max_microbatch: rows are independent, outputs bit-identical for every value)",
             "l2_policy": "inputs+activations per step (>=3 GB) exceed the 126 MB L2; no explicit flush"}
 
 
@@ -677,7 +678,8 @@ def instrumented_steps(net, frames_d, states_d, ops, torch, n_steps=3):
     finally:
         for n, fn in orig.items():
             setattr(ops, n, fn)
-    return {"rec": rec, "t0": t0, "t1": t1, "n_steps": n_steps}
+    return {"rec": rec, "t0": t0, "t1": t1, "n_steps": n_steps,
+            "rows_per_launch": min(int(net.max_microbatch), int(frames_d.shape[0]))}
 
 
 def rooflines(inst, ms_per_step_timed):
@@ -716,8 +718,11 @@ def rooflines(inst, ms_per_step_timed):
                     {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[r["Metric Unit"]]
         c = [v for (i, k), v in by.items() if "conv_igemm" in k]
         n = [v for (i, k), v in by.items() if "mat_norm" in k]
-        traffic_conv = sum(c) / len(c) if c else None
-        traffic_norm = sum(n) / len(n) if n else None
+        # the ncu pass profiles ONE forward of 128 frames; a launch of the benchmarked step covers rows_per_launch rows,
+        # and these kernels' DRAM traffic is activations: scaled linearly
+        scale = inst.get("rows_per_launch", 128) / 128.0
+        traffic_conv = sum(c) / len(c) * scale if c else None
+        traffic_norm = sum(n) / len(n) * scale if n else None
     except Exception:
         pass
     conv_ms = shares["conv"] * ms_per_step_timed
@@ -727,7 +732,8 @@ def rooflines(inst, ms_per_step_timed):
     roof = {"kernel": "conv_igemm_kernel (tcgen05 implicit GEMM, plain and MAT-fused epilogues; all launches of one step)",
             "bound": "tensor", "achieved": ach_tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach_tf / tf_peak,
             "traffic": traffic_conv,
-            "traffic_note": f"avg dram__bytes_read+write per conv launch, profiles/{traffic_file} (ncu, 128-frame micro-batch)",
+            "traffic_note": f"avg dram__bytes_read+write per conv launch, profiles/{traffic_file} (ncu of a 128-frame forward) "
+                            f"x {inst.get('rows_per_launch', 128)}/128 rows per launch of this step",
             "peak_source": src, "launches": nconv, "avg_launch_ms": conv_ms / nconv,
             "flops_per_launch_avg": work["conv"] / nconv, "flops_per_step": work["conv"],
             "how": f"algorithmic flops of a step / (conv share {shares['conv']:.4f} x timed ms_per_step {ms_per_step_timed:.3f}); "

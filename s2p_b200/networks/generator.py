@@ -143,7 +143,7 @@ class S2PGeneratorB200(nn.Module):
         self.block_4 = _BlockParams(ngf * 2, ngf, ngf, wd, nh)
         self.conv_img = nn.Conv2d(ngf, 3, 3, 1, 1)
         _init_weights(self, getattr(opt, "init_type", "xavier"), getattr(opt, "init_variance", 0.02))
-        self.max_microbatch = int(getattr(opt, "max_microbatch", 128))
+        self.max_microbatch = int(getattr(opt, "max_microbatch", 512))
         # fuse_mat: the gamma/beta conv applies the MAT norm in its own epilogue (default).
         # False keeps the two-kernel form (conv -> bf16 maps -> mat_norm kernel).
         self.fuse_mat = bool(getattr(opt, "fuse_mat", True))

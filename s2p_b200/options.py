@@ -25,7 +25,10 @@ def make_options(argv=None, **overrides):
     p.add_argument("--mapping_layers", type=int, default=8)
     p.add_argument("--init_type", type=str, default="xavier")
     p.add_argument("--init_variance", type=float, default=0.02)
-    p.add_argument("--max_microbatch", type=int, default=128)
+    # rows per launch set of the bulk path.  Rows are independent (outputs are bit-identical for every value); 512 instead
+    # of 128 amortises each launch's ramp-up and tail over 4x the tiles: +1-3 % frames/s for 37 GiB of workspace
+    # (tools/microbatch_sweep.py, tools/ab_forward.py --mb)
+    p.add_argument("--max_microbatch", type=int, default=512)
     # "high": wide (bf16 hi + lo) residual stream / pre-norm maps and split-precision encoder convs, PSNR >= 50 dB
     # vs the fp32 oracle; "standard": single-bf16 storage everywhere (round-1 schedule, ~48.6 dB), for A/B timing
     p.add_argument("--precision", type=str, default="high", choices=["high", "standard"])

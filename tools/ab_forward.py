@@ -14,6 +14,7 @@ ap.add_argument("--lib", type=str, default=None)
 ap.add_argument("--rows", type=int, default=1024)
 ap.add_argument("--reps", type=int, default=12)
 ap.add_argument("--precision", type=str, default="high")
+ap.add_argument("--mb", type=int, default=0, help="rows per launch set (0: the default of options.py)")
 a = ap.parse_args()
 if a.lib:
     import ctypes
@@ -24,7 +25,8 @@ if a.lib:
 import s2p_b200  # noqa: E402
 
 torch.manual_seed(1234)
-net = s2p_b200.define_G(s2p_b200.make_options(env_type="cheetah", gpu_ids="0", init_type="scaled", precision=a.precision)).eval()
+kw = {"max_microbatch": a.mb} if a.mb else {}
+net = s2p_b200.define_G(s2p_b200.make_options(env_type="cheetah", gpu_ids="0", init_type="scaled", precision=a.precision, **kw)).eval()
 net.pack()
 g = torch.Generator().manual_seed(0)
 frames = torch.randint(0, 256, (a.rows, 100, 100, 3), dtype=torch.uint8, generator=g).cuda()
@@ -39,5 +41,5 @@ for i in range(a.reps):
     ev[i + 1].record()
 torch.cuda.synchronize()
 ms = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(a.reps))
-print(f"ab_forward lib={a.lib or 'product'} rows={a.rows} ms median={ms[len(ms) // 2]:.3f} min={ms[0]:.3f} "
+print(f"ab_forward lib={a.lib or 'product'} mb={net.max_microbatch} rows={a.rows} ms median={ms[len(ms) // 2]:.3f} min={ms[0]:.3f} "
       f"frames/s={a.rows / ms[len(ms) // 2] * 1e3:.0f} checksum={int(out.sum().item())}")
