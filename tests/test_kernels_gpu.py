@@ -604,3 +604,21 @@ def test_colsum_rows(ops):
         assert (got - ref).abs().max().item() <= 1e-5 * max(1.0, ref.abs().max().item())
     xs = torch.randn(64, 100, generator=g).cuda()[:, :40]          # a column slice: pitch 100
     assert (ops.colsum_rows(xs) - xs.double().sum(0).float()).abs().max().item() <= 1e-5
+
+
+@pytest.mark.parametrize("b,hw,cin,cout,k,act,bias", [(2, 50, 64, 256, 3, 1, True), (1, 25, 128, 192, 3, 2, True),
+                                                      (2, 100, 64, 64, 3, 0, False), (3, 37, 64, 128, 1, 1, True),
+                                                      (2, 51, 64, 128, 4, 2, True)])
+def test_simple_epilogue_kernel_is_bit_identical_to_the_general_one(ops, b, hw, cin, cout, k, act, bias):
+    # bias / activation-only launches run a kernel of their own (kEpiSimple); asking for statistics selects the general
+    # epilogue: same accumulators, same roundings -> the stored bf16 values must be the same bits
+    g = torch.Generator().manual_seed(23)
+    x = torch.randn(b, hw, hw, cin, generator=g).cuda().to(torch.bfloat16)
+    w = ops.pack_conv_weight((torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).cuda())
+    bv = torch.randn(cout, generator=g).cuda() if bias else None
+    stride, pad = (2, 2) if k == 4 else (1, k // 2)
+    y_simple = ops.conv_igemm(x, w, bv, cout, k, stride, act, pad=pad)
+    ho = y_simple.shape[1]
+    st = torch.empty(b, ops.conv_stats_rows(ho, ho, cout, k, stride), cout, 2, device="cuda")
+    y_general = ops.conv_igemm(x, w, bv, cout, k, stride, act, stats=st, pad=pad)
+    assert torch.equal(y_simple, y_general)
